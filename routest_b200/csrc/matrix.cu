@@ -1,0 +1,233 @@
+// matrix.cu — stop-to-stop distance/time matrix from coordinates (SPEC.md §1-§2).
+//
+// Takes over Flaskr/utils.py:94-109 of the reference, where the matrix is fetched from a remote service.
+//
+// Kernel shape.  The matrix is pure output: n^2 cells of 8 B against 24 B of input per stop, so the kernel is
+// bound by HBM *writes* (algorithmic bytes per cell: 8 = int32 dist + int32 time).  Each thread owns four columns
+// and keeps their unit vectors in registers for the lifetime of the block; the block walks down a strip of rows
+// whose unit vectors sit in shared memory (one broadcast LDS per row), so per cell the work is 6 FP64 ops for the
+// chord, one F2F, an FP32 tail (sqrt + 3 FMA) and two F2I — well under the issue budget that the HBM write rate
+// allows (~40 instructions per cell per SM at 6.4 TB/s), and every store is a full 16-byte STG whose warp
+// footprint is 512 contiguous bytes.
+#include "common.cuh"
+#include "geometry.cuh"
+
+namespace rt {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kColsPerBlock = kThreads * 4;
+constexpr int kMaxRowsPerBlock = 64;
+
+__global__ void __launch_bounds__(256) unit_vectors_kernel(const double *__restrict__ lat,
+                                                           const double *__restrict__ lon, int n, int total,
+                                                           double *__restrict__ xyz)
+{
+    const double DEG = 0.017453292519943295;
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    int b = idx / n, i = idx - b * n;
+    double sp, cp, sl, cl;
+    det_sincos(lat[idx] * DEG, sp, cp);
+    det_sincos(lon[idx] * DEG, sl, cl);
+    double *o = xyz + static_cast<size_t>(b) * 3 * n;
+    o[i] = cp * cl;
+    o[n + i] = cp * sl;
+    o[2 * n + i] = sp;
+}
+
+struct MatArgs {
+    const double *xyz;
+    int n, r0, r1, rows_per_block;
+    float fd, ft;
+    int2 *cells;      // MODE 0
+    int pitch;        //   cells per row
+    int32_t *dist;    // MODE 1 (either may be null)
+    int32_t *tim;
+    int pitch_i32;
+    double *metres;   // MODE 2
+    int pitch_f64;
+};
+
+enum { kCells = 0, kPlanes = 1, kMetres = 2 };
+
+template <int MODE>
+__global__ void __launch_bounds__(kThreads) matrix_kernel(const MatArgs a)
+{
+    __shared__ double srow[3][kMaxRowsPerBlock];
+
+    const int n = a.n;
+    const double *__restrict__ X = a.xyz + static_cast<size_t>(blockIdx.z) * 3 * n;
+    const double *__restrict__ Y = X + n;
+    const double *__restrict__ Z = Y + n;
+    const int lane = threadIdx.x & 31;
+    const int wb = blockIdx.x * kColsPerBlock + (threadIdx.x >> 5) * 128;
+
+    // column ownership: 16-byte stores, 512 contiguous bytes per warp-wide store instruction
+    int col[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        col[k] = (MODE == kPlanes) ? wb + 4 * lane + k : wb + (k >> 1) * 64 + 2 * lane + (k & 1);
+
+    double bx[4], by[4], bz[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        int c = col[k] < n ? col[k] : 0;
+        bx[k] = X[c];
+        by[k] = Y[c];
+        bz[k] = Z[c];
+    }
+
+    const int row0 = a.r0 + blockIdx.y * a.rows_per_block;
+    const int nrows = min(a.rows_per_block, a.r1 - row0);
+    for (int t = threadIdx.x; t < 3 * nrows; t += kThreads) {
+        int comp = t / nrows, r = t - comp * nrows;
+        srow[comp][r] = (comp == 0 ? X : comp == 1 ? Y : Z)[row0 + r];
+    }
+    __syncthreads();
+
+    const size_t rows_total = static_cast<size_t>(a.r1 - a.r0);
+    const size_t out_row0 = static_cast<size_t>(blockIdx.z) * rows_total + static_cast<size_t>(row0 - a.r0);
+
+    if (MODE == kCells) {
+        if (col[0] >= a.pitch) return;  // warp-uniform per 64-column group is not guaranteed; per-thread exit is fine (no later sync)
+        int4 *out0 = reinterpret_cast<int4 *>(a.cells + out_row0 * a.pitch + col[0]);
+        int4 *out1 = reinterpret_cast<int4 *>(a.cells + out_row0 * a.pitch + col[2]);
+        const bool st1 = col[2] < a.pitch;
+        const size_t step = static_cast<size_t>(a.pitch) / 2;  // int4 = 2 cells
+#pragma unroll 2
+        for (int r = 0; r < nrows; ++r) {
+            const double ax = srow[0][r], ay = srow[1][r], az = srow[2][r];
+            int2 c[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                c[k] = cell_i32(ax, ay, az, bx[k], by[k], bz[k], a.fd, a.ft);
+                if (col[k] >= n) c[k] = make_int2(0, 0);
+            }
+            out0[r * step] = make_int4(c[0].x, c[0].y, c[1].x, c[1].y);
+            if (st1) out1[r * step] = make_int4(c[2].x, c[2].y, c[3].x, c[3].y);
+        }
+    } else if (MODE == kPlanes) {
+        if (col[0] >= a.pitch_i32) return;
+        const size_t base = out_row0 * a.pitch_i32 + col[0];
+        int4 *od = a.dist ? reinterpret_cast<int4 *>(a.dist + base) : nullptr;
+        int4 *ot = a.tim ? reinterpret_cast<int4 *>(a.tim + base) : nullptr;
+        const size_t step = static_cast<size_t>(a.pitch_i32) / 4;
+#pragma unroll 2
+        for (int r = 0; r < nrows; ++r) {
+            const double ax = srow[0][r], ay = srow[1][r], az = srow[2][r];
+            int2 c[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                c[k] = cell_i32(ax, ay, az, bx[k], by[k], bz[k], a.fd, a.ft);
+                if (col[k] >= n) c[k] = make_int2(0, 0);
+            }
+            if (od) od[r * step] = make_int4(c[0].x, c[1].x, c[2].x, c[3].x);
+            if (ot) ot[r * step] = make_int4(c[0].y, c[1].y, c[2].y, c[3].y);
+        }
+    } else {
+        if (col[0] >= a.pitch_f64) return;
+        double2 *out0 = reinterpret_cast<double2 *>(a.metres + out_row0 * a.pitch_f64 + col[0]);
+        double2 *out1 = reinterpret_cast<double2 *>(a.metres + out_row0 * a.pitch_f64 + col[2]);
+        const bool st1 = col[2] < a.pitch_f64;
+        const size_t step = static_cast<size_t>(a.pitch_f64) / 2;
+        for (int r = 0; r < nrows; ++r) {
+            const double ax = srow[0][r], ay = srow[1][r], az = srow[2][r];
+            double m[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                int kk;
+                double s = chord2(ax, ay, az, bx[k], by[k], bz[k], kk);
+                m[k] = col[k] < n ? theta_f64(s, kk) * RT_EARTH_RADIUS_M : 0.0;
+            }
+            out0[r * step] = make_double2(m[0], m[1]);
+            if (st1) out1[r * step] = make_double2(m[2], m[3]);
+        }
+    }
+}
+
+// Rows per block: as many as keep the grid at >= 8 blocks per SM (a few waves), capped by the shared-memory strip.
+int pick_rows_per_block(int rows, int col_blocks, int batch)
+{
+    const long long want_blocks = 8LL * kNumSMs;
+    int rpb = kMaxRowsPerBlock;
+    while (rpb > 4 && static_cast<long long>((rows + rpb - 1) / rpb) * col_blocks * batch < want_blocks) rpb >>= 1;
+    return rpb;
+}
+
+template <int MODE>
+int launch_matrix(rt_engine *e, MatArgs a, int batch, int pitch_cols, cudaStream_t st)
+{
+    const int rows = a.r1 - a.r0;
+    if (rows <= 0 || batch <= 0) return RT_OK;
+    const int col_blocks = (pitch_cols + kColsPerBlock - 1) / kColsPerBlock;
+    a.rows_per_block = pick_rows_per_block(rows, col_blocks, batch);
+    const int row_blocks = (rows + a.rows_per_block - 1) / a.rows_per_block;
+    if (row_blocks > 65535 || batch > 65535) return fail(e, RT_ERR_INVALID_ARG, "matrix grid too large");
+    dim3 grid(col_blocks, row_blocks, batch);
+    matrix_kernel<MODE><<<grid, kThreads, 0, st>>>(a);
+    RT_CUDA(e, cudaGetLastError());
+    return RT_OK;
+}
+
+}  // namespace
+
+int check_scales(rt_engine *e, double dist_scale, double time_scale)
+{
+    const double lim = 536870912.0;  // 2^29: a four-term delta of cells must fit an int32
+    const double half_circ = 3.14159265358979323846 * RT_EARTH_RADIUS_M;
+    if (!(dist_scale > 0.0) || !(time_scale > 0.0) || !(half_circ * dist_scale < lim) || !(half_circ * time_scale < lim))
+        return fail(e, RT_ERR_INVALID_ARG, "dist_scale/time_scale must be > 0 and keep pi*R*scale below 2^29");
+    return RT_OK;
+}
+
+int launch_unit_vectors(rt_engine *e, const double *lat_d, const double *lon_d, int n, int batch, double *xyz_d,
+                        cudaStream_t st)
+{
+    const long long total = static_cast<long long>(n) * batch;
+    if (total <= 0) return RT_OK;
+    if (total > 0x7fffffffLL) return fail(e, RT_ERR_INVALID_ARG, "n*batch too large");
+    unit_vectors_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(lat_d, lon_d, n,
+                                                                                    static_cast<int>(total), xyz_d);
+    RT_CUDA(e, cudaGetLastError());
+    return RT_OK;
+}
+
+int launch_matrix_cells(rt_engine *e, const double *xyz_d, int n, int batch, int r0, int r1, double dist_scale,
+                        double time_scale, int2 *cells_d, cudaStream_t st)
+{
+    MatArgs a{};
+    a.xyz = xyz_d;
+    a.n = n;
+    a.r0 = r0;
+    a.r1 = r1;
+    a.fd = static_cast<float>(RT_EARTH_RADIUS_M * dist_scale);
+    a.ft = static_cast<float>(RT_EARTH_RADIUS_M * time_scale);
+    a.cells = cells_d;
+    a.pitch = rt_matrix_pitch(n);
+    return launch_matrix<kCells>(e, a, batch, a.pitch, st);
+}
+
+int launch_matrix_planes(rt_engine *e, const double *xyz_d, int n, int r0, int r1, double dist_scale, double time_scale,
+                         int32_t *dist_d, int32_t *time_d, double *metres_d, int pitch_i32, int pitch_f64,
+                         cudaStream_t st)
+{
+    MatArgs a{};
+    a.xyz = xyz_d;
+    a.n = n;
+    a.r0 = r0;
+    a.r1 = r1;
+    a.fd = static_cast<float>(RT_EARTH_RADIUS_M * dist_scale);
+    a.ft = static_cast<float>(RT_EARTH_RADIUS_M * time_scale);
+    a.dist = dist_d;
+    a.tim = time_d;
+    a.pitch_i32 = pitch_i32;
+    a.metres = metres_d;
+    a.pitch_f64 = pitch_f64;
+    if (dist_d || time_d) RT_TRY(launch_matrix<kPlanes>(e, a, 1, pitch_i32, st));
+    if (metres_d) RT_TRY(launch_matrix<kMetres>(e, a, 1, pitch_f64, st));
+    return RT_OK;
+}
+
+}  // namespace rt
