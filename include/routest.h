@@ -13,7 +13,8 @@
  *   - no exception crosses the boundary, and there is NO CPU fallback: without a usable GPU rt_create fails;
  *   - plain pointers and sizes only.  Functions without a suffix take HOST buffers owned by the caller and do
  *     their own host<->device copies; functions ending in _dev take DEVICE pointers on the engine's GPU plus a
- *     cudaStream_t passed as void* (NULL = the engine's own stream) and never synchronise;
+ *     cudaStream_t passed as void* — taken literally, so NULL is CUDA's default stream (which is also what
+ *     torch.cuda.current_stream().cuda_stream is unless the caller changed it) — and never synchronise;
  *   - an engine is bound to one GPU and serialises calls made on it from several threads (the reference runs
  *     its handlers on arbitrary Flask worker threads, app.py:8); use one engine per GPU and per process.
  */
@@ -48,6 +49,9 @@ int rt_create(int device, rt_engine **out);
 void rt_destroy(rt_engine *e);
 const char *rt_last_error(const rt_engine *e);
 
+/* The engine's own non-blocking stream as a cudaStream_t (what the host-buffer entry points run on). */
+void *rt_engine_stream(rt_engine *e);
+
 /* Pinned host memory for callers that want asynchronous copies (optional; any host pointer is accepted). */
 int rt_host_alloc(rt_engine *e, size_t bytes, void **out);
 int rt_host_free(rt_engine *e, void *p);
@@ -77,6 +81,10 @@ int rt_unit_vectors_dev(rt_engine *e, const double *lat_d, const double *lon_d, 
  * move-evaluation kernels read.  Same reference lines as rt_matrix_build. */
 int rt_matrix_cells_dev(rt_engine *e, const double *xyz_d, int n, int batch, int row_begin, int row_end,
                         double dist_scale, double time_scale, void *cells_d, void *stream);
+
+/* Self-test: counts floats with bit pattern in [lo_bits, hi_bits) for which the matrix kernel's straight-line
+ * square root differs from IEEE sqrtf (must be 0; SPEC.md §2 relies on it).  No reference counterpart. */
+int rt_selftest_fast_sqrt(rt_engine *e, uint32_t lo_bits, uint32_t hi_bits, uint64_t *mismatches);
 
 #ifdef __cplusplus
 }

@@ -31,11 +31,13 @@ SIGNATURES = {
     "rt_create": (C.c_int, [C.c_int, C.POINTER(c_engine_p)]),
     "rt_destroy": (None, [c_engine_p]),
     "rt_last_error": (C.c_char_p, [c_engine_p]),
+    "rt_engine_stream": (C.c_void_p, [c_engine_p]),
     "rt_host_alloc": (C.c_int, [c_engine_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "rt_host_free": (C.c_int, [c_engine_p, C.c_void_p]),
     "rt_matrix_pitch": (C.c_int, [C.c_int]),
     "rt_matrix_build": (C.c_int, [c_engine_p, c_f64_p, c_f64_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double,
                                   c_i32_p, c_i32_p, c_f64_p]),
+    "rt_selftest_fast_sqrt": (C.c_int, [c_engine_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]),
     "rt_unit_vectors_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_matrix_cells_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
                                       C.c_double, C.c_void_p, C.c_void_p]),

@@ -109,6 +109,8 @@ void rt_destroy(rt_engine *e)
 
 const char *rt_last_error(const rt_engine *e) { return e ? e->err : g_create_err; }
 
+void *rt_engine_stream(rt_engine *e) { return e ? static_cast<void *>(e->stream) : nullptr; }
+
 int rt_host_alloc(rt_engine *e, size_t bytes, void **out)
 {
     if (!e || !out) return fail(e, RT_ERR_INVALID_ARG, "rt_host_alloc: NULL argument");
@@ -122,6 +124,25 @@ int rt_host_free(rt_engine *e, void *p)
     if (!e) return fail(e, RT_ERR_INVALID_ARG, "rt_host_free: NULL engine");
     DeviceGuard g(e->device);
     if (p) RT_CUDA(e, cudaFreeHost(p));
+    return RT_OK;
+}
+
+int rt_selftest_fast_sqrt(rt_engine *e, uint32_t lo_bits, uint32_t hi_bits, uint64_t *mismatches)
+{
+    if (!e) return RT_ERR_INVALID_ARG;
+    if (!mismatches || lo_bits > hi_bits) return fail(e, RT_ERR_INVALID_ARG, "rt_selftest_fast_sqrt: bad argument");
+    if (lo_bits < 0x0D000000u || hi_bits > 0x7F800000u)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_selftest_fast_sqrt: range must lie in [2^-101, inf)");
+    std::lock_guard<std::mutex> lk(e->mu);
+    DeviceGuard g(e->device);
+    RT_TRY(reserve(e, e->coords, 8));
+    unsigned long long *cnt = static_cast<unsigned long long *>(e->coords.p);
+    RT_CUDA(e, cudaMemsetAsync(cnt, 0, 8, e->stream));
+    RT_TRY(run_fast_sqrt_check(e, lo_bits, hi_bits, cnt, e->stream));
+    unsigned long long h = 0;
+    RT_CUDA(e, cudaMemcpyAsync(&h, cnt, 8, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    *mismatches = h;
     return RT_OK;
 }
 

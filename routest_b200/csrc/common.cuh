@@ -65,7 +65,7 @@ struct DeviceGuard {
     }
 };
 
-inline cudaStream_t pick_stream(rt_engine *e, void *s) { return s ? reinterpret_cast<cudaStream_t>(s) : e->stream; }
+inline cudaStream_t pick_stream(rt_engine *, void *s) { return reinterpret_cast<cudaStream_t>(s); }
 
 // launchers implemented in matrix.cu
 int launch_unit_vectors(rt_engine *e, const double *lat_d, const double *lon_d, int n, int batch, double *xyz_d,
@@ -76,5 +76,6 @@ int launch_matrix_planes(rt_engine *e, const double *xyz_d, int n, int r0, int r
                          int32_t *dist_d, int32_t *time_d, double *metres_d, int pitch_i32, int pitch_f64,
                          cudaStream_t st);
 int check_scales(rt_engine *e, double dist_scale, double time_scale);
+int run_fast_sqrt_check(rt_engine *e, unsigned lo, unsigned hi, unsigned long long *mismatches_d, cudaStream_t st);
 
 }  // namespace rt

@@ -4,11 +4,12 @@
 //
 // Kernel shape.  The matrix is pure output: n^2 cells of 8 B against 24 B of input per stop, so the kernel is
 // bound by HBM *writes* (algorithmic bytes per cell: 8 = int32 dist + int32 time).  Each thread owns four columns
-// and keeps their unit vectors in registers for the lifetime of the block; the block walks down a strip of rows
-// whose unit vectors sit in shared memory (one broadcast LDS per row), so per cell the work is 6 FP64 ops for the
-// chord, one F2F, an FP32 tail (sqrt + 3 FMA) and two F2I — well under the issue budget that the HBM write rate
-// allows (~40 instructions per cell per SM at 6.4 TB/s), and every store is a full 16-byte STG whose warp
-// footprint is 512 contiguous bytes.
+// and keeps their unit vectors in registers while its block walks down a strip of rows, whose unit vectors sit in
+// shared memory (one broadcast LDS per row).  Per cell the straight-line path costs 6 FP64 ops for the chord, one F2F, one
+// MUFU and ~14 FP32/INT ops (geometry.cuh), i.e. ~25 issue slots against the ~40 per cell per SM that the HBM
+// write rate leaves room for; every store is a full 16-byte STG whose warp footprint is 512 contiguous bytes.
+#include <algorithm>
+
 #include "common.cuh"
 #include "geometry.cuh"
 
@@ -19,6 +20,8 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kColsPerBlock = kThreads * 4;
 constexpr int kMaxRowsPerBlock = 64;
+constexpr int kBlocksPerSM = 4;
+constexpr int kMinWaves = 10;
 
 __global__ void __launch_bounds__(256) unit_vectors_kernel(const double *__restrict__ lat,
                                                            const double *__restrict__ lon, int n, int total,
@@ -41,6 +44,7 @@ struct MatArgs {
     const double *xyz;
     int n, r0, r1, rows_per_block;
     float fd, ft;
+    int lim_hi;       // fast_path_limit_hi(fd, ft)
     int2 *cells;      // MODE 0
     int pitch;        //   cells per row
     int32_t *dist;    // MODE 1 (either may be null)
@@ -52,8 +56,10 @@ struct MatArgs {
 
 enum { kCells = 0, kPlanes = 1, kMetres = 2 };
 
+// grid = (column blocks of 1024, row strips of rows_per_block, instances).  The strip's unit vectors are staged in
+// shared memory once (broadcast LDS per row); the four column vectors of a thread stay in registers.
 template <int MODE>
-__global__ void __launch_bounds__(kThreads) matrix_kernel(const MatArgs a)
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) matrix_kernel(const MatArgs a)
 {
     __shared__ double srow[3][kMaxRowsPerBlock];
 
@@ -90,21 +96,44 @@ __global__ void __launch_bounds__(kThreads) matrix_kernel(const MatArgs a)
     const size_t rows_total = static_cast<size_t>(a.r1 - a.r0);
     const size_t out_row0 = static_cast<size_t>(blockIdx.z) * rows_total + static_cast<size_t>(row0 - a.r0);
 
+    // four cells of one row: chord^2 in FP64, then either the straight-line tail (all four below the fast-path
+    // limit, i.e. every cell of a metro instance, the diagonal included) or the fully guarded generic cell
+    const bool v0 = col[0] < n, v1 = col[1] < n, v2 = col[2] < n, v3 = col[3] < n;
+    auto four_cells = [&](int r, int2 (&c)[4]) {
+        const double ax = srow[0][r], ay = srow[1][r], az = srow[2][r];
+        double s[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            double dx = ax - bx[k], dy = ay - by[k], dz = az - bz[k];
+            s[k] = fma(dx, dx, fma(dy, dy, dz * dz));
+        }
+        const int hmax = max(max(__double2hiint(s[0]), __double2hiint(s[1])),
+                             max(__double2hiint(s[2]), __double2hiint(s[3])));
+        if (hmax < a.lim_hi) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) c[k] = cell_i32_fast(s[k], a.fd, a.ft);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) c[k] = cell_i32(ax, ay, az, bx[k], by[k], bz[k], a.fd, a.ft);
+        }
+        if (!v3) {  // pad columns of the last column block are written as zero
+            if (!v0) c[0] = make_int2(0, 0);
+            if (!v1) c[1] = make_int2(0, 0);
+            if (!v2) c[2] = make_int2(0, 0);
+            c[3] = make_int2(0, 0);
+        }
+    };
+
     if (MODE == kCells) {
-        if (col[0] >= a.pitch) return;  // warp-uniform per 64-column group is not guaranteed; per-thread exit is fine (no later sync)
+        if (col[0] >= a.pitch) return;  // per-thread exit is fine: no barrier follows
         int4 *out0 = reinterpret_cast<int4 *>(a.cells + out_row0 * a.pitch + col[0]);
         int4 *out1 = reinterpret_cast<int4 *>(a.cells + out_row0 * a.pitch + col[2]);
         const bool st1 = col[2] < a.pitch;
         const size_t step = static_cast<size_t>(a.pitch) / 2;  // int4 = 2 cells
 #pragma unroll 2
         for (int r = 0; r < nrows; ++r) {
-            const double ax = srow[0][r], ay = srow[1][r], az = srow[2][r];
             int2 c[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                c[k] = cell_i32(ax, ay, az, bx[k], by[k], bz[k], a.fd, a.ft);
-                if (col[k] >= n) c[k] = make_int2(0, 0);
-            }
+            four_cells(r, c);
             out0[r * step] = make_int4(c[0].x, c[0].y, c[1].x, c[1].y);
             if (st1) out1[r * step] = make_int4(c[2].x, c[2].y, c[3].x, c[3].y);
         }
@@ -116,13 +145,8 @@ __global__ void __launch_bounds__(kThreads) matrix_kernel(const MatArgs a)
         const size_t step = static_cast<size_t>(a.pitch_i32) / 4;
 #pragma unroll 2
         for (int r = 0; r < nrows; ++r) {
-            const double ax = srow[0][r], ay = srow[1][r], az = srow[2][r];
             int2 c[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                c[k] = cell_i32(ax, ay, az, bx[k], by[k], bz[k], a.fd, a.ft);
-                if (col[k] >= n) c[k] = make_int2(0, 0);
-            }
+            four_cells(r, c);
             if (od) od[r * step] = make_int4(c[0].x, c[1].x, c[2].x, c[3].x);
             if (ot) ot[r * step] = make_int4(c[0].y, c[1].y, c[2].y, c[3].y);
         }
@@ -147,12 +171,27 @@ __global__ void __launch_bounds__(kThreads) matrix_kernel(const MatArgs a)
     }
 }
 
-// Rows per block: as many as keep the grid at >= 8 blocks per SM (a few waves), capped by the shared-memory strip.
+// Self-test kernel: fast_sqrtf against the IEEE sqrtf for every float whose bit pattern lies in [lo, hi).
+__global__ void fast_sqrt_check_kernel(unsigned lo, unsigned hi, unsigned long long *mismatches)
+{
+    unsigned long long bad = 0;
+    const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * blockDim.x;
+    for (unsigned long long b = lo + static_cast<unsigned long long>(blockIdx.x) * blockDim.x + threadIdx.x; b < hi;
+         b += stride) {
+        float x = __uint_as_float(static_cast<unsigned>(b));
+        if (__float_as_uint(fast_sqrtf(x)) != __float_as_uint(sqrtf(x))) ++bad;
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
+// Rows per block: the largest strip that still yields >= kMinWaves full waves of blocks, so that the tail wave (the
+// hardware dispatches a new block whenever one retires) costs a few percent at most; never below 8 rows, which
+// keeps the per-block prologue (12 column loads + one barrier) under ~5% of the block's work.
 int pick_rows_per_block(int rows, int col_blocks, int batch)
 {
-    const long long want_blocks = 8LL * kNumSMs;
+    const long long want_blocks = static_cast<long long>(kMinWaves) * kNumSMs * kBlocksPerSM;
     int rpb = kMaxRowsPerBlock;
-    while (rpb > 4 && static_cast<long long>((rows + rpb - 1) / rpb) * col_blocks * batch < want_blocks) rpb >>= 1;
+    while (rpb > 8 && static_cast<long long>((rows + rpb - 1) / rpb) * col_blocks * batch < want_blocks) rpb >>= 1;
     return rpb;
 }
 
@@ -182,6 +221,13 @@ int check_scales(rt_engine *e, double dist_scale, double time_scale)
     return RT_OK;
 }
 
+int run_fast_sqrt_check(rt_engine *e, unsigned lo, unsigned hi, unsigned long long *mismatches_d, cudaStream_t st)
+{
+    fast_sqrt_check_kernel<<<kNumSMs * 8, 256, 0, st>>>(lo, hi, mismatches_d);
+    RT_CUDA(e, cudaGetLastError());
+    return RT_OK;
+}
+
 int launch_unit_vectors(rt_engine *e, const double *lat_d, const double *lon_d, int n, int batch, double *xyz_d,
                         cudaStream_t st)
 {
@@ -204,6 +250,7 @@ int launch_matrix_cells(rt_engine *e, const double *xyz_d, int n, int batch, int
     a.r1 = r1;
     a.fd = static_cast<float>(RT_EARTH_RADIUS_M * dist_scale);
     a.ft = static_cast<float>(RT_EARTH_RADIUS_M * time_scale);
+    a.lim_hi = fast_path_limit_hi(a.fd, a.ft);
     a.cells = cells_d;
     a.pitch = rt_matrix_pitch(n);
     return launch_matrix<kCells>(e, a, batch, a.pitch, st);
@@ -220,6 +267,7 @@ int launch_matrix_planes(rt_engine *e, const double *xyz_d, int n, int r0, int r
     a.r1 = r1;
     a.fd = static_cast<float>(RT_EARTH_RADIUS_M * dist_scale);
     a.ft = static_cast<float>(RT_EARTH_RADIUS_M * time_scale);
+    a.lim_hi = fast_path_limit_hi(a.fd, a.ft);
     a.dist = dist_d;
     a.tim = time_d;
     a.pitch_i32 = pitch_i32;

@@ -97,6 +97,11 @@ class Engine:
     def handle(self):
         return self._h
 
+    @property
+    def stream(self) -> int:
+        """The engine's own stream (cudaStream_t as int); `_dev` methods take a stream literally, 0 = default."""
+        return int(self._lib.rt_engine_stream(self._h) or 0)
+
     # -- matrix (utils.py:94-109) -----------------------------------------------------------------------------------
     @staticmethod
     def matrix_pitch(n: int) -> int:
@@ -126,6 +131,12 @@ class Engine:
                                               float(time_scale), _i32(res.get("dist")), _i32(res.get("time")),
                                               _f64(res.get("metres"))))
         return res
+
+    def selftest_fast_sqrt(self, lo_bits: int, hi_bits: int) -> int:
+        """Number of floats in the bit-pattern range whose straight-line sqrt differs from IEEE sqrtf (expect 0)."""
+        bad = C.c_uint64(0)
+        self._check(self._lib.rt_selftest_fast_sqrt(self._h, lo_bits, hi_bits, C.byref(bad)))
+        return int(bad.value)
 
     def unit_vectors_dev(self, lat_ptr: int, lon_ptr: int, n: int, batch: int, xyz_ptr: int, stream: int = 0):
         self._check(self._lib.rt_unit_vectors_dev(self._h, lat_ptr, lon_ptr, int(n), int(batch), xyz_ptr, stream or None))

@@ -115,3 +115,11 @@ def test_matrix_rejects_bad_input(engine):
         engine.matrix_build([0.0, float("nan")], [0.0, 0.0])
     with pytest.raises(EngineError):
         engine.matrix_build([0.0, 1.0], [0.0, 1.0], dist_scale=1e6)
+
+
+def test_fast_sqrt_is_ieee_on_the_whole_admitted_range(engine):
+    """The straight-line cell uses nvcc's own post-range-check sqrt sequence; it must equal sqrtf bit for bit for
+    EVERY float the fast path admits: [2^-100, 0.0625] (checked up to 4.0 for margin)."""
+    lo = int(np.float32(2.0 ** -100).view(np.uint32))
+    hi = int(np.float32(4.0).view(np.uint32)) + 1
+    assert engine.selftest_fast_sqrt(lo, hi) == 0
