@@ -19,8 +19,8 @@ ERR_INFEASIBLE_STOP = 5
 
 def build(force: bool = False) -> str:
     so = os.path.join(_HERE, "liboracle.so")
-    src = os.path.join(_HERE, "routest_oracle.c")
-    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("routest_oracle.c", "routest_moves.c", "Makefile")]
+    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
     return so
 
@@ -33,6 +33,10 @@ def lib() -> C.CDLL:
         _LIB.or_greedy_trips.restype = C.c_int
         _LIB.or_p2p_check.restype = C.c_int
         _LIB.or_p2p_check.argtypes = [C.c_double] * 4
+        _LIB.or_build_positions.restype = C.c_int
+        _LIB.or_route_state.restype = C.c_int
+        _LIB.or_best_move.restype = C.c_uint64
+        _LIB.or_local_search.restype = C.c_int
     return _LIB
 
 
@@ -114,3 +118,137 @@ def greedy_trips(D, demand, cap, max_dist, T=None, tw=None):
 
 def p2p_check(payload, cap, dist_m, max_dist) -> int:
     return int(lib().or_p2p_check(float(payload), float(cap), float(dist_m), float(max_dist)))
+
+
+# ----------------------------------------------------------------------------------------------- SPEC §6-§8
+
+NO_MOVE = 0xFFFFFFFFFFFFFFFF
+FAM_2OPT, FAM_RELOCATE, FAM_SWAP = 0, 1, 2
+ALL_FAMILIES = 7
+
+
+def key_unpack(k: int):
+    """(delta, family, p, q) of a packed key (SPEC §7)."""
+    k = int(k)
+    return ((k >> 32) - 0x80000000, (k >> 30) & 3, (k >> 15) & 0x7FFF, k & 0x7FFF)
+
+
+def key_pack(delta: int, family: int, p: int, q: int) -> int:
+    return ((delta + 0x80000000) << 32) | (family << 30) | (p << 15) | q
+
+
+def build_positions(trips, n):
+    """trips: list of lists of customer ids -> node[] position array (SPEC §6)."""
+    order = np.array([i for t in trips for i in t], dtype=np.int32)
+    off = np.zeros(len(trips) + 1, np.int32)
+    off[1:] = np.cumsum([len(t) for t in trips])
+    node = np.zeros(n + len(trips), np.int32)
+    P = lib().or_build_positions(_p(order, C.c_int32), _p(off, C.c_int32), C.c_int(len(trips)), _p(node, C.c_int32))
+    assert P == node.size
+    return node
+
+
+def positions_to_trips(node):
+    trips, cur = [], []
+    for v in list(node)[1:]:
+        if v == 0:
+            trips.append(cur)
+            cur = []
+        else:
+            cur.append(int(v))
+    return trips
+
+
+class Instance:
+    """Dense int32 D/T planes + stops {ready,due,service,demand} + limits, as the oracle functions take them."""
+
+    def __init__(self, D, T, stops, cap, max_dist=2 ** 62):
+        self.D = np.ascontiguousarray(D, dtype=np.int32)
+        self.T = np.ascontiguousarray(T, dtype=np.int32)
+        self.stops = np.ascontiguousarray(stops, dtype=np.int32)
+        self.n = self.D.shape[0]
+        assert self.D.shape == (self.n, self.n) and self.T.shape == (self.n, self.n) and self.stops.shape == (self.n, 4)
+        self.cap = int(cap)
+        self.max_dist = int(max_dist)
+
+    def _args(self):
+        return (C.c_int(self.n), _p(self.D, C.c_int32), _p(self.T, C.c_int32), _p(self.stops, C.c_int32),
+                C.c_int32(self.cap), C.c_int64(self.max_dist))
+
+
+def route_state(inst: Instance, node):
+    node = np.ascontiguousarray(node, dtype=np.int32)
+    P = node.size
+    R = P - inst.n
+    route = np.zeros(P, np.int32)
+    B = np.zeros(P, np.int32)
+    Z = np.zeros(P, np.int32)
+    rload = np.zeros(P, np.int64)
+    rdist = np.zeros(P, np.int64)
+    cost = C.c_int64(0)
+    feas = lib().or_route_state(*inst._args(), _p(node, C.c_int32), C.c_int(P), _p(route, C.c_int32), _p(B, C.c_int32),
+                                _p(Z, C.c_int32), _p(rload, C.c_int64), _p(rdist, C.c_int64), C.byref(cost))
+    return dict(feasible=bool(feas), route=route, B=B, Z=Z, rload=rload[:R], rdist=rdist[:R], cost=int(cost.value))
+
+
+def _eval(fn, inst, node, family):
+    node = np.ascontiguousarray(node, dtype=np.int32)
+    P = node.size
+    delta = np.zeros((P, P), np.int32)
+    feas = np.zeros((P, P), np.uint8)
+    fn(*inst._args(), _p(node, C.c_int32), C.c_int(P), C.c_int(family), _p(delta, C.c_int32), _p(feas, C.c_uint8))
+    return delta, feas
+
+
+def eval_bruteforce(inst, node, family):
+    """(delta[P,P], feas[P,P]) by apply-and-recompute; feas: 0 infeasible, 1 feasible, 2 not a candidate."""
+    return _eval(lib().or_eval_bruteforce, inst, node, family)
+
+
+def eval_fast(inst, node, family):
+    """Same through the O(1)/sweep algebra of SPEC §7 (what the engine implements)."""
+    return _eval(lib().or_eval_fast, inst, node, family)
+
+
+def best_move(inst, node, families=ALL_FAMILIES, shard=None, threads=1) -> int:
+    node = np.ascontiguousarray(node, dtype=np.int32)
+    P = node.size
+    p0, p1 = shard if shard is not None else (0, P)
+    return int(lib().or_best_move(*inst._args(), _p(node, C.c_int32), C.c_int(P), C.c_int(families), C.c_int(p0),
+                                  C.c_int(p1), C.c_int(threads), None))
+
+
+def best_from_dump(delta, feas, family):
+    """Minimum key over a dumped family (for cross-checking best_move against the dumps)."""
+    ok = feas == 1
+    if not ok.any():
+        return NO_MOVE
+    P = delta.shape[0]
+    p, q = np.nonzero(ok)
+    keys = ((delta[p, q].astype(np.int64) + 0x80000000).astype(np.uint64) << np.uint64(32)) | \
+        (np.uint64(family) << np.uint64(30)) | (p.astype(np.uint64) << np.uint64(15)) | q.astype(np.uint64)
+    return int(keys.min())
+
+
+def count_candidates(node):
+    node = np.ascontiguousarray(node, dtype=np.int32)
+    counts = np.zeros(3, np.int64)
+    lib().or_count_candidates(_p(node, C.c_int32), C.c_int(node.size), _p(counts, C.c_int64))
+    return counts
+
+
+def apply_move(node, family, p, q):
+    node = np.array(node, dtype=np.int32)
+    lib().or_apply_move(_p(node, C.c_int32), C.c_int(family), C.c_int(p), C.c_int(q))
+    return node
+
+
+def local_search(inst, node, families=ALL_FAMILIES, max_moves=1 << 30, threads=1):
+    """Returns (final node[], applied keys, final cost)."""
+    node = np.array(node, dtype=np.int32)
+    cap_keys = min(max_moves, 1 << 22)
+    keys = np.zeros(cap_keys, np.uint64)
+    cost = C.c_int64(0)
+    m = lib().or_local_search(*inst._args(), _p(node, C.c_int32), C.c_int(node.size), C.c_int(families),
+                              C.c_int(cap_keys), C.c_int(threads), _p(keys, C.c_uint64), C.byref(cost))
+    return node, keys[:m].copy(), int(cost.value)
