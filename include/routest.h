@@ -82,6 +82,86 @@ int rt_unit_vectors_dev(rt_engine *e, const double *lat_d, const double *lon_d, 
 int rt_matrix_cells_dev(rt_engine *e, const double *xyz_d, int n, int batch, int row_begin, int row_end,
                         double dist_scale, double time_scale, void *cells_d, void *stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Greedy trip construction on a caller-supplied matrix — takes over utils.py:111-139 decision for decision (sort
+ * by distance from the depot with ties by index, capacity/max-distance acceptance in FP64, a rejected stop does not
+ * end the trip).  D is the n x n FP64 matrix in host memory, exactly what the reference holds after utils.py:103
+ * (floats, possibly asymmetric); demand[0] is ignored; cap / max_dist as at utils.py:112-113.
+ *   order_out    int32[n-1]  stops (matrix indices 1..n-1) in visiting order
+ *   trip_off_out int32[n]    trip k is order_out[trip_off_out[k] .. trip_off_out[k+1])
+ * Returns RT_ERR_INFEASIBLE_STOP (with the trips built so far) where the reference would never return.
+ */
+int rt_greedy_trips(rt_engine *e, const double *D, int n, const double *demand, double cap, double max_dist,
+                    int32_t *order_out, int32_t *trip_off_out, int32_t *n_trips_out);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * rt_problem: `batch` independent instances of n nodes each (node 0 = depot) kept on the GPU — coordinates, stop
+ * data, the {dist,time} matrix, the current routes and everything derived from them (SPEC.md §6).  None of this
+ * has a counterpart in the reference, whose only solver state is local to utils.py:_multi_stop; the calls are
+ * ordered the way that function is: matrix (utils.py:94-109) -> trips (utils.py:111-139) -> [improvement, new].
+ * All array arguments are host memory, instance-major: [batch][...].
+ */
+typedef struct rt_problem rt_problem;
+
+int rt_problem_create(rt_engine *e, int n, int batch, rt_problem **out);
+void rt_problem_destroy(rt_problem *p);
+/* Length of the per-instance position arrays returned by rt_problem_get_state. */
+int rt_problem_position_stride(const rt_problem *p);
+
+/* lat/lon [batch][n] in degrees; computes the unit vectors (SPEC.md §1). */
+int rt_problem_set_coords(rt_problem *p, const double *lat, const double *lon);
+/* stops [batch][n][4] = {ready, due, service, demand} (int32, time units of the matrix); cap [batch]; max_dist
+ * [batch] in distance units of the matrix.  The reference's request has payload only (routes.py:32-42); windows and
+ * service times are the optional extension of SPEC.md §4/§6. */
+int rt_problem_set_stops(rt_problem *p, const int32_t *stops, const int32_t *cap, const int64_t *max_dist);
+/* Builds every instance's matrix on the device (same arithmetic as rt_matrix_build). */
+int rt_problem_build_matrix(rt_problem *p, double dist_scale, double time_scale);
+/* Installs a caller-supplied matrix for one instance (dense n x n int32 planes).  Must be symmetric: the move
+ * kernels read M[a][b] where M[b][a] is meant. */
+int rt_problem_set_matrix(rt_problem *p, int instance, const int32_t *dist, const int32_t *time);
+int rt_problem_get_matrix(rt_problem *p, int instance, int32_t *dist, int32_t *time);
+
+/* Greedy construction for every instance on its device matrix (utils.py:111-139); demand [batch][n] FP64, cap and
+ * max_dist [batch] FP64.  use_tw != 0 adds the time-window acceptance test of SPEC.md §4 (needs set_stops).
+ * order_out [batch][n-1], trip_off_out [batch][n], n_trips_out [batch], status_out [batch] (RT_OK or
+ * RT_ERR_INFEASIBLE_STOP per instance). */
+int rt_problem_greedy(rt_problem *p, const double *demand, const double *cap, const double *max_dist, int use_tw,
+                      int32_t *order_out, int32_t *trip_off_out, int32_t *n_trips_out, int32_t *status_out);
+
+/* Installs routes (same layout as the greedy's output) as the current solution and derives the route state. */
+int rt_problem_set_routes(rt_problem *p, const int32_t *order, const int32_t *trip_off, const int32_t *n_trips);
+int rt_problem_get_routes(rt_problem *p, int32_t *order_out, int32_t *trip_off_out, int32_t *n_trips_out);
+/* Route state of one instance (SPEC.md §6); position arrays have rt_problem_position_stride() entries, route
+ * arrays n entries; any output may be NULL except npos_out. */
+int rt_problem_get_state(rt_problem *p, int instance, int32_t *npos_out, int32_t *node, int32_t *route, int32_t *B,
+                         int32_t *Z, int64_t *rload, int64_t *rdist, int64_t *cost, int32_t *feasible);
+
+/* Scores this shard's local-search candidates of every instance (families: bit 0 = 2-opt, 1 = relocate, 2 = swap;
+ * delta + capacity + distance-limit + time-window feasibility each) and returns the minimum packed key per instance
+ * (SPEC.md §7; 2^64-1 = none).  The candidate space is split into shard_count parts; the minimum over all shards
+ * is the best move. */
+int rt_problem_eval_moves(rt_problem *p, int families, int shard_index, int shard_count, uint64_t *best_keys_out);
+/* Every candidate of one family for one instance: delta_out int32[P*P], feas_out uint8[P*P] indexed [p*P+q];
+ * feas 0 = infeasible, 1 = feasible, 2 = not a candidate.  For tests and diagnostics. */
+int rt_problem_eval_dump(rt_problem *p, int instance, int family, int32_t *delta_out, uint8_t *feas_out);
+/* Applies one move per instance (keys [batch]; 2^64-1 = leave unchanged) and refreshes the state. */
+int rt_problem_apply_moves(rt_problem *p, const uint64_t *keys);
+/* Best-improvement local search to a local optimum or max_moves applied moves per instance (SPEC.md §8).
+ * moves_out [batch], cost_out [batch]; keys_out [batch][keys_capacity] receives the applied keys (may be NULL). */
+int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t *moves_out, int64_t *cost_out,
+                            uint64_t *keys_out, int keys_capacity);
+
+/* The same two steps on a caller's stream, for a multi-GPU search: every rank holds a replica of the problem,
+ * evaluates its shard, all-reduces the keys with MIN (e.g. NCCL through torch.distributed) and applies the winner.
+ * Keys are exchanged as int64 in order-preserving signed form (packed key XOR 2^63, so INT64_MAX = none).
+ * best_keys_d / keys_d: device int64[batch].  apply marks an instance done when there is no move or, with
+ * improving_only, when the best delta is >= 0. */
+int rt_problem_eval_moves_dev(rt_problem *p, int families, int shard_index, int shard_count, void *best_keys_d,
+                              void *stream);
+int rt_problem_apply_moves_dev(rt_problem *p, const void *keys_d, int improving_only, void *stream);
+/* Synchronises the device and reads the search bookkeeping: done [batch], moves [batch], cost [batch]. */
+int rt_problem_search_status(rt_problem *p, int32_t *done_out, int32_t *moves_out, int64_t *cost_out);
+
 /* Self-test: counts floats with bit pattern in [lo_bits, hi_bits) for which the matrix kernel's straight-line
  * square root differs from IEEE sqrtf (must be 0; SPEC.md §2 relies on it).  No reference counterpart. */
 int rt_selftest_fast_sqrt(rt_engine *e, uint32_t lo_bits, uint32_t hi_bits, uint64_t *mismatches);

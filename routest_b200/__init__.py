@@ -4,6 +4,7 @@ Host side in Python (the reference service's own language) over a C ABI (include
 hand-written sm_100a CUDA (routest_b200/csrc).  There is no CPU fallback: without the built library or without a
 GPU every entry point raises EngineError.
 """
-from .engine import Engine, EngineError, PROFILE_SPEED_MPS, profile_for_vehicle, time_scale_for_profile  # noqa: F401
+from .engine import (ALL_FAMILIES, NO_MOVE, Engine, EngineError, Problem, PROFILE_SPEED_MPS, key_unpack,  # noqa: F401
+                     profile_for_vehicle, time_scale_for_profile)
 
 __all__ = ["Engine", "EngineError", "PROFILE_SPEED_MPS", "profile_for_vehicle", "time_scale_for_profile"]

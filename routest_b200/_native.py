@@ -24,6 +24,10 @@ RT_ERR_STATE = 6
 c_engine_p = C.c_void_p
 c_f64_p = C.POINTER(C.c_double)
 c_i32_p = C.POINTER(C.c_int32)
+c_i64_p = C.POINTER(C.c_int64)
+c_u64_p = C.POINTER(C.c_uint64)
+c_u8_p = C.POINTER(C.c_uint8)
+c_problem_p = C.c_void_p
 
 # name -> (restype, argtypes); mirrors include/routest.h one to one (tests/test_abi.py checks the header against it)
 SIGNATURES = {
@@ -37,6 +41,29 @@ SIGNATURES = {
     "rt_matrix_pitch": (C.c_int, [C.c_int]),
     "rt_matrix_build": (C.c_int, [c_engine_p, c_f64_p, c_f64_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double,
                                   c_i32_p, c_i32_p, c_f64_p]),
+    "rt_greedy_trips": (C.c_int, [c_engine_p, c_f64_p, C.c_int, c_f64_p, C.c_double, C.c_double, c_i32_p, c_i32_p,
+                                  c_i32_p]),
+    "rt_problem_create": (C.c_int, [c_engine_p, C.c_int, C.c_int, C.POINTER(c_problem_p)]),
+    "rt_problem_destroy": (None, [c_problem_p]),
+    "rt_problem_position_stride": (C.c_int, [c_problem_p]),
+    "rt_problem_set_coords": (C.c_int, [c_problem_p, c_f64_p, c_f64_p]),
+    "rt_problem_set_stops": (C.c_int, [c_problem_p, c_i32_p, c_i32_p, c_i64_p]),
+    "rt_problem_build_matrix": (C.c_int, [c_problem_p, C.c_double, C.c_double]),
+    "rt_problem_set_matrix": (C.c_int, [c_problem_p, C.c_int, c_i32_p, c_i32_p]),
+    "rt_problem_get_matrix": (C.c_int, [c_problem_p, C.c_int, c_i32_p, c_i32_p]),
+    "rt_problem_greedy": (C.c_int, [c_problem_p, c_f64_p, c_f64_p, c_f64_p, C.c_int, c_i32_p, c_i32_p, c_i32_p,
+                                    c_i32_p]),
+    "rt_problem_set_routes": (C.c_int, [c_problem_p, c_i32_p, c_i32_p, c_i32_p]),
+    "rt_problem_get_routes": (C.c_int, [c_problem_p, c_i32_p, c_i32_p, c_i32_p]),
+    "rt_problem_get_state": (C.c_int, [c_problem_p, C.c_int, c_i32_p, c_i32_p, c_i32_p, c_i32_p, c_i32_p, c_i64_p,
+                                       c_i64_p, c_i64_p, c_i32_p]),
+    "rt_problem_eval_moves": (C.c_int, [c_problem_p, C.c_int, C.c_int, C.c_int, c_u64_p]),
+    "rt_problem_eval_dump": (C.c_int, [c_problem_p, C.c_int, C.c_int, c_i32_p, c_u8_p]),
+    "rt_problem_apply_moves": (C.c_int, [c_problem_p, c_u64_p]),
+    "rt_problem_local_search": (C.c_int, [c_problem_p, C.c_int, C.c_int, c_i32_p, c_i64_p, c_u64_p, C.c_int]),
+    "rt_problem_eval_moves_dev": (C.c_int, [c_problem_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "rt_problem_apply_moves_dev": (C.c_int, [c_problem_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "rt_problem_search_status": (C.c_int, [c_problem_p, c_i32_p, c_i32_p, c_i64_p]),
     "rt_selftest_fast_sqrt": (C.c_int, [c_engine_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]),
     "rt_unit_vectors_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_matrix_cells_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,

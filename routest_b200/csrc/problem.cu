@@ -1,0 +1,546 @@
+// problem.cu — extern "C" entry points around rt_problem: a batch of device-resident instances on which the
+// matrix build, the greedy construction, move evaluation and local search run without the matrix ever leaving HBM.
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "problem.cuh"
+
+namespace rt {
+
+int greedy_f64_launch(rt_engine *e, const double *D_d, int n, const double *demand_d, const double *cap_d,
+                      const double *maxd_d, unsigned long long *keys_d, int *order_d, int *order_out_d, int *trip_off_d,
+                      int *ntrips_d, int *status_d, cudaStream_t st);
+
+namespace {
+
+template <typename T>
+int dev_alloc(rt_problem *p, T *&ptr, size_t count)
+{
+    void *raw = nullptr;
+    RT_CUDA(p->e, cudaMalloc(&raw, std::max<size_t>(count, 1) * sizeof(T)));
+    ptr = static_cast<T *>(raw);
+    p->all_allocs[p->n_allocs++] = raw;
+    return RT_OK;
+}
+
+int next_pow2(int v)
+{
+    int r = 1;
+    while (r < v) r <<= 1;
+    return r;
+}
+
+int stage(rt_problem *p, size_t bytes)
+{
+    if (bytes <= p->host_stage_bytes) return RT_OK;
+    if (p->host_stage) cudaFreeHost(p->host_stage);
+    p->host_stage = nullptr;
+    p->host_stage_bytes = 0;
+    RT_CUDA(p->e, cudaHostAlloc(&p->host_stage, bytes, cudaHostAllocDefault));
+    p->host_stage_bytes = bytes;
+    return RT_OK;
+}
+
+// interleaves / de-interleaves dense host-layout planes with the device cell layout
+__global__ void planes_to_cells_kernel(const int *__restrict__ dist, const int *__restrict__ tim, int n, int pitch,
+                                       int2 *__restrict__ cells)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= pitch) return;
+    cells[static_cast<size_t>(i) * pitch + j] =
+        j < n ? make_int2(dist[static_cast<size_t>(i) * n + j], tim[static_cast<size_t>(i) * n + j]) : make_int2(0, 0);
+}
+
+__global__ void cells_to_planes_kernel(const int2 *__restrict__ cells, int n, int pitch, int *__restrict__ dist,
+                                       int *__restrict__ tim)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= n) return;
+    const int2 c = cells[static_cast<size_t>(i) * pitch + j];
+    dist[static_cast<size_t>(i) * n + j] = c.x;
+    tim[static_cast<size_t>(i) * n + j] = c.y;
+}
+
+__global__ void reset_search_kernel(int *done, int *moves, int batch)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < batch) {
+        done[i] = 0;
+        moves[i] = 0;
+    }
+}
+
+}  // namespace
+}  // namespace rt
+
+using namespace rt;
+
+#define RT_PROBLEM_GUARD(p)                       \
+    if (!(p)) return RT_ERR_INVALID_ARG;          \
+    rt_engine *e = (p)->e;                        \
+    std::lock_guard<std::mutex> lk(e->mu);        \
+    DeviceGuard dg(e->device)
+
+extern "C" {
+
+int rt_problem_create(rt_engine *e, int n, int batch, rt_problem **out)
+{
+    if (!e) return RT_ERR_INVALID_ARG;
+    if (!out || n < 2 || batch < 1) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_create: need n >= 2, batch >= 1");
+    *out = nullptr;
+    if (2 * n > kMaxPositions)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_create: n = %d exceeds the %d positions a move key can address", n,
+                    kMaxPositions / 2);
+    std::lock_guard<std::mutex> lk(e->mu);
+    DeviceGuard dg(e->device);
+    rt_problem *p = new (std::nothrow) rt_problem();
+    if (!p) return fail(e, RT_ERR_OUT_OF_MEMORY, "out of host memory");
+    p->e = e;
+    p->n = n;
+    p->batch = batch;
+    p->pitch = rt_matrix_pitch(n);
+    p->pstride = (2 * n + 3) & ~3;  // P = n + R <= 2n - 1
+    p->rstride = n;
+    p->hist_cap = 4 * n;
+    const size_t B = batch, N = n, PS = p->pstride, RS = p->rstride;
+    const int n2 = next_pow2(n - 1);
+    int rc = RT_OK;
+    auto A = [&](int r) { if (rc == RT_OK) rc = r; };
+    A(dev_alloc(p, p->lat, B * N));
+    A(dev_alloc(p, p->lon, B * N));
+    A(dev_alloc(p, p->xyz, B * 3 * N));
+    A(dev_alloc(p, p->cells, B * N * p->pitch));
+    A(dev_alloc(p, p->stops, B * N));
+    A(dev_alloc(p, p->cap, B));
+    A(dev_alloc(p, p->max_dist, B));
+    A(dev_alloc(p, p->npos, B));
+    A(dev_alloc(p, p->nroutes, B));
+    A(dev_alloc(p, p->node, B * PS));
+    A(dev_alloc(p, p->node_tmp, B * PS));
+    A(dev_alloc(p, p->RA, B * PS));
+    A(dev_alloc(p, p->RB, B * PS));
+    A(dev_alloc(p, p->RC, B * PS));
+    A(dev_alloc(p, p->RD, B * PS));
+    A(dev_alloc(p, p->E, B * PS));
+    A(dev_alloc(p, p->SK, B * PS));
+    A(dev_alloc(p, p->Bv, B * PS));
+    A(dev_alloc(p, p->Zv, B * PS));
+    A(dev_alloc(p, p->route, B * PS));
+    A(dev_alloc(p, p->rstart, B * (RS + 1)));
+    A(dev_alloc(p, p->rload, B * RS));
+    A(dev_alloc(p, p->rdist, B * RS));
+    A(dev_alloc(p, p->cost, B));
+    A(dev_alloc(p, p->feasible, B));
+    A(dev_alloc(p, p->best, B));
+    A(dev_alloc(p, p->done, B));
+    A(dev_alloc(p, p->moves, B));
+    A(dev_alloc(p, p->hist, B * p->hist_cap));
+    A(dev_alloc(p, p->gkeys, B * n2));
+    A(dev_alloc(p, p->gorder, B * n2));
+    A(dev_alloc(p, p->gdemand, B * N));
+    A(dev_alloc(p, p->gcap, B));
+    A(dev_alloc(p, p->gmaxd, B));
+    A(dev_alloc(p, p->g_order_out, B * N));
+    A(dev_alloc(p, p->g_trip_off, B * (N + 1)));
+    A(dev_alloc(p, p->g_ntrips, B));
+    A(dev_alloc(p, p->g_status, B));
+    if (rc != RT_OK) {
+        for (int i = 0; i < p->n_allocs; ++i) cudaFree(p->all_allocs[i]);
+        delete p;
+        return rc;
+    }
+    *out = p;
+    return RT_OK;
+}
+
+void rt_problem_destroy(rt_problem *p)
+{
+    if (!p) return;
+    rt_engine *e = p->e;
+    std::lock_guard<std::mutex> lk(e->mu);
+    DeviceGuard dg(e->device);
+    cudaStreamSynchronize(e->stream);
+    for (int i = 0; i < p->n_allocs; ++i) cudaFree(p->all_allocs[i]);
+    if (p->host_stage) cudaFreeHost(p->host_stage);
+    delete p;
+}
+
+int rt_problem_set_coords(rt_problem *p, const double *lat, const double *lon)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!lat || !lon) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_set_coords: NULL argument");
+    const long long total = static_cast<long long>(p->n) * p->batch;
+    for (long long i = 0; i < total; ++i)
+        if (!(lat[i] >= -90.0 && lat[i] <= 90.0) || !(lon[i] >= -180.0 && lon[i] <= 180.0))
+            return fail(e, RT_ERR_INVALID_ARG, "coordinate %lld out of range or not finite", i);
+    RT_CUDA(e, cudaMemcpyAsync(p->lat, lat, total * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(p->lon, lon, total * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    p->has_coords = true;
+    p->has_matrix = false;
+    return RT_OK;
+}
+
+int rt_problem_set_stops(rt_problem *p, const int32_t *stops, const int32_t *cap, const int64_t *max_dist)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!stops || !cap || !max_dist) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_set_stops: NULL argument");
+    const long long total = static_cast<long long>(p->n) * p->batch;
+    for (long long i = 0; i < total; ++i) {
+        const int32_t *s = stops + 4 * i;
+        if (s[0] > s[1] || s[2] < 0 || s[3] < 0 || s[0] < 0 || s[1] > (1 << 29))
+            return fail(e, RT_ERR_INVALID_ARG,
+                        "stop %lld: need 0 <= ready <= due <= 2^29, service >= 0, demand >= 0 (got %d,%d,%d,%d)", i, s[0],
+                        s[1], s[2], s[3]);
+    }
+    for (int b = 0; b < p->batch; ++b)
+        if (cap[b] < 0 || max_dist[b] < 0) return fail(e, RT_ERR_INVALID_ARG, "negative capacity or distance limit");
+    RT_CUDA(e, cudaMemcpyAsync(p->stops, stops, total * sizeof(int4), cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, p->batch * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, p->batch * sizeof(long long), cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    p->has_stops = true;
+    return RT_OK;
+}
+
+int rt_problem_build_matrix(rt_problem *p, double dist_scale, double time_scale)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!p->has_coords) return fail(e, RT_ERR_STATE, "rt_problem_build_matrix: set coordinates first");
+    RT_TRY(check_scales(e, dist_scale, time_scale));
+    RT_TRY(launch_matrix_cells(e, p->xyz, p->n, p->batch, 0, p->n, dist_scale, time_scale, p->cells, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    p->dist_scale = dist_scale;
+    p->time_scale = time_scale;
+    p->has_matrix = true;
+    return RT_OK;
+}
+
+int rt_problem_set_matrix(rt_problem *p, int instance, const int32_t *dist, const int32_t *tim)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!dist || !tim || instance < 0 || instance >= p->batch)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_set_matrix: bad argument");
+    const size_t cnt = static_cast<size_t>(p->n) * p->n;
+    for (size_t i = 0; i < cnt; ++i)
+        if (dist[i] < 0 || tim[i] < 0 || dist[i] >= (1 << 29) || tim[i] >= (1 << 29))
+            return fail(e, RT_ERR_INVALID_ARG, "matrix entries must lie in [0, 2^29)");
+    for (int i = 0; i < p->n; ++i)
+        for (int j = 0; j < i; ++j)
+            if (dist[static_cast<size_t>(i) * p->n + j] != dist[static_cast<size_t>(j) * p->n + i] ||
+                tim[static_cast<size_t>(i) * p->n + j] != tim[static_cast<size_t>(j) * p->n + i])
+                return fail(e, RT_ERR_INVALID_ARG, "the move kernels need a symmetric matrix (cell %d,%d differs)", i, j);
+    RT_TRY(reserve(e, e->plane_a[0], cnt * 4));
+    RT_TRY(reserve(e, e->plane_b[0], cnt * 4));
+    int *dd = static_cast<int *>(e->plane_a[0].p), *td = static_cast<int *>(e->plane_b[0].p);
+    RT_CUDA(e, cudaMemcpyAsync(dd, dist, cnt * 4, cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(td, tim, cnt * 4, cudaMemcpyHostToDevice, e->stream));
+    dim3 grid((p->pitch + 255) / 256, p->n);
+    planes_to_cells_kernel<<<grid, 256, 0, e->stream>>>(dd, td, p->n, p->pitch,
+                                                        p->cells + static_cast<size_t>(instance) * p->n * p->pitch);
+    RT_CUDA(e, cudaGetLastError());
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    p->has_matrix = true;
+    return RT_OK;
+}
+
+int rt_problem_get_matrix(rt_problem *p, int instance, int32_t *dist, int32_t *tim)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!dist || !tim || instance < 0 || instance >= p->batch)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_get_matrix: bad argument");
+    if (!p->has_matrix) return fail(e, RT_ERR_STATE, "rt_problem_get_matrix: no matrix yet");
+    const size_t cnt = static_cast<size_t>(p->n) * p->n;
+    RT_TRY(reserve(e, e->plane_a[0], cnt * 4));
+    RT_TRY(reserve(e, e->plane_b[0], cnt * 4));
+    int *dd = static_cast<int *>(e->plane_a[0].p), *td = static_cast<int *>(e->plane_b[0].p);
+    dim3 grid((p->n + 255) / 256, p->n);
+    cells_to_planes_kernel<<<grid, 256, 0, e->stream>>>(p->cells + static_cast<size_t>(instance) * p->n * p->pitch, p->n,
+                                                        p->pitch, dd, td);
+    RT_CUDA(e, cudaGetLastError());
+    RT_CUDA(e, cudaMemcpyAsync(dist, dd, cnt * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(tim, td, cnt * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    return RT_OK;
+}
+
+int rt_problem_greedy(rt_problem *p, const double *demand, const double *cap, const double *max_dist, int use_tw,
+                      int32_t *order_out, int32_t *trip_off_out, int32_t *n_trips_out, int32_t *status_out)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!demand || !cap || !max_dist || !order_out || !trip_off_out || !n_trips_out || !status_out)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_greedy: NULL argument");
+    if (!p->has_matrix) return fail(e, RT_ERR_STATE, "rt_problem_greedy: no matrix yet");
+    if (use_tw && !p->has_stops) return fail(e, RT_ERR_STATE, "rt_problem_greedy: time windows requested but no stops set");
+    const size_t B = p->batch, N = p->n;
+    RT_CUDA(e, cudaMemcpyAsync(p->gdemand, demand, B * N * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(p->gcap, cap, B * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(p->gmaxd, max_dist, B * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    RT_TRY(greedy_launch(p, use_tw != 0, e->stream));
+    // results: order [B][n-1] (device rows have stride n), trip offsets [B][n+1] -> host [B][n]
+    std::vector<int> tmp(B * (N + 1));
+    RT_CUDA(e, cudaMemcpy2DAsync(order_out, (N - 1) * 4, p->g_order_out, N * 4, (N - 1) * 4, B, cudaMemcpyDeviceToHost,
+                                 e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(tmp.data(), p->g_trip_off, B * (N + 1) * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(n_trips_out, p->g_ntrips, B * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(status_out, p->g_status, B * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    for (size_t b = 0; b < B; ++b)
+        for (size_t k = 0; k < N; ++k) trip_off_out[b * N + k] = k <= static_cast<size_t>(n_trips_out[b]) ? tmp[b * (N + 1) + k] : 0;
+    return RT_OK;
+}
+
+int rt_greedy_trips(rt_engine *e, const double *D, int n, const double *demand, double cap, double max_dist,
+                    int32_t *order_out, int32_t *trip_off_out, int32_t *n_trips_out)
+{
+    if (!e) return RT_ERR_INVALID_ARG;
+    if (!D || !demand || !order_out || !trip_off_out || !n_trips_out || n < 1)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_greedy_trips: bad argument");
+    *n_trips_out = 0;
+    trip_off_out[0] = 0;
+    if (n == 1) return RT_OK;
+    std::lock_guard<std::mutex> lk(e->mu);
+    DeviceGuard dg(e->device);
+    const size_t N = n, n2 = next_pow2(n - 1);
+    // one scratch block: D | demand | cap,maxd | keys | order | order_out | trip_off | ntrips,status
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~size_t(255); return o; };
+    const size_t oD = take(N * N * 8), oDem = take(N * 8), oLim = take(16), oKeys = take(n2 * 8), oOrd = take(n2 * 4),
+                 oOut = take(N * 4), oOff = take((N + 1) * 4), oRes = take(8);
+    RT_TRY(reserve(e, e->plane_c[0], off));
+    char *base = static_cast<char *>(e->plane_c[0].p);
+    const double lim[2] = {cap, max_dist};
+    RT_CUDA(e, cudaMemcpyAsync(base + oD, D, N * N * 8, cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(base + oDem, demand, N * 8, cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(base + oLim, lim, 16, cudaMemcpyHostToDevice, e->stream));
+    RT_TRY(greedy_f64_launch(e, reinterpret_cast<double *>(base + oD), n, reinterpret_cast<double *>(base + oDem),
+                             reinterpret_cast<double *>(base + oLim), reinterpret_cast<double *>(base + oLim) + 1,
+                             reinterpret_cast<unsigned long long *>(base + oKeys), reinterpret_cast<int *>(base + oOrd),
+                             reinterpret_cast<int *>(base + oOut), reinterpret_cast<int *>(base + oOff),
+                             reinterpret_cast<int *>(base + oRes), reinterpret_cast<int *>(base + oRes) + 1, e->stream));
+    int res[2] = {0, 0};
+    std::vector<int> offs(N + 1);
+    RT_CUDA(e, cudaMemcpyAsync(order_out, base + oOut, (N - 1) * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(offs.data(), base + oOff, (N + 1) * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(res, base + oRes, 8, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    *n_trips_out = res[0];
+    for (int k = 0; k <= res[0]; ++k) trip_off_out[k] = offs[k];
+    if (res[1] != RT_OK)
+        return fail(e, res[1], "a stop fits no trip on its own (capacity or maximum_distance); %d trips built", res[0]);
+    return RT_OK;
+}
+
+int rt_problem_set_routes(rt_problem *p, const int32_t *order, const int32_t *trip_off, const int32_t *n_trips)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!order || !trip_off || !n_trips) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_set_routes: NULL argument");
+    if (!p->has_matrix || !p->has_stops) return fail(e, RT_ERR_STATE, "rt_problem_set_routes: matrix and stops first");
+    const size_t B = p->batch, N = p->n, PS = p->pstride;
+    std::vector<int> node(B * PS, 0), npos(B);
+    std::vector<char> seen(N);
+    for (size_t b = 0; b < B; ++b) {
+        const int R = n_trips[b];
+        const int32_t *off = trip_off + b * N, *ord = order + b * (N - 1);
+        if (R < 1 || R > static_cast<int>(N) - 1 || off[0] != 0 || off[R] != static_cast<int>(N) - 1)
+            return fail(e, RT_ERR_INVALID_ARG, "instance %zu: trips must cover all %zu customers exactly once", b, N - 1);
+        std::fill(seen.begin(), seen.end(), 0);
+        int *nd = node.data() + b * PS, P = 0;
+        nd[P++] = 0;
+        for (int k = 0; k < R; ++k) {
+            if (off[k + 1] < off[k]) return fail(e, RT_ERR_INVALID_ARG, "instance %zu: trip offsets must not decrease", b);
+            for (int i = off[k]; i < off[k + 1]; ++i) {
+                const int c = ord[i];
+                if (c < 1 || c >= static_cast<int>(N) || seen[c])
+                    return fail(e, RT_ERR_INVALID_ARG, "instance %zu: customer %d out of range or repeated", b, c);
+                seen[c] = 1;
+                nd[P++] = c;
+            }
+            nd[P++] = 0;
+        }
+        npos[b] = P;
+    }
+    RT_CUDA(e, cudaMemcpyAsync(p->node, node.data(), B * PS * 4, cudaMemcpyHostToDevice, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(p->npos, npos.data(), B * 4, cudaMemcpyHostToDevice, e->stream));
+    reset_search_kernel<<<(p->batch + 255) / 256, 256, 0, e->stream>>>(p->done, p->moves, p->batch);
+    RT_CUDA(e, cudaGetLastError());
+    RT_TRY(state_refresh(p, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    p->has_routes = true;
+    return RT_OK;
+}
+
+int rt_problem_get_routes(rt_problem *p, int32_t *order_out, int32_t *trip_off_out, int32_t *n_trips_out)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!order_out || !trip_off_out || !n_trips_out) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_get_routes: NULL argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_get_routes: no routes set");
+    const size_t B = p->batch, N = p->n, PS = p->pstride;
+    std::vector<int> node(B * PS), npos(B);
+    RT_CUDA(e, cudaMemcpyAsync(node.data(), p->node, B * PS * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(npos.data(), p->npos, B * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    for (size_t b = 0; b < B; ++b) {
+        const int *nd = node.data() + b * PS;
+        int32_t *off = trip_off_out + b * N, *ord = order_out + b * (N - 1);
+        int R = 0, c = 0;
+        off[0] = 0;
+        for (int q = 1; q < npos[b]; ++q) {
+            if (nd[q] == 0) off[++R] = c;
+            else ord[c++] = nd[q];
+        }
+        n_trips_out[b] = R;
+    }
+    return RT_OK;
+}
+
+int rt_problem_get_state(rt_problem *p, int instance, int32_t *npos_out, int32_t *node, int32_t *route, int32_t *Bv,
+                         int32_t *Zv, int64_t *rload, int64_t *rdist, int64_t *cost, int32_t *feasible)
+{
+    RT_PROBLEM_GUARD(p);
+    if (instance < 0 || instance >= p->batch || !npos_out)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_get_state: bad argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_get_state: no routes set");
+    const size_t PS = p->pstride, RS = p->rstride, po = instance * PS, ro = instance * RS;
+    auto D2H = [&](void *dst, const void *src, size_t bytes) {
+        return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, e->stream) : cudaSuccess;
+    };
+    RT_CUDA(e, D2H(npos_out, p->npos + instance, 4));
+    RT_CUDA(e, D2H(node, p->node + po, PS * 4));
+    RT_CUDA(e, D2H(route, p->route + po, PS * 4));
+    RT_CUDA(e, D2H(Bv, p->Bv + po, PS * 4));
+    RT_CUDA(e, D2H(Zv, p->Zv + po, PS * 4));
+    RT_CUDA(e, D2H(rload, p->rload + ro, RS * 8));
+    RT_CUDA(e, D2H(rdist, p->rdist + ro, RS * 8));
+    RT_CUDA(e, D2H(cost, p->cost + instance, 8));
+    RT_CUDA(e, D2H(feasible, p->feasible + instance, 4));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    return RT_OK;
+}
+
+int rt_problem_position_stride(const rt_problem *p) { return p ? p->pstride : 0; }
+
+int rt_problem_eval_moves(rt_problem *p, int families, int shard_index, int shard_count, uint64_t *best_keys_out)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!best_keys_out || shard_count < 1 || shard_index < 0 || shard_index >= shard_count || !(families & 7))
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_eval_moves: bad argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_eval_moves: no routes set");
+    RT_TRY(eval_moves_launch(p, families, shard_index, shard_count, p->best, false, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(best_keys_out, p->best, p->batch * 8, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    return RT_OK;
+}
+
+int rt_problem_eval_moves_dev(rt_problem *p, int families, int shard_index, int shard_count, void *best_keys_d,
+                              void *stream)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    rt_engine *e = p->e;
+    if (!best_keys_d || shard_count < 1 || shard_index < 0 || shard_index >= shard_count || !(families & 7))
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_eval_moves_dev: bad argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_eval_moves_dev: no routes set");
+    DeviceGuard dg(e->device);
+    return eval_moves_launch(p, families, shard_index, shard_count, static_cast<unsigned long long *>(best_keys_d), true,
+                             pick_stream(e, stream));
+}
+
+int rt_problem_eval_dump(rt_problem *p, int instance, int family, int32_t *delta_out, uint8_t *feas_out)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!delta_out || !feas_out || instance < 0 || instance >= p->batch || family < 0 || family > 2)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_eval_dump: bad argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_eval_dump: no routes set");
+    int P = 0;
+    RT_CUDA(e, cudaMemcpy(&P, p->npos + instance, 4, cudaMemcpyDeviceToHost));
+    const size_t cnt = static_cast<size_t>(P) * P;
+    RT_TRY(reserve(e, e->plane_a[0], cnt * 4));
+    RT_TRY(reserve(e, e->plane_b[0], cnt));
+    int *dd = static_cast<int *>(e->plane_a[0].p);
+    unsigned char *fd = static_cast<unsigned char *>(e->plane_b[0].p);
+    RT_CUDA(e, cudaMemsetAsync(dd, 0, cnt * 4, e->stream));
+    RT_CUDA(e, cudaMemsetAsync(fd, 2, cnt, e->stream));  // 2 = not a candidate
+    RT_TRY(eval_dump_launch(p, instance, family, dd, fd, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(delta_out, dd, cnt * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(feas_out, fd, cnt, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    return RT_OK;
+}
+
+int rt_problem_apply_moves(rt_problem *p, const uint64_t *keys)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!keys) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_apply_moves: NULL argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_apply_moves: no routes set");
+    RT_CUDA(e, cudaMemcpyAsync(p->best, keys, p->batch * 8, cudaMemcpyHostToDevice, e->stream));
+    RT_TRY(apply_moves_launch(p, p->best, false, false, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    return RT_OK;
+}
+
+int rt_problem_apply_moves_dev(rt_problem *p, const void *keys_d, int improving_only, void *stream)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    rt_engine *e = p->e;
+    if (!keys_d) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_apply_moves_dev: NULL argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_apply_moves_dev: no routes set");
+    DeviceGuard dg(e->device);
+    return apply_moves_launch(p, static_cast<const unsigned long long *>(keys_d), true, improving_only != 0,
+                              pick_stream(e, stream));
+}
+
+int rt_problem_search_status(rt_problem *p, int32_t *done_out, int32_t *moves_out, int64_t *cost_out)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_search_status: no routes set");
+    RT_CUDA(e, cudaDeviceSynchronize());  // _dev calls may have used any stream
+    if (done_out) RT_CUDA(e, cudaMemcpy(done_out, p->done, p->batch * 4, cudaMemcpyDeviceToHost));
+    if (moves_out) RT_CUDA(e, cudaMemcpy(moves_out, p->moves, p->batch * 4, cudaMemcpyDeviceToHost));
+    if (cost_out) RT_CUDA(e, cudaMemcpy(cost_out, p->cost, p->batch * 8, cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t *moves_out, int64_t *cost_out,
+                            uint64_t *keys_out, int keys_capacity)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!(families & 7) || max_moves < 0) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_local_search: bad argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_local_search: no routes set");
+    RT_TRY(stage(p, static_cast<size_t>(p->batch) * 4));
+    int *done_h = static_cast<int *>(p->host_stage);
+    reset_search_kernel<<<(p->batch + 255) / 256, 256, 0, e->stream>>>(p->done, p->moves, p->batch);
+    RT_CUDA(e, cudaGetLastError());
+    RT_TRY(state_refresh(p, e->stream));
+    // The host only paces the loop: kChunk iterations are enqueued blind (an instance that has reached its local
+    // optimum turns its own later iterations into no-ops on the device), then one 4-byte-per-instance read decides
+    // whether to go on.
+    const int kChunk = 32;
+    int issued = 0;
+    bool all_done = false;
+    while (!all_done && issued < max_moves) {
+        const int todo = std::min(kChunk, max_moves - issued);
+        for (int i = 0; i < todo; ++i) {
+            RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, e->stream));
+            RT_TRY(apply_moves_launch(p, p->best, false, true, e->stream));
+        }
+        issued += todo;
+        RT_CUDA(e, cudaMemcpyAsync(done_h, p->done, p->batch * 4, cudaMemcpyDeviceToHost, e->stream));
+        RT_CUDA(e, cudaStreamSynchronize(e->stream));
+        all_done = true;
+        for (int b = 0; b < p->batch; ++b) all_done = all_done && done_h[b] != 0;
+    }
+    if (moves_out) RT_CUDA(e, cudaMemcpyAsync(moves_out, p->moves, p->batch * 4, cudaMemcpyDeviceToHost, e->stream));
+    if (cost_out) RT_CUDA(e, cudaMemcpyAsync(cost_out, p->cost, p->batch * 8, cudaMemcpyDeviceToHost, e->stream));
+    if (keys_out && keys_capacity > 0) {
+        const int w = std::min(keys_capacity, p->hist_cap);
+        RT_CUDA(e, cudaMemcpy2DAsync(keys_out, static_cast<size_t>(keys_capacity) * 8, p->hist,
+                                     static_cast<size_t>(p->hist_cap) * 8, static_cast<size_t>(w) * 8, p->batch,
+                                     cudaMemcpyDeviceToHost, e->stream));
+    }
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,76 @@
+// problem.cuh — a batch of device-resident VRPTW instances: coordinates, stop data, the interleaved {dist,time}
+// matrix, the current solution in position space (SPEC.md §6) and everything derived from it.
+#pragma once
+
+#include "common.cuh"
+
+namespace rt {
+
+constexpr unsigned long long kNoMove = 0xFFFFFFFFFFFFFFFFull;
+constexpr int kMaxPositions = 32768;  // key layout: 15 bits per position (SPEC.md §7)
+
+// Per-position records written by the state refresh and read by the move kernels (all int4 => one LDG.128 each).
+//   RA = {dep = B[p]+service[node p], zn = Z[p+1], E.d = D[node p][node p+1], route[p]}      "edge after p"
+//   RB = {ready, due, service, demand} of node p
+//   RC = {dep[p-1], rem_delta[p], oe[p] = D[node p-1][node p]+D[node p][node p+1], flags}    flags: 1 customer, 2 rem_ok
+//   RD = {cap - rload[route p], min(max_dist - rdist[route p], INT_MAX), E.t, SK.t}
+struct StateView {
+    int n, pitch, pstride, rstride;
+    const int2 *cells;   // [n][pitch]
+    const int4 *stops;   // [n]
+    int *node;           // [pstride]
+    int4 *RA, *RB, *RC, *RD;
+    int2 *E, *SK;        // E[p] = cell(node p, node p+1), SK[p] = cell(node p-1, node p+1)
+    int *Bv, *Zv, *route;  // [pstride] plain copies for the getters
+    int *rstart;         // [rstride+1] separator positions
+    long long *rload, *rdist;  // [rstride]
+};
+
+}  // namespace rt
+
+struct rt_problem {
+    rt_engine *e = nullptr;
+    int n = 0, batch = 0, pitch = 0, pstride = 0, rstride = 0;
+    bool has_coords = false, has_stops = false, has_matrix = false, has_routes = false;
+    double dist_scale = 0, time_scale = 0;
+    // device arrays, all [batch][...]
+    double *lat = nullptr, *lon = nullptr, *xyz = nullptr;
+    int2 *cells = nullptr;
+    int4 *stops = nullptr;
+    int *cap = nullptr;
+    long long *max_dist = nullptr;
+    int *npos = nullptr, *nroutes = nullptr;
+    int *node = nullptr, *node_tmp = nullptr;
+    int4 *RA = nullptr, *RB = nullptr, *RC = nullptr, *RD = nullptr;
+    int2 *E = nullptr, *SK = nullptr;
+    int *Bv = nullptr, *Zv = nullptr, *route = nullptr, *rstart = nullptr;
+    long long *rload = nullptr, *rdist = nullptr;
+    long long *cost = nullptr;             // [batch]
+    int *feasible = nullptr;               // [batch]
+    unsigned long long *best = nullptr;    // [batch] packed keys (SPEC §7)
+    int *done = nullptr, *moves = nullptr; // [batch] local-search bookkeeping
+    unsigned long long *hist = nullptr;    // [batch][hist_cap] applied keys
+    int hist_cap = 0;
+    // greedy scratch
+    unsigned long long *gkeys = nullptr;   // [batch][npow2]
+    int *gorder = nullptr;                 // [batch][n]
+    double *gdemand = nullptr;             // [batch][n]
+    double *gcap = nullptr, *gmaxd = nullptr;  // [batch]
+    int *g_order_out = nullptr, *g_trip_off = nullptr, *g_ntrips = nullptr, *g_status = nullptr;
+    void *host_stage = nullptr;            // pinned staging for small D2H results
+    size_t host_stage_bytes = 0;
+    void *all_allocs[64] = {nullptr};
+    int n_allocs = 0;
+};
+
+namespace rt {
+
+int state_refresh(rt_problem *p, cudaStream_t st);
+int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d,
+                      bool signed_keys, cudaStream_t st);
+int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsigned char *feas_d, cudaStream_t st);
+int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
+                       cudaStream_t st);
+int greedy_launch(rt_problem *p, bool use_tw, cudaStream_t st);
+
+}  // namespace rt

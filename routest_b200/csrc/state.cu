@@ -1,0 +1,250 @@
+// state.cu — route state in position space (SPEC.md §6): the refresh that derives every per-position record the
+// move kernels read, and the kernel that applies a chosen move (SPEC.md §8).
+//
+// No reference counterpart: the reference's only solver loop is the greedy constructor (utils.py:111-139).
+#include <climits>
+
+#include "problem.cuh"
+
+namespace rt {
+
+namespace {
+
+// K1: everything that depends only on node[] — one thread per position, gathers from the matrix in parallel.
+__global__ void __launch_bounds__(256) state_gather_kernel(const int2 *__restrict__ cells, const int4 *__restrict__ stops,
+                                                           const int *__restrict__ node, const int *__restrict__ npos,
+                                                           int n, int pitch, int pstride, int4 *__restrict__ RB,
+                                                           int2 *__restrict__ E, int2 *__restrict__ SK)
+{
+    const int b = blockIdx.y;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int P = npos[b];
+    if (p >= P) return;
+    const int *nd = node + static_cast<size_t>(b) * pstride;
+    const int2 *M = cells + static_cast<size_t>(b) * n * pitch;
+    const int cur = nd[p], nxt = p + 1 < P ? nd[p + 1] : 0, prv = p > 0 ? nd[p - 1] : 0;
+    const size_t o = static_cast<size_t>(b) * pstride + p;
+    RB[o] = stops[static_cast<size_t>(b) * n + cur];
+    E[o] = p + 1 < P ? M[static_cast<size_t>(cur) * pitch + nxt] : make_int2(0, 0);
+    SK[o] = cur != 0 ? M[static_cast<size_t>(prv) * pitch + nxt] : make_int2(0, 0);
+}
+
+// K2: one block per instance.  (A) route ids by a block scan over the separators, (B) one thread per route walks
+// it forwards (B, load, distance) and backwards (Z), (C) the packed records.
+constexpr int kWalkThreads = 1024;
+
+__global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
+    const int *__restrict__ node_all, const int *__restrict__ npos, int *__restrict__ nroutes_out, int n, int pstride,
+    int rstride, const int4 *__restrict__ stops_all, const int *__restrict__ cap_all,
+    const long long *__restrict__ maxd_all, const int4 *__restrict__ RB_all, const int2 *__restrict__ E_all,
+    const int2 *__restrict__ SK_all, int4 *__restrict__ RA_all, int4 *__restrict__ RC_all, int4 *__restrict__ RD_all,
+    int *__restrict__ Bv_all, int *__restrict__ Zv_all, int *__restrict__ route_all, int *__restrict__ rstart_all,
+    long long *__restrict__ rload_all, long long *__restrict__ rdist_all, long long *__restrict__ cost_all,
+    int *__restrict__ feasible_all, unsigned long long *__restrict__ best_all)
+{
+    __shared__ int s_scan[kWalkThreads];
+    __shared__ int s_feas;
+    __shared__ unsigned long long s_cost;
+
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int P = npos[b];
+    const size_t po = static_cast<size_t>(b) * pstride, ro = static_cast<size_t>(b) * rstride;
+    const int *node = node_all + po;
+    const int4 *RB = RB_all + po;
+    const int2 *E = E_all + po, *SK = SK_all + po;
+    int *Bv = Bv_all + po, *Zv = Zv_all + po, *route = route_all + po, *rstart = rstart_all + ro + b;  // rstride+1 each
+    long long *rload = rload_all + ro, *rdist = rdist_all + ro;
+    const int4 depot = stops_all[static_cast<size_t>(b) * n];
+    const int cap = cap_all[b];
+    const long long maxd = maxd_all[b];
+
+    if (tid == 0) {
+        s_feas = 1;
+        s_cost = 0;
+    }
+
+    // (A) route[p] = #separators at positions <= p, minus 1
+    const int chunk = (P + kWalkThreads - 1) / kWalkThreads;
+    const int c0 = min(P, tid * chunk), c1 = min(P, c0 + chunk);
+    int cnt = 0;
+    for (int p = c0; p < c1; ++p) cnt += node[p] == 0;
+    s_scan[tid] = cnt;
+    __syncthreads();
+    for (int off = 1; off < kWalkThreads; off <<= 1) {  // Hillis-Steele inclusive scan
+        int v = tid >= off ? s_scan[tid - off] : 0;
+        __syncthreads();
+        s_scan[tid] += v;
+        __syncthreads();
+    }
+    int r = s_scan[tid] - cnt - 1;  // separators before this chunk, minus 1
+    for (int p = c0; p < c1; ++p) {
+        if (node[p] == 0) {
+            ++r;
+            rstart[r] = p;
+        }
+        route[p] = r;
+    }
+    const int R = s_scan[kWalkThreads - 1] - 1;
+    if (tid == 0) nroutes_out[b] = R;
+    __syncthreads();
+
+    // (B) walks
+    bool feas = true;
+    unsigned long long cost = 0;
+    for (int rr = tid; rr < R; rr += kWalkThreads) {
+        const int s = rstart[rr], e = rstart[rr + 1];
+        int Bcur = depot.x, svc_prev = depot.z;
+        long long load = 0, dist = 0;
+        Bv[s] = depot.x;
+        Zv[s] = depot.y;
+        for (int p = s + 1; p < e; ++p) {
+            const int2 ed = E[p - 1];
+            const int4 rb = RB[p];
+            Bcur = max(rb.x, Bcur + svc_prev + ed.y);
+            feas = feas && Bcur <= rb.y;
+            Bv[p] = Bcur;
+            svc_prev = rb.z;
+            load += rb.w;
+            dist += ed.x;
+        }
+        const int2 last = E[e - 1];
+        feas = feas && (Bcur + svc_prev + last.y <= depot.y);
+        dist += last.x;
+        rload[rr] = load;
+        rdist[rr] = dist;
+        feas = feas && load <= cap && dist <= maxd;
+        cost += static_cast<unsigned long long>(dist);
+        int Zn = depot.y;
+        for (int p = e - 1; p > s; --p) {
+            const int4 rb = RB[p];
+            Zn = min(rb.y, Zn - E[p].y - rb.z);
+            Zv[p] = Zn;
+        }
+    }
+    if (tid == 0) {
+        Bv[P - 1] = depot.x;
+        Zv[P - 1] = depot.y;
+    }
+    if (!feas) s_feas = 0;
+    if (cost) atomicAdd(&s_cost, cost);
+    __syncthreads();
+
+    // (C) records
+    int4 *RA = RA_all + po, *RC = RC_all + po, *RD = RD_all + po;
+    for (int p = tid; p < P; p += kWalkThreads) {
+        const int rt_ = route[p];
+        const int4 rb = RB[p];
+        const int2 ed = E[p], sk = SK[p];
+        const int dep = Bv[p] + rb.z;
+        const int zn = p + 1 < P ? Zv[p + 1] : depot.y;
+        RA[p] = make_int4(dep, zn, ed.x, rt_);
+        int capsl = -1, dsl = INT_MIN;
+        if (rt_ < R) {
+            capsl = static_cast<int>(min(static_cast<long long>(INT_MAX), cap - rload[rt_]));
+            const long long sl = maxd - rdist[rt_];
+            dsl = static_cast<int>(max(static_cast<long long>(INT_MIN), min(static_cast<long long>(INT_MAX), sl)));
+        }
+        RD[p] = make_int4(capsl, dsl, ed.y, sk.y);
+        if (node[p] != 0) {
+            const int2 ep = E[p - 1];
+            const int dep_prev = Bv[p - 1] + RB[p - 1].z;
+            const int rem_delta = sk.x - ep.x - ed.x;
+            const bool rem_ok = dep_prev + sk.y <= zn && rem_delta <= dsl;
+            RC[p] = make_int4(dep_prev, rem_delta, ep.x + ed.x, 1 | (rem_ok ? 2 : 0));
+        } else {
+            RC[p] = make_int4(0, 0, 0, 0);
+        }
+    }
+    if (tid == 0) {
+        cost_all[b] = static_cast<long long>(s_cost);
+        feasible_all[b] = s_feas;
+        best_all[b] = kNoMove;
+    }
+}
+
+// Applies one move per instance (SPEC.md §8).  keys are the packed keys of SPEC.md §7, optionally in the
+// order-preserving signed form (key ^ 2^63) that the _dev entry points exchange with NCCL.
+__global__ void __launch_bounds__(256) apply_moves_kernel(const unsigned long long *__restrict__ keys, int signed_keys,
+                                                          int improving_only, int *__restrict__ node_all,
+                                                          int *__restrict__ tmp_all, const int *__restrict__ npos,
+                                                          int pstride, int *__restrict__ done, int *__restrict__ moves,
+                                                          unsigned long long *__restrict__ hist, int hist_cap)
+{
+    const int b = blockIdx.x, tid = threadIdx.x;
+    unsigned long long key = keys[b];
+    if (signed_keys) key ^= 0x8000000000000000ull;
+    if (done[b]) return;
+    const int delta = static_cast<int>(static_cast<unsigned>(key >> 32) - 0x80000000u);
+    if (key == kNoMove || (improving_only && delta >= 0)) {
+        if (tid == 0) done[b] = 1;
+        return;
+    }
+    const int family = static_cast<int>((key >> 30) & 3), p = static_cast<int>((key >> 15) & 0x7FFF),
+              q = static_cast<int>(key & 0x7FFF);
+    const int P = npos[b];
+    int *node = node_all + static_cast<size_t>(b) * pstride;
+    int *tmp = tmp_all + static_cast<size_t>(b) * pstride;
+    if (p >= P || q >= P) {  // malformed key: refuse
+        if (tid == 0) done[b] = 2;
+        return;
+    }
+    if (family == 2) {
+        if (tid == 0) {
+            int t = node[p];
+            node[p] = node[q];
+            node[q] = t;
+        }
+    } else {
+        // affected span [lo, hi]; new[i] = old[src(i)]
+        int lo, hi;
+        if (family == 1) {
+            lo = q > p ? p : q + 1;
+            hi = q > p ? q : p;
+        } else {
+            lo = p + 1;
+            hi = q;
+        }
+        for (int i = lo + tid; i <= hi; i += blockDim.x) tmp[i] = node[i];
+        __syncthreads();
+        for (int i = lo + tid; i <= hi; i += blockDim.x) {
+            int src;
+            if (family == 1) src = q > p ? (i == q ? p : i + 1) : (i == q + 1 ? p : i - 1);
+            else src = lo + hi - i;
+            node[i] = tmp[src];
+        }
+    }
+    if (tid == 0) {
+        const int m = moves[b];
+        if (hist && m < hist_cap) hist[static_cast<size_t>(b) * hist_cap + m] = key;
+        moves[b] = m + 1;
+    }
+}
+
+}  // namespace
+
+int state_refresh(rt_problem *p, cudaStream_t st)
+{
+    rt_engine *e = p->e;
+    dim3 g1((p->pstride + 255) / 256, p->batch);
+    state_gather_kernel<<<g1, 256, 0, st>>>(p->cells, p->stops, p->node, p->npos, p->n, p->pitch, p->pstride, p->RB,
+                                            p->E, p->SK);
+    RT_CUDA(e, cudaGetLastError());
+    state_walk_kernel<<<p->batch, kWalkThreads, 0, st>>>(p->node, p->npos, p->nroutes, p->n, p->pstride, p->rstride,
+                                                         p->stops, p->cap, p->max_dist, p->RB, p->E, p->SK, p->RA, p->RC,
+                                                         p->RD, p->Bv, p->Zv, p->route, p->rstart, p->rload, p->rdist,
+                                                         p->cost, p->feasible, p->best);
+    RT_CUDA(e, cudaGetLastError());
+    return RT_OK;
+}
+
+int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
+                       cudaStream_t st)
+{
+    apply_moves_kernel<<<p->batch, 256, 0, st>>>(keys_d, signed_keys ? 1 : 0, improving_only ? 1 : 0, p->node,
+                                                 p->node_tmp, p->npos, p->pstride, p->done, p->moves, p->hist,
+                                                 p->hist_cap);
+    RT_CUDA(p->e, cudaGetLastError());
+    return state_refresh(p, st);
+}
+
+}  // namespace rt

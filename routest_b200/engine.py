@@ -148,3 +148,210 @@ class Engine:
             time_scale = time_scale_for_profile("driving-car")
         self._check(self._lib.rt_matrix_cells_dev(self._h, xyz_ptr, int(n), int(batch), int(r0), int(r1),
                                                   float(dist_scale), float(time_scale), cells_ptr, stream or None))
+
+    # -- greedy on a caller-supplied matrix (utils.py:111-139) --------------------------------------------------------
+    def greedy_trips(self, D, demand, cap: float, max_dist: float):
+        """Trips over an (n x n) matrix D held by the caller (floats allowed, asymmetric allowed), node 0 = depot.
+        Returns (trips, infeasible): trips is a list of lists of matrix indices without the depot; infeasible is
+        True where the reference would loop forever (SPEC.md §4)."""
+        D = np.ascontiguousarray(D, dtype=np.float64)
+        n = D.shape[0]
+        if D.shape != (n, n):
+            raise ValueError("D must be square")
+        demand = np.ascontiguousarray(demand, dtype=np.float64)
+        if demand.shape != (n,):
+            raise ValueError("demand must have one entry per node (entry 0 is ignored)")
+        order = np.zeros(max(n - 1, 1), np.int32)
+        off = np.zeros(n, np.int32)
+        nt = C.c_int32(0)
+        rc = self._lib.rt_greedy_trips(self._h, _f64(D), n, _f64(demand), float(cap), float(max_dist), _i32(order),
+                                       _i32(off), C.byref(nt))
+        if rc not in (N.RT_OK, N.RT_ERR_INFEASIBLE_STOP):
+            self._check(rc)
+        trips = [order[off[k]:off[k + 1]].tolist() for k in range(nt.value)]
+        return trips, rc == N.RT_ERR_INFEASIBLE_STOP
+
+    def problem(self, n: int, batch: int = 1) -> "Problem":
+        return Problem(self, n, batch)
+
+
+NO_MOVE = 0xFFFFFFFFFFFFFFFF
+FAM_2OPT, FAM_RELOCATE, FAM_SWAP = 0, 1, 2
+ALL_FAMILIES = 7
+
+
+def key_unpack(k: int):
+    """(delta, family, p, q) of a packed move key (SPEC.md §7)."""
+    k = int(k)
+    return ((k >> 32) - 0x80000000, (k >> 30) & 3, (k >> 15) & 0x7FFF, k & 0x7FFF)
+
+
+def _u64(a):
+    return a.ctypes.data_as(N.c_u64_p)
+
+
+def _i64(a):
+    return a.ctypes.data_as(N.c_i64_p) if a is not None else None
+
+
+class Problem:
+    """A batch of device-resident instances (include/routest.h: rt_problem).  Arrays are instance-major."""
+
+    def __init__(self, engine: Engine, n: int, batch: int = 1):
+        self.engine = engine
+        self._lib = engine._lib
+        self._p = N.c_problem_p()
+        engine._check(self._lib.rt_problem_create(engine.handle, int(n), int(batch), C.byref(self._p)))
+        self.n, self.batch = int(n), int(batch)
+        self.pstride = int(self._lib.rt_problem_position_stride(self._p))
+
+    def close(self):
+        if getattr(self, "_p", None):
+            self._lib.rt_problem_destroy(self._p)
+            self._p = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._p
+
+    def _check(self, rc):
+        self.engine._check(rc)
+
+    def _arr(self, a, dtype, shape):
+        a = np.ascontiguousarray(a, dtype=dtype)
+        if a.shape != shape:
+            if a.size == int(np.prod(shape)):
+                a = a.reshape(shape)
+            else:
+                raise ValueError(f"expected shape {shape}, got {a.shape}")
+        return a
+
+    # -- inputs
+    def set_coords(self, lat, lon):
+        lat = self._arr(lat, np.float64, (self.batch, self.n))
+        lon = self._arr(lon, np.float64, (self.batch, self.n))
+        self._check(self._lib.rt_problem_set_coords(self._p, _f64(lat), _f64(lon)))
+
+    def set_stops(self, stops, cap, max_dist=None):
+        stops = self._arr(stops, np.int32, (self.batch, self.n, 4))
+        cap = self._arr(np.broadcast_to(np.asarray(cap), (self.batch,)), np.int32, (self.batch,))
+        md = np.full(self.batch, 2 ** 62, np.int64) if max_dist is None else \
+            self._arr(np.broadcast_to(np.asarray(max_dist), (self.batch,)), np.int64, (self.batch,))
+        self._check(self._lib.rt_problem_set_stops(self._p, _i32(stops), _i32(cap), _i64(md)))
+
+    def build_matrix(self, dist_scale: float = DEFAULT_DIST_SCALE, time_scale: float | None = None):
+        if time_scale is None:
+            time_scale = time_scale_for_profile("driving-car")
+        self._check(self._lib.rt_problem_build_matrix(self._p, float(dist_scale), float(time_scale)))
+
+    def set_matrix(self, instance: int, dist, time):
+        dist = self._arr(dist, np.int32, (self.n, self.n))
+        time = self._arr(time, np.int32, (self.n, self.n))
+        self._check(self._lib.rt_problem_set_matrix(self._p, int(instance), _i32(dist), _i32(time)))
+
+    def get_matrix(self, instance: int = 0):
+        d = np.empty((self.n, self.n), np.int32)
+        t = np.empty((self.n, self.n), np.int32)
+        self._check(self._lib.rt_problem_get_matrix(self._p, int(instance), _i32(d), _i32(t)))
+        return d, t
+
+    # -- construction (utils.py:111-139)
+    def greedy(self, demand, cap, max_dist=9e12, use_tw: bool = False):
+        """Returns (trips per instance, status per instance)."""
+        demand = self._arr(demand, np.float64, (self.batch, self.n))
+        cap = self._arr(np.broadcast_to(np.asarray(cap, dtype=np.float64), (self.batch,)), np.float64, (self.batch,))
+        md = self._arr(np.broadcast_to(np.asarray(max_dist, dtype=np.float64), (self.batch,)), np.float64, (self.batch,))
+        order = np.zeros((self.batch, self.n - 1), np.int32)
+        off = np.zeros((self.batch, self.n), np.int32)
+        nt = np.zeros(self.batch, np.int32)
+        status = np.zeros(self.batch, np.int32)
+        self._check(self._lib.rt_problem_greedy(self._p, _f64(demand), _f64(cap), _f64(md), int(bool(use_tw)),
+                                                _i32(order), _i32(off), _i32(nt), _i32(status)))
+        trips = [[order[b, off[b, k]:off[b, k + 1]].tolist() for k in range(nt[b])] for b in range(self.batch)]
+        return trips, status
+
+    # -- routes and state (SPEC.md §6)
+    def set_routes(self, trips):
+        """trips: per instance, a list of lists of customer ids."""
+        order = np.zeros((self.batch, self.n - 1), np.int32)
+        off = np.zeros((self.batch, self.n), np.int32)
+        nt = np.zeros(self.batch, np.int32)
+        for b, tr in enumerate(trips):
+            flat = [c for t in tr for c in t]
+            order[b, :len(flat)] = flat
+            nt[b] = len(tr)
+            off[b, 1:len(tr) + 1] = np.cumsum([len(t) for t in tr])
+        self._check(self._lib.rt_problem_set_routes(self._p, _i32(order), _i32(off), _i32(nt)))
+
+    def get_routes(self):
+        order = np.zeros((self.batch, self.n - 1), np.int32)
+        off = np.zeros((self.batch, self.n), np.int32)
+        nt = np.zeros(self.batch, np.int32)
+        self._check(self._lib.rt_problem_get_routes(self._p, _i32(order), _i32(off), _i32(nt)))
+        return [[order[b, off[b, k]:off[b, k + 1]].tolist() for k in range(nt[b])] for b in range(self.batch)]
+
+    def get_state(self, instance: int = 0):
+        ps, n = self.pstride, self.n
+        npos = C.c_int32(0)
+        node, route, B, Z = (np.zeros(ps, np.int32) for _ in range(4))
+        rload, rdist = np.zeros(n, np.int64), np.zeros(n, np.int64)
+        cost, feas = C.c_int64(0), C.c_int32(0)
+        self._check(self._lib.rt_problem_get_state(self._p, int(instance), C.byref(npos), _i32(node), _i32(route),
+                                                   _i32(B), _i32(Z), _i64(rload), _i64(rdist), C.byref(cost),
+                                                   C.byref(feas)))
+        P = npos.value
+        R = P - n
+        return dict(P=P, node=node[:P], route=route[:P], B=B[:P], Z=Z[:P], rload=rload[:R], rdist=rdist[:R],
+                    cost=int(cost.value), feasible=bool(feas.value))
+
+    # -- moves (SPEC.md §7-§8)
+    def eval_moves(self, families: int = ALL_FAMILIES, shard=(0, 1)):
+        keys = np.zeros(self.batch, np.uint64)
+        self._check(self._lib.rt_problem_eval_moves(self._p, int(families), int(shard[0]), int(shard[1]), _u64(keys)))
+        return keys
+
+    def eval_dump(self, instance: int, family: int, P: int):
+        delta = np.zeros((P, P), np.int32)
+        feas = np.zeros((P, P), np.uint8)
+        self._check(self._lib.rt_problem_eval_dump(self._p, int(instance), int(family), _i32(delta),
+                                                   feas.ctypes.data_as(N.c_u8_p)))
+        return delta, feas
+
+    def apply_moves(self, keys):
+        keys = self._arr(keys, np.uint64, (self.batch,))
+        self._check(self._lib.rt_problem_apply_moves(self._p, _u64(keys)))
+
+    def local_search(self, families: int = ALL_FAMILIES, max_moves: int = 1 << 30, keys_capacity: int = 0):
+        moves = np.zeros(self.batch, np.int32)
+        cost = np.zeros(self.batch, np.int64)
+        keys = np.zeros((self.batch, max(keys_capacity, 1)), np.uint64)
+        self._check(self._lib.rt_problem_local_search(self._p, int(families), int(min(max_moves, 2 ** 31 - 1)),
+                                                      _i32(moves), _i64(cost), _u64(keys) if keys_capacity else None,
+                                                      int(keys_capacity)))
+        return moves, cost, [keys[b, :min(moves[b], keys_capacity)].copy() for b in range(self.batch)]
+
+    def eval_moves_dev(self, keys_ptr: int, families: int = ALL_FAMILIES, shard=(0, 1), stream: int = 0):
+        self._check(self._lib.rt_problem_eval_moves_dev(self._p, int(families), int(shard[0]), int(shard[1]), keys_ptr,
+                                                        stream or None))
+
+    def apply_moves_dev(self, keys_ptr: int, improving_only: bool = True, stream: int = 0):
+        self._check(self._lib.rt_problem_apply_moves_dev(self._p, keys_ptr, int(bool(improving_only)), stream or None))
+
+    def search_status(self):
+        done = np.zeros(self.batch, np.int32)
+        moves = np.zeros(self.batch, np.int32)
+        cost = np.zeros(self.batch, np.int64)
+        self._check(self._lib.rt_problem_search_status(self._p, _i32(done), _i32(moves), _i64(cost)))
+        return done, moves, cost

@@ -1,0 +1,175 @@
+"""GPU: route state, move evaluation (every candidate's delta and feasibility flag), best-move keys and local
+search through the C ABI, bit-exact against the oracle (whose algebra is itself pinned to brute force on the CPU)."""
+import numpy as np
+import pytest
+
+from conftest import TS_CAR, synth_vrptw
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _load(engine, insts, states=None):
+    """Problem holding the given oracle instances with the oracle's own matrices installed."""
+    B, n = len(insts), insts[0][0].n
+    pr = engine.problem(n, B)
+    pr.set_coords(np.stack([r["lat"] for _, _, r in insts]), np.stack([r["lon"] for _, _, r in insts]))
+    pr.build_matrix(10.0, TS_CAR)
+    pr.set_stops(np.stack([i.stops for i, _, _ in insts]), [i.cap for i, _, _ in insts],
+                 [i.max_dist for i, _, _ in insts])
+    nodes = states if states is not None else [nd for _, nd, _ in insts]
+    pr.set_routes([O.positions_to_trips(nd) for nd in nodes])
+    return pr
+
+
+def _walk(inst, node, seed, moves):
+    rng = np.random.default_rng(seed)
+    node = node.copy()
+    for _ in range(moves):
+        fam = int(rng.integers(0, 3))
+        _, f = O.eval_fast(inst, node, fam)
+        p, q = np.nonzero(f == 1)
+        if p.size:
+            i = int(rng.integers(0, p.size))
+            node = O.apply_move(node, fam, int(p[i]), int(q[i]))
+    return node
+
+
+def test_device_matrix_equals_oracle_matrix(engine):
+    inst, node, raw = synth_vrptw(21, 90, 6)
+    with _load(engine, [(inst, node, raw)]) as pr:
+        d, t = pr.get_matrix(0)
+    assert np.array_equal(d, inst.D) and np.array_equal(t, inst.T)
+
+
+@pytest.mark.parametrize("seed,stops,veh,kw", [(1, 12, 3, {}), (2, 25, 4, {}), (3, 60, 5, dict(half_lo=300, half_hi=900)),
+                                                (4, 100, 10, {}), (5, 150, 4, dict(half_lo=7200, half_hi=20000)),
+                                                (6, 70, 2, dict(half_lo=20000, half_hi=43200))])
+def test_route_state_and_every_candidate(engine, seed, stops, veh, kw):
+    inst, node0, raw = synth_vrptw(seed, stops, veh, **kw)
+    for node in (node0, _walk(inst, node0, seed, 15)):
+        with _load(engine, [(inst, node0, raw)], [node]) as pr:
+            st = pr.get_state(0)
+            ref = O.route_state(inst, node)
+            assert st["P"] == node.size and np.array_equal(st["node"], node)
+            for k in ("route", "B", "Z", "rload", "rdist"):
+                assert np.array_equal(st[k], ref[k]), k
+            assert st["cost"] == ref["cost"] and st["feasible"] == ref["feasible"] is True
+            best = []
+            for fam in (0, 1, 2):
+                d, f = pr.eval_dump(0, fam, node.size)
+                dr, fr = O.eval_fast(inst, node, fam)
+                assert np.array_equal(f, fr), f"feasibility flags differ in family {fam}"
+                assert np.array_equal(d[fr != 2], dr[fr != 2]), f"deltas differ in family {fam}"
+                best.append(O.best_from_dump(dr, fr, fam))
+                assert int(pr.eval_moves(1 << fam)[0]) == best[-1]
+            assert int(pr.eval_moves()[0]) == min(best) == O.best_move(inst, node)
+
+
+def test_distance_limit_flags(engine):
+    inst, node, raw = synth_vrptw(7, 80, 6)
+    rdist = O.route_state(inst, node)["rdist"]
+    lim = O.Instance(inst.D, inst.T, inst.stops, inst.cap, max_dist=int(rdist.max()) + 2000)
+    with _load(engine, [(lim, node, raw)]) as pr:
+        for fam in (0, 1, 2):
+            d, f = pr.eval_dump(0, fam, node.size)
+            dr, fr = O.eval_bruteforce(lim, node, fam)   # straight against brute force here
+            assert np.array_equal(f, fr) and np.array_equal(d[fr != 2], dr[fr != 2])
+
+
+def test_caller_supplied_symmetric_matrix(engine):
+    """A matrix that is not great-circle (the ORS case): installed through rt_problem_set_matrix."""
+    inst, node, raw = synth_vrptw(8, 40, 4)
+    rng = np.random.default_rng(8)
+    bump = rng.integers(0, 300, inst.D.shape).astype(np.int32)
+    bump = np.triu(bump, 1)
+    D = inst.D + bump + bump.T
+    T = inst.T + (bump + bump.T) // 10
+    alt = O.Instance(D, T, inst.stops, inst.cap)
+    if not O.route_state(alt, node)["feasible"]:
+        pytest.skip("perturbed instance lost feasibility of the start")
+    with _load(engine, [(alt, node, raw)]) as pr:
+        pr.set_matrix(0, D, T)
+        pr.set_routes([O.positions_to_trips(node)])
+        for fam in (0, 1, 2):
+            d, f = pr.eval_dump(0, fam, node.size)
+            dr, fr = O.eval_bruteforce(alt, node, fam)
+            assert np.array_equal(f, fr) and np.array_equal(d[fr != 2], dr[fr != 2])
+        from routest_b200 import EngineError
+        D[1, 2] += 1
+        with pytest.raises(EngineError):
+            pr.set_matrix(0, D, T)
+
+
+def test_best_move_batched_and_sharded(engine):
+    """A batch of instances with different route counts; the minimum over shards is the unsharded best move."""
+    insts = [synth_vrptw(100 + b, 200, 5 + b) for b in range(6)]
+    with _load(engine, insts) as pr:
+        full = pr.eval_moves()
+        for b, (inst, node, _) in enumerate(insts):
+            assert int(full[b]) == O.best_move(inst, node, threads=O.num_threads())
+        for count in (2, 3, 8):
+            parts = np.stack([pr.eval_moves(shard=(i, count)) for i in range(count)])
+            assert np.array_equal(parts.min(axis=0), full)
+
+
+def test_apply_moves_matches_oracle(engine):
+    inst, node, raw = synth_vrptw(9, 90, 6)
+    with _load(engine, [(inst, node, raw)]) as pr:
+        cur = node
+        for fam in (1, 2, 0, 1, 0, 2, 1):
+            key = int(pr.eval_moves(1 << fam)[0])
+            assert key == O.best_move(inst, cur, families=1 << fam)
+            if key == O.NO_MOVE:
+                continue
+            _, f, p, q = O.key_unpack(key)
+            cur = O.apply_move(cur, f, p, q)
+            pr.apply_moves(np.array([key], np.uint64))
+            st = pr.get_state(0)
+            assert np.array_equal(st["node"], cur) and st["feasible"]
+            assert st["cost"] == O.route_state(inst, cur)["cost"]
+
+
+@pytest.mark.parametrize("seed,stops,veh", [(10, 45, 5), (11, 100, 10), (12, 300, 12)])
+def test_local_search_moves_and_final_routes_bit_exact(engine, seed, stops, veh):
+    inst, node, raw = synth_vrptw(seed, stops, veh)
+    final, keys, cost = O.local_search(inst, node, threads=O.num_threads())
+    with _load(engine, [(inst, node, raw)]) as pr:
+        moves, gcost, gkeys = pr.local_search(keys_capacity=4 * inst.n)
+        st = pr.get_state(0)
+        trips = pr.get_routes()[0]
+    assert moves[0] == len(keys) and np.array_equal(gkeys[0], keys)
+    assert gcost[0] == cost and st["cost"] == cost and st["feasible"]
+    assert np.array_equal(st["node"], final)
+    assert trips == O.positions_to_trips(final)
+
+
+def test_local_search_batch_and_max_moves(engine):
+    insts = [synth_vrptw(200 + b, 80, 6) for b in range(4)]
+    refs = [O.local_search(inst, node, max_moves=25) for inst, node, _ in insts]
+    with _load(engine, insts) as pr:
+        moves, cost, keys = pr.local_search(max_moves=25, keys_capacity=64)
+        for b in range(4):
+            assert moves[b] == len(refs[b][1]) and np.array_equal(keys[b], refs[b][1]) and cost[b] == refs[b][2]
+            assert np.array_equal(pr.get_state(b)["node"], refs[b][0])
+
+
+def test_multi_shard_search_through_dev_entry_points(engine):
+    """The two _dev steps a multi-GPU search is made of, with the NCCL MIN replaced by torch.minimum over the
+    shards' key tensors (one GPU here): same applied moves and final routes as the oracle."""
+    import torch
+    inst, node, raw = synth_vrptw(13, 120, 8)
+    final, keys, cost = O.local_search(inst, node, threads=O.num_threads())
+    shards = 4
+    with _load(engine, [(inst, node, raw)]) as pr:
+        s = torch.cuda.current_stream().cuda_stream
+        bufs = [torch.empty(1, dtype=torch.int64, device="cuda") for _ in range(shards)]
+        for it in range(len(keys) + 5):
+            for i in range(shards):
+                pr.eval_moves_dev(bufs[i].data_ptr(), shard=(i, shards), stream=s)
+            best = torch.stack(bufs).min(dim=0).values.contiguous()
+            pr.apply_moves_dev(best.data_ptr(), improving_only=True, stream=s)
+        done, moves, gcost = pr.search_status()
+        st = pr.get_state(0)
+    assert done[0] == 1 and moves[0] == len(keys) and gcost[0] == cost
+    assert np.array_equal(st["node"], final)
