@@ -151,6 +151,18 @@ int rt_problem_apply_moves(rt_problem *p, const uint64_t *keys);
 int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t *moves_out, int64_t *cost_out,
                             uint64_t *keys_out, int keys_capacity);
 
+/* One pass of the hot path from host inputs to best moves, for every instance: uploads coordinates, stop data
+ * and the current solution, builds the matrices (utils.py:94-109), derives the route state and scores the full
+ * neighbourhood; only the best keys [batch] come back (the matrices stay on the GPU).  node is the position array
+ * of SPEC.md §6, [batch][rt_problem_position_stride()], npos [batch] its used length. */
+int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
+                    const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
+                    double time_scale, int families, uint64_t *best_keys_out);
+
+/* Stream-ordered pieces of the same pass for inputs that are already on the device (no synchronisation). */
+int rt_problem_build_matrix_dev(rt_problem *p, double dist_scale, double time_scale, void *stream);
+int rt_problem_refresh_dev(rt_problem *p, void *stream);
+
 /* The same two steps on a caller's stream, for a multi-GPU search: every rank holds a replica of the problem,
  * evaluates its shard, all-reduces the keys with MIN (e.g. NCCL through torch.distributed) and applies the winner.
  * Keys are exchanged as int64 in order-preserving signed form (packed key XOR 2^63, so INT64_MAX = none).

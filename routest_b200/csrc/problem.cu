@@ -420,6 +420,67 @@ int rt_problem_get_state(rt_problem *p, int instance, int32_t *npos_out, int32_t
     return RT_OK;
 }
 
+int rt_problem_build_matrix_dev(rt_problem *p, double dist_scale, double time_scale, void *stream)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    rt_engine *e = p->e;
+    if (!p->has_coords) return fail(e, RT_ERR_STATE, "rt_problem_build_matrix_dev: set coordinates first");
+    RT_TRY(check_scales(e, dist_scale, time_scale));
+    DeviceGuard dg(e->device);
+    cudaStream_t st = pick_stream(e, stream);
+    RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, st));
+    RT_TRY(launch_matrix_cells(e, p->xyz, p->n, p->batch, 0, p->n, dist_scale, time_scale, p->cells, st));
+    p->dist_scale = dist_scale;
+    p->time_scale = time_scale;
+    p->has_matrix = true;
+    return RT_OK;
+}
+
+int rt_problem_refresh_dev(rt_problem *p, void *stream)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    rt_engine *e = p->e;
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_refresh_dev: no routes set");
+    DeviceGuard dg(e->device);
+    return state_refresh(p, pick_stream(e, stream));
+}
+
+int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
+                    const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
+                    double time_scale, int families, uint64_t *best_keys_out)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!lat || !lon || !stops || !cap || !max_dist || !node || !npos || !best_keys_out || !(families & 7))
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_plan: bad argument");
+    RT_TRY(check_scales(e, dist_scale, time_scale));
+    const size_t B = p->batch, N = p->n, PS = p->pstride;
+    for (size_t i = 0; i < B * N; ++i)
+        if (!(lat[i] >= -90.0 && lat[i] <= 90.0) || !(lon[i] >= -180.0 && lon[i] <= 180.0))
+            return fail(e, RT_ERR_INVALID_ARG, "coordinate %zu out of range or not finite", i);
+    for (size_t b = 0; b < B; ++b)
+        if (npos[b] < static_cast<int>(N) + 1 || npos[b] > static_cast<int>(PS) || node[b * PS] != 0 ||
+            node[b * PS + npos[b] - 1] != 0)
+            return fail(e, RT_ERR_INVALID_ARG, "instance %zu: malformed position array", b);
+    cudaStream_t st = e->stream;
+    RT_CUDA(e, cudaMemcpyAsync(p->lat, lat, B * N * 8, cudaMemcpyHostToDevice, st));
+    RT_CUDA(e, cudaMemcpyAsync(p->lon, lon, B * N * 8, cudaMemcpyHostToDevice, st));
+    RT_CUDA(e, cudaMemcpyAsync(p->stops, stops, B * N * 16, cudaMemcpyHostToDevice, st));
+    RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, B * 4, cudaMemcpyHostToDevice, st));
+    RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, B * 8, cudaMemcpyHostToDevice, st));
+    RT_CUDA(e, cudaMemcpyAsync(p->node, node, B * PS * 4, cudaMemcpyHostToDevice, st));
+    RT_CUDA(e, cudaMemcpyAsync(p->npos, npos, B * 4, cudaMemcpyHostToDevice, st));
+    RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, st));
+    RT_TRY(launch_matrix_cells(e, p->xyz, p->n, p->batch, 0, p->n, dist_scale, time_scale, p->cells, st));
+    p->has_coords = p->has_stops = p->has_matrix = p->has_routes = true;
+    p->dist_scale = dist_scale;
+    p->time_scale = time_scale;
+    RT_TRY(state_refresh(p, st));
+    RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, st));
+    RT_CUDA(e, cudaMemcpyAsync(best_keys_out, p->best, B * 8, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(e, cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
 int rt_problem_position_stride(const rt_problem *p) { return p ? p->pstride : 0; }
 
 int rt_problem_eval_moves(rt_problem *p, int families, int shard_index, int shard_count, uint64_t *best_keys_out)

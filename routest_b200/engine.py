@@ -342,6 +342,33 @@ class Problem:
                                                       int(keys_capacity)))
         return moves, cost, [keys[b, :min(moves[b], keys_capacity)].copy() for b in range(self.batch)]
 
+    def plan(self, lat, lon, stops, cap, max_dist, node, npos, *, dist_scale=DEFAULT_DIST_SCALE, time_scale=None,
+             families: int = ALL_FAMILIES, out=None):
+        """One pass of the hot path from host arrays to the best move of every instance (rt_problem_plan).  The
+        arrays are used as given when they already have the right dtype/shape (so pinned buffers stay pinned)."""
+        if time_scale is None:
+            time_scale = time_scale_for_profile("driving-car")
+        lat = self._arr(lat, np.float64, (self.batch, self.n))
+        lon = self._arr(lon, np.float64, (self.batch, self.n))
+        stops = self._arr(stops, np.int32, (self.batch, self.n, 4))
+        cap = self._arr(cap, np.int32, (self.batch,))
+        max_dist = self._arr(max_dist, np.int64, (self.batch,))
+        node = self._arr(node, np.int32, (self.batch, self.pstride))
+        npos = self._arr(npos, np.int32, (self.batch,))
+        keys = out if out is not None else np.zeros(self.batch, np.uint64)
+        self._check(self._lib.rt_problem_plan(self._p, _f64(lat), _f64(lon), _i32(stops), _i32(cap), _i64(max_dist),
+                                              _i32(node), _i32(npos), float(dist_scale), float(time_scale),
+                                              int(families), _u64(keys)))
+        return keys
+
+    def build_matrix_dev(self, dist_scale=DEFAULT_DIST_SCALE, time_scale=None, stream: int = 0):
+        if time_scale is None:
+            time_scale = time_scale_for_profile("driving-car")
+        self._check(self._lib.rt_problem_build_matrix_dev(self._p, float(dist_scale), float(time_scale), stream or None))
+
+    def refresh_dev(self, stream: int = 0):
+        self._check(self._lib.rt_problem_refresh_dev(self._p, stream or None))
+
     def eval_moves_dev(self, keys_ptr: int, families: int = ALL_FAMILIES, shard=(0, 1), stream: int = 0):
         self._check(self._lib.rt_problem_eval_moves_dev(self._p, int(families), int(shard[0]), int(shard[1]), keys_ptr,
                                                         stream or None))
