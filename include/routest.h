@@ -82,6 +82,25 @@ int rt_unit_vectors_dev(rt_engine *e, const double *lat_d, const double *lon_d, 
 int rt_matrix_cells_dev(rt_engine *e, const double *xyz_d, int n, int batch, int row_begin, int row_end,
                         double dist_scale, double time_scale, void *cells_d, void *stream);
 
+/*
+ * The same device-resident matrix as rt_unit_vectors_dev + rt_matrix_cells_dev (one instance, all rows), for callers
+ * that cannot allocate: processes that gave all GPU memory to a pool at start-up, or that must keep cudaMalloc's
+ * device-wide synchronisation off their request path, have no buffer to offer for the per-stop unit vectors.  Here
+ * that scratch lives in a static device array inside the library (384 KiB per GPU, held until exit), so the call
+ * allocates nothing; the caller passes only its inputs (lat_d, lon_d: n doubles each) and its output (cells_d:
+ * n x rt_matrix_pitch(n) cells), all device pointers.
+ *   - n may not exceed rt_matrix_static_max_nodes() (16384); larger sizes are refused with RT_ERR_INVALID_ARG;
+ *   - the first call on a GPU looks the array's device address up once (cudaGetSymbolAddress): make that call
+ *     before starting any stream capture;
+ *   - every call on a GPU shares the one array, which keeps the previous call's contents (nothing needs clearing:
+ *     each call rewrites the 3n entries it reads); calls that can overlap on the GPU race — keep them on one stream
+ *     or order them with events.
+ * This entry point has no counterpart in the reference (which neither builds a matrix nor manages device memory).
+ */
+int rt_matrix_static_max_nodes(void);
+int rt_matrix_cells_static_dev(rt_engine *e, const double *lat_d, const double *lon_d, int n, double dist_scale,
+                               double time_scale, void *cells_d, void *stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Greedy trip construction on a caller-supplied matrix — takes over utils.py:111-139 decision for decision (sort
  * by distance from the depot with ties by index, capacity/max-distance acceptance in FP64, a rejected stop does not

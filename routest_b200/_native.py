@@ -41,6 +41,9 @@ SIGNATURES = {
     "rt_matrix_pitch": (C.c_int, [C.c_int]),
     "rt_matrix_build": (C.c_int, [c_engine_p, c_f64_p, c_f64_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double,
                                   c_i32_p, c_i32_p, c_f64_p]),
+    "rt_matrix_static_max_nodes": (C.c_int, []),
+    "rt_matrix_cells_static_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_double,
+                                             C.c_void_p, C.c_void_p]),
     "rt_greedy_trips": (C.c_int, [c_engine_p, c_f64_p, C.c_int, c_f64_p, C.c_double, C.c_double, c_i32_p, c_i32_p,
                                   c_i32_p]),
     "rt_problem_create": (C.c_int, [c_engine_p, C.c_int, C.c_int, C.POINTER(c_problem_p)]),

@@ -149,6 +149,21 @@ class Engine:
         self._check(self._lib.rt_matrix_cells_dev(self._h, xyz_ptr, int(n), int(batch), int(r0), int(r1),
                                                   float(dist_scale), float(time_scale), cells_ptr, stream or None))
 
+    def matrix_cells_static_dev(self, lat_ptr: int, lon_ptr: int, n: int, cells_ptr: int, *,
+                                dist_scale: float = DEFAULT_DIST_SCALE, time_scale: float | None = None, stream: int = 0):
+        """rt_matrix_cells_static_dev: the device-resident matrix of one instance without any allocation — the unit
+        vectors go through a static array inside the library instead of a caller buffer.  For processes whose GPU
+        memory all belongs to a pool, or that keep cudaMalloc off the request path.  n <= static_max_nodes(); the
+        array is shared per GPU, so keep calls on one stream; make the first call outside stream capture."""
+        if time_scale is None:
+            time_scale = time_scale_for_profile("driving-car")
+        self._check(self._lib.rt_matrix_cells_static_dev(self._h, lat_ptr, lon_ptr, int(n), float(dist_scale),
+                                                         float(time_scale), cells_ptr, stream or None))
+
+    @staticmethod
+    def static_max_nodes() -> int:
+        return int(N.lib().rt_matrix_static_max_nodes())
+
     # -- greedy on a caller-supplied matrix (utils.py:111-139) --------------------------------------------------------
     def greedy_trips(self, D, demand, cap: float, max_dist: float):
         """Trips over an (n x n) matrix D held by the caller (floats allowed, asymmetric allowed), node 0 = depot.
