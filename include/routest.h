@@ -193,6 +193,26 @@ int rt_problem_apply_moves_dev(rt_problem *p, const void *keys_d, int improving_
 /* Synchronises the device and reads the search bookkeeping: done [batch], moves [batch], cost [batch]. */
 int rt_problem_search_status(rt_problem *p, int32_t *done_out, int32_t *moves_out, int64_t *cost_out);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * ETA scoring (SPEC.md §9) — takes over Flaskr/ml.py:35-53: the 12-feature row (ml.py:35-48) and model.predict on it
+ * (ml.py:51-53), batched.  Inputs are SoA over n stop pairs: distance_m FP64 (the value routes.py:100-103 reads from
+ * properties.summary.distance), weather u8 {0 Cloudy,1 Stormy,2 Sunny,3 Windy, other = none}, traffic u8 {0 High,
+ * 1 Jam, 2 Low, 3 Medium, other = none}, weekday u8 (0 = Monday, ml.py:44), hour u8 (ml.py:45), driver_age f32
+ * (0 means 30, ml.py:47).  The model replaces the pickle of ml.py:6-21: an ensemble in the engine's tree format
+ * (SPEC.md §9.2), copied to the GPU by rt_eta_load_model.  Without a model the scoring calls return RT_ERR_STATE
+ * (the reference returns (None, None) there, ml.py:25-26).
+ */
+int rt_eta_load_model(rt_engine *e, const void *blob, size_t bytes);
+int rt_eta_model_info(rt_engine *e, int32_t *n_trees, int32_t *n_nodes); /* -1 when no model is loaded */
+int rt_eta_score(rt_engine *e, const double *distance_m, const uint8_t *weather, const uint8_t *traffic,
+                 const uint8_t *weekday, const uint8_t *hour, const float *driver_age, int64_t n, float *minutes_out);
+/* The feature rows alone, float32 [n][12] in the column order of ml.py:35-48 (what model.predict is handed). */
+int rt_eta_features(rt_engine *e, const double *distance_m, const uint8_t *weather, const uint8_t *traffic,
+                    const uint8_t *weekday, const uint8_t *hour, const float *driver_age, int64_t n, float *rows_out);
+int rt_eta_score_dev(rt_engine *e, const double *distance_m_d, const uint8_t *weather_d, const uint8_t *traffic_d,
+                     const uint8_t *weekday_d, const uint8_t *hour_d, const float *driver_age_d, int64_t n,
+                     float *minutes_d, void *stream);
+
 /* Self-test: counts floats with bit pattern in [lo_bits, hi_bits) for which the matrix kernel's straight-line
  * square root differs from IEEE sqrtf (must be 0; SPEC.md §2 relies on it).  No reference counterpart. */
 int rt_selftest_fast_sqrt(rt_engine *e, uint32_t lo_bits, uint32_t hi_bits, uint64_t *mismatches);

@@ -252,3 +252,27 @@ def local_search(inst, node, families=ALL_FAMILIES, max_moves=1 << 30, threads=1
     m = lib().or_local_search(*inst._args(), _p(node, C.c_int32), C.c_int(node.size), C.c_int(families),
                               C.c_int(cap_keys), C.c_int(threads), _p(keys, C.c_uint64), C.byref(cost))
     return node, keys[:m].copy(), int(cost.value)
+
+
+# ----------------------------------------------------------------------------------------------- SPEC §9
+
+def eta_features(distance_m, weather, traffic, weekday, hour, age):
+    distance_m = np.ascontiguousarray(distance_m, dtype=np.float64)
+    n = distance_m.size
+    cols = [np.ascontiguousarray(a, dtype=np.uint8) for a in (weather, traffic, weekday, hour)]
+    age = np.ascontiguousarray(age, dtype=np.float32)
+    rows = np.zeros((n, 12), np.float32)
+    lib().or_eta_features(_p(distance_m, C.c_double), *[_p(c, C.c_uint8) for c in cols], _p(age, C.c_float),
+                          C.c_int64(n), _p(rows, C.c_float))
+    return rows
+
+
+def eta_eval(blob: bytes, rows, threads=1):
+    rows = np.ascontiguousarray(rows, dtype=np.float32)
+    out = np.zeros(rows.shape[0], np.float32)
+    buf = np.frombuffer(blob, dtype=np.uint8)
+    lib().or_eta_eval.restype = C.c_int
+    rc = lib().or_eta_eval(_p(buf, C.c_uint8), C.c_int64(buf.size), _p(rows, C.c_float), C.c_int64(rows.shape[0]),
+                           _p(out, C.c_float), C.c_int(threads))
+    assert rc == 0, "bad model blob"
+    return out

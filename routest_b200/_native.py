@@ -71,6 +71,14 @@ SIGNATURES = {
     "rt_problem_eval_moves_dev": (C.c_int, [c_problem_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_problem_apply_moves_dev": (C.c_int, [c_problem_p, C.c_void_p, C.c_int, C.c_void_p]),
     "rt_problem_search_status": (C.c_int, [c_problem_p, c_i32_p, c_i32_p, c_i64_p]),
+    "rt_eta_load_model": (C.c_int, [c_engine_p, C.c_void_p, C.c_size_t]),
+    "rt_eta_model_info": (C.c_int, [c_engine_p, c_i32_p, c_i32_p]),
+    "rt_eta_score": (C.c_int, [c_engine_p, c_f64_p, c_u8_p, c_u8_p, c_u8_p, c_u8_p, C.POINTER(C.c_float), C.c_int64,
+                               C.POINTER(C.c_float)]),
+    "rt_eta_features": (C.c_int, [c_engine_p, c_f64_p, c_u8_p, c_u8_p, c_u8_p, c_u8_p, C.POINTER(C.c_float), C.c_int64,
+                                  C.POINTER(C.c_float)]),
+    "rt_eta_score_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_int64, C.c_void_p, C.c_void_p]),
     "rt_selftest_fast_sqrt": (C.c_int, [c_engine_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]),
     "rt_unit_vectors_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_matrix_cells_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,

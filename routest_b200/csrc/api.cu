@@ -95,6 +95,7 @@ void rt_destroy(rt_engine *e)
         DeviceGuard g(e->device);
         if (e->stream) cudaStreamSynchronize(e->stream);
         if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
+        eta_model_free(e);
         DevBuf *bufs[] = {&e->coords, &e->xyz, &e->plane_a[0], &e->plane_a[1], &e->plane_b[0],
                           &e->plane_b[1], &e->plane_c[0], &e->plane_c[1]};
         for (DevBuf *b : bufs)

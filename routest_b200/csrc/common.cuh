@@ -31,6 +31,7 @@ struct rt_engine {
     std::mutex mu;
     char err[512] = {0};
     rt::DevBuf coords, xyz, plane_a[2], plane_b[2], plane_c[2];
+    void *eta_model = nullptr;  // rt::EtaModel*, owned (eta.cu)
 };
 
 namespace rt {
@@ -76,6 +77,7 @@ int launch_matrix_planes(rt_engine *e, const double *xyz_d, int n, int r0, int r
                          int32_t *dist_d, int32_t *time_d, double *metres_d, int pitch_i32, int pitch_f64,
                          cudaStream_t st);
 int check_scales(rt_engine *e, double dist_scale, double time_scale);
+int eta_model_free(rt_engine *e);
 int run_fast_sqrt_check(rt_engine *e, unsigned lo, unsigned hi, unsigned long long *mismatches_d, cudaStream_t st);
 
 }  // namespace rt

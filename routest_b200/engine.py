@@ -164,6 +164,47 @@ class Engine:
     def static_max_nodes() -> int:
         return int(N.lib().rt_matrix_static_max_nodes())
 
+    # -- ETA (ml.py:35-53) ------------------------------------------------------------------------------------------
+    def eta_load_model(self, blob: bytes):
+        buf = (C.c_char * len(blob)).from_buffer_copy(blob)
+        self._check(self._lib.rt_eta_load_model(self._h, C.cast(buf, C.c_void_p), len(blob)))
+
+    def eta_model_info(self):
+        nt, nn = C.c_int32(0), C.c_int32(0)
+        self._check(self._lib.rt_eta_model_info(self._h, C.byref(nt), C.byref(nn)))
+        return int(nt.value), int(nn.value)
+
+    def _eta_cols(self, distance_m, weather, traffic, weekday, hour, age):
+        d = np.ascontiguousarray(distance_m, dtype=np.float64)
+        n = d.size
+        cols = [np.ascontiguousarray(a, dtype=np.uint8) for a in (weather, traffic, weekday, hour)]
+        a = np.ascontiguousarray(age, dtype=np.float32)
+        if any(c.size != n for c in cols) or a.size != n:
+            raise ValueError("all ETA input columns must have the same length")
+        return d, cols, a, n
+
+    def eta_score(self, distance_m, weather, traffic, weekday, hour, age):
+        """Minutes (float32[n]) for n stop pairs; columns as in include/routest.h (rt_eta_score)."""
+        d, cols, a, n = self._eta_cols(distance_m, weather, traffic, weekday, hour, age)
+        out = np.zeros(n, np.float32)
+        fp = C.POINTER(C.c_float)
+        self._check(self._lib.rt_eta_score(self._h, _f64(d), *[c.ctypes.data_as(N.c_u8_p) for c in cols],
+                                           a.ctypes.data_as(fp), n, out.ctypes.data_as(fp)))
+        return out
+
+    def eta_features(self, distance_m, weather, traffic, weekday, hour, age):
+        """The float32 [n,12] rows model.predict is handed (ml.py:35-48 column order)."""
+        d, cols, a, n = self._eta_cols(distance_m, weather, traffic, weekday, hour, age)
+        out = np.zeros((n, 12), np.float32)
+        fp = C.POINTER(C.c_float)
+        self._check(self._lib.rt_eta_features(self._h, _f64(d), *[c.ctypes.data_as(N.c_u8_p) for c in cols],
+                                              a.ctypes.data_as(fp), n, out.ctypes.data_as(fp)))
+        return out
+
+    def eta_score_dev(self, dist_ptr, weather_ptr, traffic_ptr, weekday_ptr, hour_ptr, age_ptr, n, out_ptr, stream=0):
+        self._check(self._lib.rt_eta_score_dev(self._h, dist_ptr, weather_ptr, traffic_ptr, weekday_ptr, hour_ptr,
+                                               age_ptr, int(n), out_ptr, stream or None))
+
     # -- greedy on a caller-supplied matrix (utils.py:111-139) --------------------------------------------------------
     def greedy_trips(self, D, demand, cap: float, max_dist: float):
         """Trips over an (n x n) matrix D held by the caller (floats allowed, asymmetric allowed), node 0 = depot.
