@@ -37,6 +37,20 @@ class _Resp:
         return self._payload
 
 
+def stub_directions(coords):
+    """Deterministic stand-in for an ORS directions answer: straight segments, Manhattan degrees x 1e5 as metres,
+    10 m/s.  Used on both sides of the wrapper-parity tests (reference via StubORS, solver via directions_fn)."""
+    segs, td, tt = [], 0.0, 0.0
+    for a, b in zip(coords[:-1], coords[1:]):
+        d = round((abs(a[0] - b[0]) + abs(a[1] - b[1])) * 1e5, 1)
+        segs.append({"distance": d, "duration": d / 10.0,
+                     "steps": [{"distance": d, "duration": d / 10.0, "type": 11, "instruction": "Head on", "name": "-"}]})
+        td += d
+        tt += d / 10.0
+    return {"type": "Feature", "geometry": {"type": "LineString", "coordinates": [list(c) for c in coords]},
+            "properties": {"segments": segs, "summary": {"distance": td, "duration": tt}}}
+
+
 class StubORS:
     """Stands in for requests.post: serves a caller-supplied matrix for /matrix/ URLs and a straight-line
     Feature for /directions/ URLs, and records the calls."""
@@ -49,14 +63,7 @@ class StubORS:
         self.calls.append((url, json))
         if "/matrix/" in url:
             return _Resp({"distances": self.matrix})
-        coords = json["coordinates"]
-        feat = {
-            "type": "Feature",
-            "geometry": {"type": "LineString", "coordinates": coords},
-            "properties": {"segments": [{"distance": 0.0, "duration": 0.0, "steps": []}],
-                           "summary": {"distance": 0.0, "duration": 0.0}},
-        }
-        return _Resp({"features": [feat]})
+        return _Resp({"features": [stub_directions(json["coordinates"])]})
 
 
 def load_utils(matrix):

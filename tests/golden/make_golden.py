@@ -184,10 +184,53 @@ def eta_cases():
     return out
 
 
+def optimize_route_cases():
+    """Whole-function goldens: utils.optimize_route (utils.py:10-48) on request bodies, ORS stubbed with a fixed
+    matrix and oracle.ref_loader.stub_directions; the stored value is the reference's complete return dict."""
+    out = []
+
+    def run(name, body, matrix):
+        mod, stub = RL.load_utils(matrix)
+        res = mod.optimize_route(json.loads(json.dumps(body)))
+        out.append({"name": name, "body": body, "matrix": matrix, "result": res})
+
+    fixture = {"source_point": {"lat": 14.584630, "lon": 121.056885},                     # tests/test_get_route.py:3-12
+               "destination_points": [{"lat": 14.544145, "lon": 121.056617, "payload": 4},
+                                      {"lat": 14.557855, "lon": 121.066139, "payload": 4}],
+               "driver_details": {"driver_name": "John Doe", "vehicle_type": "car", "vehicle_capacity": 5,
+                                  "maximum_distance": 50000}}
+    run("ref_fixture", fixture, [[0, 4500.5, 3100.2], [4510.0, 0, 1900.7], [3050.9, 1950.1, 0]])
+    run("empty_body", {}, None)
+    run("no_destinations", {"source_point": {"lat": 1, "lon": 2}, "destination_points": []}, None)
+    one = {"source_point": {"lat": 14.58, "lon": 121.05}, "destination_points": [{"lat": 14.55, "lon": 121.06, "payload": 3}],
+           "driver_details": {"vehicle_type": " Truck ", "vehicle_capacity": 5, "driver_name": "A"}}
+    run("single_stop_ok", one, None)
+    one_bad = json.loads(json.dumps(one))
+    one_bad["driver_details"].update(vehicle_capacity=2, maximum_distance=100)
+    run("single_stop_both_errors", one_bad, None)
+    rng = np.random.default_rng(5)
+    n = 9
+    M = np.round(rng.uniform(500, 9000, (n, n)), 1)
+    np.fill_diagonal(M, 0.0)
+    body = {"source_point": {"lat": 14.58, "lon": 121.04},
+            "destination_points": [{"lat": round(14.45 + 0.02 * i, 4), "lon": round(120.98 + 0.01 * i, 4),
+                                    "payload": int(rng.integers(1, 5))} for i in range(n - 1)],
+            "driver_details": {"vehicle_type": "motorcycle", "vehicle_capacity": 7, "maximum_distance": 26000.0},
+            "meta": {"origin_id": 1}, "use_ml_eta": False}
+    run("eight_stops_float_matrix", body, M.tolist())
+    body2 = json.loads(json.dumps(body))
+    body2["driver_details"] = {}
+    for d in body2["destination_points"][::2]:
+        d.pop("payload")
+    run("eight_stops_defaults_missing_payloads", body2, M.tolist())
+    run("matrix_missing", body, [])
+    return out
+
+
 def main():
     assert RL.available(), "run this where /root/reference exists"
     for name, fn in (("greedy_cases.json", greedy_cases), ("p2p_cases.json", p2p_cases),
-                     ("eta_feature_cases.json", eta_cases)):
+                     ("eta_feature_cases.json", eta_cases), ("optimize_route_cases.json", optimize_route_cases)):
         with open(os.path.join(HERE, name), "w") as f:
             json.dump(fn(), f, indent=None, separators=(",", ":"))
             f.write("\n")

@@ -1,0 +1,119 @@
+"""The solver front end (routest_b200/solver.py) against whole-function goldens of the reference's
+utils.optimize_route (utils.py:10-48) and, for the network-free default path, against the oracle."""
+import json
+
+import numpy as np
+import pytest
+
+from conftest import TS_CAR, load_golden, synth_instance
+from oracle import oracle as O
+from oracle.ref_loader import stub_directions
+from routest_b200 import solver as S
+
+CASES = {c["name"]: c for c in load_golden("optimize_route_cases.json")}
+
+
+def _hooks(case):
+    matrix = case["matrix"]
+    return dict(matrix_fn=lambda coords, profile: {"distances": matrix},
+                directions_fn=lambda coords, profile: stub_directions(coords), engine_label="backend:ors")
+
+
+@pytest.mark.parametrize("name", ["empty_body", "no_destinations", "single_stop_ok", "single_stop_both_errors"])
+def test_host_only_paths_equal_reference(name):
+    """No matrix, no trips: validation (utils.py:15-16) and the single-stop checks (utils.py:68-80)."""
+    case = CASES[name]
+    assert S.optimize_route(json.loads(json.dumps(case["body"])), **_hooks(case)) == case["result"]
+
+
+def test_missing_source_point_raises_like_the_reference():
+    with pytest.raises(KeyError):  # utils.py:31 indexes input_data["source_point"]
+        S.optimize_route({"destination_points": [{"lat": 1, "lon": 2}]}, **_hooks(CASES["single_stop_ok"]))
+
+
+def test_matrix_service_without_distances():
+    case = CASES["matrix_missing"]
+    assert S.optimize_route(json.loads(json.dumps(case["body"])), **_hooks(case)) == case["result"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["ref_fixture", "eight_stops_float_matrix", "eight_stops_defaults_missing_payloads"])
+def test_multi_stop_equals_reference_whole_feature(engine, name):
+    """Same request, same matrix answer, same directions answers => the reference's complete return dict."""
+    case = CASES[name]
+    got = S.optimize_route(json.loads(json.dumps(case["body"])), engine=engine, **_hooks(case))
+    assert got == case["result"]
+
+
+@pytest.mark.gpu
+def test_infeasible_stop_is_reported_not_hung(engine):
+    body = json.loads(json.dumps(CASES["eight_stops_float_matrix"]["body"]))
+    body["driver_details"]["vehicle_capacity"] = 1
+    res = S.optimize_route(body, engine=engine, **_hooks(CASES["eight_stops_float_matrix"]))
+    assert "error" in res and "fit no trip" in res["error"]
+
+
+def _request(seed, stops, veh, **extra):
+    lat, lon, demand, cap = synth_instance(seed, stops, veh)
+    body = {"source_point": {"lat": float(lat[0]), "lon": float(lon[0])},
+            "destination_points": [{"lat": float(lat[i]), "lon": float(lon[i]), "payload": int(demand[i])}
+                                   for i in range(1, stops + 1)],
+            "driver_details": {"driver_name": "D", "vehicle_type": "car", "vehicle_capacity": cap, **extra}}
+    return body, lat, lon, demand, cap
+
+
+@pytest.mark.gpu
+def test_offline_default_path_shape_and_trips(engine):
+    """No hooks: engine matrix + engine greedy + straight-line directions.  Trips equal the oracle greedy on the
+    oracle matrix; the Feature has every field the frontend reads."""
+    body, lat, lon, demand, cap = _request(1234, 100, 10)
+    res = S.optimize_route(body, engine=engine)
+    m = O.matrix_rows(O.unit_vectors(lat, lon), 0, 101, 10.0, TS_CAR)
+    rc, trips = O.greedy_trips(m["dist"], demand.astype(float), float(cap), 9e12 * 10)
+    assert rc == 0
+    p = res["properties"]
+    assert p["optimized_order"] == [i - 1 for t in trips for i in t]
+    assert p["summary"]["trips"] == len(trips) and p["engine"] == "backend:b200" and p["vehicle_type"] == "car"
+    want_d = sum(m["dist"][a, b] for t in trips for a, b in zip([0] + t, t + [0])) / 10.0
+    want_t = sum(int(m["time"][a, b]) for t in trips for a, b in zip([0] + t, t + [0]))
+    assert abs(p["summary"]["distance"] - want_d) < 1e-6 and p["summary"]["duration"] == want_t
+    assert res["type"] == "Feature" and res["geometry"]["type"] == "LineString"
+    assert len(res["geometry"]["coordinates"]) == 100 + 2 * len(trips)
+    assert len(res["bbox"]) == 4 and p["destinations"] == body["destination_points"] and p["source"] == body["source_point"]
+    step = p["segments"][0]["steps"][0]
+    assert {"instruction", "type", "name", "distance", "duration"} <= set(step)
+    json.dumps(res)  # plain JSON types only
+
+
+@pytest.mark.gpu
+def test_single_stop_offline(engine):
+    body, *_ = _request(77, 1, 1)
+    res = S.optimize_route(body, engine=engine)
+    assert res["properties"]["optimized_order"] == [0] and res["properties"]["summary"]["distance"] > 0
+    body["driver_details"]["maximum_distance"] = 1.0
+    assert S.optimize_route(body, engine=engine) == {"error": "route distance exceeds maximum_distance"}
+
+
+@pytest.mark.gpu
+def test_time_windows_and_improve_extension(engine):
+    """Optional fields: windows respected by the construction, local search never worsens the distance."""
+    body, lat, lon, demand, cap = _request(4321, 120, 8)
+    m = O.matrix_rows(O.unit_vectors(lat, lon), 0, 121, 10.0, TS_CAR)
+    rng = np.random.default_rng(1)
+    for i, d in enumerate(body["destination_points"], start=1):
+        c = int(np.clip(rng.integers(0, 43200), m["time"][0, i], 43200 - 300 - m["time"][i, 0]))
+        d.update(tw_start=max(0, c - 3000), tw_end=min(43200, c + 3000), service_time=300)
+    base = S.optimize_route(json.loads(json.dumps(body)), engine=engine)
+    body["driver_details"]["improve"] = True
+    better = S.optimize_route(json.loads(json.dumps(body)), engine=engine)
+    assert "error" not in base and "error" not in better
+    assert sorted(base["properties"]["optimized_order"]) == list(range(120))
+    assert sorted(better["properties"]["optimized_order"]) == list(range(120))
+    assert better["properties"]["summary"]["distance"] < base["properties"]["summary"]["distance"]
+    # the greedy with windows equals the oracle's
+    stops = np.zeros((121, 3), np.int32)
+    stops[0] = (0, 43200, 0)
+    for i, d in enumerate(body["destination_points"], start=1):
+        stops[i] = (d["tw_start"], d["tw_end"], d["service_time"])
+    rc, trips = O.greedy_trips(m["dist"], demand.astype(float), float(cap), 9e13, T=m["time"], tw=stops)
+    assert rc == 0 and base["properties"]["optimized_order"] == [i - 1 for t in trips for i in t]
