@@ -10,6 +10,7 @@ import json
 import os
 import sys
 import time
+import zlib
 
 import numpy as np
 import torch
@@ -63,7 +64,7 @@ def main():
     routes_multi = pr.get_routes()[0]
     ok = True
     if world > 1:
-        sig = torch.tensor([int(moves[0]), int(cost[0]), hash(json.dumps(routes_multi)) % (2 ** 31)], device="cuda")
+        sig = torch.tensor([int(moves[0]), int(cost[0]), zlib.crc32(json.dumps(routes_multi).encode()) % (2 ** 31)], device="cuda")
         gathered = [torch.zeros_like(sig) for _ in range(world)]
         dist.all_gather(gathered, sig)
         ok = all(bool((g == gathered[0]).all()) for g in gathered)
