@@ -17,6 +17,7 @@
 // The matrix is assumed symmetric here (true for SPEC.md §2 matrices): M[a][b] is read where M[b][a] is meant.
 #include <climits>
 
+#include "geometry.cuh"
 #include "problem.cuh"
 
 namespace rt {
@@ -61,8 +62,11 @@ struct EvalArgs {
     const int2 *cells;
     const int *node;
     const int *npos;
-    const int4 *RA, *RB, *RC, *RD;
+    const int4 *RA, *RB, *RC, *RD, *H;
     const int2 *E, *SK;
+    const double *PX;      // unit vectors in position order [3][pstride] per instance
+    float fd, ft;          // cell scales and fast-path limit (geometry.cuh), for rebuilt cells
+    int lim_hi;
     int n, pitch, pstride;
     int families;            // bit 0 = 2-opt, 1 = relocate, 2 = swap
     int shard_index, shard_count;
@@ -79,12 +83,41 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
     hi = static_cast<int>(static_cast<long long>(P) * (idx + 1) / cnt);
 }
 
-template <bool DUMP>
+// Full evaluation of one inter-route candidate from the cold records (global memory): only reached by the few
+// candidates whose delta beats the current bound, or by every candidate in dump mode.
+__device__ __noinline__ bool check_relocate(const EvalArgs &a, size_t po, int p, int q, int2 c_pq, int2 c_pq1)
+{
+    const int4 pB = a.RB[po + p], pC = a.RC[po + p];
+    const int4 qA = a.RA[po + q], qD = a.RD[po + q];
+    const int ins = c_pq.x + c_pq1.x - qA.z;
+    const int tu = max(pB.x, qA.x + c_pq.y);
+    return (pC.w & 2) && pB.w <= qD.x && ins <= qD.y && tu <= pB.y && tu + pB.z + c_pq1.y <= qA.y;
+}
+
+__device__ __noinline__ bool check_swap(const EvalArgs &a, size_t po, int p, int q, int2 c_up, int2 c_dn, int2 c_lf,
+                                        int2 c_rt)
+{
+    const int4 pA = a.RA[po + p], pB = a.RB[po + p], pC = a.RC[po + p], pD = a.RD[po + p];
+    const int4 qA = a.RA[po + q], qB = a.RB[po + q], qC = a.RC[po + q], qD = a.RD[po + q];
+    const int d1 = c_up.x + c_dn.x - pC.z;  // route of p: pu -> v -> nu
+    const int d2 = c_lf.x + c_rt.x - qC.z;  // route of q: pw -> u -> nw
+    const int tv = max(qB.x, pC.x + c_up.y);
+    const int tu = max(pB.x, qC.x + c_lf.y);
+    return qB.w - pB.w <= pD.x && pB.w - qB.w <= qD.x && d1 <= pD.y && d2 <= qD.y && tv <= qB.y &&
+           tv + qB.z + c_dn.y <= pA.y && tu <= pB.y && tu + pB.z + c_rt.y <= qA.y;
+}
+
+// COMPUTED: the tile's cells are rebuilt from the unit vectors of the 66 + 66 positions (SPEC.md §2, the same
+// function as the matrix kernel, so the same bits) instead of being gathered from the stored matrix: ~25 ALU
+// instructions per cell replace a scattered 32-byte sector fetch per cell.  Only valid while the stored matrix is
+// the great-circle matrix of the problem's coordinates; a caller-supplied matrix takes the gather path.
+template <bool DUMP, bool COMPUTED>
 __global__ void __launch_bounds__(kInterThreads) eval_inter_kernel(const EvalArgs a)
 {
     __shared__ int2 S[kTP + 2][kTQ + 2];
-    __shared__ int4 sRA[kTP], sRB[kTP], sRC[kTP], sRD[kTP];
+    __shared__ int4 sH[kTP];
     __shared__ int s_nodeP[kTP + 2], s_nodeQ[kTQ + 2];
+    __shared__ double sPX[3][kTP + 2], sQX[3][kTQ + 2];
 
     const int b = DUMP ? a.dump_instance : blockIdx.z;
     const int P = a.npos[b];
@@ -94,92 +127,110 @@ __global__ void __launch_bounds__(kInterThreads) eval_inter_kernel(const EvalArg
     if (p0 >= p_hi || q0 >= P) return;
 
     const size_t po = static_cast<size_t>(b) * a.pstride;
-    const int *node = a.node + po;
-    const int2 *M = a.cells + static_cast<size_t>(b) * a.n * a.pitch;
     const int tid = threadIdx.x;
 
-    for (int k = tid; k < kTP + 2; k += kInterThreads) {
-        int p = p0 - 1 + k;
-        s_nodeP[k] = (p >= 0 && p < P) ? node[p] : -1;
-    }
-    for (int k = tid; k < kTQ + 2; k += kInterThreads) {
-        int q = q0 - 1 + k;
-        s_nodeQ[k] = (q >= 0 && q < P) ? node[q] : -1;
-    }
-    for (int k = tid; k < kTP; k += kInterThreads) {
-        int p = p0 + k;
-        if (p < P) {
-            sRA[k] = a.RA[po + p];
-            sRB[k] = a.RB[po + p];
-            sRC[k] = a.RC[po + p];
-            sRD[k] = a.RD[po + p];
-        } else {
-            sRC[k] = make_int4(0, 0, 0, 0);
+    for (int k = tid; k < kTP; k += kInterThreads) sH[k] = p0 + k < P ? a.H[po + p0 + k] : make_int4(0, 0, 0, 0);
+    if (COMPUTED) {
+        const double *px = a.PX + static_cast<size_t>(b) * 3 * a.pstride;
+        for (int k = tid; k < 3 * (kTP + 2); k += kInterThreads) {
+            const int comp = k / (kTP + 2), i = k - comp * (kTP + 2), p = min(max(p0 - 1 + i, 0), P - 1);
+            sPX[comp][i] = px[static_cast<size_t>(comp) * a.pstride + p];
         }
-    }
-    __syncthreads();
-    // the one gather of the tile: 66 x 66 cells, scattered within matrix rows (L2-resident)
-    for (int k = tid; k < (kTP + 2) * (kTQ + 2); k += kInterThreads) {
-        const int i = k / (kTQ + 2), j = k - i * (kTQ + 2);
-        const int na = s_nodeP[i], nb = s_nodeQ[j];
-        S[i][j] = (na >= 0 && nb >= 0) ? __ldg(&M[static_cast<size_t>(na) * a.pitch + nb]) : make_int2(0, 0);
+        for (int k = tid; k < 3 * (kTQ + 2); k += kInterThreads) {
+            const int comp = k / (kTQ + 2), j = k - comp * (kTQ + 2), q = min(max(q0 - 1 + j, 0), P - 1);
+            sQX[comp][j] = px[static_cast<size_t>(comp) * a.pstride + q];
+        }
+        __syncthreads();
+        for (int k = tid; k < (kTP + 2) * (kTQ + 2); k += kInterThreads) {
+            const int i = k / (kTQ + 2), j = k - i * (kTQ + 2);
+            const double ax = sPX[0][i], ay = sPX[1][i], az = sPX[2][i];
+            const double bx = sQX[0][j], by = sQX[1][j], bz = sQX[2][j];
+            const double dx = ax - bx, dy = ay - by, dz = az - bz;
+            const double s2 = fma(dx, dx, fma(dy, dy, dz * dz));
+            S[i][j] = __double2hiint(s2) < a.lim_hi ? cell_i32_fast(s2, a.fd, a.ft)
+                                                    : cell_i32(ax, ay, az, bx, by, bz, a.fd, a.ft);
+        }
+    } else {
+        const int *node = a.node + po;
+        const int2 *M = a.cells + static_cast<size_t>(b) * a.n * a.pitch;
+        for (int k = tid; k < kTP + 2; k += kInterThreads) {
+            const int p = p0 - 1 + k;
+            s_nodeP[k] = (p >= 0 && p < P) ? node[p] : -1;
+        }
+        for (int k = tid; k < kTQ + 2; k += kInterThreads) {
+            const int q = q0 - 1 + k;
+            s_nodeQ[k] = (q >= 0 && q < P) ? node[q] : -1;
+        }
+        __syncthreads();
+        // the one gather of the tile: 66 x 66 cells, scattered within matrix rows
+        for (int k = tid; k < (kTP + 2) * (kTQ + 2); k += kInterThreads) {
+            const int i = k / (kTQ + 2), j = k - i * (kTQ + 2);
+            const int na = s_nodeP[i], nb = s_nodeQ[j];
+            S[i][j] = (na >= 0 && nb >= 0) ? __ldg(&M[static_cast<size_t>(na) * a.pitch + nb]) : make_int2(0, 0);
+        }
     }
     __syncthreads();
 
     const int c = tid & (kTQ - 1), g = tid / kTQ;  // column of the tile, group of rows
     const int q = q0 + c, j = c + 1;
+    const bool q_in = q < P;
+    const int4 Hq = q_in ? a.H[po + q] : make_int4(0, 0, 0, -1);
+    const int q_route = Hq.w & 0x3FFFFFFF;
+    const bool q_cust = q_in && ((Hq.w >> 30) & 1);
+    const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
+    const bool swap_q = q_cust && (a.families & 4);
+
+    // Only the minimum key matters, so a candidate is fully evaluated (feasibility, cold records) only if its delta
+    // can still beat the best feasible key seen so far by this warp; the bound starts from whatever other blocks
+    // have already published for this instance.  Exact: a pruned candidate has a larger key than an existing one.
     unsigned long long best = kNoMove;
-    if (q < P) {
-        const int4 qA = a.RA[po + q], qB = a.RB[po + q], qC = a.RC[po + q], qD = a.RD[po + q];
-        const bool q_cust = qC.w & 1;
-        const bool do_rel = a.families & 2, do_swap = a.families & 4;
-        constexpr int kRows = kTP / (kInterThreads / kTQ);
-#pragma unroll 2
-        for (int rr = 0; rr < kRows; ++rr) {
-            const int pi = g * kRows + rr, p = p0 + pi, i = pi + 1;
-            if (p >= p_hi) break;
-            const int4 pC = sRC[pi];
-            if (!(pC.w & 1)) continue;  // p must be a customer for both families
-            const int4 pA = sRA[pi], pB = sRB[pi], pD = sRD[pi];
-            if (pA.w == qA.w) continue;  // same route: the sweep kernel's business
-            const int2 c_pq = S[i][j], c_pq1 = S[i][j + 1];
-            // relocate(p -> between q and q+1), receiving route = route[q]
-            if (do_rel && q <= P - 2) {
-                const int ins = c_pq.x + c_pq1.x - qA.z;
-                const int delta = pC.y + ins;
-                const int tu = max(pB.x, qA.x + c_pq.y);
-                const bool ok = (pC.w & 2) && pB.w <= qD.x && ins <= qD.y && tu <= pB.y && tu + pB.z + c_pq1.y <= qA.y;
-                if (DUMP) {
-                    if (a.dump_family == 1) {
-                        a.dump_delta[static_cast<size_t>(p) * P + q] = delta;
-                        a.dump_feas[static_cast<size_t>(p) * P + q] = ok ? 1 : 0;
-                    }
-                } else if (ok) {
-                    const unsigned long long k = pack_key(delta, 1, p, q);
-                    best = k < best ? k : best;
+    int bound = INT_MAX;
+    if (!DUMP) {
+        const unsigned long long seen = *reinterpret_cast<const volatile unsigned long long *>(a.best + b);
+        if (seen != kNoMove) bound = static_cast<int>(static_cast<unsigned>(seen >> 32) - 0x80000000u);
+    }
+    constexpr int kRows = kTP / (kInterThreads / kTQ);
+    const int pi0 = g * kRows;
+    int2 c_up = S[pi0][j], c_cur = S[pi0 + 1][j];
+    for (int rr = 0; rr < kRows; ++rr) {
+        const int pi = pi0 + rr, p = p0 + pi, i = pi + 1;
+        if (p >= p_hi) break;  // warp-uniform
+        const int2 c_dn = S[i + 1][j], c_lf = S[i][j - 1], c_rt = S[i][j + 1];
+        const int4 Hp = sH[pi];
+        if ((Hp.w >> 30) & 1) {  // p is a customer (warp-uniform)
+            const bool other = (Hp.w & 0x3FFFFFFF) != q_route;
+            const int d_rel = Hp.x + c_cur.x + c_rt.x - Hq.z;
+            const int d_swap = c_up.x + c_dn.x - Hp.y + c_lf.x + c_rt.x - Hq.y;
+            const bool v_rel = rel_q && other, v_swap = swap_q && other && p < q;
+            if (DUMP) {
+                if (v_rel && a.dump_family == 1) {
+                    a.dump_delta[static_cast<size_t>(p) * P + q] = d_rel;
+                    a.dump_feas[static_cast<size_t>(p) * P + q] = check_relocate(a, po, p, q, c_cur, c_rt) ? 1 : 0;
                 }
-            }
-            // swap(p, q), p < q, both customers
-            if (do_swap && q_cust && p < q) {
-                const int2 c_up = S[i - 1][j], c_dn = S[i + 1][j], c_lf = S[i][j - 1];
-                const int d1 = c_up.x + c_dn.x - pC.z;    // route of p: pu -> v -> nu
-                const int d2 = c_lf.x + c_pq1.x - qC.z;   // route of q: pw -> u -> nw
-                const int delta = d1 + d2;
-                const int tv = max(qB.x, pC.x + c_up.y);
-                const int tu = max(pB.x, qC.x + c_lf.y);
-                const bool ok = qB.w - pB.w <= pD.x && pB.w - qB.w <= qD.x && d1 <= pD.y && d2 <= qD.y && tv <= qB.y &&
-                                tv + qB.z + c_dn.y <= pA.y && tu <= pB.y && tu + pB.z + c_pq1.y <= qA.y;
-                if (DUMP) {
-                    if (a.dump_family == 2) {
-                        a.dump_delta[static_cast<size_t>(p) * P + q] = delta;
-                        a.dump_feas[static_cast<size_t>(p) * P + q] = ok ? 1 : 0;
-                    }
-                } else if (ok) {
-                    const unsigned long long k = pack_key(delta, 2, p, q);
-                    best = k < best ? k : best;
+                if (v_swap && a.dump_family == 2) {
+                    a.dump_delta[static_cast<size_t>(p) * P + q] = d_swap;
+                    a.dump_feas[static_cast<size_t>(p) * P + q] = check_swap(a, po, p, q, c_up, c_dn, c_lf, c_rt) ? 1 : 0;
                 }
+            } else {
+                if (v_rel && d_rel <= bound && check_relocate(a, po, p, q, c_cur, c_rt)) {
+                    const unsigned long long k = pack_key(d_rel, 1, p, q);
+                    if (k < best) {
+                        best = k;
+                        bound = d_rel;
+                    }
+                }
+                if (v_swap && d_swap <= bound && check_swap(a, po, p, q, c_up, c_dn, c_lf, c_rt)) {
+                    const unsigned long long k = pack_key(d_swap, 2, p, q);
+                    if (k < best) {
+                        best = k;
+                        bound = d_swap;
+                    }
+                }
+                bound = __reduce_min_sync(0xffffffffu, bound);  // share the bound across the warp (one REDUX)
             }
         }
+        c_up = c_cur;
+        c_cur = c_dn;
     }
     if (!DUMP) block_min_to_global<kInterThreads>(best, a.best + b);
 }
@@ -358,6 +409,11 @@ EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count
     a.RB = p->RB;
     a.RC = p->RC;
     a.RD = p->RD;
+    a.H = p->H;
+    a.PX = p->PX;
+    a.fd = static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale);
+    a.ft = static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale);
+    a.lim_hi = fast_path_limit_hi(a.fd, a.ft);
     a.E = p->E;
     a.SK = p->SK;
     a.n = p->n;
@@ -393,11 +449,12 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     rt_engine *e = p->e;
     fill_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, p->batch);
     EvalArgs a = make_args(p, families, shard_index, shard_count, p->best);
-    const int pmax = p->pstride;  // upper bound of P over the batch
+    const int pmax = p->pmax > 0 ? p->pmax : p->pstride;  // largest P of the batch
     const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
     if (families & 6) {
         dim3 grid((pmax + kTQ - 1) / kTQ, (shard_rows + kTP - 1) / kTP, p->batch);
-        eval_inter_kernel<false><<<grid, kInterThreads, 0, st>>>(a);
+        if (p->cells_from_coords) eval_inter_kernel<false, true><<<grid, kInterThreads, 0, st>>>(a);
+        else eval_inter_kernel<false, false><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     {
@@ -418,10 +475,11 @@ int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsi
     a.dump_family = family;
     a.dump_delta = delta_d;
     a.dump_feas = feas_d;
-    const int pmax = p->pstride;
+    const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
     if (family != 0) {
         dim3 grid((pmax + kTQ - 1) / kTQ, (pmax + kTP - 1) / kTP, 1);
-        eval_inter_kernel<true><<<grid, kInterThreads, 0, st>>>(a);
+        if (p->cells_from_coords) eval_inter_kernel<true, true><<<grid, kInterThreads, 0, st>>>(a);
+        else eval_inter_kernel<true, false><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     dim3 grid((pmax + kIntraThreads - 1) / kIntraThreads, 1);

@@ -122,6 +122,8 @@ int rt_problem_create(rt_engine *e, int n, int batch, rt_problem **out)
     A(dev_alloc(p, p->RB, B * PS));
     A(dev_alloc(p, p->RC, B * PS));
     A(dev_alloc(p, p->RD, B * PS));
+    A(dev_alloc(p, p->H, B * PS));
+    A(dev_alloc(p, p->PX, B * 3 * PS));
     A(dev_alloc(p, p->E, B * PS));
     A(dev_alloc(p, p->SK, B * PS));
     A(dev_alloc(p, p->Bv, B * PS));
@@ -180,6 +182,7 @@ int rt_problem_set_coords(rt_problem *p, const double *lat, const double *lon)
     RT_CUDA(e, cudaStreamSynchronize(e->stream));
     p->has_coords = true;
     p->has_matrix = false;
+    p->cells_from_coords = false;
     return RT_OK;
 }
 
@@ -215,6 +218,7 @@ int rt_problem_build_matrix(rt_problem *p, double dist_scale, double time_scale)
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     p->has_matrix = true;
+    p->cells_from_coords = true;
     return RT_OK;
 }
 
@@ -243,6 +247,7 @@ int rt_problem_set_matrix(rt_problem *p, int instance, const int32_t *dist, cons
     RT_CUDA(e, cudaGetLastError());
     RT_CUDA(e, cudaStreamSynchronize(e->stream));
     p->has_matrix = true;
+    p->cells_from_coords = false;
     return RT_OK;
 }
 
@@ -362,6 +367,7 @@ int rt_problem_set_routes(rt_problem *p, const int32_t *order, const int32_t *tr
         }
         npos[b] = P;
     }
+    p->pmax = *std::max_element(npos.begin(), npos.end());
     RT_CUDA(e, cudaMemcpyAsync(p->node, node.data(), B * PS * 4, cudaMemcpyHostToDevice, e->stream));
     RT_CUDA(e, cudaMemcpyAsync(p->npos, npos.data(), B * 4, cudaMemcpyHostToDevice, e->stream));
     reset_search_kernel<<<(p->batch + 255) / 256, 256, 0, e->stream>>>(p->done, p->moves, p->batch);
@@ -433,6 +439,7 @@ int rt_problem_build_matrix_dev(rt_problem *p, double dist_scale, double time_sc
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     p->has_matrix = true;
+    p->cells_from_coords = true;
     return RT_OK;
 }
 
@@ -472,6 +479,9 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, st));
     RT_TRY(launch_matrix_cells(e, p->xyz, p->n, p->batch, 0, p->n, dist_scale, time_scale, p->cells, st));
     p->has_coords = p->has_stops = p->has_matrix = p->has_routes = true;
+    p->cells_from_coords = true;
+    p->pmax = 0;
+    for (size_t b = 0; b < B; ++b) p->pmax = std::max(p->pmax, npos[b]);
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     RT_TRY(state_refresh(p, st));

@@ -14,6 +14,7 @@ constexpr int kMaxPositions = 32768;  // key layout: 15 bits per position (SPEC.
 //   RB = {ready, due, service, demand} of node p
 //   RC = {dep[p-1], rem_delta[p], oe[p] = D[node p-1][node p]+D[node p][node p+1], flags}    flags: 1 customer, 2 rem_ok
 //   RD = {cap - rload[route p], min(max_dist - rdist[route p], INT_MAX), E.t, SK.t}
+//   H  = {rem_delta[p], oe[p], E.d, route[p] | customer << 30}   the "hot" record: all a cost delta needs
 struct StateView {
     int n, pitch, pstride, rstride;
     const int2 *cells;   // [n][pitch]
@@ -41,8 +42,11 @@ struct rt_problem {
     long long *max_dist = nullptr;
     int *npos = nullptr, *nroutes = nullptr;
     int *node = nullptr, *node_tmp = nullptr;
-    int4 *RA = nullptr, *RB = nullptr, *RC = nullptr, *RD = nullptr;
+    int4 *RA = nullptr, *RB = nullptr, *RC = nullptr, *RD = nullptr, *H = nullptr;
     int2 *E = nullptr, *SK = nullptr;
+    double *PX = nullptr;                  // [batch][3][pstride] unit vectors in position order
+    int pmax = 0;                          // max npos over the batch (host copy; sizes the move grids)
+    bool cells_from_coords = false;        // the matrix is SPEC §2 of this problem's coordinates
     int *Bv = nullptr, *Zv = nullptr, *route = nullptr, *rstart = nullptr;
     long long *rload = nullptr, *rdist = nullptr;
     long long *cost = nullptr;             // [batch]

@@ -14,7 +14,8 @@ namespace {
 __global__ void __launch_bounds__(256) state_gather_kernel(const int2 *__restrict__ cells, const int4 *__restrict__ stops,
                                                            const int *__restrict__ node, const int *__restrict__ npos,
                                                            int n, int pitch, int pstride, int4 *__restrict__ RB,
-                                                           int2 *__restrict__ E, int2 *__restrict__ SK)
+                                                           int2 *__restrict__ E, int2 *__restrict__ SK,
+                                                           const double *__restrict__ xyz, double *__restrict__ PX)
 {
     const int b = blockIdx.y;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -27,6 +28,13 @@ __global__ void __launch_bounds__(256) state_gather_kernel(const int2 *__restric
     RB[o] = stops[static_cast<size_t>(b) * n + cur];
     E[o] = p + 1 < P ? M[static_cast<size_t>(cur) * pitch + nxt] : make_int2(0, 0);
     SK[o] = cur != 0 ? M[static_cast<size_t>(prv) * pitch + nxt] : make_int2(0, 0);
+    if (xyz) {  // unit vectors in position order: lets the move kernel rebuild matrix cells instead of gathering them
+        const double *v = xyz + static_cast<size_t>(b) * 3 * n;
+        double *px = PX + static_cast<size_t>(b) * 3 * pstride;
+        px[p] = v[cur];
+        px[pstride + p] = v[n + cur];
+        px[2 * pstride + p] = v[2 * n + cur];
+    }
 }
 
 // K2: one block per instance.  (A) route ids by a block scan over the separators, (B) one thread per route walks
@@ -38,6 +46,7 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
     int rstride, const int4 *__restrict__ stops_all, const int *__restrict__ cap_all,
     const long long *__restrict__ maxd_all, const int4 *__restrict__ RB_all, const int2 *__restrict__ E_all,
     const int2 *__restrict__ SK_all, int4 *__restrict__ RA_all, int4 *__restrict__ RC_all, int4 *__restrict__ RD_all,
+    int4 *__restrict__ H_all,
     int *__restrict__ Bv_all, int *__restrict__ Zv_all, int *__restrict__ route_all, int *__restrict__ rstart_all,
     long long *__restrict__ rload_all, long long *__restrict__ rdist_all, long long *__restrict__ cost_all,
     int *__restrict__ feasible_all, unsigned long long *__restrict__ best_all)
@@ -130,7 +139,7 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
     __syncthreads();
 
     // (C) records
-    int4 *RA = RA_all + po, *RC = RC_all + po, *RD = RD_all + po;
+    int4 *RA = RA_all + po, *RC = RC_all + po, *RD = RD_all + po, *H = H_all + po;
     for (int p = tid; p < P; p += kWalkThreads) {
         const int rt_ = route[p];
         const int4 rb = RB[p];
@@ -151,8 +160,10 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
             const int rem_delta = sk.x - ep.x - ed.x;
             const bool rem_ok = dep_prev + sk.y <= zn && rem_delta <= dsl;
             RC[p] = make_int4(dep_prev, rem_delta, ep.x + ed.x, 1 | (rem_ok ? 2 : 0));
+            H[p] = make_int4(rem_delta, ep.x + ed.x, ed.x, rt_ | (1 << 30));
         } else {
             RC[p] = make_int4(0, 0, 0, 0);
+            H[p] = make_int4(0, 0, ed.x, rt_);
         }
     }
     if (tid == 0) {
@@ -227,11 +238,11 @@ int state_refresh(rt_problem *p, cudaStream_t st)
     rt_engine *e = p->e;
     dim3 g1((p->pstride + 255) / 256, p->batch);
     state_gather_kernel<<<g1, 256, 0, st>>>(p->cells, p->stops, p->node, p->npos, p->n, p->pitch, p->pstride, p->RB,
-                                            p->E, p->SK);
+                                            p->E, p->SK, p->has_coords ? p->xyz : nullptr, p->PX);
     RT_CUDA(e, cudaGetLastError());
     state_walk_kernel<<<p->batch, kWalkThreads, 0, st>>>(p->node, p->npos, p->nroutes, p->n, p->pstride, p->rstride,
                                                          p->stops, p->cap, p->max_dist, p->RB, p->E, p->SK, p->RA, p->RC,
-                                                         p->RD, p->Bv, p->Zv, p->route, p->rstart, p->rload, p->rdist,
+                                                         p->RD, p->H, p->Bv, p->Zv, p->route, p->rstart, p->rload, p->rdist,
                                                          p->cost, p->feasible, p->best);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
