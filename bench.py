@@ -3,7 +3,7 @@
 
 A step = one pass of the hot path over one batch of synthetic input: for each of `--batch` independent
 1,000-stop VRPTW instances (BASELINE.json configs[1]) build the 1,001 x 1,001 distance/time matrix from the
-coordinates, derive the route state of the current solution and score the full 2-opt/relocate/swap neighbourhood
+coordinates (in route order: one row per position of the current solution), derive the route state of the current solution and score the full 2-opt/relocate/swap neighbourhood
 (delta + capacity + time-window feasibility per candidate), ending in one best-move key per instance.
 
   value        matrix cells/s over the whole step, inputs resident in HBM, CUDA events on the launching stream
@@ -238,15 +238,16 @@ def run_engine(args, rank, world):
     cand = [count_candidates(t, n) for t in trips]
     evals_step = sum(sum(c.values()) for c in cand)
     eval_bytes = sum(c[f] * BYTES_PER_EVAL[f] for c in cand for f in c)
-    cells_step = B * n * n
+    cells_step = B * n * n                       # the metric counts the n x n matrix of the instance ...
+    pmax = max(n + len(t) for t in trips)
+    cells_built = B * pmax * ((pmax + 15) // 16 * 16)   # ... the kernel writes it in route order with one depot row per route
 
     stream = torch.cuda.current_stream().cuda_stream
     keys_d = torch.empty(B, dtype=torch.int64, device="cuda")
 
     def step():
-        pr.build_matrix_dev(DIST_SCALE, TS_CAR, stream)
-        pr.refresh_dev(stream)
-        pr.eval_moves_dev(keys_d.data_ptr(), ALL_FAMILIES, (0, 1), stream)
+        # unit vectors -> matrix (route order) -> route state -> full neighbourhood -> best keys, all on `stream`
+        pr.plan_dev(keys_d.data_ptr(), dist_scale=DIST_SCALE, time_scale=TS_CAR, families=ALL_FAMILIES, stream=stream)
 
     def barrier():
         torch.cuda.synchronize()
@@ -291,8 +292,8 @@ def run_engine(args, rank, world):
         return a.elapsed_time(b) / reps
 
     reps = max(args.steps, 10)
-    ms_matrix = timed(lambda: pr.build_matrix_dev(DIST_SCALE, TS_CAR, stream), reps)
-    ms_refresh = timed(lambda: pr.refresh_dev(stream), reps)
+    ms_matrix = timed(lambda: pr.refresh_dev(1, stream), reps)   # position vectors + matrix kernel (route order)
+    ms_refresh = timed(lambda: pr.refresh_dev(2, stream), reps)  # gather + walk
     ms_eval = timed(lambda: pr.eval_moves_dev(keys_d.data_ptr(), ALL_FAMILIES, (0, 1), stream), reps)
     clocks = sampler.stop(t_wall0, time.perf_counter()) if rank == 0 else None
 
@@ -339,8 +340,10 @@ def run_engine(args, rank, world):
             traffic = json.load(open(tp))
         kern = {
             "matrix_kernel": {"ms": ms_matrix, "algorithmic_bytes": cells_step * 8,
-                              "GBs": cells_step * 8 / ms_matrix / 1e6},
-            "state_refresh(2 kernels)": {"ms": ms_refresh},
+                              "GBs": cells_step * 8 / ms_matrix / 1e6, "bytes_written": cells_built * 8,
+                              "GBs_written": cells_built * 8 / ms_matrix / 1e6,
+                              "note": "position_vectors_kernel + matrix_kernel<0> on the route-ordered stops"},
+            "state_tables(2 kernels)": {"ms": ms_refresh},
             "eval_moves(inter+intra)": {"ms": ms_eval, "algorithmic_bytes": eval_bytes,
                                         "GBs": eval_bytes / ms_eval / 1e6, "move_evals_per_s": evals_step / ms_eval * 1e3},
         }
@@ -371,7 +374,7 @@ def run_engine(args, rank, world):
                     "move_evals_per_s": evals_step * world * args.steps / e2e_s,
                     "call": "rt_problem_plan (host buffers in, best keys out; matrices stay in HBM)",
                     "keys_equal_device_path": same},
-            "gpu_launches": 8 * args.steps,
+            "gpu_launches": 9 * args.steps,
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:

@@ -155,6 +155,10 @@ int rt_problem_get_routes(rt_problem *p, int32_t *order_out, int32_t *trip_off_o
 int rt_problem_get_state(rt_problem *p, int instance, int32_t *npos_out, int32_t *node, int32_t *route, int32_t *B,
                          int32_t *Z, int64_t *rload, int64_t *rdist, int64_t *cost, int32_t *feasible);
 
+/* The stop matrix in ROUTE ORDER that the move kernels read: G[p][q] = M[node p][node q] for the P positions of the
+ * current solution (SPEC.md §6), dense int32 [P][P] planes.  It is rebuilt by every state refresh. */
+int rt_problem_get_position_matrix(rt_problem *p, int instance, int32_t *dist, int32_t *time);
+
 /* Scores this shard's local-search candidates of every instance (families: bit 0 = 2-opt, 1 = relocate, 2 = swap;
  * delta + capacity + distance-limit + time-window feasibility each) and returns the minimum packed key per instance
  * (SPEC.md §7; 2^64-1 = none).  The candidate space is split into shard_count parts; the minimum over all shards
@@ -171,16 +175,23 @@ int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t 
                             uint64_t *keys_out, int keys_capacity);
 
 /* One pass of the hot path from host inputs to best moves, for every instance: uploads coordinates, stop data
- * and the current solution, builds the matrices (utils.py:94-109), derives the route state and scores the full
- * neighbourhood; only the best keys [batch] come back (the matrices stay on the GPU).  node is the position array
+ * and the current solution, builds the matrices (utils.py:94-109) — in route order, G[p][q] = M[node p][node q],
+ * which is the layout the move kernels stream — derives the route state and scores the full neighbourhood; only
+ * the best keys [batch] come back (the matrices stay on the GPU).  node is the position array
  * of SPEC.md §6, [batch][rt_problem_position_stride()], npos [batch] its used length. */
 int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
                     const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
                     double time_scale, int families, uint64_t *best_keys_out);
 
-/* Stream-ordered pieces of the same pass for inputs that are already on the device (no synchronisation). */
+/* The same pass for inputs that are already on the device (coordinates, stops and routes installed earlier), on
+ * the caller's stream, without synchronisation: unit vectors -> route-order matrix -> route state -> best keys
+ * (device int64[batch] in signed-order form, see rt_problem_eval_moves_dev). */
+int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int families, void *best_keys_d,
+                        void *stream);
+/* Its pieces, stream-ordered: the node-order matrix of rt_problem_build_matrix; the refresh (what: bit 0 = rebuild
+ * the route-order matrix from the current routes, bit 1 = re-derive the route state tables from it). */
 int rt_problem_build_matrix_dev(rt_problem *p, double dist_scale, double time_scale, void *stream);
-int rt_problem_refresh_dev(rt_problem *p, void *stream);
+int rt_problem_refresh_dev(rt_problem *p, int what, void *stream);
 
 /* The same two steps on a caller's stream, for a multi-GPU search: every rank holds a replica of the problem,
  * evaluates its shard, all-reduces the keys with MIN (e.g. NCCL through torch.distributed) and applies the winner.

@@ -60,6 +60,7 @@ SIGNATURES = {
     "rt_problem_get_routes": (C.c_int, [c_problem_p, c_i32_p, c_i32_p, c_i32_p]),
     "rt_problem_get_state": (C.c_int, [c_problem_p, C.c_int, c_i32_p, c_i32_p, c_i32_p, c_i32_p, c_i32_p, c_i64_p,
                                        c_i64_p, c_i64_p, c_i32_p]),
+    "rt_problem_get_position_matrix": (C.c_int, [c_problem_p, C.c_int, c_i32_p, c_i32_p]),
     "rt_problem_eval_moves": (C.c_int, [c_problem_p, C.c_int, C.c_int, C.c_int, c_u64_p]),
     "rt_problem_eval_dump": (C.c_int, [c_problem_p, C.c_int, C.c_int, c_i32_p, c_u8_p]),
     "rt_problem_apply_moves": (C.c_int, [c_problem_p, c_u64_p]),
@@ -67,7 +68,8 @@ SIGNATURES = {
     "rt_problem_plan": (C.c_int, [c_problem_p, c_f64_p, c_f64_p, c_i32_p, c_i32_p, c_i64_p, c_i32_p, c_i32_p,
                                   C.c_double, C.c_double, C.c_int, c_u64_p]),
     "rt_problem_build_matrix_dev": (C.c_int, [c_problem_p, C.c_double, C.c_double, C.c_void_p]),
-    "rt_problem_refresh_dev": (C.c_int, [c_problem_p, C.c_void_p]),
+    "rt_problem_refresh_dev": (C.c_int, [c_problem_p, C.c_int, C.c_void_p]),
+    "rt_problem_plan_dev": (C.c_int, [c_problem_p, C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_problem_eval_moves_dev": (C.c_int, [c_problem_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_problem_apply_moves_dev": (C.c_int, [c_problem_p, C.c_void_p, C.c_int, C.c_void_p]),
     "rt_problem_search_status": (C.c_int, [c_problem_p, c_i32_p, c_i32_p, c_i64_p]),

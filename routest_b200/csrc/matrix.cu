@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(256) unit_vectors_kernel(const double *__restr
 
 struct MatArgs {
     const double *xyz;
-    int n, r0, r1, rows_per_block;
+    int n, ld, r0, r1, rows_per_block;  // ld: stride between the x/y/z component arrays (>= n); instance stride 3*ld
     float fd, ft;
     int lim_hi;       // fast_path_limit_hi(fd, ft)
     int2 *cells;      // MODE 0
@@ -64,9 +64,9 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) matrix_kernel(const Ma
     __shared__ double srow[3][kMaxRowsPerBlock];
 
     const int n = a.n;
-    const double *__restrict__ X = a.xyz + static_cast<size_t>(blockIdx.z) * 3 * n;
-    const double *__restrict__ Y = X + n;
-    const double *__restrict__ Z = Y + n;
+    const double *__restrict__ X = a.xyz + static_cast<size_t>(blockIdx.z) * 3 * a.ld;
+    const double *__restrict__ Y = X + a.ld;
+    const double *__restrict__ Z = Y + a.ld;
     const int lane = threadIdx.x & 31;
     const int wb = blockIdx.x * kColsPerBlock + (threadIdx.x >> 5) * 128;
 
@@ -240,12 +240,32 @@ int launch_unit_vectors(rt_engine *e, const double *lat_d, const double *lon_d, 
     return RT_OK;
 }
 
+// The same kernel on unit vectors whose component arrays are ld apart (the position-ordered vectors of a route
+// state): n x n cells per instance into rows of `pitch` cells.
+int launch_matrix_cells_ld(rt_engine *e, const double *xyz_d, int n, int ld, int batch, double dist_scale,
+                           double time_scale, int2 *cells_d, int pitch, cudaStream_t st)
+{
+    MatArgs a{};
+    a.xyz = xyz_d;
+    a.n = n;
+    a.ld = ld;
+    a.r0 = 0;
+    a.r1 = n;
+    a.fd = static_cast<float>(RT_EARTH_RADIUS_M * dist_scale);
+    a.ft = static_cast<float>(RT_EARTH_RADIUS_M * time_scale);
+    a.lim_hi = fast_path_limit_hi(a.fd, a.ft);
+    a.cells = cells_d;
+    a.pitch = pitch;
+    return launch_matrix<kCells>(e, a, batch, pitch, st);
+}
+
 int launch_matrix_cells(rt_engine *e, const double *xyz_d, int n, int batch, int r0, int r1, double dist_scale,
                         double time_scale, int2 *cells_d, cudaStream_t st)
 {
     MatArgs a{};
     a.xyz = xyz_d;
     a.n = n;
+    a.ld = n;
     a.r0 = r0;
     a.r1 = r1;
     a.fd = static_cast<float>(RT_EARTH_RADIUS_M * dist_scale);
@@ -263,6 +283,7 @@ int launch_matrix_planes(rt_engine *e, const double *xyz_d, int n, int r0, int r
     MatArgs a{};
     a.xyz = xyz_d;
     a.n = n;
+    a.ld = n;
     a.r0 = r0;
     a.r1 = r1;
     a.fd = static_cast<float>(RT_EARTH_RADIUS_M * dist_scale);

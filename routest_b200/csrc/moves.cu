@@ -1,12 +1,14 @@
 // moves.cu — cost delta + capacity/distance/time-window feasibility of local-search moves and the best-move
 // argmin (SPEC.md §7).  No reference counterpart (the reference has no improvement phase, utils.py:111-139).
 //
-// Two kernels share the work:
-//   * eval_inter_kernel — candidates between two different routes (relocate, swap): O(1) each.  A block owns a
-//     64 x 64 tile of (p, q) position pairs; the 66 x 66 haloed tile of matrix cells M[node p][node q] is gathered
-//     ONCE into shared memory and then serves every candidate of the tile (each cell is read by up to five
-//     (p,q) sites and two families); the per-position records of the q side live in registers, those of the p
-//     side are broadcast from shared memory.
+// Both kernels read the stop matrix in ROUTE ORDER, G[p][q] = M[node p][node q] (state.cu), so a thread that owns
+// insertion point / partner q and walks down the moved positions p touches G[p-1..p+1][q-1..q+1]: each warp-wide
+// load is one contiguous 256-byte run of a row, every cell comes from DRAM/L2 once per strip and its four
+// re-uses (left/right/up/down neighbours) are L1 hits or register rotations.
+//   * eval_inter_kernel — candidates between two different routes (relocate, swap): O(1) each from the 16-byte
+//     "hot" record of p and of q (removal delta, old-edge sum, edge after, route id) plus five cells.  Only the
+//     minimum key matters, so the full feasibility test (capacity, distance limit, time windows; cold records)
+//     runs only for candidates whose delta can still beat the best feasible key seen so far.
 //   * eval_intra_kernel — candidates inside one route (2-opt, relocate, swap): one thread per anchor position
 //     sweeps its route keeping two segment summaries (a, b, L) — forward and reversed — so every candidate is
 //     again O(1) and exact for time windows.
@@ -14,18 +16,17 @@
 // reduce it to one 64-bit atomicMin per block.  The minimum of packed keys is order independent, so the chosen
 // move does not depend on the thread, block or GPU partition.
 //
-// The matrix is assumed symmetric here (true for SPEC.md §2 matrices): M[a][b] is read where M[b][a] is meant.
+// The matrix is assumed symmetric here (true for SPEC.md §2 matrices): G[a][b] is read where G[b][a] is meant.
 #include <climits>
 
-#include "geometry.cuh"
 #include "problem.cuh"
 
 namespace rt {
 
 namespace {
 
-constexpr int kTP = 64, kTQ = 64;  // tile of (p, q) pairs per block
-constexpr int kInterThreads = 256;
+constexpr int kInterThreads = 128;  // one column q per thread
+constexpr int kStripRows = 32;     // rows p per block
 
 __device__ __forceinline__ unsigned long long pack_key(int delta, int family, int p, int q)
 {
@@ -59,14 +60,12 @@ __device__ __forceinline__ void block_min_to_global(unsigned long long best, uns
 }
 
 struct EvalArgs {
-    const int2 *cells;
+    const int2 *G;         // [batch][grows][gpitch] route-order matrix
+    int grows, gpitch;
     const int *node;
     const int *npos;
     const int4 *RA, *RB, *RC, *RD, *H;
     const int2 *E, *SK;
-    const double *PX;      // unit vectors in position order [3][pstride] per instance
-    float fd, ft;          // cell scales and fast-path limit (geometry.cuh), for rebuilt cells
-    int lim_hi;
     int n, pitch, pstride;
     int families;            // bit 0 = 2-opt, 1 = relocate, 2 = swap
     int shard_index, shard_count;
@@ -83,22 +82,18 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
     hi = static_cast<int>(static_cast<long long>(P) * (idx + 1) / cnt);
 }
 
-// Full evaluation of one inter-route candidate from the cold records (global memory): only reached by the few
-// candidates whose delta beats the current bound, or by every candidate in dump mode.
-__device__ __noinline__ bool check_relocate(const EvalArgs &a, size_t po, int p, int q, int2 c_pq, int2 c_pq1)
+// Full feasibility of one inter-route candidate from the cold records (SPEC.md §7): capacity, distance limit and
+// time windows of both routes.  Only reached by candidates whose delta can still win, or by all in dump mode.
+__device__ __forceinline__ bool check_relocate(int4 pB, int4 pC, int4 qA, int4 qD, int2 c_pq, int2 c_pq1)
 {
-    const int4 pB = a.RB[po + p], pC = a.RC[po + p];
-    const int4 qA = a.RA[po + q], qD = a.RD[po + q];
     const int ins = c_pq.x + c_pq1.x - qA.z;
     const int tu = max(pB.x, qA.x + c_pq.y);
     return (pC.w & 2) && pB.w <= qD.x && ins <= qD.y && tu <= pB.y && tu + pB.z + c_pq1.y <= qA.y;
 }
 
-__device__ __noinline__ bool check_swap(const EvalArgs &a, size_t po, int p, int q, int2 c_up, int2 c_dn, int2 c_lf,
-                                        int2 c_rt)
+__device__ __forceinline__ bool check_swap(int4 pA, int4 pB, int4 pC, int4 pD, int4 qA, int4 qB, int4 qC, int4 qD,
+                                           int2 c_up, int2 c_dn, int2 c_lf, int2 c_rt)
 {
-    const int4 pA = a.RA[po + p], pB = a.RB[po + p], pC = a.RC[po + p], pD = a.RD[po + p];
-    const int4 qA = a.RA[po + q], qB = a.RB[po + q], qC = a.RC[po + q], qD = a.RD[po + q];
     const int d1 = c_up.x + c_dn.x - pC.z;  // route of p: pu -> v -> nu
     const int d2 = c_lf.x + c_rt.x - qC.z;  // route of q: pw -> u -> nw
     const int tv = max(qB.x, pC.x + c_up.y);
@@ -107,96 +102,74 @@ __device__ __noinline__ bool check_swap(const EvalArgs &a, size_t po, int p, int
            tv + qB.z + c_dn.y <= pA.y && tu <= pB.y && tu + pB.z + c_rt.y <= qA.y;
 }
 
-// COMPUTED: the tile's cells are rebuilt from the unit vectors of the 66 + 66 positions (SPEC.md §2, the same
-// function as the matrix kernel, so the same bits) instead of being gathered from the stored matrix: ~25 ALU
-// instructions per cell replace a scattered 32-byte sector fetch per cell.  Only valid while the stored matrix is
-// the great-circle matrix of the problem's coordinates; a caller-supplied matrix takes the gather path.
-template <bool DUMP, bool COMPUTED>
-__global__ void __launch_bounds__(kInterThreads) eval_inter_kernel(const EvalArgs a)
+// grid (column strips of 128, row strips of kStripRows within the shard, instances)
+template <bool DUMP>
+__global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const EvalArgs a)
 {
-    __shared__ int2 S[kTP + 2][kTQ + 2];
-    __shared__ int4 sH[kTP];
-    __shared__ int s_nodeP[kTP + 2], s_nodeQ[kTQ + 2];
-    __shared__ double sPX[3][kTP + 2], sQX[3][kTQ + 2];
+    // hot and cold records of the strip's rows (p side) and of the block's columns (q side): the slow path never
+    // waits on global memory
+    __shared__ int4 sH[kStripRows], sPA[kStripRows], sPB[kStripRows], sPC[kStripRows], sPD[kStripRows];
+    __shared__ int4 sQA[kInterThreads], sQB[kInterThreads], sQC[kInterThreads], sQD[kInterThreads];
 
     const int b = DUMP ? a.dump_instance : blockIdx.z;
     const int P = a.npos[b];
     int p_lo, p_hi;
     shard_range(P, a.shard_index, a.shard_count, p_lo, p_hi);
-    const int p0 = p_lo + blockIdx.y * kTP, q0 = blockIdx.x * kTQ;
+    const int p0 = p_lo + blockIdx.y * kStripRows, q0 = blockIdx.x * kInterThreads;
     if (p0 >= p_hi || q0 >= P) return;
 
     const size_t po = static_cast<size_t>(b) * a.pstride;
+    const int2 *G = a.G + static_cast<size_t>(b) * a.grows * a.gpitch;
     const int tid = threadIdx.x;
-
-    for (int k = tid; k < kTP; k += kInterThreads) sH[k] = p0 + k < P ? a.H[po + p0 + k] : make_int4(0, 0, 0, 0);
-    if (COMPUTED) {
-        const double *px = a.PX + static_cast<size_t>(b) * 3 * a.pstride;
-        for (int k = tid; k < 3 * (kTP + 2); k += kInterThreads) {
-            const int comp = k / (kTP + 2), i = k - comp * (kTP + 2), p = min(max(p0 - 1 + i, 0), P - 1);
-            sPX[comp][i] = px[static_cast<size_t>(comp) * a.pstride + p];
-        }
-        for (int k = tid; k < 3 * (kTQ + 2); k += kInterThreads) {
-            const int comp = k / (kTQ + 2), j = k - comp * (kTQ + 2), q = min(max(q0 - 1 + j, 0), P - 1);
-            sQX[comp][j] = px[static_cast<size_t>(comp) * a.pstride + q];
-        }
-        __syncthreads();
-        for (int k = tid; k < (kTP + 2) * (kTQ + 2); k += kInterThreads) {
-            const int i = k / (kTQ + 2), j = k - i * (kTQ + 2);
-            const double ax = sPX[0][i], ay = sPX[1][i], az = sPX[2][i];
-            const double bx = sQX[0][j], by = sQX[1][j], bz = sQX[2][j];
-            const double dx = ax - bx, dy = ay - by, dz = az - bz;
-            const double s2 = fma(dx, dx, fma(dy, dy, dz * dz));
-            S[i][j] = __double2hiint(s2) < a.lim_hi ? cell_i32_fast(s2, a.fd, a.ft)
-                                                    : cell_i32(ax, ay, az, bx, by, bz, a.fd, a.ft);
-        }
-    } else {
-        const int *node = a.node + po;
-        const int2 *M = a.cells + static_cast<size_t>(b) * a.n * a.pitch;
-        for (int k = tid; k < kTP + 2; k += kInterThreads) {
-            const int p = p0 - 1 + k;
-            s_nodeP[k] = (p >= 0 && p < P) ? node[p] : -1;
-        }
-        for (int k = tid; k < kTQ + 2; k += kInterThreads) {
-            const int q = q0 - 1 + k;
-            s_nodeQ[k] = (q >= 0 && q < P) ? node[q] : -1;
-        }
-        __syncthreads();
-        // the one gather of the tile: 66 x 66 cells, scattered within matrix rows
-        for (int k = tid; k < (kTP + 2) * (kTQ + 2); k += kInterThreads) {
-            const int i = k / (kTQ + 2), j = k - i * (kTQ + 2);
-            const int na = s_nodeP[i], nb = s_nodeQ[j];
-            S[i][j] = (na >= 0 && nb >= 0) ? __ldg(&M[static_cast<size_t>(na) * a.pitch + nb]) : make_int2(0, 0);
-        }
+    const int q = q0 + tid;
+    const bool q_in = q < P;
+    if (tid < kStripRows) {
+        const bool in = p0 + tid < P;
+        const size_t o = po + p0 + tid;
+        sH[tid] = in ? a.H[o] : make_int4(0, 0, 0, 0);
+        sPA[tid] = in ? a.RA[o] : make_int4(0, 0, 0, 0);
+        sPB[tid] = in ? a.RB[o] : make_int4(0, 0, 0, 0);
+        sPC[tid] = in ? a.RC[o] : make_int4(0, 0, 0, 0);
+        sPD[tid] = in ? a.RD[o] : make_int4(0, 0, 0, 0);
     }
+    const int4 Hq = q_in ? a.H[po + q] : make_int4(0, 0, 0, -1);
+    sQA[tid] = q_in ? a.RA[po + q] : make_int4(0, 0, 0, 0);
+    sQB[tid] = q_in ? a.RB[po + q] : make_int4(0, 0, 0, 0);
+    sQC[tid] = q_in ? a.RC[po + q] : make_int4(0, 0, 0, 0);
+    sQD[tid] = q_in ? a.RD[po + q] : make_int4(0, 0, 0, 0);
     __syncthreads();
 
-    const int c = tid & (kTQ - 1), g = tid / kTQ;  // column of the tile, group of rows
-    const int q = q0 + c, j = c + 1;
-    const bool q_in = q < P;
-    const int4 Hq = q_in ? a.H[po + q] : make_int4(0, 0, 0, -1);
+    // columns are clamped so that every lane can load unconditionally (pad columns of G are valid depot cells)
+    const int qc = min(q, a.gpitch - 1), ql = max(qc - 1, 0), qr = min(qc + 1, a.gpitch - 1);
     const int q_route = Hq.w & 0x3FFFFFFF;
     const bool q_cust = q_in && ((Hq.w >> 30) & 1);
     const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
     const bool swap_q = q_cust && (a.families & 4);
 
-    // Only the minimum key matters, so a candidate is fully evaluated (feasibility, cold records) only if its delta
-    // can still beat the best feasible key seen so far by this warp; the bound starts from whatever other blocks
-    // have already published for this instance.  Exact: a pruned candidate has a larger key than an existing one.
+    // Only the minimum key matters, so a candidate is fully evaluated only if its delta can still beat the best
+    // feasible key seen so far by this warp; the bound starts from whatever other blocks have already published
+    // for this instance.  Exact: a pruned candidate has a larger key than an existing feasible one.
     unsigned long long best = kNoMove;
     int bound = INT_MAX;
     if (!DUMP) {
         const unsigned long long seen = *reinterpret_cast<const volatile unsigned long long *>(a.best + b);
         if (seen != kNoMove) bound = static_cast<int>(static_cast<unsigned>(seen >> 32) - 0x80000000u);
     }
-    constexpr int kRows = kTP / (kInterThreads / kTQ);
-    const int pi0 = g * kRows;
-    int2 c_up = S[pi0][j], c_cur = S[pi0 + 1][j];
-    for (int rr = 0; rr < kRows; ++rr) {
-        const int pi = pi0 + rr, p = p0 + pi, i = pi + 1;
-        if (p >= p_hi) break;  // warp-uniform
-        const int2 c_dn = S[i + 1][j], c_lf = S[i][j - 1], c_rt = S[i][j + 1];
-        const int4 Hp = sH[pi];
+    const int rows = min(kStripRows, p_hi - p0);
+    const int last_row = a.grows - 1;
+    auto row_ptr = [&](int r) { return G + static_cast<size_t>(min(max(r, 0), last_row)) * a.gpitch; };
+    // register window over three rows of G, loaded two rows ahead of use
+    int2 c_up = __ldg(row_ptr(p0 - 1) + qc);
+    const int2 *g0 = row_ptr(p0), *g1 = row_ptr(p0 + 1);
+    int2 c_lf = __ldg(g0 + ql), c_cur = __ldg(g0 + qc), c_rt = __ldg(g0 + qr);
+    int2 n_lf = __ldg(g1 + ql), n_cur = __ldg(g1 + qc), n_rt = __ldg(g1 + qr);
+#pragma unroll 2
+    for (int rr = 0; rr < rows; ++rr) {
+        const int p = p0 + rr;
+        const int2 *g2 = row_ptr(p + 2);
+        const int2 m_lf = __ldg(g2 + ql), m_cur = __ldg(g2 + qc), m_rt = __ldg(g2 + qr);
+        const int2 c_dn = n_cur;
+        const int4 Hp = sH[rr];
         if ((Hp.w >> 30) & 1) {  // p is a customer (warp-uniform)
             const bool other = (Hp.w & 0x3FFFFFFF) != q_route;
             const int d_rel = Hp.x + c_cur.x + c_rt.x - Hq.z;
@@ -205,21 +178,26 @@ __global__ void __launch_bounds__(kInterThreads) eval_inter_kernel(const EvalArg
             if (DUMP) {
                 if (v_rel && a.dump_family == 1) {
                     a.dump_delta[static_cast<size_t>(p) * P + q] = d_rel;
-                    a.dump_feas[static_cast<size_t>(p) * P + q] = check_relocate(a, po, p, q, c_cur, c_rt) ? 1 : 0;
+                    a.dump_feas[static_cast<size_t>(p) * P + q] =
+                        check_relocate(sPB[rr], sPC[rr], sQA[tid], sQD[tid], c_cur, c_rt) ? 1 : 0;
                 }
                 if (v_swap && a.dump_family == 2) {
                     a.dump_delta[static_cast<size_t>(p) * P + q] = d_swap;
-                    a.dump_feas[static_cast<size_t>(p) * P + q] = check_swap(a, po, p, q, c_up, c_dn, c_lf, c_rt) ? 1 : 0;
+                    a.dump_feas[static_cast<size_t>(p) * P + q] =
+                        check_swap(sPA[rr], sPB[rr], sPC[rr], sPD[rr], sQA[tid], sQB[tid], sQC[tid], sQD[tid], c_up, c_dn,
+                                   c_lf, c_rt) ? 1 : 0;
                 }
             } else {
-                if (v_rel && d_rel <= bound && check_relocate(a, po, p, q, c_cur, c_rt)) {
+                if (v_rel && d_rel <= bound && check_relocate(sPB[rr], sPC[rr], sQA[tid], sQD[tid], c_cur, c_rt)) {
                     const unsigned long long k = pack_key(d_rel, 1, p, q);
                     if (k < best) {
                         best = k;
                         bound = d_rel;
                     }
                 }
-                if (v_swap && d_swap <= bound && check_swap(a, po, p, q, c_up, c_dn, c_lf, c_rt)) {
+                if (v_swap && d_swap <= bound &&
+                    check_swap(sPA[rr], sPB[rr], sPC[rr], sPD[rr], sQA[tid], sQB[tid], sQC[tid], sQD[tid], c_up, c_dn, c_lf,
+                               c_rt)) {
                     const unsigned long long k = pack_key(d_swap, 2, p, q);
                     if (k < best) {
                         best = k;
@@ -230,7 +208,12 @@ __global__ void __launch_bounds__(kInterThreads) eval_inter_kernel(const EvalArg
             }
         }
         c_up = c_cur;
-        c_cur = c_dn;
+        c_lf = n_lf;
+        c_cur = n_cur;
+        c_rt = n_rt;
+        n_lf = m_lf;
+        n_cur = m_cur;
+        n_rt = m_rt;
     }
     if (!DUMP) block_min_to_global<kInterThreads>(best, a.best + b);
 }
@@ -276,7 +259,7 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
     if (t < t_hi && t < P - 1) {
         const size_t po = static_cast<size_t>(b) * a.pstride;
         const int *node = a.node + po;
-        const int2 *M = a.cells + static_cast<size_t>(b) * a.n * a.pitch;
+        const int2 *G = a.G + static_cast<size_t>(b) * a.grows * a.gpitch;
         const int4 *RA = a.RA + po, *RB = a.RB + po, *RC = a.RC + po, *RD = a.RD + po;
         const int2 *E = a.E + po, *SK = a.SK + po;
 
@@ -289,9 +272,10 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
         const int dep_t = tA.x;            // B[t] + service[node t]
         const int dep_tm1 = tC.x;          // B[t-1] + service[node t-1]   (customers only)
         const int2 SKt = SK[t];            // cell(node t-1, node t+1)
-        const int2 *row_m = t_cust ? M + static_cast<size_t>(node[t - 1]) * a.pitch : M;
-        const int2 *row_0 = M + static_cast<size_t>(nt) * a.pitch;
-        const int2 *row_p = M + static_cast<size_t>(node[t + 1]) * a.pitch;
+        // rows t-1, t, t+1 of the route-order matrix; the sweep reads them at consecutive columns x+1
+        const int2 *row_m = G + static_cast<size_t>(max(t - 1, 0)) * a.gpitch;
+        const int2 *row_0 = G + static_cast<size_t>(t) * a.gpitch;
+        const int2 *row_p = G + static_cast<size_t>(t + 1) * a.gpitch;
         const bool f2 = a.families & 1, f_rel = a.families & 2, f_swap = a.families & 4;
 
         // cells of rows node[t-1], node[t], node[t+1] at column node[x]: start at x = t+1
@@ -303,14 +287,13 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
         for (int x = t + 1; x < P; ++x) {
             const int nx = node[x];
             if (nx == 0) break;
-            const int nxn = node[x + 1];
             const int4 xA = RA[x], xB = RB[x], xC = RC[x], xD = RD[x];
             const int2 Ex = make_int2(xA.z, xD.z);  // cell(node x, node x+1)
             const int zn = xA.y;                    // Z[x+1]
             // next column's cells (rows fixed per thread): the only scattered loads of the step
-            const int2 cm1 = t_cust ? __ldg(row_m + nxn) : make_int2(0, 0);
-            const int2 c01 = __ldg(row_0 + nxn);
-            const int2 cp1 = __ldg(row_p + nxn);
+            const int2 cm1 = __ldg(row_m + x + 1);
+            const int2 c01 = __ldg(row_0 + x + 1);
+            const int2 cp1 = __ldg(row_p + x + 1);
             const Seg sx = seg_single(xB.x, xB.y);
 
             // reversed segment node[x..t+1]: prepend x
@@ -402,7 +385,9 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
 EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d)
 {
     EvalArgs a{};
-    a.cells = p->cells;
+    a.G = static_cast<const int2 *>(p->Gbuf.p);
+    a.grows = p->grows;
+    a.gpitch = p->gpitch;
     a.node = p->node;
     a.npos = p->npos;
     a.RA = p->RA;
@@ -410,10 +395,6 @@ EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count
     a.RC = p->RC;
     a.RD = p->RD;
     a.H = p->H;
-    a.PX = p->PX;
-    a.fd = static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale);
-    a.ft = static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale);
-    a.lim_hi = fast_path_limit_hi(a.fd, a.ft);
     a.E = p->E;
     a.SK = p->SK;
     a.n = p->n;
@@ -452,9 +433,8 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;  // largest P of the batch
     const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
     if (families & 6) {
-        dim3 grid((pmax + kTQ - 1) / kTQ, (shard_rows + kTP - 1) / kTP, p->batch);
-        if (p->cells_from_coords) eval_inter_kernel<false, true><<<grid, kInterThreads, 0, st>>>(a);
-        else eval_inter_kernel<false, false><<<grid, kInterThreads, 0, st>>>(a);
+        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + kStripRows - 1) / kStripRows, p->batch);
+        eval_inter_kernel<false><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     {
@@ -477,9 +457,8 @@ int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsi
     a.dump_feas = feas_d;
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
     if (family != 0) {
-        dim3 grid((pmax + kTQ - 1) / kTQ, (pmax + kTP - 1) / kTP, 1);
-        if (p->cells_from_coords) eval_inter_kernel<true, true><<<grid, kInterThreads, 0, st>>>(a);
-        else eval_inter_kernel<true, false><<<grid, kInterThreads, 0, st>>>(a);
+        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (pmax + kStripRows - 1) / kStripRows, 1);
+        eval_inter_kernel<true><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     dim3 grid((pmax + kIntraThreads - 1) / kIntraThreads, 1);

@@ -164,6 +164,7 @@ void rt_problem_destroy(rt_problem *p)
     DeviceGuard dg(e->device);
     cudaStreamSynchronize(e->stream);
     for (int i = 0; i < p->n_allocs; ++i) cudaFree(p->all_allocs[i]);
+    if (p->Gbuf.p) cudaFree(p->Gbuf.p);
     if (p->host_stage) cudaFreeHost(p->host_stage);
     delete p;
 }
@@ -368,6 +369,7 @@ int rt_problem_set_routes(rt_problem *p, const int32_t *order, const int32_t *tr
         npos[b] = P;
     }
     p->pmax = *std::max_element(npos.begin(), npos.end());
+    RT_TRY(ensure_position_matrix(p));
     RT_CUDA(e, cudaMemcpyAsync(p->node, node.data(), B * PS * 4, cudaMemcpyHostToDevice, e->stream));
     RT_CUDA(e, cudaMemcpyAsync(p->npos, npos.data(), B * 4, cudaMemcpyHostToDevice, e->stream));
     reset_search_kernel<<<(p->batch + 255) / 256, 256, 0, e->stream>>>(p->done, p->moves, p->batch);
@@ -443,13 +445,36 @@ int rt_problem_build_matrix_dev(rt_problem *p, double dist_scale, double time_sc
     return RT_OK;
 }
 
-int rt_problem_refresh_dev(rt_problem *p, void *stream)
+int rt_problem_refresh_dev(rt_problem *p, int what, void *stream)
 {
     if (!p) return RT_ERR_INVALID_ARG;
     rt_engine *e = p->e;
     if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_refresh_dev: no routes set");
+    if (!(what & 3)) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_refresh_dev: what must have bit 0 and/or bit 1 set");
     DeviceGuard dg(e->device);
-    return state_refresh(p, pick_stream(e, stream));
+    cudaStream_t st = pick_stream(e, stream);
+    if (what & 1) RT_TRY(position_matrix_refresh(p, st));
+    if (what & 2) RT_TRY(state_tables_refresh(p, st));
+    return RT_OK;
+}
+
+int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int families, void *best_keys_d,
+                        void *stream)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    rt_engine *e = p->e;
+    if (!best_keys_d || !(families & 7)) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_plan_dev: bad argument");
+    if (!p->has_coords || !p->has_stops || !p->has_routes)
+        return fail(e, RT_ERR_STATE, "rt_problem_plan_dev: coordinates, stops and routes must be on the device");
+    RT_TRY(check_scales(e, dist_scale, time_scale));
+    DeviceGuard dg(e->device);
+    cudaStream_t st = pick_stream(e, stream);
+    RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, st));
+    p->dist_scale = dist_scale;
+    p->time_scale = time_scale;
+    p->cells_from_coords = true;
+    RT_TRY(state_refresh(p, st));
+    return eval_moves_launch(p, families, 0, 1, static_cast<unsigned long long *>(best_keys_d), true, st);
 }
 
 int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
@@ -477,17 +502,42 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     RT_CUDA(e, cudaMemcpyAsync(p->node, node, B * PS * 4, cudaMemcpyHostToDevice, st));
     RT_CUDA(e, cudaMemcpyAsync(p->npos, npos, B * 4, cudaMemcpyHostToDevice, st));
     RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, st));
-    RT_TRY(launch_matrix_cells(e, p->xyz, p->n, p->batch, 0, p->n, dist_scale, time_scale, p->cells, st));
-    p->has_coords = p->has_stops = p->has_matrix = p->has_routes = true;
+    // the matrix of this pass is built in route order by the refresh below (state.cu); the node-order copy that
+    // rt_problem_build_matrix keeps for the greedy and for rt_problem_get_matrix is not needed here
+    p->has_coords = p->has_stops = p->has_routes = true;
+    p->has_matrix = false;
     p->cells_from_coords = true;
     p->pmax = 0;
     for (size_t b = 0; b < B; ++b) p->pmax = std::max(p->pmax, npos[b]);
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
+    RT_TRY(ensure_position_matrix(p));
     RT_TRY(state_refresh(p, st));
     RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, st));
     RT_CUDA(e, cudaMemcpyAsync(best_keys_out, p->best, B * 8, cudaMemcpyDeviceToHost, st));
     RT_CUDA(e, cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
+int rt_problem_get_position_matrix(rt_problem *p, int instance, int32_t *dist, int32_t *tim)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!dist || !tim || instance < 0 || instance >= p->batch)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_get_position_matrix: bad argument");
+    if (!p->has_routes || !p->Gbuf.p) return fail(e, RT_ERR_STATE, "rt_problem_get_position_matrix: no routes set");
+    int P = 0;
+    RT_CUDA(e, cudaMemcpy(&P, p->npos + instance, 4, cudaMemcpyDeviceToHost));
+    const size_t cnt = static_cast<size_t>(P) * P;
+    RT_TRY(reserve(e, e->plane_a[0], cnt * 4));
+    RT_TRY(reserve(e, e->plane_b[0], cnt * 4));
+    int *dd = static_cast<int *>(e->plane_a[0].p), *td = static_cast<int *>(e->plane_b[0].p);
+    dim3 grid((P + 255) / 256, P);
+    cells_to_planes_kernel<<<grid, 256, 0, e->stream>>>(
+        static_cast<const int2 *>(p->Gbuf.p) + static_cast<size_t>(instance) * p->grows * p->gpitch, P, p->gpitch, dd, td);
+    RT_CUDA(e, cudaGetLastError());
+    RT_CUDA(e, cudaMemcpyAsync(dist, dd, cnt * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(tim, td, cnt * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaStreamSynchronize(e->stream));
     return RT_OK;
 }
 

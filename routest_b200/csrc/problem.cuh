@@ -45,6 +45,8 @@ struct rt_problem {
     int4 *RA = nullptr, *RB = nullptr, *RC = nullptr, *RD = nullptr, *H = nullptr;
     int2 *E = nullptr, *SK = nullptr;
     double *PX = nullptr;                  // [batch][3][pstride] unit vectors in position order
+    rt::DevBuf Gbuf;                       // position-space matrix G[batch][grows][gpitch], G[p][q] = M[node p][node q]
+    int grows = 0, gpitch = 0;             // grows = pmax at the time G was sized
     int pmax = 0;                          // max npos over the batch (host copy; sizes the move grids)
     bool cells_from_coords = false;        // the matrix is SPEC §2 of this problem's coordinates
     int *Bv = nullptr, *Zv = nullptr, *route = nullptr, *rstart = nullptr;
@@ -70,11 +72,14 @@ struct rt_problem {
 namespace rt {
 
 int state_refresh(rt_problem *p, cudaStream_t st);
+int position_matrix_refresh(rt_problem *p, cudaStream_t st);
+int state_tables_refresh(rt_problem *p, cudaStream_t st);
 int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d,
                       bool signed_keys, cudaStream_t st);
 int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsigned char *feas_d, cudaStream_t st);
 int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
                        cudaStream_t st);
 int greedy_launch(rt_problem *p, bool use_tw, cudaStream_t st);
+int ensure_position_matrix(rt_problem *p);  // sizes G for p->pmax (may allocate; not stream-ordered)
 
 }  // namespace rt

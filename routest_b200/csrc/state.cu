@@ -1,7 +1,13 @@
-// state.cu — route state in position space (SPEC.md §6): the refresh that derives every per-position record the
-// move kernels read, and the kernel that applies a chosen move (SPEC.md §8).
+// state.cu — route state in position space (SPEC.md §6): the refresh that derives everything the move kernels read,
+// and the kernel that applies a chosen move (SPEC.md §8).
 //
 // No reference counterpart: the reference's only solver loop is the greedy constructor (utils.py:111-139).
+//
+// The refresh first lays the stop matrix out in ROUTE ORDER: G[p][q] = M[node p][node q] for positions p, q of
+// the current solution.  When the matrix is the great-circle matrix of the problem's coordinates, G is produced by
+// the matrix kernel itself running on the position-ordered unit vectors (same cell function, so the same bits, at
+// the HBM write roofline); a caller-supplied matrix is permuted instead.  Every later access of the move kernels
+// — a row of G per moved stop, consecutive columns per insertion point — is then contiguous.
 #include <climits>
 
 #include "problem.cuh"
@@ -10,31 +16,56 @@ namespace rt {
 
 namespace {
 
-// K1: everything that depends only on node[] — one thread per position, gathers from the matrix in parallel.
-__global__ void __launch_bounds__(256) state_gather_kernel(const int2 *__restrict__ cells, const int4 *__restrict__ stops,
+// PX[c][p] = xyz[c][node p]; positions beyond P repeat the depot so that G needs no bounds checks.
+__global__ void __launch_bounds__(256) position_vectors_kernel(const double *__restrict__ xyz,
+                                                               const int *__restrict__ node,
+                                                               const int *__restrict__ npos, int n, int pstride,
+                                                               double *__restrict__ PX)
+{
+    const int b = blockIdx.y;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pstride) return;
+    const int cur = p < npos[b] ? node[static_cast<size_t>(b) * pstride + p] : 0;
+    const double *v = xyz + static_cast<size_t>(b) * 3 * n;
+    double *px = PX + static_cast<size_t>(b) * 3 * pstride;
+    px[p] = v[cur];
+    px[pstride + p] = v[n + cur];
+    px[2 * pstride + p] = v[2 * n + cur];
+}
+
+// G[p][q] = M[node p][node q] for a stored (caller-supplied) matrix: coalesced writes, scattered reads within a row.
+__global__ void __launch_bounds__(256) permute_matrix_kernel(const int2 *__restrict__ cells,
+                                                             const int *__restrict__ node,
+                                                             const int *__restrict__ npos, int n, int pitch,
+                                                             int pstride, int grows, int gpitch, int2 *__restrict__ G)
+{
+    const int b = blockIdx.z, p = blockIdx.y;
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= gpitch) return;
+    const int P = npos[b];
+    const int *nd = node + static_cast<size_t>(b) * pstride;
+    const int a = p < P ? nd[p] : 0, c = q < P ? nd[q] : 0;
+    G[(static_cast<size_t>(b) * grows + p) * gpitch + q] =
+        __ldg(&cells[static_cast<size_t>(b) * n * pitch + static_cast<size_t>(a) * pitch + c]);
+}
+
+// K1: everything that depends only on node[] — one thread per position.
+__global__ void __launch_bounds__(256) state_gather_kernel(const int2 *__restrict__ G, const int4 *__restrict__ stops,
                                                            const int *__restrict__ node, const int *__restrict__ npos,
-                                                           int n, int pitch, int pstride, int4 *__restrict__ RB,
-                                                           int2 *__restrict__ E, int2 *__restrict__ SK,
-                                                           const double *__restrict__ xyz, double *__restrict__ PX)
+                                                           int n, int pstride, int grows, int gpitch,
+                                                           int4 *__restrict__ RB, int2 *__restrict__ E,
+                                                           int2 *__restrict__ SK)
 {
     const int b = blockIdx.y;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     const int P = npos[b];
     if (p >= P) return;
-    const int *nd = node + static_cast<size_t>(b) * pstride;
-    const int2 *M = cells + static_cast<size_t>(b) * n * pitch;
-    const int cur = nd[p], nxt = p + 1 < P ? nd[p + 1] : 0, prv = p > 0 ? nd[p - 1] : 0;
+    const int2 *Gb = G + static_cast<size_t>(b) * grows * gpitch;
+    const int cur = node[static_cast<size_t>(b) * pstride + p];
     const size_t o = static_cast<size_t>(b) * pstride + p;
     RB[o] = stops[static_cast<size_t>(b) * n + cur];
-    E[o] = p + 1 < P ? M[static_cast<size_t>(cur) * pitch + nxt] : make_int2(0, 0);
-    SK[o] = cur != 0 ? M[static_cast<size_t>(prv) * pitch + nxt] : make_int2(0, 0);
-    if (xyz) {  // unit vectors in position order: lets the move kernel rebuild matrix cells instead of gathering them
-        const double *v = xyz + static_cast<size_t>(b) * 3 * n;
-        double *px = PX + static_cast<size_t>(b) * 3 * pstride;
-        px[p] = v[cur];
-        px[pstride + p] = v[n + cur];
-        px[2 * pstride + p] = v[2 * n + cur];
-    }
+    E[o] = p + 1 < P ? Gb[static_cast<size_t>(p) * gpitch + p + 1] : make_int2(0, 0);
+    SK[o] = (cur != 0) ? Gb[static_cast<size_t>(p - 1) * gpitch + p + 1] : make_int2(0, 0);
 }
 
 // K2: one block per instance.  (A) route ids by a block scan over the separators, (B) one thread per route walks
@@ -46,10 +77,9 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
     int rstride, const int4 *__restrict__ stops_all, const int *__restrict__ cap_all,
     const long long *__restrict__ maxd_all, const int4 *__restrict__ RB_all, const int2 *__restrict__ E_all,
     const int2 *__restrict__ SK_all, int4 *__restrict__ RA_all, int4 *__restrict__ RC_all, int4 *__restrict__ RD_all,
-    int4 *__restrict__ H_all,
-    int *__restrict__ Bv_all, int *__restrict__ Zv_all, int *__restrict__ route_all, int *__restrict__ rstart_all,
-    long long *__restrict__ rload_all, long long *__restrict__ rdist_all, long long *__restrict__ cost_all,
-    int *__restrict__ feasible_all, unsigned long long *__restrict__ best_all)
+    int4 *__restrict__ H_all, int *__restrict__ Bv_all, int *__restrict__ Zv_all, int *__restrict__ route_all,
+    int *__restrict__ rstart_all, long long *__restrict__ rload_all, long long *__restrict__ rdist_all,
+    long long *__restrict__ cost_all, int *__restrict__ feasible_all, unsigned long long *__restrict__ best_all)
 {
     __shared__ int s_scan[kWalkThreads];
     __shared__ int s_feas;
@@ -233,19 +263,58 @@ __global__ void __launch_bounds__(256) apply_moves_kernel(const unsigned long lo
 
 }  // namespace
 
-int state_refresh(rt_problem *p, cudaStream_t st)
+int ensure_position_matrix(rt_problem *p)
+{
+    const int rows = p->pmax > 0 ? p->pmax : p->pstride;
+    const int pitch = (rows + 15) & ~15;
+    p->grows = rows;
+    p->gpitch = pitch;
+    return reserve(p->e, p->Gbuf, static_cast<size_t>(p->batch) * rows * pitch * sizeof(int2));
+}
+
+// node[] -> G (route-order matrix).  Stream-ordered, no allocation (G is sized by ensure_position_matrix when routes
+// are installed).
+int position_matrix_refresh(rt_problem *p, cudaStream_t st)
 {
     rt_engine *e = p->e;
-    dim3 g1((p->pstride + 255) / 256, p->batch);
-    state_gather_kernel<<<g1, 256, 0, st>>>(p->cells, p->stops, p->node, p->npos, p->n, p->pitch, p->pstride, p->RB,
-                                            p->E, p->SK, p->has_coords ? p->xyz : nullptr, p->PX);
+    int2 *G = static_cast<int2 *>(p->Gbuf.p);
+    if (!G || p->grows <= 0) return fail(e, RT_ERR_STATE, "route state refresh before routes were installed");
+    if (p->cells_from_coords) {
+        dim3 g0((p->pstride + 255) / 256, p->batch);
+        position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
+        RT_CUDA(e, cudaGetLastError());
+        RT_TRY(launch_matrix_cells_ld(e, p->PX, p->grows, p->pstride, p->batch, p->dist_scale, p->time_scale, G,
+                                      p->gpitch, st));
+    } else {
+        dim3 gp((p->gpitch + 255) / 256, p->grows, p->batch);
+        permute_matrix_kernel<<<gp, 256, 0, st>>>(p->cells, p->node, p->npos, p->n, p->pitch, p->pstride, p->grows,
+                                                  p->gpitch, G);
+        RT_CUDA(e, cudaGetLastError());
+    }
+    return RT_OK;
+}
+
+// G -> E/SK/RB, B/Z/load/dist, the packed records; resets the best keys.
+int state_tables_refresh(rt_problem *p, cudaStream_t st)
+{
+    rt_engine *e = p->e;
+    const int2 *G = static_cast<const int2 *>(p->Gbuf.p);
+    dim3 g1((p->grows + 255) / 256, p->batch);
+    state_gather_kernel<<<g1, 256, 0, st>>>(G, p->stops, p->node, p->npos, p->n, p->pstride, p->grows, p->gpitch, p->RB,
+                                            p->E, p->SK);
     RT_CUDA(e, cudaGetLastError());
     state_walk_kernel<<<p->batch, kWalkThreads, 0, st>>>(p->node, p->npos, p->nroutes, p->n, p->pstride, p->rstride,
                                                          p->stops, p->cap, p->max_dist, p->RB, p->E, p->SK, p->RA, p->RC,
-                                                         p->RD, p->H, p->Bv, p->Zv, p->route, p->rstart, p->rload, p->rdist,
-                                                         p->cost, p->feasible, p->best);
+                                                         p->RD, p->H, p->Bv, p->Zv, p->route, p->rstart, p->rload,
+                                                         p->rdist, p->cost, p->feasible, p->best);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
+}
+
+int state_refresh(rt_problem *p, cudaStream_t st)
+{
+    RT_TRY(position_matrix_refresh(p, st));
+    return state_tables_refresh(p, st);
 }
 
 int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,

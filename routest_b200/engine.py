@@ -372,6 +372,13 @@ class Problem:
         return dict(P=P, node=node[:P], route=route[:P], B=B[:P], Z=Z[:P], rload=rload[:R], rdist=rdist[:R],
                     cost=int(cost.value), feasible=bool(feas.value))
 
+    def get_position_matrix(self, instance: int, P: int):
+        """The route-order matrix the move kernels read: (dist, time), each int32 [P, P]."""
+        d = np.empty((P, P), np.int32)
+        t = np.empty((P, P), np.int32)
+        self._check(self._lib.rt_problem_get_position_matrix(self._p, int(instance), _i32(d), _i32(t)))
+        return d, t
+
     # -- moves (SPEC.md §7-§8)
     def eval_moves(self, families: int = ALL_FAMILIES, shard=(0, 1)):
         keys = np.zeros(self.batch, np.uint64)
@@ -422,8 +429,16 @@ class Problem:
             time_scale = time_scale_for_profile("driving-car")
         self._check(self._lib.rt_problem_build_matrix_dev(self._p, float(dist_scale), float(time_scale), stream or None))
 
-    def refresh_dev(self, stream: int = 0):
-        self._check(self._lib.rt_problem_refresh_dev(self._p, stream or None))
+    def refresh_dev(self, what: int = 3, stream: int = 0):
+        """what: bit 0 = route-order matrix, bit 1 = route state tables."""
+        self._check(self._lib.rt_problem_refresh_dev(self._p, int(what), stream or None))
+
+    def plan_dev(self, keys_ptr: int, *, dist_scale=DEFAULT_DIST_SCALE, time_scale=None, families: int = ALL_FAMILIES,
+                 stream: int = 0):
+        if time_scale is None:
+            time_scale = time_scale_for_profile("driving-car")
+        self._check(self._lib.rt_problem_plan_dev(self._p, float(dist_scale), float(time_scale), int(families),
+                                                  keys_ptr, stream or None))
 
     def eval_moves_dev(self, keys_ptr: int, families: int = ALL_FAMILIES, shard=(0, 1), stream: int = 0):
         self._check(self._lib.rt_problem_eval_moves_dev(self._p, int(families), int(shard[0]), int(shard[1]), keys_ptr,

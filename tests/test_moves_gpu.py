@@ -42,6 +42,19 @@ def test_device_matrix_equals_oracle_matrix(engine):
     assert np.array_equal(d, inst.D) and np.array_equal(t, inst.T)
 
 
+def test_route_order_matrix_is_a_permutation_of_the_matrix(engine):
+    """G[p][q] == M[node p][node q], both for the matrix rebuilt from coordinates and for a supplied one."""
+    inst, node, raw = synth_vrptw(22, 130, 7)
+    with _load(engine, [(inst, node, raw)]) as pr:
+        P = node.size
+        d, t = pr.get_position_matrix(0, P)
+        assert np.array_equal(d, inst.D[np.ix_(node, node)]) and np.array_equal(t, inst.T[np.ix_(node, node)])
+        pr.set_matrix(0, inst.D, inst.T)           # now the gather/permutation path
+        pr.set_routes([O.positions_to_trips(node)])
+        d2, t2 = pr.get_position_matrix(0, P)
+        assert np.array_equal(d2, d) and np.array_equal(t2, t)
+
+
 @pytest.mark.parametrize("seed,stops,veh,kw", [(1, 12, 3, {}), (2, 25, 4, {}), (3, 60, 5, dict(half_lo=300, half_hi=900)),
                                                 (4, 100, 10, {}), (5, 150, 4, dict(half_lo=7200, half_hi=20000)),
                                                 (6, 70, 2, dict(half_lo=20000, half_hi=43200))])
