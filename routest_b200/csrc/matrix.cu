@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) matrix_kernel(const Ma
     const double *__restrict__ Y = X + a.ld;
     const double *__restrict__ Z = Y + a.ld;
     const int lane = threadIdx.x & 31;
-    const int wb = blockIdx.x * kColsPerBlock + (threadIdx.x >> 5) * 128;
+    const int wb = blockIdx.x * (blockDim.x * 4) + (threadIdx.x >> 5) * 128;  // a block spans blockDim.x * 4 columns
 
     // column ownership: 16-byte stores, 512 contiguous bytes per warp-wide store instruction
     int col[4];
@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) matrix_kernel(const Ma
 
     const int row0 = a.r0 + blockIdx.y * a.rows_per_block;
     const int nrows = min(a.rows_per_block, a.r1 - row0);
-    for (int t = threadIdx.x; t < 3 * nrows; t += kThreads) {
+    for (int t = threadIdx.x; t < 3 * nrows; t += blockDim.x) {
         int comp = t / nrows, r = t - comp * nrows;
         srow[comp][r] = (comp == 0 ? X : comp == 1 ? Y : Z)[row0 + r];
     }
@@ -200,12 +200,16 @@ int launch_matrix(rt_engine *e, MatArgs a, int batch, int pitch_cols, cudaStream
 {
     const int rows = a.r1 - a.r0;
     if (rows <= 0 || batch <= 0) return RT_OK;
+    // Column blocks of equal width: a pitch just above a multiple of 1024 (1,040 for 1,000 stops in route order)
+    // must not leave a block with a handful of live threads, so the block shrinks instead (multiples of a warp).
     const int col_blocks = (pitch_cols + kColsPerBlock - 1) / kColsPerBlock;
+    const int cols_per_block = (pitch_cols + col_blocks - 1) / col_blocks;
+    const int threads = std::min(kThreads, ((cols_per_block + 3) / 4 + 31) & ~31);
     a.rows_per_block = pick_rows_per_block(rows, col_blocks, batch);
     const int row_blocks = (rows + a.rows_per_block - 1) / a.rows_per_block;
     if (row_blocks > 65535 || batch > 65535) return fail(e, RT_ERR_INVALID_ARG, "matrix grid too large");
     dim3 grid(col_blocks, row_blocks, batch);
-    matrix_kernel<MODE><<<grid, kThreads, 0, st>>>(a);
+    matrix_kernel<MODE><<<grid, threads, 0, st>>>(a);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }

@@ -28,6 +28,15 @@ namespace {
 constexpr int kInterThreads = 128;  // one column q per thread
 constexpr int kStripRows = 32;     // rows p per block
 
+// a + b on the FMA pipe (IMAD with multiplier 1): the move kernels are bound by the ALU pipe (compares, min/max,
+// selects, three-input adds), while the FMA pipe idles — plain sums go there.
+__device__ __forceinline__ int fadd(int a, int b)
+{
+    int r;
+    asm("mad.lo.s32 %0, %1, 1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+
 __device__ __forceinline__ unsigned long long pack_key(int delta, int family, int p, int q)
 {
     return (static_cast<unsigned long long>(static_cast<unsigned>(delta) + 0x80000000u) << 32) |
@@ -82,34 +91,17 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
     hi = static_cast<int>(static_cast<long long>(P) * (idx + 1) / cnt);
 }
 
-// Full feasibility of one inter-route candidate from the cold records (SPEC.md §7): capacity, distance limit and
-// time windows of both routes.  Only reached by candidates whose delta can still win, or by all in dump mode.
-__device__ __forceinline__ bool check_relocate(int4 pB, int4 pC, int4 qA, int4 qD, int2 c_pq, int2 c_pq1)
-{
-    const int ins = c_pq.x + c_pq1.x - qA.z;
-    const int tu = max(pB.x, qA.x + c_pq.y);
-    return (pC.w & 2) && pB.w <= qD.x && ins <= qD.y && tu <= pB.y && tu + pB.z + c_pq1.y <= qA.y;
-}
-
-__device__ __forceinline__ bool check_swap(int4 pA, int4 pB, int4 pC, int4 pD, int4 qA, int4 qB, int4 qC, int4 qD,
-                                           int2 c_up, int2 c_dn, int2 c_lf, int2 c_rt)
-{
-    const int d1 = c_up.x + c_dn.x - pC.z;  // route of p: pu -> v -> nu
-    const int d2 = c_lf.x + c_rt.x - qC.z;  // route of q: pw -> u -> nw
-    const int tv = max(qB.x, pC.x + c_up.y);
-    const int tu = max(pB.x, qC.x + c_lf.y);
-    return qB.w - pB.w <= pD.x && pB.w - qB.w <= qD.x && d1 <= pD.y && d2 <= qD.y && tv <= qB.y &&
-           tv + qB.z + c_dn.y <= pA.y && tu <= pB.y && tu + pB.z + c_rt.y <= qA.y;
-}
-
-// grid (column strips of 128, row strips of kStripRows within the shard, instances)
+// grid (column strips of 128, row strips of kStripRows within the shard, instances).
+// Straight-line evaluation: in a realistic state a large share of the candidates has a delta below the best
+// feasible one while being infeasible (capacity, windows), so pruning on the delta leaves almost every warp with
+// some lane in the slow path; computing delta AND feasibility for every candidate without a branch is cheaper.
+// Per row three broadcast LDS.128 bring everything about p; everything about q lives in registers.
 template <bool DUMP>
 __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const EvalArgs a)
 {
-    // hot and cold records of the strip's rows (p side) and of the block's columns (q side): the slow path never
-    // waits on global memory
-    __shared__ int4 sH[kStripRows], sPA[kStripRows], sPB[kStripRows], sPC[kStripRows], sPD[kStripRows];
-    __shared__ int4 sQA[kInterThreads], sQB[kInterThreads], sQC[kInterThreads], sQD[kInterThreads];
+    __shared__ int4 sH[kStripRows];   // {rem_delta, oe, -, route | customer << 30 | rem_ok << 29}
+    __shared__ int4 sP1[kStripRows];  // {ready, due, service, demand}
+    __shared__ int4 sP2[kStripRows];  // {Z[p+1], B[p-1]+service[p-1], capacity slack, distance slack} of p's route
 
     const int b = DUMP ? a.dump_instance : blockIdx.z;
     const int P = a.npos[b];
@@ -124,87 +116,105 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const Eval
     const int q = q0 + tid;
     const bool q_in = q < P;
     if (tid < kStripRows) {
-        const bool in = p0 + tid < P;
-        const size_t o = po + p0 + tid;
-        sH[tid] = in ? a.H[o] : make_int4(0, 0, 0, 0);
-        sPA[tid] = in ? a.RA[o] : make_int4(0, 0, 0, 0);
-        sPB[tid] = in ? a.RB[o] : make_int4(0, 0, 0, 0);
-        sPC[tid] = in ? a.RC[o] : make_int4(0, 0, 0, 0);
-        sPD[tid] = in ? a.RD[o] : make_int4(0, 0, 0, 0);
+        int4 h = make_int4(0, 0, 0, 0), p1 = h, p2 = h;
+        if (p0 + tid < P) {
+            const size_t o = po + p0 + tid;
+            const int4 rA = a.RA[o], rC = a.RC[o], rD = a.RD[o];
+            h = a.H[o];
+            h.w |= (rC.w & 2) << 28;  // rem_ok -> bit 29
+            p1 = a.RB[o];
+            p2 = make_int4(rA.y, rC.x, rD.x, rD.y);
+        }
+        sH[tid] = h;
+        sP1[tid] = p1;
+        sP2[tid] = p2;
     }
-    const int4 Hq = q_in ? a.H[po + q] : make_int4(0, 0, 0, -1);
-    sQA[tid] = q_in ? a.RA[po + q] : make_int4(0, 0, 0, 0);
-    sQB[tid] = q_in ? a.RB[po + q] : make_int4(0, 0, 0, 0);
-    sQC[tid] = q_in ? a.RC[po + q] : make_int4(0, 0, 0, 0);
-    sQD[tid] = q_in ? a.RD[po + q] : make_int4(0, 0, 0, 0);
+    int4 Hq = make_int4(0, 0, 0, -1), qB = make_int4(0, 0, 0, 0);
+    int dep_q = 0, zn_q = 0, depprev_q = 0, capsl_q = 0, distsl_q = 0;
+    if (q_in) {
+        const int4 rA = a.RA[po + q], rC = a.RC[po + q], rD = a.RD[po + q];
+        Hq = a.H[po + q];
+        qB = a.RB[po + q];
+        dep_q = rA.x;
+        zn_q = rA.y;
+        depprev_q = rC.x;
+        capsl_q = rD.x;
+        distsl_q = rD.y;
+    }
     __syncthreads();
 
-    // columns are clamped so that every lane can load unconditionally (pad columns of G are valid depot cells)
-    const int qc = min(q, a.gpitch - 1), ql = max(qc - 1, 0), qr = min(qc + 1, a.gpitch - 1);
-    const int q_route = Hq.w & 0x3FFFFFFF;
+    const int qc = min(q, a.gpitch - 1);  // lanes beyond the last position re-read a pad column
+    const int q_route = Hq.w & 0x7FFF;
     const bool q_cust = q_in && ((Hq.w >> 30) & 1);
     const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
     const bool swap_q = q_cust && (a.families & 4);
+    const bool swap_tile = (a.families & 4) && p0 < q0 + kInterThreads - 1;  // some pair of the tile has p < q
 
-    // Only the minimum key matters, so a candidate is fully evaluated only if its delta can still beat the best
-    // feasible key seen so far by this warp; the bound starts from whatever other blocks have already published
-    // for this instance.  Exact: a pruned candidate has a larger key than an existing feasible one.
-    unsigned long long best = kNoMove;
-    int bound = INT_MAX;
-    if (!DUMP) {
-        const unsigned long long seen = *reinterpret_cast<const volatile unsigned long long *>(a.best + b);
-        if (seen != kNoMove) bound = static_cast<int>(static_cast<unsigned>(seen >> 32) - 0x80000000u);
-    }
+    int best_d = INT_MAX;
+    unsigned best_i = 0xFFFFFFFFu;  // family << 30 | p << 15 | q
     const int rows = min(kStripRows, p_hi - p0);
-    const int last_row = a.grows - 1;
-    auto row_ptr = [&](int r) { return G + static_cast<size_t>(min(max(r, 0), last_row)) * a.gpitch; };
-    // register window over three rows of G, loaded two rows ahead of use
-    int2 c_up = __ldg(row_ptr(p0 - 1) + qc);
-    const int2 *g0 = row_ptr(p0), *g1 = row_ptr(p0 + 1);
-    int2 c_lf = __ldg(g0 + ql), c_cur = __ldg(g0 + qc), c_rt = __ldg(g0 + qr);
-    int2 n_lf = __ldg(g1 + ql), n_cur = __ldg(g1 + qc), n_rt = __ldg(g1 + qr);
+    // Register window over three rows of G, loaded two rows ahead of use.  G carries a pad cell in front and two
+    // pad rows behind (ensure_position_matrix), so q-1 / q+1 / p+2 need no clamping: whatever an out-of-range
+    // neighbour holds is only ever combined into candidates that are not valid.
+    const int2 *g = G + static_cast<size_t>(max(p0 - 1, 0)) * a.gpitch + qc;
+    int2 c_up = __ldg(g);
+    g = G + static_cast<size_t>(p0) * a.gpitch + qc;
+    int2 c_lf = __ldg(g - 1), c_cur = __ldg(g), c_rt = __ldg(g + 1);
+    g += a.gpitch;
+    int2 n_lf = __ldg(g - 1), n_cur = __ldg(g), n_rt = __ldg(g + 1);
 #pragma unroll 2
     for (int rr = 0; rr < rows; ++rr) {
         const int p = p0 + rr;
-        const int2 *g2 = row_ptr(p + 2);
-        const int2 m_lf = __ldg(g2 + ql), m_cur = __ldg(g2 + qc), m_rt = __ldg(g2 + qr);
+        g += a.gpitch;
+        const int2 m_lf = __ldg(g - 1), m_cur = __ldg(g), m_rt = __ldg(g + 1);
         const int2 c_dn = n_cur;
         const int4 Hp = sH[rr];
         if ((Hp.w >> 30) & 1) {  // p is a customer (warp-uniform)
-            const bool other = (Hp.w & 0x3FFFFFFF) != q_route;
-            const int d_rel = Hp.x + c_cur.x + c_rt.x - Hq.z;
-            const int d_swap = c_up.x + c_dn.x - Hp.y + c_lf.x + c_rt.x - Hq.y;
-            const bool v_rel = rel_q && other, v_swap = swap_q && other && p < q;
+            const int4 p1 = sP1[rr], p2 = sP2[rr];
+            const bool other = (Hp.w & 0x7FFF) != q_route;
+            // relocate(p -> between q and q+1): a -> u -> b replaces a -> b in route[q]
+            const int ins = fadd(fadd(c_cur.x, c_rt.x), -Hq.z);
+            const int d_rel = fadd(Hp.x, ins);
+            const int tu = max(p1.x, fadd(dep_q, c_cur.y));
+            const bool v_rel = rel_q && other;
+            const bool ok_rel = v_rel && ((Hp.w >> 29) & 1) && p1.w <= capsl_q && ins <= distsl_q && tu <= p1.y &&
+                                fadd(fadd(tu, p1.z), c_rt.y) <= zn_q;
             if (DUMP) {
                 if (v_rel && a.dump_family == 1) {
                     a.dump_delta[static_cast<size_t>(p) * P + q] = d_rel;
-                    a.dump_feas[static_cast<size_t>(p) * P + q] =
-                        check_relocate(sPB[rr], sPC[rr], sQA[tid], sQD[tid], c_cur, c_rt) ? 1 : 0;
+                    a.dump_feas[static_cast<size_t>(p) * P + q] = ok_rel ? 1 : 0;
                 }
-                if (v_swap && a.dump_family == 2) {
-                    a.dump_delta[static_cast<size_t>(p) * P + q] = d_swap;
-                    a.dump_feas[static_cast<size_t>(p) * P + q] =
-                        check_swap(sPA[rr], sPB[rr], sPC[rr], sPD[rr], sQA[tid], sQB[tid], sQC[tid], sQD[tid], c_up, c_dn,
-                                   c_lf, c_rt) ? 1 : 0;
+            } else if (ok_rel && d_rel <= best_d) {  // rarely true: the update stays off the straight-line path
+                const unsigned idx = (1u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q);
+                if (d_rel < best_d || idx < best_i) {
+                    best_d = d_rel;
+                    best_i = idx;
                 }
-            } else {
-                if (v_rel && d_rel <= bound && check_relocate(sPB[rr], sPC[rr], sQA[tid], sQD[tid], c_cur, c_rt)) {
-                    const unsigned long long k = pack_key(d_rel, 1, p, q);
-                    if (k < best) {
-                        best = k;
-                        bound = d_rel;
+            }
+            if (swap_tile) {
+                // swap(p, q), p < q: pu -> v -> nu in route[p], pw -> u -> nw in route[q]
+                const int d1 = fadd(fadd(c_up.x, c_dn.x), -Hp.y);
+                const int d2 = fadd(fadd(c_lf.x, c_rt.x), -Hq.y);
+                const int d_swap = fadd(d1, d2);
+                const int tv = max(qB.x, fadd(p2.y, c_up.y));
+                const int tw = max(p1.x, fadd(depprev_q, c_lf.y));
+                const int dd = fadd(qB.w, -p1.w);
+                const bool v_swap = swap_q && other && p < q;
+                const bool ok_swap = v_swap && dd <= p2.z && -dd <= capsl_q && d1 <= p2.w && d2 <= distsl_q &&
+                                     tv <= qB.y && fadd(fadd(tv, qB.z), c_dn.y) <= p2.x && tw <= p1.y &&
+                                     fadd(fadd(tw, p1.z), c_rt.y) <= zn_q;
+                if (DUMP) {
+                    if (v_swap && a.dump_family == 2) {
+                        a.dump_delta[static_cast<size_t>(p) * P + q] = d_swap;
+                        a.dump_feas[static_cast<size_t>(p) * P + q] = ok_swap ? 1 : 0;
+                    }
+                } else if (ok_swap && d_swap <= best_d) {
+                    const unsigned idx = (2u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q);
+                    if (d_swap < best_d || idx < best_i) {
+                        best_d = d_swap;
+                        best_i = idx;
                     }
                 }
-                if (v_swap && d_swap <= bound &&
-                    check_swap(sPA[rr], sPB[rr], sPC[rr], sPD[rr], sQA[tid], sQB[tid], sQC[tid], sQD[tid], c_up, c_dn, c_lf,
-                               c_rt)) {
-                    const unsigned long long k = pack_key(d_swap, 2, p, q);
-                    if (k < best) {
-                        best = k;
-                        bound = d_swap;
-                    }
-                }
-                bound = __reduce_min_sync(0xffffffffu, bound);  // share the bound across the warp (one REDUX)
             }
         }
         c_up = c_cur;
@@ -215,7 +225,13 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const Eval
         n_cur = m_cur;
         n_rt = m_rt;
     }
-    if (!DUMP) block_min_to_global<kInterThreads>(best, a.best + b);
+    if (!DUMP) {
+        const unsigned long long best =
+            best_i == 0xFFFFFFFFu
+                ? kNoMove
+                : (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i;
+        block_min_to_global<kInterThreads>(best, a.best + b);
+    }
 }
 
 // ---- same-route candidates ------------------------------------------------------------------------------------
@@ -385,7 +401,7 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
 EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d)
 {
     EvalArgs a{};
-    a.G = static_cast<const int2 *>(p->Gbuf.p);
+    a.G = position_matrix(p);
     a.grows = p->grows;
     a.gpitch = p->gpitch;
     a.node = p->node;

@@ -533,7 +533,7 @@ int rt_problem_get_position_matrix(rt_problem *p, int instance, int32_t *dist, i
     int *dd = static_cast<int *>(e->plane_a[0].p), *td = static_cast<int *>(e->plane_b[0].p);
     dim3 grid((P + 255) / 256, P);
     cells_to_planes_kernel<<<grid, 256, 0, e->stream>>>(
-        static_cast<const int2 *>(p->Gbuf.p) + static_cast<size_t>(instance) * p->grows * p->gpitch, P, p->gpitch, dd, td);
+        position_matrix(p) + static_cast<size_t>(instance) * p->grows * p->gpitch, P, p->gpitch, dd, td);
     RT_CUDA(e, cudaGetLastError());
     RT_CUDA(e, cudaMemcpyAsync(dist, dd, cnt * 4, cudaMemcpyDeviceToHost, e->stream));
     RT_CUDA(e, cudaMemcpyAsync(tim, td, cnt * 4, cudaMemcpyDeviceToHost, e->stream));

@@ -71,6 +71,9 @@ struct rt_problem {
 
 namespace rt {
 
+// first cell of G (the buffer starts with 16 pad cells)
+inline int2 *position_matrix(const rt_problem *p) { return p->Gbuf.p ? static_cast<int2 *>(p->Gbuf.p) + 16 : nullptr; }
+
 int state_refresh(rt_problem *p, cudaStream_t st);
 int position_matrix_refresh(rt_problem *p, cudaStream_t st);
 int state_tables_refresh(rt_problem *p, cudaStream_t st);

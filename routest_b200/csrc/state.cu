@@ -269,7 +269,8 @@ int ensure_position_matrix(rt_problem *p)
     const int pitch = (rows + 15) & ~15;
     p->grows = rows;
     p->gpitch = pitch;
-    return reserve(p->e, p->Gbuf, static_cast<size_t>(p->batch) * rows * pitch * sizeof(int2));
+    // 16 pad cells in front and two pad rows behind: the move kernels read q-1, q+1 and p+2 without clamping
+    return reserve(p->e, p->Gbuf, (static_cast<size_t>(p->batch) * rows * pitch + 16 + 2 * static_cast<size_t>(pitch)) * sizeof(int2));
 }
 
 // node[] -> G (route-order matrix).  Stream-ordered, no allocation (G is sized by ensure_position_matrix when routes
@@ -277,8 +278,8 @@ int ensure_position_matrix(rt_problem *p)
 int position_matrix_refresh(rt_problem *p, cudaStream_t st)
 {
     rt_engine *e = p->e;
-    int2 *G = static_cast<int2 *>(p->Gbuf.p);
-    if (!G || p->grows <= 0) return fail(e, RT_ERR_STATE, "route state refresh before routes were installed");
+    int2 *G = position_matrix(p);
+    if (!p->Gbuf.p || p->grows <= 0) return fail(e, RT_ERR_STATE, "route state refresh before routes were installed");
     if (p->cells_from_coords) {
         dim3 g0((p->pstride + 255) / 256, p->batch);
         position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
@@ -298,7 +299,7 @@ int position_matrix_refresh(rt_problem *p, cudaStream_t st)
 int state_tables_refresh(rt_problem *p, cudaStream_t st)
 {
     rt_engine *e = p->e;
-    const int2 *G = static_cast<const int2 *>(p->Gbuf.p);
+    const int2 *G = position_matrix(p);
     dim3 g1((p->grows + 255) / 256, p->batch);
     state_gather_kernel<<<g1, 256, 0, st>>>(G, p->stops, p->node, p->npos, p->n, p->pstride, p->grows, p->gpitch, p->RB,
                                             p->E, p->SK);
