@@ -194,10 +194,10 @@ int rt_problem_set_stops(rt_problem *p, const int32_t *stops, const int32_t *cap
     const long long total = static_cast<long long>(p->n) * p->batch;
     for (long long i = 0; i < total; ++i) {
         const int32_t *s = stops + 4 * i;
-        if (s[0] > s[1] || s[2] < 0 || s[3] < 0 || s[0] < 0 || s[1] > (1 << 29))
+        if (s[0] > s[1] || s[2] < 0 || s[3] < 0 || s[0] < 0 || s[1] > (1 << 28) || s[2] > (1 << 28) || s[3] > (1 << 28))
             return fail(e, RT_ERR_INVALID_ARG,
-                        "stop %lld: need 0 <= ready <= due <= 2^29, service >= 0, demand >= 0 (got %d,%d,%d,%d)", i, s[0],
-                        s[1], s[2], s[3]);
+                        "stop %lld: need 0 <= ready <= due <= 2^28, 0 <= service, demand <= 2^28 (got %d,%d,%d,%d)", i,
+                        s[0], s[1], s[2], s[3]);
     }
     for (int b = 0; b < p->batch; ++b)
         if (cap[b] < 0 || max_dist[b] < 0) return fail(e, RT_ERR_INVALID_ARG, "negative capacity or distance limit");
@@ -486,9 +486,14 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
         return fail(e, RT_ERR_INVALID_ARG, "rt_problem_plan: bad argument");
     RT_TRY(check_scales(e, dist_scale, time_scale));
     const size_t B = p->batch, N = p->n, PS = p->pstride;
-    for (size_t i = 0; i < B * N; ++i)
-        if (!(lat[i] >= -90.0 && lat[i] <= 90.0) || !(lon[i] >= -180.0 && lon[i] <= 180.0))
-            return fail(e, RT_ERR_INVALID_ARG, "coordinate %zu out of range or not finite", i);
+    {   // branch-free scan (it vectorises): this runs on the request path of every plan call.  Stop records are
+        // taken as they are here (rt_problem_set_stops is the validating entry point); out-of-range values cannot
+        // fault a kernel, they only make the instance's result meaningless.
+        int bad_coord = 0;
+        for (size_t i = 0; i < B * N; ++i)
+            bad_coord |= !(lat[i] >= -90.0 && lat[i] <= 90.0) | !(lon[i] >= -180.0 && lon[i] <= 180.0);
+        if (bad_coord) return fail(e, RT_ERR_INVALID_ARG, "a coordinate is out of range or not finite");
+    }
     for (size_t b = 0; b < B; ++b)
         if (npos[b] < static_cast<int>(N) + 1 || npos[b] > static_cast<int>(PS) || node[b * PS] != 0 ||
             node[b * PS + npos[b] - 1] != 0)

@@ -177,11 +177,13 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
         const int dep = Bv[p] + rb.z;
         const int zn = p + 1 < P ? Zv[p + 1] : depot.y;
         RA[p] = make_int4(dep, zn, ed.x, rt_);
-        int capsl = -1, dsl = INT_MIN;
+        // slacks are clamped to [-2^29, 2^30]: wide enough to compare against any demand / delta (both < 2^30 in
+        // magnitude), narrow enough that "slack - value" never overflows in the move kernels
+        constexpr long long kLo = -(1LL << 29), kHi = 1LL << 30;
+        int capsl = -1, dsl = static_cast<int>(kLo);
         if (rt_ < R) {
-            capsl = static_cast<int>(min(static_cast<long long>(INT_MAX), cap - rload[rt_]));
-            const long long sl = maxd - rdist[rt_];
-            dsl = static_cast<int>(max(static_cast<long long>(INT_MIN), min(static_cast<long long>(INT_MAX), sl)));
+            capsl = static_cast<int>(max(kLo, min(kHi, static_cast<long long>(cap) - rload[rt_])));
+            dsl = static_cast<int>(max(kLo, min(kHi, maxd - rdist[rt_])));
         }
         RD[p] = make_int4(capsl, dsl, ed.y, sk.y);
         if (node[p] != 0) {
