@@ -48,6 +48,7 @@ struct rt_problem {
     rt::DevBuf Gbuf;                       // position-space matrix G[batch][grows][gpitch], G[p][q] = M[node p][node q]
     int grows = 0, gpitch = 0;             // grows = pmax at the time G was sized
     int pmax = 0;                          // max npos over the batch (host copy; sizes the move grids)
+    bool walk_smem_opted = false;          // cudaFuncSetAttribute for the walk kernel's staging area done
     bool cells_from_coords = false;        // the matrix is SPEC §2 of this problem's coordinates
     int *Bv = nullptr, *Zv = nullptr, *route = nullptr, *rstart = nullptr;
     long long *rload = nullptr, *rdist = nullptr;

@@ -79,8 +79,12 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
     const int2 *__restrict__ SK_all, int4 *__restrict__ RA_all, int4 *__restrict__ RC_all, int4 *__restrict__ RD_all,
     int4 *__restrict__ H_all, int *__restrict__ Bv_all, int *__restrict__ Zv_all, int *__restrict__ route_all,
     int *__restrict__ rstart_all, long long *__restrict__ rload_all, long long *__restrict__ rdist_all,
-    long long *__restrict__ cost_all, int *__restrict__ feasible_all, unsigned long long *__restrict__ best_all)
+    long long *__restrict__ cost_all, int *__restrict__ feasible_all, unsigned long long *__restrict__ best_all,
+    int staged_positions)
 {
+    // When the instance fits, its stop records and edge cells are staged in shared memory first (coalesced), so the
+    // sequential per-route walks run at shared-memory latency instead of paying an L2 round trip per position.
+    extern __shared__ __align__(16) unsigned char s_dyn[];
     __shared__ int s_scan[kWalkThreads];
     __shared__ int s_feas;
     __shared__ unsigned long long s_cost;
@@ -91,6 +95,16 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
     const int *node = node_all + po;
     const int4 *RB = RB_all + po;
     const int2 *E = E_all + po, *SK = SK_all + po;
+    const bool staged = staged_positions >= P;
+    int4 *sRB = reinterpret_cast<int4 *>(s_dyn);
+    int2 *sE = reinterpret_cast<int2 *>(s_dyn + sizeof(int4) * static_cast<size_t>(staged_positions));
+    if (staged)
+        for (int p = tid; p < P; p += kWalkThreads) {
+            sRB[p] = RB[p];
+            sE[p] = E[p];
+        }
+    const int4 *wRB = staged ? sRB : RB;   // what the walks read
+    const int2 *wE = staged ? sE : E;
     int *Bv = Bv_all + po, *Zv = Zv_all + po, *route = route_all + po, *rstart = rstart_all + ro + b;  // rstride+1 each
     long long *rload = rload_all + ro, *rdist = rdist_all + ro;
     const int4 depot = stops_all[static_cast<size_t>(b) * n];
@@ -137,8 +151,8 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
         Bv[s] = depot.x;
         Zv[s] = depot.y;
         for (int p = s + 1; p < e; ++p) {
-            const int2 ed = E[p - 1];
-            const int4 rb = RB[p];
+            const int2 ed = wE[p - 1];
+            const int4 rb = wRB[p];
             Bcur = max(rb.x, Bcur + svc_prev + ed.y);
             feas = feas && Bcur <= rb.y;
             Bv[p] = Bcur;
@@ -146,7 +160,7 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
             load += rb.w;
             dist += ed.x;
         }
-        const int2 last = E[e - 1];
+        const int2 last = wE[e - 1];
         feas = feas && (Bcur + svc_prev + last.y <= depot.y);
         dist += last.x;
         rload[rr] = load;
@@ -155,8 +169,8 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
         cost += static_cast<unsigned long long>(dist);
         int Zn = depot.y;
         for (int p = e - 1; p > s; --p) {
-            const int4 rb = RB[p];
-            Zn = min(rb.y, Zn - E[p].y - rb.z);
+            const int4 rb = wRB[p];
+            Zn = min(rb.y, Zn - wE[p].y - rb.z);
             Zv[p] = Zn;
         }
     }
@@ -306,10 +320,17 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st)
     state_gather_kernel<<<g1, 256, 0, st>>>(G, p->stops, p->node, p->npos, p->n, p->pstride, p->grows, p->gpitch, p->RB,
                                             p->E, p->SK);
     RT_CUDA(e, cudaGetLastError());
-    state_walk_kernel<<<p->batch, kWalkThreads, 0, st>>>(p->node, p->npos, p->nroutes, p->n, p->pstride, p->rstride,
+    // stage the walk's inputs in shared memory when an instance's positions fit (24 B each, <= 96 KB)
+    const int staged = p->grows <= 4096 ? p->grows : 0;
+    const size_t walk_smem = static_cast<size_t>(staged) * (sizeof(int4) + sizeof(int2));
+    if (walk_smem > 48 * 1024 && !p->walk_smem_opted) {
+        RT_CUDA(e, cudaFuncSetAttribute(state_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        p->walk_smem_opted = true;
+    }
+    state_walk_kernel<<<p->batch, kWalkThreads, walk_smem, st>>>(p->node, p->npos, p->nroutes, p->n, p->pstride, p->rstride,
                                                          p->stops, p->cap, p->max_dist, p->RB, p->E, p->SK, p->RA, p->RC,
                                                          p->RD, p->H, p->Bv, p->Zv, p->route, p->rstart, p->rload,
-                                                         p->rdist, p->cost, p->feasible, p->best);
+                                                         p->rdist, p->cost, p->feasible, p->best, staged);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }
