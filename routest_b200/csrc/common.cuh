@@ -73,8 +73,8 @@ int launch_unit_vectors(rt_engine *e, const double *lat_d, const double *lon_d, 
                         cudaStream_t st);
 int launch_matrix_cells(rt_engine *e, const double *xyz_d, int n, int batch, int r0, int r1, double dist_scale,
                         double time_scale, int2 *cells_d, cudaStream_t st);
-int launch_matrix_cells_ld(rt_engine *e, const double *xyz_d, int n, int ld, int batch, double dist_scale,
-                           double time_scale, int2 *cells_d, int pitch, cudaStream_t st);
+int launch_matrix_cells_ld(rt_engine *e, const double *xyz_d, int n, int ld, int batch, int r0, int r1,
+                           double dist_scale, double time_scale, int2 *cells_d, int pitch, cudaStream_t st);
 int launch_matrix_planes(rt_engine *e, const double *xyz_d, int n, int r0, int r1, double dist_scale, double time_scale,
                          int32_t *dist_d, int32_t *time_d, double *metres_d, int pitch_i32, int pitch_f64,
                          cudaStream_t st);

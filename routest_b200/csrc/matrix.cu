@@ -43,6 +43,7 @@ __global__ void __launch_bounds__(256) unit_vectors_kernel(const double *__restr
 struct MatArgs {
     const double *xyz;
     int n, ld, r0, r1, rows_per_block;  // ld: stride between the x/y/z component arrays (>= n); instance stride 3*ld
+    int out_rows;     // rows between two instances in the output (0: r1 - r0, the dense default)
     float fd, ft;
     int lim_hi;       // fast_path_limit_hi(fd, ft)
     int2 *cells;      // MODE 0
@@ -93,7 +94,7 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) matrix_kernel(const Ma
     }
     __syncthreads();
 
-    const size_t rows_total = static_cast<size_t>(a.r1 - a.r0);
+    const size_t rows_total = static_cast<size_t>(a.out_rows ? a.out_rows : a.r1 - a.r0);
     const size_t out_row0 = static_cast<size_t>(blockIdx.z) * rows_total + static_cast<size_t>(row0 - a.r0);
 
     // four cells of one row: chord^2 in FP64, then either the straight-line tail (all four below the fast-path
@@ -246,15 +247,18 @@ int launch_unit_vectors(rt_engine *e, const double *lat_d, const double *lon_d, 
 
 // The same kernel on unit vectors whose component arrays are ld apart (the position-ordered vectors of a route
 // state): n x n cells per instance into rows of `pitch` cells.
-int launch_matrix_cells_ld(rt_engine *e, const double *xyz_d, int n, int ld, int batch, double dist_scale,
-                           double time_scale, int2 *cells_d, int pitch, cudaStream_t st)
+int launch_matrix_cells_ld(rt_engine *e, const double *xyz_d, int n, int ld, int batch, int r0, int r1,
+                           double dist_scale, double time_scale, int2 *cells_d, int pitch, cudaStream_t st)
 {
+    // rows [r0, r1) of every instance, written in place: row r of instance b lands at cells_d[(b*n + r) * pitch]
     MatArgs a{};
     a.xyz = xyz_d;
     a.n = n;
     a.ld = ld;
-    a.r0 = 0;
-    a.r1 = n;
+    a.r0 = r0;
+    a.r1 = r1;
+    a.out_rows = n;
+    cells_d += static_cast<size_t>(r0) * pitch;
     a.fd = static_cast<float>(RT_EARTH_RADIUS_M * dist_scale);
     a.ft = static_cast<float>(RT_EARTH_RADIUS_M * time_scale);
     a.lim_hi = fast_path_limit_hi(a.fd, a.ft);

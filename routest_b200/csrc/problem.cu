@@ -369,6 +369,7 @@ int rt_problem_set_routes(rt_problem *p, const int32_t *order, const int32_t *tr
         npos[b] = P;
     }
     p->pmax = *std::max_element(npos.begin(), npos.end());
+    p->pmin = *std::min_element(npos.begin(), npos.end());
     RT_TRY(ensure_position_matrix(p));
     RT_CUDA(e, cudaMemcpyAsync(p->node, node.data(), B * PS * 4, cudaMemcpyHostToDevice, e->stream));
     RT_CUDA(e, cudaMemcpyAsync(p->npos, npos.data(), B * 4, cudaMemcpyHostToDevice, e->stream));
@@ -513,7 +514,11 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     p->has_matrix = false;
     p->cells_from_coords = true;
     p->pmax = 0;
-    for (size_t b = 0; b < B; ++b) p->pmax = std::max(p->pmax, npos[b]);
+    p->pmin = npos[0];
+    for (size_t b = 0; b < B; ++b) {
+        p->pmax = std::max(p->pmax, npos[b]);
+        p->pmin = std::min(p->pmin, npos[b]);
+    }
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     RT_TRY(ensure_position_matrix(p));
@@ -530,6 +535,7 @@ int rt_problem_get_position_matrix(rt_problem *p, int instance, int32_t *dist, i
     if (!dist || !tim || instance < 0 || instance >= p->batch)
         return fail(e, RT_ERR_INVALID_ARG, "rt_problem_get_position_matrix: bad argument");
     if (!p->has_routes || !p->Gbuf.p) return fail(e, RT_ERR_STATE, "rt_problem_get_position_matrix: no routes set");
+    if (p->shard_count != 1) return fail(e, RT_ERR_STATE, "rt_problem_get_position_matrix needs shard 0/1");
     int P = 0;
     RT_CUDA(e, cudaMemcpy(&P, p->npos + instance, 4, cudaMemcpyDeviceToHost));
     const size_t cnt = static_cast<size_t>(P) * P;
@@ -548,12 +554,34 @@ int rt_problem_get_position_matrix(rt_problem *p, int instance, int32_t *dist, i
 
 int rt_problem_position_stride(const rt_problem *p) { return p ? p->pstride : 0; }
 
+// true when the rows of G this replica keeps fresh cover shard (index, count)
+static bool shard_covered(const rt_problem *p, int index, int count)
+{
+    return p->shard_count == 1 || (p->shard_count == count && p->shard_index == index);
+}
+
+int rt_problem_set_shard(rt_problem *p, int shard_index, int shard_count)
+{
+    RT_PROBLEM_GUARD(p);
+    if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count)
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_set_shard: bad argument");
+    p->shard_index = shard_index;
+    p->shard_count = shard_count;
+    if (p->has_routes) {
+        RT_TRY(state_refresh(p, e->stream));
+        RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    }
+    return RT_OK;
+}
+
 int rt_problem_eval_moves(rt_problem *p, int families, int shard_index, int shard_count, uint64_t *best_keys_out)
 {
     RT_PROBLEM_GUARD(p);
     if (!best_keys_out || shard_count < 1 || shard_index < 0 || shard_index >= shard_count || !(families & 7))
         return fail(e, RT_ERR_INVALID_ARG, "rt_problem_eval_moves: bad argument");
     if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_eval_moves: no routes set");
+    if (!shard_covered(p, shard_index, shard_count))
+        return fail(e, RT_ERR_STATE, "rt_problem_eval_moves: shard %d/%d is not the one set by rt_problem_set_shard", shard_index, shard_count);
     RT_TRY(eval_moves_launch(p, families, shard_index, shard_count, p->best, false, e->stream));
     RT_CUDA(e, cudaMemcpyAsync(best_keys_out, p->best, p->batch * 8, cudaMemcpyDeviceToHost, e->stream));
     RT_CUDA(e, cudaStreamSynchronize(e->stream));
@@ -568,6 +596,9 @@ int rt_problem_eval_moves_dev(rt_problem *p, int families, int shard_index, int 
     if (!best_keys_d || shard_count < 1 || shard_index < 0 || shard_index >= shard_count || !(families & 7))
         return fail(e, RT_ERR_INVALID_ARG, "rt_problem_eval_moves_dev: bad argument");
     if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_eval_moves_dev: no routes set");
+    if (!shard_covered(p, shard_index, shard_count))
+        return fail(e, RT_ERR_STATE, "rt_problem_eval_moves_dev: shard %d/%d is not the one set by rt_problem_set_shard",
+                    shard_index, shard_count);
     DeviceGuard dg(e->device);
     return eval_moves_launch(p, families, shard_index, shard_count, static_cast<unsigned long long *>(best_keys_d), true,
                              pick_stream(e, stream));
@@ -579,6 +610,7 @@ int rt_problem_eval_dump(rt_problem *p, int instance, int family, int32_t *delta
     if (!delta_out || !feas_out || instance < 0 || instance >= p->batch || family < 0 || family > 2)
         return fail(e, RT_ERR_INVALID_ARG, "rt_problem_eval_dump: bad argument");
     if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_eval_dump: no routes set");
+    if (p->shard_count != 1) return fail(e, RT_ERR_STATE, "rt_problem_eval_dump needs the whole route-order matrix (shard 0/1)");
     int P = 0;
     RT_CUDA(e, cudaMemcpy(&P, p->npos + instance, 4, cudaMemcpyDeviceToHost));
     const size_t cnt = static_cast<size_t>(P) * P;
@@ -633,6 +665,7 @@ int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t 
 {
     RT_PROBLEM_GUARD(p);
     if (!(families & 7) || max_moves < 0) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_local_search: bad argument");
+    if (p->shard_count != 1) return fail(e, RT_ERR_STATE, "rt_problem_local_search runs on an unsharded replica (shard 0/1)");
     if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_local_search: no routes set");
     RT_TRY(stage(p, static_cast<size_t>(p->batch) * 4));
     int *done_h = static_cast<int *>(p->host_stage);

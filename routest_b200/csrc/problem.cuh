@@ -47,7 +47,8 @@ struct rt_problem {
     double *PX = nullptr;                  // [batch][3][pstride] unit vectors in position order
     rt::DevBuf Gbuf;                       // position-space matrix G[batch][grows][gpitch], G[p][q] = M[node p][node q]
     int grows = 0, gpitch = 0;             // grows = pmax at the time G was sized
-    int pmax = 0;                          // max npos over the batch (host copy; sizes the move grids)
+    int pmax = 0, pmin = 0;                // max / min npos over the batch (host copies; size grids and shards)
+    int shard_index = 0, shard_count = 1;  // which part of the candidate space this replica evaluates (multi-GPU)
     bool walk_smem_opted = false;          // cudaFuncSetAttribute for the walk kernel's staging area done
     bool cells_from_coords = false;        // the matrix is SPEC §2 of this problem's coordinates
     int *Bv = nullptr, *Zv = nullptr, *route = nullptr, *rstart = nullptr;

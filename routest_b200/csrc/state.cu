@@ -8,8 +8,10 @@
 // the matrix kernel itself running on the position-ordered unit vectors (same cell function, so the same bits, at
 // the HBM write roofline); a caller-supplied matrix is permuted instead.  Every later access of the move kernels
 // — a row of G per moved stop, consecutive columns per insertion point — is then contiguous.
+#include <algorithm>
 #include <climits>
 
+#include "geometry.cuh"
 #include "problem.cuh"
 
 namespace rt {
@@ -37,9 +39,9 @@ __global__ void __launch_bounds__(256) position_vectors_kernel(const double *__r
 __global__ void __launch_bounds__(256) permute_matrix_kernel(const int2 *__restrict__ cells,
                                                              const int *__restrict__ node,
                                                              const int *__restrict__ npos, int n, int pitch,
-                                                             int pstride, int grows, int gpitch, int2 *__restrict__ G)
+                                                             int pstride, int grows, int gpitch, int row0, int2 *__restrict__ G)
 {
-    const int b = blockIdx.z, p = blockIdx.y;
+    const int b = blockIdx.z, p = row0 + blockIdx.y;
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= gpitch) return;
     const int P = npos[b];
@@ -49,23 +51,40 @@ __global__ void __launch_bounds__(256) permute_matrix_kernel(const int2 *__restr
         __ldg(&cells[static_cast<size_t>(b) * n * pitch + static_cast<size_t>(a) * pitch + c]);
 }
 
-// K1: everything that depends only on node[] — one thread per position.
-__global__ void __launch_bounds__(256) state_gather_kernel(const int2 *__restrict__ G, const int4 *__restrict__ stops,
-                                                           const int *__restrict__ node, const int *__restrict__ npos,
-                                                           int n, int pstride, int grows, int gpitch,
-                                                           int4 *__restrict__ RB, int2 *__restrict__ E,
-                                                           int2 *__restrict__ SK)
+// K1: everything that depends only on node[] — one thread per position.  The two cells a position needs (edge to the
+// successor, predecessor -> successor) are rebuilt from the position-ordered unit vectors (same cell function as the
+// matrix kernel) or, for a caller-supplied matrix, gathered from it; either way not from G, so a replica that builds
+// only its shard's rows of G still gets the state of every route.
+__global__ void __launch_bounds__(256) state_gather_kernel(const double *__restrict__ PX, const int2 *__restrict__ cells,
+                                                           const int4 *__restrict__ stops, const int *__restrict__ node,
+                                                           const int *__restrict__ npos, int n, int pitch, int pstride,
+                                                           float fd, float ft, int4 *__restrict__ RB,
+                                                           int2 *__restrict__ E, int2 *__restrict__ SK)
 {
     const int b = blockIdx.y;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     const int P = npos[b];
     if (p >= P) return;
-    const int2 *Gb = G + static_cast<size_t>(b) * grows * gpitch;
-    const int cur = node[static_cast<size_t>(b) * pstride + p];
+    const int *nd = node + static_cast<size_t>(b) * pstride;
+    const int cur = nd[p];
     const size_t o = static_cast<size_t>(b) * pstride + p;
     RB[o] = stops[static_cast<size_t>(b) * n + cur];
-    E[o] = p + 1 < P ? Gb[static_cast<size_t>(p) * gpitch + p + 1] : make_int2(0, 0);
-    SK[o] = (cur != 0) ? Gb[static_cast<size_t>(p - 1) * gpitch + p + 1] : make_int2(0, 0);
+    int2 e = make_int2(0, 0), sk = make_int2(0, 0);
+    if (PX) {
+        const double *px = PX + static_cast<size_t>(b) * 3 * pstride, *py = px + pstride, *pz = py + pstride;
+        if (p + 1 < P) {
+            e = cell_i32(px[p], py[p], pz[p], px[p + 1], py[p + 1], pz[p + 1], fd, ft);
+            if (cur != 0) sk = cell_i32(px[p - 1], py[p - 1], pz[p - 1], px[p + 1], py[p + 1], pz[p + 1], fd, ft);
+        }
+    } else {
+        const int2 *M = cells + static_cast<size_t>(b) * n * pitch;
+        if (p + 1 < P) {
+            e = M[static_cast<size_t>(cur) * pitch + nd[p + 1]];
+            if (cur != 0) sk = M[static_cast<size_t>(nd[p - 1]) * pitch + nd[p + 1]];
+        }
+    }
+    E[o] = e;
+    SK[o] = sk;
 }
 
 // K2: one block per instance.  (A) route ids by a block scan over the separators, (B) one thread per route walks
@@ -289,23 +308,31 @@ int ensure_position_matrix(rt_problem *p)
     return reserve(p->e, p->Gbuf, (static_cast<size_t>(p->batch) * rows * pitch + 16 + 2 * static_cast<size_t>(pitch)) * sizeof(int2));
 }
 
-// node[] -> G (route-order matrix).  Stream-ordered, no allocation (G is sized by ensure_position_matrix when routes
-// are installed).
+// node[] -> G (route-order matrix), rows of this replica's shard only (plus the halo rows the move kernels read).
+// Stream-ordered, no allocation (G is sized by ensure_position_matrix when routes are installed).
 int position_matrix_refresh(rt_problem *p, cudaStream_t st)
 {
     rt_engine *e = p->e;
     int2 *G = position_matrix(p);
     if (!p->Gbuf.p || p->grows <= 0) return fail(e, RT_ERR_STATE, "route state refresh before routes were installed");
+    // rows any instance of the batch can need: shard [P*i/c, P*(i+1)/c) over P in [pmin, pmax], one halo row each side
+    int r0 = 0, r1 = p->grows;
+    if (p->shard_count > 1) {
+        const long long lo = static_cast<long long>(p->pmin) * p->shard_index / p->shard_count - 1;
+        const long long hi = static_cast<long long>(p->pmax) * (p->shard_index + 1) / p->shard_count + 2;
+        r0 = static_cast<int>(std::max<long long>(lo, 0));
+        r1 = static_cast<int>(std::min<long long>(hi, p->grows));
+    }
     if (p->cells_from_coords) {
         dim3 g0((p->pstride + 255) / 256, p->batch);
         position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
         RT_CUDA(e, cudaGetLastError());
-        RT_TRY(launch_matrix_cells_ld(e, p->PX, p->grows, p->pstride, p->batch, p->dist_scale, p->time_scale, G,
+        RT_TRY(launch_matrix_cells_ld(e, p->PX, p->grows, p->pstride, p->batch, r0, r1, p->dist_scale, p->time_scale, G,
                                       p->gpitch, st));
     } else {
-        dim3 gp((p->gpitch + 255) / 256, p->grows, p->batch);
+        dim3 gp((p->gpitch + 255) / 256, r1 - r0, p->batch);
         permute_matrix_kernel<<<gp, 256, 0, st>>>(p->cells, p->node, p->npos, p->n, p->pitch, p->pstride, p->grows,
-                                                  p->gpitch, G);
+                                                  p->gpitch, r0, G);
         RT_CUDA(e, cudaGetLastError());
     }
     return RT_OK;
@@ -315,10 +342,11 @@ int position_matrix_refresh(rt_problem *p, cudaStream_t st)
 int state_tables_refresh(rt_problem *p, cudaStream_t st)
 {
     rt_engine *e = p->e;
-    const int2 *G = position_matrix(p);
     dim3 g1((p->grows + 255) / 256, p->batch);
-    state_gather_kernel<<<g1, 256, 0, st>>>(G, p->stops, p->node, p->npos, p->n, p->pstride, p->grows, p->gpitch, p->RB,
-                                            p->E, p->SK);
+    state_gather_kernel<<<g1, 256, 0, st>>>(p->cells_from_coords ? p->PX : nullptr, p->cells, p->stops, p->node, p->npos,
+                                            p->n, p->pitch, p->pstride,
+                                            static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale),
+                                            static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale), p->RB, p->E, p->SK);
     RT_CUDA(e, cudaGetLastError());
     // stage the walk's inputs in shared memory when an instance's positions fit (24 B each, <= 96 KB)
     const int staged = p->grows <= 4096 ? p->grows : 0;

@@ -43,6 +43,8 @@ class DistributedSearch:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.keys = torch.full((batch,), INT64_NONE, dtype=torch.int64, device=device)
+        if hasattr(problem, "set_shard"):  # the replica then keeps only its shard's rows of the route-order matrix fresh
+            problem.set_shard(self.rank, self.world)
 
     def _stream(self) -> int:
         return torch.cuda.current_stream().cuda_stream if self.keys.is_cuda else 0

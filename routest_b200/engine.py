@@ -440,6 +440,10 @@ class Problem:
         self._check(self._lib.rt_problem_plan_dev(self._p, float(dist_scale), float(time_scale), int(families),
                                                   keys_ptr, stream or None))
 
+    def set_shard(self, index: int, count: int):
+        """This replica evaluates part `index` of `count` of the candidate space (multi-GPU search)."""
+        self._check(self._lib.rt_problem_set_shard(self._p, int(index), int(count)))
+
     def eval_moves_dev(self, keys_ptr: int, families: int = ALL_FAMILIES, shard=(0, 1), stream: int = 0):
         self._check(self._lib.rt_problem_eval_moves_dev(self._p, int(families), int(shard[0]), int(shard[1]), keys_ptr,
                                                         stream or None))

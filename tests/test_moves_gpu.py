@@ -126,6 +126,31 @@ def test_best_move_batched_and_sharded(engine):
             assert np.array_equal(parts.min(axis=0), full)
 
 
+def test_replica_with_a_shard_keeps_only_its_rows_fresh(engine):
+    """rt_problem_set_shard: the refresh rebuilds just the shard's rows of the route-order matrix (what each rank of
+    a multi-GPU search does); every shard still finds its part of the best move, other shards are refused."""
+    from routest_b200 import EngineError
+    insts = [synth_vrptw(300 + b, 260, 9) for b in range(3)]
+    with _load(engine, insts) as pr:
+        full = pr.eval_moves()
+        for count in (2, 5):
+            parts = []
+            for i in range(count):
+                pr.set_shard(i, count)
+                parts.append(pr.eval_moves(shard=(i, count)))
+                with pytest.raises(EngineError):
+                    pr.eval_moves(shard=((i + 1) % count, count))
+            assert np.array_equal(np.stack(parts).min(axis=0), full)
+        with pytest.raises(EngineError):
+            pr.eval_dump(0, 1, insts[0][1].size)
+        pr.set_shard(0, 1)
+        assert np.array_equal(pr.eval_moves(), full)
+        # state tables do not depend on the shard
+        st = pr.get_state(1)
+        ref = O.route_state(insts[1][0], insts[1][1])
+        assert st["cost"] == ref["cost"] and np.array_equal(st["Z"], ref["Z"])
+
+
 def test_apply_moves_matches_oracle(engine):
     inst, node, raw = synth_vrptw(9, 90, 6)
     with _load(engine, [(inst, node, raw)]) as pr:
