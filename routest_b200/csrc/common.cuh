@@ -69,8 +69,9 @@ struct DeviceGuard {
 inline cudaStream_t pick_stream(rt_engine *, void *s) { return reinterpret_cast<cudaStream_t>(s); }
 
 // launchers implemented in matrix.cu
+// bad_flag_d (optional): set to 1 on the device when a coordinate is out of range or not finite
 int launch_unit_vectors(rt_engine *e, const double *lat_d, const double *lon_d, int n, int batch, double *xyz_d,
-                        cudaStream_t st);
+                        cudaStream_t st, int *bad_flag_d = nullptr);
 int launch_matrix_cells(rt_engine *e, const double *xyz_d, int n, int batch, int r0, int r1, double dist_scale,
                         double time_scale, int2 *cells_d, cudaStream_t st);
 int launch_matrix_cells_ld(rt_engine *e, const double *xyz_d, int n, int ld, int batch, int r0, int r1,

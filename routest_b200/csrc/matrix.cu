@@ -25,15 +25,21 @@ constexpr int kMinWaves = 10;
 
 __global__ void __launch_bounds__(256) unit_vectors_kernel(const double *__restrict__ lat,
                                                            const double *__restrict__ lon, int n, int total,
-                                                           double *__restrict__ xyz)
+                                                           double *__restrict__ xyz, int *__restrict__ bad_flag)
 {
     const double DEG = 0.017453292519943295;
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     int b = idx / n, i = idx - b * n;
+    double la = lat[idx], lo = lon[idx];
+    if (bad_flag && (!(la >= -90.0 && la <= 90.0) || !(lo >= -180.0 && lo <= 180.0))) {
+        *bad_flag = 1;  // out of range or not finite: reported by the host after the pass; the value is neutralised
+        la = 0.0;
+        lo = 0.0;
+    }
     double sp, cp, sl, cl;
-    det_sincos(lat[idx] * DEG, sp, cp);
-    det_sincos(lon[idx] * DEG, sl, cl);
+    det_sincos(la * DEG, sp, cp);
+    det_sincos(lo * DEG, sl, cl);
     double *o = xyz + static_cast<size_t>(b) * 3 * n;
     o[i] = cp * cl;
     o[n + i] = cp * sl;
@@ -234,13 +240,13 @@ int run_fast_sqrt_check(rt_engine *e, unsigned lo, unsigned hi, unsigned long lo
 }
 
 int launch_unit_vectors(rt_engine *e, const double *lat_d, const double *lon_d, int n, int batch, double *xyz_d,
-                        cudaStream_t st)
+                        cudaStream_t st, int *bad_flag_d)
 {
     const long long total = static_cast<long long>(n) * batch;
     if (total <= 0) return RT_OK;
     if (total > 0x7fffffffLL) return fail(e, RT_ERR_INVALID_ARG, "n*batch too large");
     unit_vectors_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(lat_d, lon_d, n,
-                                                                                    static_cast<int>(total), xyz_d);
+                                                                                    static_cast<int>(total), xyz_d, bad_flag_d);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }

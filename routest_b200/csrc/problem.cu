@@ -137,6 +137,7 @@ int rt_problem_create(rt_engine *e, int n, int batch, rt_problem **out)
     A(dev_alloc(p, p->best, B));
     A(dev_alloc(p, p->done, B));
     A(dev_alloc(p, p->moves, B));
+    A(dev_alloc(p, p->coord_flag, 1));
     A(dev_alloc(p, p->hist, B * p->hist_cap));
     A(dev_alloc(p, p->gkeys, B * n2));
     A(dev_alloc(p, p->gorder, B * n2));
@@ -487,14 +488,6 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
         return fail(e, RT_ERR_INVALID_ARG, "rt_problem_plan: bad argument");
     RT_TRY(check_scales(e, dist_scale, time_scale));
     const size_t B = p->batch, N = p->n, PS = p->pstride;
-    {   // branch-free scan (it vectorises): this runs on the request path of every plan call.  Stop records are
-        // taken as they are here (rt_problem_set_stops is the validating entry point); out-of-range values cannot
-        // fault a kernel, they only make the instance's result meaningless.
-        int bad_coord = 0;
-        for (size_t i = 0; i < B * N; ++i)
-            bad_coord |= !(lat[i] >= -90.0 && lat[i] <= 90.0) | !(lon[i] >= -180.0 && lon[i] <= 180.0);
-        if (bad_coord) return fail(e, RT_ERR_INVALID_ARG, "a coordinate is out of range or not finite");
-    }
     for (size_t b = 0; b < B; ++b)
         if (npos[b] < static_cast<int>(N) + 1 || npos[b] > static_cast<int>(PS) || node[b * PS] != 0 ||
             node[b * PS + npos[b] - 1] != 0)
@@ -507,7 +500,11 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, B * 8, cudaMemcpyHostToDevice, st));
     RT_CUDA(e, cudaMemcpyAsync(p->node, node, B * PS * 4, cudaMemcpyHostToDevice, st));
     RT_CUDA(e, cudaMemcpyAsync(p->npos, npos, B * 4, cudaMemcpyHostToDevice, st));
-    RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, st));
+    // Coordinates are range-checked by the unit-vector kernel (off the host's critical path); stop records are taken
+    // as they are (rt_problem_set_stops is the validating entry point) — out-of-range values cannot fault a kernel.
+    int *bad_flag = p->coord_flag;
+    RT_CUDA(e, cudaMemsetAsync(bad_flag, 0, 4, st));
+    RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, st, bad_flag));
     // the matrix of this pass is built in route order by the refresh below (state.cu); the node-order copy that
     // rt_problem_build_matrix keeps for the greedy and for rt_problem_get_matrix is not needed here
     p->has_coords = p->has_stops = p->has_routes = true;
@@ -524,8 +521,15 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     RT_TRY(ensure_position_matrix(p));
     RT_TRY(state_refresh(p, st));
     RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, st));
+    RT_TRY(stage(p, 8));
+    int *flag_h = static_cast<int *>(p->host_stage);
+    RT_CUDA(e, cudaMemcpyAsync(flag_h, bad_flag, 4, cudaMemcpyDeviceToHost, st));
     RT_CUDA(e, cudaMemcpyAsync(best_keys_out, p->best, B * 8, cudaMemcpyDeviceToHost, st));
     RT_CUDA(e, cudaStreamSynchronize(st));
+    if (*flag_h) {
+        p->has_coords = p->has_routes = false;
+        return fail(e, RT_ERR_INVALID_ARG, "a coordinate is out of range or not finite");
+    }
     return RT_OK;
 }
 

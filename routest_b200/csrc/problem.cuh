@@ -57,6 +57,7 @@ struct rt_problem {
     int *feasible = nullptr;               // [batch]
     unsigned long long *best = nullptr;    // [batch] packed keys (SPEC §7)
     int *done = nullptr, *moves = nullptr; // [batch] local-search bookkeeping
+    int *coord_flag = nullptr;             // [1] set by the unit-vector kernel on a bad coordinate (rt_problem_plan)
     unsigned long long *hist = nullptr;    // [batch][hist_cap] applied keys
     int hist_cap = 0;
     // greedy scratch

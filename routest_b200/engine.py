@@ -424,6 +424,30 @@ class Problem:
                                               int(families), _u64(keys)))
         return keys
 
+    def plan_call(self, lat, lon, stops, cap, max_dist, node, npos, out, *, dist_scale=DEFAULT_DIST_SCALE,
+                  time_scale=None, families: int = ALL_FAMILIES):
+        """`plan` for callers that reuse the same host buffers request after request: the arrays are checked and
+        their addresses taken once; the returned function makes exactly one C call per invocation and returns
+        `out`.  The buffers must keep their dtype, shape and address (fill them in place, e.g. pinned arrays)."""
+        if time_scale is None:
+            time_scale = time_scale_for_profile("driving-car")
+        spec = ((lat, np.float64, (self.batch, self.n)), (lon, np.float64, (self.batch, self.n)),
+                (stops, np.int32, (self.batch, self.n, 4)), (cap, np.int32, (self.batch,)),
+                (max_dist, np.int64, (self.batch,)), (node, np.int32, (self.batch, self.pstride)),
+                (npos, np.int32, (self.batch,)), (out, np.uint64, (self.batch,)))
+        for a, dt, shape in spec:
+            if not isinstance(a, np.ndarray) or a.dtype != dt or a.shape != shape or not a.flags.c_contiguous:
+                raise ValueError(f"plan_call needs C-contiguous {np.dtype(dt).name} arrays of shape {shape}")
+        fn, check, handle = self._lib.rt_problem_plan, self._check, self._p
+        args = (handle, _f64(lat), _f64(lon), _i32(stops), _i32(cap), _i64(max_dist), _i32(node), _i32(npos),
+                C.c_double(dist_scale), C.c_double(time_scale), C.c_int(families), _u64(out))
+        keep = (lat, lon, stops, cap, max_dist, node, npos, out)
+
+        def call(_keep=keep):
+            check(fn(*args))
+            return out
+        return call
+
     def build_matrix_dev(self, dist_scale=DEFAULT_DIST_SCALE, time_scale=None, stream: int = 0):
         if time_scale is None:
             time_scale = time_scale_for_profile("driving-car")

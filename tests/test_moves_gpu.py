@@ -126,6 +126,37 @@ def test_best_move_batched_and_sharded(engine):
             assert np.array_equal(parts.min(axis=0), full)
 
 
+def test_plan_from_host_buffers(engine):
+    """rt_problem_plan: host arrays in, best keys out, in one call — equals the step-by-step path and the oracle;
+    a bad coordinate is reported (the range check runs on the device, off the host's critical path)."""
+    from routest_b200 import EngineError
+    insts = [synth_vrptw(400 + b, 150, 6) for b in range(4)]
+    B, n = 4, 151
+    with engine.problem(n, B) as pr:
+        node = np.zeros((B, pr.pstride), np.int32)
+        npos = np.zeros(B, np.int32)
+        for b, (_, nd, _) in enumerate(insts):
+            node[b, :nd.size] = nd
+            npos[b] = nd.size
+        lat = np.stack([r["lat"] for _, _, r in insts])
+        lon = np.stack([r["lon"] for _, _, r in insts])
+        stops = np.stack([i.stops for i, _, _ in insts])
+        cap = np.array([i.cap for i, _, _ in insts], np.int32)
+        md = np.full(B, 2 ** 62, np.int64)
+        keys = pr.plan(lat, lon, stops, cap, md, node, npos, dist_scale=10.0, time_scale=TS_CAR)
+        for b, (inst, nd, _) in enumerate(insts):
+            assert int(keys[b]) == O.best_move(inst, nd)
+        out = np.zeros(B, np.uint64)
+        call = pr.plan_call(lat, lon, stops, cap, md, node, npos, out, dist_scale=10.0, time_scale=TS_CAR)
+        assert np.array_equal(call(), keys) and call() is out
+        lat[2, 7] = 91.0
+        with pytest.raises(EngineError) as ei:
+            call()
+        assert "coordinate" in str(ei.value)
+        lat[2, 7] = insts[2][2]["lat"][7]
+        assert np.array_equal(call(), keys)
+
+
 def test_replica_with_a_shard_keeps_only_its_rows_fresh(engine):
     """rt_problem_set_shard: the refresh rebuilds just the shard's rows of the route-order matrix (what each rank of
     a multi-GPU search does); every shard still finds its part of the best move, other shards are refused."""
