@@ -5,6 +5,7 @@
 // stop pairs; their feature rows are built in shared memory ([feature][slot] layout, so the data-dependent feature
 // index of a tree node is a conflict-free LDS), the ensemble streams through shared memory in chunks of whole trees,
 // and every pair accumulates its leaves in tree order in FP32 (bit-reproducible against the scalar evaluator).
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -27,6 +28,7 @@ struct EtaModel {
     TreeNode *nodes_d = nullptr;     // [offsets[n_trees]]
     int *chunk_first_d = nullptr;    // [n_chunks + 1] first tree of each shared-memory chunk
     int n_chunks = 0, total_nodes = 0;
+    int max_depth = 0;               // edges on the longest root-to-leaf path over all trees
 };
 
 namespace {
@@ -34,6 +36,7 @@ namespace {
 constexpr int kEtaThreads = 256;
 constexpr int kPairsPerThread = 4;
 constexpr int kFeatures = 12;
+constexpr int kFeatRows = kFeatures + 1;  // row 12 holds -inf: the feature a leaf "tests" so that it loops on itself
 constexpr int kChunkNodes = 6144;   // 48 KB of nodes per chunk + 48 KB of feature rows => 2 blocks per SM
 constexpr int kChunkTrees = 512;    // trees per chunk (their offsets sit in static shared memory)
 
@@ -66,22 +69,28 @@ __global__ void __launch_bounds__(kEtaThreads) eta_features_kernel(const double 
     for (int k = 0; k < kFeatures; ++k) rows[i * kFeatures + k] = f[k];
 }
 
+// Device copies of the nodes are re-encoded at load time so that the traversal needs no leaf test: a leaf points to
+// itself (left = own index) and tests feature row 12 (-inf), so "x < value" holds and it stays where it is.  Every
+// pair then takes exactly max_depth steps per tree; the four pairs of a thread advance in lock step (four
+// independent LDS chains in flight instead of one).  Rows with a NaN feature are rare and take the exact,
+// branchy walk (default directions) instead.
 __global__ void __launch_bounds__(kEtaThreads) eta_score_kernel(
     const double *__restrict__ dist_m, const unsigned char *__restrict__ weather,
     const unsigned char *__restrict__ traffic, const unsigned char *__restrict__ weekday,
     const unsigned char *__restrict__ hour, const float *__restrict__ age, long long n, float *__restrict__ out,
     const TreeNode *__restrict__ nodes, const unsigned *__restrict__ offsets, const int *__restrict__ chunk_first,
-    int n_chunks, float base)
+    int n_chunks, float base, int max_depth)
 {
     extern __shared__ __align__(16) unsigned char smem[];
-    float *sfeat = reinterpret_cast<float *>(smem);  // [kFeatures][kPairsPerThread * kEtaThreads]
+    float *sfeat = reinterpret_cast<float *>(smem);  // [kFeatRows][kPairsPerThread * kEtaThreads]
     constexpr int kSlots = kPairsPerThread * kEtaThreads;
-    TreeNode *snodes = reinterpret_cast<TreeNode *>(smem + sizeof(float) * kFeatures * kSlots);
+    TreeNode *snodes = reinterpret_cast<TreeNode *>(smem + sizeof(float) * kFeatRows * kSlots);
     __shared__ unsigned s_off[kChunkTrees + 1];  // node offset of every tree of the chunk
 
     const int tid = threadIdx.x;
     const long long base_i = static_cast<long long>(blockIdx.x) * kSlots;
     float acc[kPairsPerThread];
+    bool any_nan = false;
 #pragma unroll
     for (int j = 0; j < kPairsPerThread; ++j) {
         const int slot = j * kEtaThreads + tid;  // coalesced input loads
@@ -93,7 +102,11 @@ __global__ void __launch_bounds__(kEtaThreads) eta_score_kernel(
             for (int k = 0; k < kFeatures; ++k) f[k] = 0.f;
         }
 #pragma unroll
-        for (int k = 0; k < kFeatures; ++k) sfeat[k * kSlots + slot] = f[k];
+        for (int k = 0; k < kFeatures; ++k) {
+            sfeat[k * kSlots + slot] = f[k];
+            any_nan = any_nan || (f[k] != f[k]);
+        }
+        sfeat[kFeatures * kSlots + slot] = -INFINITY;
         acc[j] = base;
     }
 
@@ -108,20 +121,36 @@ __global__ void __launch_bounds__(kEtaThreads) eta_score_kernel(
             for (int k = tid; k <= t1 - t0; k += kEtaThreads) s_off[k] = offsets[t0 + k] - n0;
         }
         __syncthreads();
-        for (int t = 0; t < t1 - t0; ++t) {
-            const TreeNode *tr = snodes + s_off[t];
+        if (!any_nan) {
+            for (int t = 0; t < t1 - t0; ++t) {
+                const TreeNode *tr = snodes + s_off[t];
+                TreeNode nd[kPairsPerThread];
 #pragma unroll
-            for (int j = 0; j < kPairsPerThread; ++j) {
-                const int slot = j * kEtaThreads + tid;
-                unsigned k = 0;
-                TreeNode nd = tr[0];
-                while (!(nd.flags & 1)) {
-                    const float v = sfeat[nd.feature * kSlots + slot];
-                    const bool left = isnan(v) ? ((nd.flags >> 1) & 1) : (v < nd.value);
-                    k = nd.left + (left ? 0u : 1u);
-                    nd = tr[k];
+                for (int j = 0; j < kPairsPerThread; ++j) nd[j] = tr[0];
+                for (int d = 0; d < max_depth; ++d) {
+#pragma unroll
+                    for (int j = 0; j < kPairsPerThread; ++j) {
+                        const float v = sfeat[nd[j].feature * kSlots + j * kEtaThreads + tid];
+                        nd[j] = tr[nd[j].left + (v < nd[j].value ? 0u : 1u)];
+                    }
                 }
-                acc[j] += nd.value;
+#pragma unroll
+                for (int j = 0; j < kPairsPerThread; ++j) acc[j] += nd[j].value;
+            }
+        } else {
+            for (int t = 0; t < t1 - t0; ++t) {
+                const TreeNode *tr = snodes + s_off[t];
+#pragma unroll
+                for (int j = 0; j < kPairsPerThread; ++j) {
+                    const int slot = j * kEtaThreads + tid;
+                    TreeNode nd = tr[0];
+                    while (!(nd.flags & 1)) {
+                        const float v = sfeat[nd.feature * kSlots + slot];
+                        const bool left = isnan(v) ? ((nd.flags >> 1) & 1) : (v < nd.value);
+                        nd = tr[nd.left + (left ? 0u : 1u)];
+                    }
+                    acc[j] += nd.value;
+                }
             }
         }
     }
@@ -132,7 +161,7 @@ __global__ void __launch_bounds__(kEtaThreads) eta_score_kernel(
     }
 }
 
-constexpr size_t kEtaSmem = sizeof(float) * kFeatures * kPairsPerThread * kEtaThreads + sizeof(TreeNode) * kChunkNodes;
+constexpr size_t kEtaSmem = sizeof(float) * kFeatRows * kPairsPerThread * kEtaThreads + sizeof(TreeNode) * kChunkNodes;
 
 }  // namespace
 
@@ -154,6 +183,9 @@ int eta_model_load(rt_engine *e, const unsigned char *blob, size_t bytes)
     const size_t total = off[n_trees], hdr = 16 + 4 * static_cast<size_t>(n_trees + 1);
     if (off[0] != 0 || bytes < hdr + 8 * total) return fail(e, RT_ERR_INVALID_ARG, "model blob: truncated node table");
     const TreeNode *nodes = reinterpret_cast<const TreeNode *>(blob + hdr);
+    std::vector<TreeNode> dev_nodes(nodes, nodes + total);   // device encoding: leaves loop on themselves
+    std::vector<int> depth(total, 0);
+    int max_depth = 0;
     // validate every tree: offsets increasing, children inside the tree, features in range, every walk ends in a leaf
     std::vector<int> chunk_first{0};
     unsigned chunk_nodes = 0;
@@ -164,9 +196,17 @@ int eta_model_load(rt_engine *e, const unsigned char *blob, size_t bytes)
             return fail(e, RT_ERR_INVALID_ARG, "model blob: tree %u has %u nodes (limit %d)", t, cnt, kChunkNodes);
         for (unsigned k = 0; k < cnt; ++k) {
             const TreeNode &nd = nodes[off[t] + k];
-            if (nd.flags & 1) continue;
+            if (nd.flags & 1) {
+                if (!std::isfinite(nd.value)) return fail(e, RT_ERR_INVALID_ARG, "model blob: tree %u leaf %u is not finite", t, k);
+                TreeNode &dn = dev_nodes[off[t] + k];
+                dn.left = static_cast<unsigned short>(k);   // self loop
+                dn.feature = kFeatures;                     // the constant -inf row: "x < value" always holds
+                max_depth = std::max(max_depth, depth[off[t] + k]);
+                continue;
+            }
             if (nd.feature >= kFeatures || nd.left <= k || static_cast<unsigned>(nd.left) + 1 >= cnt)
                 return fail(e, RT_ERR_INVALID_ARG, "model blob: tree %u node %u is malformed", t, k);
+            depth[off[t] + nd.left] = depth[off[t] + nd.left + 1] = depth[off[t] + k] + 1;  // children come after parents
         }
         if (chunk_nodes + cnt > kChunkNodes || static_cast<size_t>(t - chunk_first.back()) + 1 > kChunkTrees) {
             chunk_first.push_back(static_cast<int>(t));
@@ -181,13 +221,14 @@ int eta_model_load(rt_engine *e, const unsigned char *blob, size_t bytes)
     m->n_features = static_cast<int>(n_feat);
     m->base = base;
     m->total_nodes = static_cast<int>(total);
+    m->max_depth = max_depth;
     m->n_chunks = static_cast<int>(chunk_first.size()) - 1;
     if (n_trees == 0) m->n_chunks = 0;
     cudaError_t st = cudaMalloc(&m->offsets_d, 4 * (n_trees + 1));
     if (st == cudaSuccess) st = cudaMalloc(&m->nodes_d, 8 * std::max<size_t>(total, 1));
     if (st == cudaSuccess) st = cudaMalloc(&m->chunk_first_d, 4 * chunk_first.size());
     if (st == cudaSuccess) st = cudaMemcpy(m->offsets_d, off.data(), 4 * (n_trees + 1), cudaMemcpyHostToDevice);
-    if (st == cudaSuccess && total) st = cudaMemcpy(m->nodes_d, nodes, 8 * total, cudaMemcpyHostToDevice);
+    if (st == cudaSuccess && total) st = cudaMemcpy(m->nodes_d, dev_nodes.data(), 8 * total, cudaMemcpyHostToDevice);
     if (st == cudaSuccess) st = cudaMemcpy(m->chunk_first_d, chunk_first.data(), 4 * chunk_first.size(), cudaMemcpyHostToDevice);
     if (st == cudaSuccess)
         st = cudaFuncSetAttribute(eta_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kEtaSmem));
@@ -227,7 +268,7 @@ int eta_score_launch(rt_engine *e, const double *dist_m, const unsigned char *we
     if (blocks > 0x7fffffffLL) return fail(e, RT_ERR_INVALID_ARG, "too many pairs for one launch");
     eta_score_kernel<<<static_cast<unsigned>(blocks), kEtaThreads, kEtaSmem, st>>>(
         dist_m, weather, traffic, weekday, hour, age, n, out, m->nodes_d, m->offsets_d, m->chunk_first_d, m->n_chunks,
-        m->base);
+        m->base, m->max_depth);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }
