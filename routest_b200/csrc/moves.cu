@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const Eval
     int best_d = INT_MAX;
     unsigned best_i = 0xFFFFFFFFu;  // family << 30 | p << 15 | q
     const int rows = min(kStripRows, p_hi - p0);
-    // Register window over three rows of G, loaded two rows ahead of use.  G carries a pad cell in front and two
+    // Register window over three rows of G, loaded two rows ahead of use.  G carries a pad cell in front and a dozen
     // pad rows behind (ensure_position_matrix), so q-1 / q+1 / p+2 need no clamping: whatever an out-of-range
     // neighbour holds is only ever combined into candidates that are not valid.
     const int2 *g = G + static_cast<size_t>(max(p0 - 1, 0)) * a.gpitch + qc;
@@ -167,6 +167,9 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const Eval
         const int p = p0 + rr;
         g += a.gpitch;
         const int2 m_lf = __ldg(g - 1), m_cur = __ldg(g), m_rt = __ldg(g + 1);
+        // the register window covers two rows; pull the row after next-but-eight towards L2 already (one lane per
+        // 128-byte line is enough)
+        if ((threadIdx.x & 15) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + 8 * static_cast<size_t>(a.gpitch)));
         const int2 c_dn = n_cur;
         const int4 Hp = sH[rr];
         if ((Hp.w >> 30) & 1) {  // p is a customer (warp-uniform)

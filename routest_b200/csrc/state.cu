@@ -304,8 +304,9 @@ int ensure_position_matrix(rt_problem *p)
     const int pitch = (rows + 15) & ~15;
     p->grows = rows;
     p->gpitch = pitch;
-    // 16 pad cells in front and two pad rows behind: the move kernels read q-1, q+1 and p+2 without clamping
-    return reserve(p->e, p->Gbuf, (static_cast<size_t>(p->batch) * rows * pitch + 16 + 2 * static_cast<size_t>(pitch)) * sizeof(int2));
+    // 16 pad cells in front and pad rows behind: the move kernels read q-1, q+1 and p+2 without clamping and
+    // prefetch up to ten rows ahead
+    return reserve(p->e, p->Gbuf, (static_cast<size_t>(p->batch) * rows * pitch + 16 + 12 * static_cast<size_t>(pitch)) * sizeof(int2));
 }
 
 // node[] -> G (route-order matrix), rows of this replica's shard only (plus the halo rows the move kernels read).
