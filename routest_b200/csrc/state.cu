@@ -87,62 +87,32 @@ __global__ void __launch_bounds__(256) state_gather_kernel(const double *__restr
     SK[o] = sk;
 }
 
-// K2: one block per instance.  (A) route ids by a block scan over the separators, (B) one thread per route walks
-// it forwards (B, load, distance) and backwards (Z), (C) the packed records.
-constexpr int kWalkThreads = 1024;
+// K2a: one block per instance — route ids by a block scan over the separators; resets the per-instance results.
+constexpr int kScanThreads = 1024;
 
-__global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
-    const int *__restrict__ node_all, const int *__restrict__ npos, int *__restrict__ nroutes_out, int n, int pstride,
-    int rstride, const int4 *__restrict__ stops_all, const int *__restrict__ cap_all,
-    const long long *__restrict__ maxd_all, const int4 *__restrict__ RB_all, const int2 *__restrict__ E_all,
-    const int2 *__restrict__ SK_all, int4 *__restrict__ RA_all, int4 *__restrict__ RC_all, int4 *__restrict__ RD_all,
-    int4 *__restrict__ H_all, int *__restrict__ Bv_all, int *__restrict__ Zv_all, int *__restrict__ route_all,
-    int *__restrict__ rstart_all, long long *__restrict__ rload_all, long long *__restrict__ rdist_all,
-    long long *__restrict__ cost_all, int *__restrict__ feasible_all, unsigned long long *__restrict__ best_all,
-    int staged_positions)
+__global__ void __launch_bounds__(kScanThreads) state_routes_kernel(const int *__restrict__ node_all,
+                                                                    const int *__restrict__ npos,
+                                                                    int *__restrict__ nroutes_out, int pstride,
+                                                                    int rstride, int *__restrict__ route_all,
+                                                                    int *__restrict__ rstart_all,
+                                                                    long long *__restrict__ cost_all,
+                                                                    int *__restrict__ feasible_all,
+                                                                    unsigned long long *__restrict__ best_all)
 {
-    // When the instance fits, its stop records and edge cells are staged in shared memory first (coalesced), so the
-    // sequential per-route walks run at shared-memory latency instead of paying an L2 round trip per position.
-    extern __shared__ __align__(16) unsigned char s_dyn[];
-    __shared__ int s_scan[kWalkThreads];
-    __shared__ int s_feas;
-    __shared__ unsigned long long s_cost;
-
+    __shared__ int s_scan[kScanThreads];
     const int b = blockIdx.x, tid = threadIdx.x;
     const int P = npos[b];
-    const size_t po = static_cast<size_t>(b) * pstride, ro = static_cast<size_t>(b) * rstride;
-    const int *node = node_all + po;
-    const int4 *RB = RB_all + po;
-    const int2 *E = E_all + po, *SK = SK_all + po;
-    const bool staged = staged_positions >= P;
-    int4 *sRB = reinterpret_cast<int4 *>(s_dyn);
-    int2 *sE = reinterpret_cast<int2 *>(s_dyn + sizeof(int4) * static_cast<size_t>(staged_positions));
-    if (staged)
-        for (int p = tid; p < P; p += kWalkThreads) {
-            sRB[p] = RB[p];
-            sE[p] = E[p];
-        }
-    const int4 *wRB = staged ? sRB : RB;   // what the walks read
-    const int2 *wE = staged ? sE : E;
-    int *Bv = Bv_all + po, *Zv = Zv_all + po, *route = route_all + po, *rstart = rstart_all + ro + b;  // rstride+1 each
-    long long *rload = rload_all + ro, *rdist = rdist_all + ro;
-    const int4 depot = stops_all[static_cast<size_t>(b) * n];
-    const int cap = cap_all[b];
-    const long long maxd = maxd_all[b];
-
-    if (tid == 0) {
-        s_feas = 1;
-        s_cost = 0;
-    }
-
-    // (A) route[p] = #separators at positions <= p, minus 1
-    const int chunk = (P + kWalkThreads - 1) / kWalkThreads;
+    const int *node = node_all + static_cast<size_t>(b) * pstride;
+    int *route = route_all + static_cast<size_t>(b) * pstride;
+    int *rstart = rstart_all + static_cast<size_t>(b) * (rstride + 1);
+    // route[p] = #separators at positions <= p, minus 1
+    const int chunk = (P + kScanThreads - 1) / kScanThreads;
     const int c0 = min(P, tid * chunk), c1 = min(P, c0 + chunk);
     int cnt = 0;
     for (int p = c0; p < c1; ++p) cnt += node[p] == 0;
     s_scan[tid] = cnt;
     __syncthreads();
-    for (int off = 1; off < kWalkThreads; off <<= 1) {  // Hillis-Steele inclusive scan
+    for (int off = 1; off < kScanThreads; off <<= 1) {  // Hillis-Steele inclusive scan
         int v = tid >= off ? s_scan[tid - off] : 0;
         __syncthreads();
         s_scan[tid] += v;
@@ -156,85 +126,139 @@ __global__ void __launch_bounds__(kWalkThreads) state_walk_kernel(
         }
         route[p] = r;
     }
-    const int R = s_scan[kWalkThreads - 1] - 1;
-    if (tid == 0) nroutes_out[b] = R;
-    __syncthreads();
+    if (tid == 0) {
+        nroutes_out[b] = s_scan[kScanThreads - 1] - 1;
+        cost_all[b] = 0;
+        feasible_all[b] = 1;
+        best_all[b] = kNoMove;
+    }
+}
 
-    // (B) walks
+// K2b: one warp per route.  The recurrences for B (forwards) and Z (backwards) are sequential, but their inputs are
+// not: each lane loads one position of a 32-position chunk (coalesced), then the warp replays the chunk in order
+// from registers via shuffles — no dependent memory round trip per position.
+constexpr int kWalkWarps = 4;
+
+__global__ void __launch_bounds__(kWalkWarps * 32) state_walk_kernel(
+    const int *__restrict__ npos, int n, int pstride, int rstride, const int4 *__restrict__ stops_all,
+    const int *__restrict__ cap_all, const long long *__restrict__ maxd_all, const int4 *__restrict__ RB_all,
+    const int2 *__restrict__ E_all, int *__restrict__ Bv_all, int *__restrict__ Zv_all,
+    const int *__restrict__ rstart_all, long long *__restrict__ rload_all, long long *__restrict__ rdist_all,
+    long long *__restrict__ cost_all, int *__restrict__ feasible_all)
+{
+    const int b = blockIdx.y, lane = threadIdx.x & 31;
+    const int rr = blockIdx.x * kWalkWarps + (threadIdx.x >> 5);
+    const int P = npos[b];
+    const int R = P - n;
+    if (rr >= R) return;
+    const size_t po = static_cast<size_t>(b) * pstride, ro = static_cast<size_t>(b) * rstride;
+    const int4 *RB = RB_all + po;
+    const int2 *E = E_all + po;
+    int *Bv = Bv_all + po, *Zv = Zv_all + po;
+    const int *rstart = rstart_all + ro + b;
+    const int4 depot = stops_all[static_cast<size_t>(b) * n];
+    const int s = rstart[rr], e = rstart[rr + 1];
+    const unsigned full = 0xffffffffu;
+
+    int Bcur = depot.x, svc_prev = depot.z;
+    long long load = 0, dist = 0;
     bool feas = true;
-    unsigned long long cost = 0;
-    for (int rr = tid; rr < R; rr += kWalkThreads) {
-        const int s = rstart[rr], e = rstart[rr + 1];
-        int Bcur = depot.x, svc_prev = depot.z;
-        long long load = 0, dist = 0;
+    for (int base = s + 1; base < e; base += 32) {
+        const int p = base + lane;
+        const bool in = p < e;
+        const int4 rb = in ? RB[p] : make_int4(0, 0, 0, 0);
+        const int2 ed = in ? E[p - 1] : make_int2(0, 0);
+        const int cntc = min(32, e - base);
+        int myB = 0;
+        for (int k = 0; k < cntc; ++k) {
+            const int ready = __shfl_sync(full, rb.x, k), due = __shfl_sync(full, rb.y, k);
+            const int svc = __shfl_sync(full, rb.z, k), dem = __shfl_sync(full, rb.w, k);
+            const int ed_d = __shfl_sync(full, ed.x, k), ed_t = __shfl_sync(full, ed.y, k);
+            Bcur = max(ready, Bcur + svc_prev + ed_t);
+            feas = feas && Bcur <= due;
+            if (k == lane) myB = Bcur;
+            svc_prev = svc;
+            load += dem;
+            dist += ed_d;
+        }
+        if (in) Bv[p] = myB;
+    }
+    const int2 last = E[e - 1];
+    feas = feas && (Bcur + svc_prev + last.y <= depot.y);
+    dist += last.x;
+    feas = feas && load <= cap_all[b] && dist <= maxd_all[b];
+
+    int Zn = depot.y;
+    for (int top = e - 1; top > s; top -= 32) {  // chunk [top-31, top], replayed from the highest position down
+        const int p = top - lane;
+        const bool in = p > s;
+        const int4 rb = in ? RB[p] : make_int4(0, 0, 0, 0);
+        const int2 ed = in ? E[p] : make_int2(0, 0);
+        const int cntc = min(32, top - s);
+        int myZ = 0;
+        for (int k = 0; k < cntc; ++k) {
+            const int due = __shfl_sync(full, rb.y, k), svc = __shfl_sync(full, rb.z, k);
+            const int ed_t = __shfl_sync(full, ed.y, k);
+            Zn = min(due, Zn - ed_t - svc);
+            if (k == lane) myZ = Zn;
+        }
+        if (in) Zv[p] = myZ;
+    }
+    if (lane == 0) {
         Bv[s] = depot.x;
         Zv[s] = depot.y;
-        for (int p = s + 1; p < e; ++p) {
-            const int2 ed = wE[p - 1];
-            const int4 rb = wRB[p];
-            Bcur = max(rb.x, Bcur + svc_prev + ed.y);
-            feas = feas && Bcur <= rb.y;
-            Bv[p] = Bcur;
-            svc_prev = rb.z;
-            load += rb.w;
-            dist += ed.x;
+        if (rr == R - 1) {
+            Bv[P - 1] = depot.x;
+            Zv[P - 1] = depot.y;
         }
-        const int2 last = wE[e - 1];
-        feas = feas && (Bcur + svc_prev + last.y <= depot.y);
-        dist += last.x;
-        rload[rr] = load;
-        rdist[rr] = dist;
-        feas = feas && load <= cap && dist <= maxd;
-        cost += static_cast<unsigned long long>(dist);
-        int Zn = depot.y;
-        for (int p = e - 1; p > s; --p) {
-            const int4 rb = wRB[p];
-            Zn = min(rb.y, Zn - wE[p].y - rb.z);
-            Zv[p] = Zn;
-        }
+        rload_all[ro + rr] = load;
+        rdist_all[ro + rr] = dist;
+        atomicAdd(reinterpret_cast<unsigned long long *>(cost_all + b), static_cast<unsigned long long>(dist));
+        if (!feas) feasible_all[b] = 0;
     }
-    if (tid == 0) {
-        Bv[P - 1] = depot.x;
-        Zv[P - 1] = depot.y;
-    }
-    if (!feas) s_feas = 0;
-    if (cost) atomicAdd(&s_cost, cost);
-    __syncthreads();
+}
 
-    // (C) records
-    int4 *RA = RA_all + po, *RC = RC_all + po, *RD = RD_all + po, *H = H_all + po;
-    for (int p = tid; p < P; p += kWalkThreads) {
-        const int rt_ = route[p];
-        const int4 rb = RB[p];
-        const int2 ed = E[p], sk = SK[p];
-        const int dep = Bv[p] + rb.z;
-        const int zn = p + 1 < P ? Zv[p + 1] : depot.y;
-        RA[p] = make_int4(dep, zn, ed.x, rt_);
-        // slacks are clamped to [-2^29, 2^30]: wide enough to compare against any demand / delta (both < 2^30 in
-        // magnitude), narrow enough that "slack - value" never overflows in the move kernels
-        constexpr long long kLo = -(1LL << 29), kHi = 1LL << 30;
-        int capsl = -1, dsl = static_cast<int>(kLo);
-        if (rt_ < R) {
-            capsl = static_cast<int>(max(kLo, min(kHi, static_cast<long long>(cap) - rload[rt_])));
-            dsl = static_cast<int>(max(kLo, min(kHi, maxd - rdist[rt_])));
-        }
-        RD[p] = make_int4(capsl, dsl, ed.y, sk.y);
-        if (node[p] != 0) {
-            const int2 ep = E[p - 1];
-            const int dep_prev = Bv[p - 1] + RB[p - 1].z;
-            const int rem_delta = sk.x - ep.x - ed.x;
-            const bool rem_ok = dep_prev + sk.y <= zn && rem_delta <= dsl;
-            RC[p] = make_int4(dep_prev, rem_delta, ep.x + ed.x, 1 | (rem_ok ? 2 : 0));
-            H[p] = make_int4(rem_delta, ep.x + ed.x, ed.x, rt_ | (1 << 30));
-        } else {
-            RC[p] = make_int4(0, 0, 0, 0);
-            H[p] = make_int4(0, 0, ed.x, rt_);
-        }
+// K2c: the packed per-position records, one thread per position.
+__global__ void __launch_bounds__(256) state_records_kernel(
+    const int *__restrict__ node_all, const int *__restrict__ npos, int n, int pstride, int rstride,
+    const int4 *__restrict__ stops_all, const int *__restrict__ cap_all, const long long *__restrict__ maxd_all,
+    const int4 *__restrict__ RB_all, const int2 *__restrict__ E_all, const int2 *__restrict__ SK_all,
+    const int *__restrict__ Bv_all, const int *__restrict__ Zv_all, const int *__restrict__ route_all,
+    const long long *__restrict__ rload_all, const long long *__restrict__ rdist_all, int4 *__restrict__ RA_all,
+    int4 *__restrict__ RC_all, int4 *__restrict__ RD_all, int4 *__restrict__ H_all)
+{
+    const int b = blockIdx.y;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int P = npos[b];
+    if (p >= P) return;
+    const int R = P - n;
+    const size_t po = static_cast<size_t>(b) * pstride, ro = static_cast<size_t>(b) * rstride, o = po + p;
+    const int4 depot = stops_all[static_cast<size_t>(b) * n];
+    const int rt_ = route_all[o];
+    const int4 rb = RB_all[o];
+    const int2 ed = E_all[o], sk = SK_all[o];
+    const int dep = Bv_all[o] + rb.z;
+    const int zn = p + 1 < P ? Zv_all[o + 1] : depot.y;
+    RA_all[o] = make_int4(dep, zn, ed.x, rt_);
+    // slacks are clamped to [-2^29, 2^30]: wide enough to compare against any demand / delta (both < 2^30 in
+    // magnitude), narrow enough that "slack - value" never overflows in the move kernels
+    constexpr long long kLo = -(1LL << 29), kHi = 1LL << 30;
+    int capsl = -1, dsl = static_cast<int>(kLo);
+    if (rt_ < R) {
+        capsl = static_cast<int>(max(kLo, min(kHi, static_cast<long long>(cap_all[b]) - rload_all[ro + rt_])));
+        dsl = static_cast<int>(max(kLo, min(kHi, maxd_all[b] - rdist_all[ro + rt_])));
     }
-    if (tid == 0) {
-        cost_all[b] = static_cast<long long>(s_cost);
-        feasible_all[b] = s_feas;
-        best_all[b] = kNoMove;
+    RD_all[o] = make_int4(capsl, dsl, ed.y, sk.y);
+    if (node_all[o] != 0) {
+        const int2 ep = E_all[o - 1];
+        const int dep_prev = Bv_all[o - 1] + RB_all[o - 1].z;
+        const int rem_delta = sk.x - ep.x - ed.x;
+        const bool rem_ok = dep_prev + sk.y <= zn && rem_delta <= dsl;
+        RC_all[o] = make_int4(dep_prev, rem_delta, ep.x + ed.x, 1 | (rem_ok ? 2 : 0));
+        H_all[o] = make_int4(rem_delta, ep.x + ed.x, ed.x, rt_ | (1 << 30));
+    } else {
+        RC_all[o] = make_int4(0, 0, 0, 0);
+        H_all[o] = make_int4(0, 0, ed.x, rt_);
     }
 }
 
@@ -349,17 +373,18 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st)
                                             static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale),
                                             static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale), p->RB, p->E, p->SK);
     RT_CUDA(e, cudaGetLastError());
-    // stage the walk's inputs in shared memory when an instance's positions fit (24 B each, <= 96 KB)
-    const int staged = p->grows <= 4096 ? p->grows : 0;
-    const size_t walk_smem = static_cast<size_t>(staged) * (sizeof(int4) + sizeof(int2));
-    if (walk_smem > 48 * 1024 && !p->walk_smem_opted) {
-        RT_CUDA(e, cudaFuncSetAttribute(state_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        p->walk_smem_opted = true;
-    }
-    state_walk_kernel<<<p->batch, kWalkThreads, walk_smem, st>>>(p->node, p->npos, p->nroutes, p->n, p->pstride, p->rstride,
-                                                         p->stops, p->cap, p->max_dist, p->RB, p->E, p->SK, p->RA, p->RC,
-                                                         p->RD, p->H, p->Bv, p->Zv, p->route, p->rstart, p->rload,
-                                                         p->rdist, p->cost, p->feasible, p->best, staged);
+    state_routes_kernel<<<p->batch, kScanThreads, 0, st>>>(p->node, p->npos, p->nroutes, p->pstride, p->rstride, p->route,
+                                                           p->rstart, p->cost, p->feasible, p->best);
+    RT_CUDA(e, cudaGetLastError());
+    const int rmax = std::max(1, p->grows - p->n);  // most routes of any instance
+    dim3 gw((rmax + kWalkWarps - 1) / kWalkWarps, p->batch);
+    state_walk_kernel<<<gw, kWalkWarps * 32, 0, st>>>(p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap, p->max_dist,
+                                                      p->RB, p->E, p->Bv, p->Zv, p->rstart, p->rload, p->rdist, p->cost,
+                                                      p->feasible);
+    RT_CUDA(e, cudaGetLastError());
+    state_records_kernel<<<g1, 256, 0, st>>>(p->node, p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap,
+                                             p->max_dist, p->RB, p->E, p->SK, p->Bv, p->Zv, p->route, p->rload, p->rdist,
+                                             p->RA, p->RC, p->RD, p->H);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }

@@ -1,0 +1,108 @@
+"""North-star configuration: ONE 10,000-stop VRPTW instance, matrix rows and move neighbourhood sharded across the
+ranks, one NCCL MIN all-reduce of the best-move key per pass (BASELINE.json configs[3]).  Strong scaling.
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29533 \
+      tools/bench_10k.py --stops 10000 --steps 20
+A pass = every rank rebuilds its rows of the route-order matrix (+ the replicated route state), scores its shard
+of the full 2-opt/relocate/swap neighbourhood, and the ranks all-reduce one int64 key.  Timed with CUDA events on
+the launching stream, max over ranks.  Rank 0 also times the CPU oracle on the same instance (all host threads).
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from bench import DIST_SCALE, TS_CAR, count_candidates, synth_coords, synth_windows  # noqa: E402
+from routest_b200 import ALL_FAMILIES, Engine  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--stops", type=int, default=10000)
+    ap.add_argument("--vehicles", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--cpu", action="store_true", help="rank 0 also times the CPU oracle on the same pass")
+    a = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    eng = Engine(local)
+    n = a.stops + 1
+    lat, lon, demand, cap = synth_coords(4567, a.stops, a.vehicles)
+    pr = eng.problem(n, 1)
+    pr.set_coords(lat, lon)
+    pr.build_matrix(DIST_SCALE, TS_CAR)
+    _, t = pr.get_matrix(0)
+    st = np.zeros((1, n, 4), np.int32)
+    st[0, :, :3] = synth_windows(4567, t[0, 1:], t[1:, 0])
+    st[0, :, 3] = demand
+    pr.set_stops(st, [cap])
+    trips, status = pr.greedy(demand[None].astype(float), [float(cap)], use_tw=True)
+    assert status[0] == 0
+    pr.set_routes(trips)
+    pr.set_shard(rank, world)
+    P = n + len(trips[0])
+    keys = torch.empty(1, dtype=torch.int64, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        pr.refresh_dev(3, s)                                   # this rank's rows of the matrix + route state
+        pr.eval_moves_dev(keys.data_ptr(), ALL_FAMILIES, (rank, world), s)
+        if world > 1:
+            dist.all_reduce(keys, op=dist.ReduceOp.MIN)
+
+    for _ in range(5):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / a.steps], device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    best = int(keys.item())
+    if rank == 0:
+        cand = count_candidates(trips[0], n)
+        evals = sum(cand.values())
+        line = {"workload": f"one {a.stops}-stop VRPTW instance ({len(trips[0])} routes, P = {P}), rows and neighbourhood "
+                            f"sharded over {world} GPU(s), one NCCL MIN all-reduce per pass",
+                "n_gpus": world, "ms_per_pass": ms, "matrix_cells_per_s": P * P / ms * 1e3,
+                "move_evals_per_s": evals / ms * 1e3, "cells_per_pass": P * P, "move_evals_per_pass": evals,
+                "best_key": best & (2 ** 64 - 1)}
+        if a.cpu:
+            from oracle import oracle as O
+            th = O.num_threads()
+            t0 = time.perf_counter()
+            m = O.matrix_rows(O.unit_vectors(lat, lon), 0, n, DIST_SCALE, TS_CAR, threads=th)
+            t1 = time.perf_counter()
+            inst = O.Instance(m["dist"], m["time"], st[0], cap)
+            node = O.build_positions(trips[0], n)
+            k = O.best_move(inst, node, threads=th)
+            t2 = time.perf_counter()
+            line["cpu"] = {"threads": th, "matrix_s": t1 - t0, "best_move_s": t2 - t1,
+                           "matrix_cells_per_s": n * n / (t1 - t0), "move_evals_per_s": evals / (t2 - t1),
+                           "same_best_move": (k ^ (1 << 63)) == (best & (2 ** 64 - 1))}
+            line["speedup_vs_cpu"] = {"pass": (t2 - t0) / (ms / 1e3)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
