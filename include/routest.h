@@ -135,8 +135,10 @@ int rt_problem_set_coords(rt_problem *p, const double *lat, const double *lon);
 int rt_problem_set_stops(rt_problem *p, const int32_t *stops, const int32_t *cap, const int64_t *max_dist);
 /* Builds every instance's matrix on the device (same arithmetic as rt_matrix_build). */
 int rt_problem_build_matrix(rt_problem *p, double dist_scale, double time_scale);
-/* Installs a caller-supplied matrix for one instance (dense n x n int32 planes).  Must be symmetric: the move
- * kernels read M[a][b] where M[b][a] is meant. */
+/* Installs a caller-supplied matrix for one instance (dense n x n int32 planes, entries in [0, 2^29)) — what the
+ * reference holds after utils.py:103, integerised by the caller.  It may be directional (road networks are): the
+ * greedy reads D[cur][idx] and D[idx][0] in that orientation (utils.py:128) and the move kernels then keep a
+ * transposed route-order copy next to the forward one. */
 int rt_problem_set_matrix(rt_problem *p, int instance, const int32_t *dist, const int32_t *time);
 int rt_problem_get_matrix(rt_problem *p, int instance, int32_t *dist, int32_t *time);
 

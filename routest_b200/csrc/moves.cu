@@ -16,7 +16,10 @@
 // reduce it to one 64-bit atomicMin per block.  The minimum of packed keys is order independent, so the chosen
 // move does not depend on the thread, block or GPU partition.
 //
-// The matrix is assumed symmetric here (true for SPEC.md §2 matrices): G[a][b] is read where G[b][a] is meant.
+// ASYM: a caller-supplied matrix may be directional (road networks are).  The kernels then read a second array,
+// GT[p][q] = M[node q][node p], wherever a cell is needed in the "towards p" orientation, so every access stays
+// row-contiguous; for a symmetric matrix (SPEC.md §2 always is) GT is G and the extra loads disappear at compile
+// time.
 #include <climits>
 
 #include "problem.cuh"
@@ -69,7 +72,9 @@ __device__ __forceinline__ void block_min_to_global(unsigned long long best, uns
 }
 
 struct EvalArgs {
-    const int2 *G;         // [batch][grows][gpitch] route-order matrix
+    const int2 *G;         // [batch][grows][gpitch] route-order matrix, G[p][q] = M[node p][node q]
+    const int2 *GT;        // its transpose GT[p][q] = M[node q][node p] (asymmetric matrices only)
+    const int2 *ER;        // ER[p] = M[node p+1][node p], the edge after p driven backwards (asymmetric only)
     int grows, gpitch;
     const int *node;
     const int *npos;
@@ -96,8 +101,8 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
 // feasible one while being infeasible (capacity, windows), so pruning on the delta leaves almost every warp with
 // some lane in the slow path; computing delta AND feasibility for every candidate without a branch is cheaper.
 // Per row three broadcast LDS.128 bring everything about p; everything about q lives in registers.
-template <bool DUMP>
-__global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const EvalArgs a)
+template <bool DUMP, bool ASYM>
+__global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 8) eval_inter_kernel(const EvalArgs a)
 {
     __shared__ int4 sH[kStripRows];   // {rem_delta, oe, -, route | customer << 30 | rem_ok << 29}
     __shared__ int4 sP1[kStripRows];  // {ready, due, service, demand}
@@ -162,6 +167,16 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const Eval
     int2 c_lf = __ldg(g - 1), c_cur = __ldg(g), c_rt = __ldg(g + 1);
     g += a.gpitch;
     int2 n_lf = __ldg(g - 1), n_cur = __ldg(g), n_rt = __ldg(g + 1);
+    // the same window over GT (cells towards p): only (row, q-1) and (row, q) are ever needed
+    const int2 *gt = ASYM ? a.GT + static_cast<size_t>(b) * a.grows * a.gpitch + static_cast<size_t>(p0) * a.gpitch + qc : g;
+    int2 t_lf = c_lf, t_cur = c_cur, tn_lf = n_lf, tn_cur = n_cur;
+    if (ASYM) {
+        t_lf = __ldg(gt - 1);
+        t_cur = __ldg(gt);
+        gt += a.gpitch;
+        tn_lf = __ldg(gt - 1);
+        tn_cur = __ldg(gt);
+    }
 #pragma unroll 2
     for (int rr = 0; rr < rows; ++rr) {
         const int p = p0 + rr;
@@ -170,15 +185,23 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const Eval
         // the register window covers two rows; pull the row after next-but-eight towards L2 already (one lane per
         // 128-byte line is enough)
         if ((threadIdx.x & 15) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + 8 * static_cast<size_t>(a.gpitch)));
+        int2 tm_lf = m_lf, tm_cur = m_cur;
+        if (ASYM) {
+            gt += a.gpitch;
+            tm_lf = __ldg(gt - 1);
+            tm_cur = __ldg(gt);
+        }
         const int2 c_dn = n_cur;
+        // orientation: a_* are the cells that lead towards p's side (a -> u, v -> nu, pw -> u)
+        const int2 a_cur = ASYM ? t_cur : c_cur, a_lf = ASYM ? t_lf : c_lf, a_dn = ASYM ? tn_cur : c_dn;
         const int4 Hp = sH[rr];
         if ((Hp.w >> 30) & 1) {  // p is a customer (warp-uniform)
             const int4 p1 = sP1[rr], p2 = sP2[rr];
             const bool other = (Hp.w & 0x7FFF) != q_route;
             // relocate(p -> between q and q+1): a -> u -> b replaces a -> b in route[q]
-            const int ins = fadd(fadd(c_cur.x, c_rt.x), -Hq.z);
+            const int ins = fadd(fadd(a_cur.x, c_rt.x), -Hq.z);
             const int d_rel = fadd(Hp.x, ins);
-            const int tu = max(p1.x, fadd(dep_q, c_cur.y));
+            const int tu = max(p1.x, fadd(dep_q, a_cur.y));
             const bool v_rel = rel_q && other;
             const bool ok_rel = v_rel && ((Hp.w >> 29) & 1) && p1.w <= capsl_q && ins <= distsl_q && tu <= p1.y &&
                                 fadd(fadd(tu, p1.z), c_rt.y) <= zn_q;
@@ -196,15 +219,15 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const Eval
             }
             if (swap_tile) {
                 // swap(p, q), p < q: pu -> v -> nu in route[p], pw -> u -> nw in route[q]
-                const int d1 = fadd(fadd(c_up.x, c_dn.x), -Hp.y);
-                const int d2 = fadd(fadd(c_lf.x, c_rt.x), -Hq.y);
+                const int d1 = fadd(fadd(c_up.x, a_dn.x), -Hp.y);
+                const int d2 = fadd(fadd(a_lf.x, c_rt.x), -Hq.y);
                 const int d_swap = fadd(d1, d2);
                 const int tv = max(qB.x, fadd(p2.y, c_up.y));
-                const int tw = max(p1.x, fadd(depprev_q, c_lf.y));
+                const int tw = max(p1.x, fadd(depprev_q, a_lf.y));
                 const int dd = fadd(qB.w, -p1.w);
                 const bool v_swap = swap_q && other && p < q;
                 const bool ok_swap = v_swap && dd <= p2.z && -dd <= capsl_q && d1 <= p2.w && d2 <= distsl_q &&
-                                     tv <= qB.y && fadd(fadd(tv, qB.z), c_dn.y) <= p2.x && tw <= p1.y &&
+                                     tv <= qB.y && fadd(fadd(tv, qB.z), a_dn.y) <= p2.x && tw <= p1.y &&
                                      fadd(fadd(tw, p1.z), c_rt.y) <= zn_q;
                 if (DUMP) {
                     if (v_swap && a.dump_family == 2) {
@@ -227,6 +250,10 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_kernel(const Eval
         n_lf = m_lf;
         n_cur = m_cur;
         n_rt = m_rt;
+        t_lf = tn_lf;
+        t_cur = tn_cur;
+        tn_lf = tm_lf;
+        tn_cur = tm_cur;
     }
     if (!DUMP) {
         const unsigned long long best =
@@ -265,7 +292,7 @@ __device__ __forceinline__ bool seg_fits(const Seg &m, int t, int tail, int limi
 
 constexpr int kIntraThreads = 128;
 
-template <bool DUMP>
+template <bool DUMP, bool ASYM>
 __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArgs a)
 {
     const int b = DUMP ? a.dump_instance : blockIdx.y;
@@ -295,13 +322,21 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
         const int2 *row_m = G + static_cast<size_t>(max(t - 1, 0)) * a.gpitch;
         const int2 *row_0 = G + static_cast<size_t>(t) * a.gpitch;
         const int2 *row_p = G + static_cast<size_t>(t + 1) * a.gpitch;
+        // asymmetric matrices: the cells that lead from x back to t / t+1 come from the transposed array
+        const int2 *GTb = ASYM ? a.GT + static_cast<size_t>(b) * a.grows * a.gpitch : G;
+        const int2 *trow_0 = GTb + static_cast<size_t>(t) * a.gpitch;
+        const int2 *trow_p = GTb + static_cast<size_t>(t + 1) * a.gpitch;
+        const int2 *ER = ASYM ? a.ER + po : E;
         const bool f2 = a.families & 1, f_rel = a.families & 2, f_swap = a.families & 4;
 
         // cells of rows node[t-1], node[t], node[t+1] at column node[x]: start at x = t+1
         int2 cm = SKt, c0 = Et, cp = make_int2(0, 0);
-        int2 c0_prev = make_int2(0, 0);  // c0 at x-1
+        // r0 = cell(node x, node t), rp = cell(node x, node t+1): equal to c0 / cp when the matrix is symmetric
+        int2 r0 = ASYM ? ER[t] : Et, rp = make_int2(0, 0), r0_prev = make_int2(0, 0);
         Seg F = Seg{0, 0, 0, true}, Rv = Seg{0, 0, 0, true};
         int svc_xm1 = 0, Et_xm1 = 0;  // service[node x-1], T[node x-1][node x]
+        int Er_xm1 = 0;               // T[node x][node x-1]
+        int asym = 0;                 // sum over the inner edges of (reversed - forward) distance, for 2-opt
 
         for (int x = t + 1; x < P; ++x) {
             const int nx = node[x];
@@ -313,14 +348,16 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
             const int2 cm1 = __ldg(row_m + x + 1);
             const int2 c01 = __ldg(row_0 + x + 1);
             const int2 cp1 = __ldg(row_p + x + 1);
+            const int2 r01 = ASYM ? __ldg(trow_0 + x + 1) : c01;
+            const int2 rp1 = ASYM ? __ldg(trow_p + x + 1) : cp1;
             const Seg sx = seg_single(xB.x, xB.y);
 
-            // reversed segment node[x..t+1]: prepend x
-            Rv = (x == t + 1) ? sx : seg_concat(sx, xB.z + Et_xm1, Rv);
+            // reversed segment node[x..t+1]: prepend x (it is entered over the edge x -> x-1)
+            Rv = (x == t + 1) ? sx : seg_concat(sx, xB.z + (ASYM ? Er_xm1 : Et_xm1), Rv);
 
             // (A) 2-opt(t, x)
             if (f2 && x >= t + 2) {
-                const int d = c0.x + cp1.x - Et.x - Ex.x;
+                const int d = c0.x + cp1.x - Et.x - Ex.x + asym;
                 const bool ok = d <= dslack && seg_fits(Rv, dep_t + c0.y, t1B.z + cp1.y, zn);
                 if (DUMP) {
                     if (a.dump_family == 0) {
@@ -336,8 +373,8 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
                 // (B) relocate(t -> after x): prefix(..t-1) + F + [x] + [t] + suffix(x+1..)
                 if (t_cust) {
                     Seg m = (x == t + 1) ? sx : seg_concat(F, svc_xm1 + Et_xm1, sx);
-                    m = seg_concat(m, xB.z + c0.y, seg_single(tB.x, tB.y));
-                    const int d = tC.y + c0.x + c01.x - Ex.x;
+                    m = seg_concat(m, xB.z + r0.y, seg_single(tB.x, tB.y));
+                    const int d = tC.y + r0.x + c01.x - Ex.x;
                     const bool ok = d <= dslack && seg_fits(m, dep_tm1 + SKt.y, tB.z + c01.y, zn);
                     if (DUMP) {
                         if (a.dump_family == 1) {
@@ -351,8 +388,8 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
                 }
                 // (C) relocate(x -> after t): prefix(..t) + [x] + F + suffix(x+1..)
                 if (x >= t + 2) {
-                    const Seg m = seg_concat(sx, xB.z + cp.y, F);
-                    const int d = xC.y + c0.x + cp.x - Et.x;
+                    const Seg m = seg_concat(sx, xB.z + rp.y, F);
+                    const int d = xC.y + c0.x + rp.x - Et.x;
                     const bool ok = d <= dslack && seg_fits(m, dep_t + c0.y, svc_xm1 + xD.w, zn);
                     if (DUMP) {
                         if (a.dump_family == 1) {
@@ -370,12 +407,12 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
                 Seg m;
                 int d;
                 if (x == t + 1) {
-                    m = seg_concat(sx, xB.z + Et.y, seg_single(tB.x, tB.y));
-                    d = cm.x + c01.x - (tC.z - Et.x) - Ex.x;  // pv->x + x->t + t->nxt - pv->t - t->x - x->nxt
+                    m = seg_concat(sx, xB.z + r0.y, seg_single(tB.x, tB.y));
+                    d = cm.x + r0.x + c01.x - tC.z - Ex.x;  // pv->x + x->t + t->nxt - (pv->t + t->x) - x->nxt
                 } else {
-                    m = seg_concat(sx, xB.z + cp.y, F);
-                    m = seg_concat(m, svc_xm1 + c0_prev.y, seg_single(tB.x, tB.y));
-                    d = cm.x + cp.x - tC.z + c0_prev.x + c01.x - xC.z;
+                    m = seg_concat(sx, xB.z + rp.y, F);
+                    m = seg_concat(m, svc_xm1 + r0_prev.y, seg_single(tB.x, tB.y));
+                    d = cm.x + rp.x - tC.z + r0_prev.x + c01.x - xC.z;
                 }
                 const bool ok = d <= dslack && seg_fits(m, dep_tm1 + cm.y, tB.z + c01.y, zn);
                 if (DUMP) {
@@ -392,10 +429,17 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
             F = (x == t + 1) ? sx : seg_concat(F, svc_xm1 + Et_xm1, sx);
             svc_xm1 = xB.z;
             Et_xm1 = Ex.y;
-            c0_prev = c0;
+            if (ASYM) {
+                const int2 er = ER[x];  // cell(node x+1, node x)
+                Er_xm1 = er.y;
+                asym += er.x - Ex.x;
+            }
+            r0_prev = r0;
             cm = cm1;
             c0 = c01;
             cp = cp1;
+            r0 = r01;
+            rp = rp1;
         }
     }
     if (!DUMP) block_min_to_global<kIntraThreads>(best, a.best + b);
@@ -405,6 +449,8 @@ EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count
 {
     EvalArgs a{};
     a.G = position_matrix(p);
+    a.GT = position_matrix_t(p);
+    a.ER = p->ER;
     a.grows = p->grows;
     a.gpitch = p->gpitch;
     a.node = p->node;
@@ -453,12 +499,14 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
     if (families & 6) {
         dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + kStripRows - 1) / kStripRows, p->batch);
-        eval_inter_kernel<false><<<grid, kInterThreads, 0, st>>>(a);
+        if (p->symmetric) eval_inter_kernel<false, false><<<grid, kInterThreads, 0, st>>>(a);
+        else eval_inter_kernel<false, true><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     {
         dim3 grid((shard_rows + kIntraThreads - 1) / kIntraThreads, p->batch);
-        eval_intra_kernel<false><<<grid, kIntraThreads, 0, st>>>(a);
+        if (p->symmetric) eval_intra_kernel<false, false><<<grid, kIntraThreads, 0, st>>>(a);
+        else eval_intra_kernel<false, true><<<grid, kIntraThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     finish_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, best_d, p->batch, signed_keys ? 1 : 0);
@@ -477,11 +525,13 @@ int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsi
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
     if (family != 0) {
         dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (pmax + kStripRows - 1) / kStripRows, 1);
-        eval_inter_kernel<true><<<grid, kInterThreads, 0, st>>>(a);
+        if (p->symmetric) eval_inter_kernel<true, false><<<grid, kInterThreads, 0, st>>>(a);
+        else eval_inter_kernel<true, true><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     dim3 grid((pmax + kIntraThreads - 1) / kIntraThreads, 1);
-    eval_intra_kernel<true><<<grid, kIntraThreads, 0, st>>>(a);
+    if (p->symmetric) eval_intra_kernel<true, false><<<grid, kIntraThreads, 0, st>>>(a);
+    else eval_intra_kernel<true, true><<<grid, kIntraThreads, 0, st>>>(a);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }

@@ -126,6 +126,7 @@ int rt_problem_create(rt_engine *e, int n, int batch, rt_problem **out)
     A(dev_alloc(p, p->PX, B * 3 * PS));
     A(dev_alloc(p, p->E, B * PS));
     A(dev_alloc(p, p->SK, B * PS));
+    A(dev_alloc(p, p->ER, B * PS));
     A(dev_alloc(p, p->Bv, B * PS));
     A(dev_alloc(p, p->Zv, B * PS));
     A(dev_alloc(p, p->route, B * PS));
@@ -166,6 +167,7 @@ void rt_problem_destroy(rt_problem *p)
     cudaStreamSynchronize(e->stream);
     for (int i = 0; i < p->n_allocs; ++i) cudaFree(p->all_allocs[i]);
     if (p->Gbuf.p) cudaFree(p->Gbuf.p);
+    if (p->GTbuf.p) cudaFree(p->GTbuf.p);
     if (p->host_stage) cudaFreeHost(p->host_stage);
     delete p;
 }
@@ -221,6 +223,8 @@ int rt_problem_build_matrix(rt_problem *p, double dist_scale, double time_scale)
     p->time_scale = time_scale;
     p->has_matrix = true;
     p->cells_from_coords = true;
+    p->symmetric = true;
+    p->supplied = 0;
     return RT_OK;
 }
 
@@ -233,11 +237,14 @@ int rt_problem_set_matrix(rt_problem *p, int instance, const int32_t *dist, cons
     for (size_t i = 0; i < cnt; ++i)
         if (dist[i] < 0 || tim[i] < 0 || dist[i] >= (1 << 29) || tim[i] >= (1 << 29))
             return fail(e, RT_ERR_INVALID_ARG, "matrix entries must lie in [0, 2^29)");
-    for (int i = 0; i < p->n; ++i)
+    bool sym = true;
+    for (int i = 0; i < p->n && sym; ++i)
         for (int j = 0; j < i; ++j)
             if (dist[static_cast<size_t>(i) * p->n + j] != dist[static_cast<size_t>(j) * p->n + i] ||
-                tim[static_cast<size_t>(i) * p->n + j] != tim[static_cast<size_t>(j) * p->n + i])
-                return fail(e, RT_ERR_INVALID_ARG, "the move kernels need a symmetric matrix (cell %d,%d differs)", i, j);
+                tim[static_cast<size_t>(i) * p->n + j] != tim[static_cast<size_t>(j) * p->n + i]) {
+                sym = false;
+                break;
+            }
     RT_TRY(reserve(e, e->plane_a[0], cnt * 4));
     RT_TRY(reserve(e, e->plane_b[0], cnt * 4));
     int *dd = static_cast<int *>(e->plane_a[0].p), *td = static_cast<int *>(e->plane_b[0].p);
@@ -249,7 +256,15 @@ int rt_problem_set_matrix(rt_problem *p, int instance, const int32_t *dist, cons
     RT_CUDA(e, cudaGetLastError());
     RT_CUDA(e, cudaStreamSynchronize(e->stream));
     p->has_matrix = true;
+    // one flag for the whole batch: the first installed matrix decides, later ones may only clear it
+    p->symmetric = (p->cells_from_coords || p->supplied == 0) ? sym : (p->symmetric && sym);
     p->cells_from_coords = false;
+    ++p->supplied;
+    if (p->has_routes) {  // routes installed earlier refer to the old matrix
+        RT_TRY(ensure_position_matrix(p));
+        RT_TRY(state_refresh(p, e->stream));
+        RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    }
     return RT_OK;
 }
 

@@ -45,6 +45,10 @@ struct rt_problem {
     int4 *RA = nullptr, *RB = nullptr, *RC = nullptr, *RD = nullptr, *H = nullptr;
     int2 *E = nullptr, *SK = nullptr;
     double *PX = nullptr;                  // [batch][3][pstride] unit vectors in position order
+    rt::DevBuf GTbuf;                      // its transpose (only for asymmetric caller-supplied matrices)
+    int2 *ER = nullptr;                    // [batch][pstride] cell(node p+1, node p) (asymmetric only)
+    int supplied = 0;                      // matrices installed with rt_problem_set_matrix since the last build
+    bool symmetric = true;                 // the stored matrix is symmetric (always true for SPEC §2 matrices)
     rt::DevBuf Gbuf;                       // position-space matrix G[batch][grows][gpitch], G[p][q] = M[node p][node q]
     int grows = 0, gpitch = 0;             // grows = pmax at the time G was sized
     int pmax = 0, pmin = 0;                // max / min npos over the batch (host copies; size grids and shards)
@@ -75,6 +79,7 @@ namespace rt {
 
 // first cell of G (the buffer starts with 16 pad cells)
 inline int2 *position_matrix(const rt_problem *p) { return p->Gbuf.p ? static_cast<int2 *>(p->Gbuf.p) + 16 : nullptr; }
+inline int2 *position_matrix_t(const rt_problem *p) { return p->GTbuf.p ? static_cast<int2 *>(p->GTbuf.p) + 16 : nullptr; }
 
 int state_refresh(rt_problem *p, cudaStream_t st);
 int position_matrix_refresh(rt_problem *p, cudaStream_t st);

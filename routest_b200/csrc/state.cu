@@ -39,7 +39,8 @@ __global__ void __launch_bounds__(256) position_vectors_kernel(const double *__r
 __global__ void __launch_bounds__(256) permute_matrix_kernel(const int2 *__restrict__ cells,
                                                              const int *__restrict__ node,
                                                              const int *__restrict__ npos, int n, int pitch,
-                                                             int pstride, int grows, int gpitch, int row0, int2 *__restrict__ G)
+                                                             int pstride, int grows, int gpitch, int row0, int transpose,
+                                                             int2 *__restrict__ G)
 {
     const int b = blockIdx.z, p = row0 + blockIdx.y;
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
@@ -47,8 +48,9 @@ __global__ void __launch_bounds__(256) permute_matrix_kernel(const int2 *__restr
     const int P = npos[b];
     const int *nd = node + static_cast<size_t>(b) * pstride;
     const int a = p < P ? nd[p] : 0, c = q < P ? nd[q] : 0;
+    const int from = transpose ? c : a, to = transpose ? a : c;
     G[(static_cast<size_t>(b) * grows + p) * gpitch + q] =
-        __ldg(&cells[static_cast<size_t>(b) * n * pitch + static_cast<size_t>(a) * pitch + c]);
+        __ldg(&cells[static_cast<size_t>(b) * n * pitch + static_cast<size_t>(from) * pitch + to]);
 }
 
 // K1: everything that depends only on node[] — one thread per position.  The two cells a position needs (edge to the
@@ -59,7 +61,8 @@ __global__ void __launch_bounds__(256) state_gather_kernel(const double *__restr
                                                            const int4 *__restrict__ stops, const int *__restrict__ node,
                                                            const int *__restrict__ npos, int n, int pitch, int pstride,
                                                            float fd, float ft, int4 *__restrict__ RB,
-                                                           int2 *__restrict__ E, int2 *__restrict__ SK)
+                                                           int2 *__restrict__ E, int2 *__restrict__ SK,
+                                                           int2 *__restrict__ ER)
 {
     const int b = blockIdx.y;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -81,6 +84,9 @@ __global__ void __launch_bounds__(256) state_gather_kernel(const double *__restr
         if (p + 1 < P) {
             e = M[static_cast<size_t>(cur) * pitch + nd[p + 1]];
             if (cur != 0) sk = M[static_cast<size_t>(nd[p - 1]) * pitch + nd[p + 1]];
+            if (ER) ER[o] = M[static_cast<size_t>(nd[p + 1]) * pitch + cur];
+        } else if (ER) {
+            ER[o] = make_int2(0, 0);
         }
     }
     E[o] = e;
@@ -330,6 +336,8 @@ int ensure_position_matrix(rt_problem *p)
     p->gpitch = pitch;
     // 16 pad cells in front and pad rows behind: the move kernels read q-1, q+1 and p+2 without clamping and
     // prefetch up to ten rows ahead
+    if (!p->symmetric)
+        RT_TRY(reserve(p->e, p->GTbuf, (static_cast<size_t>(p->batch) * rows * pitch + 16 + 12 * static_cast<size_t>(pitch)) * sizeof(int2)));
     return reserve(p->e, p->Gbuf, (static_cast<size_t>(p->batch) * rows * pitch + 16 + 12 * static_cast<size_t>(pitch)) * sizeof(int2));
 }
 
@@ -357,8 +365,13 @@ int position_matrix_refresh(rt_problem *p, cudaStream_t st)
     } else {
         dim3 gp((p->gpitch + 255) / 256, r1 - r0, p->batch);
         permute_matrix_kernel<<<gp, 256, 0, st>>>(p->cells, p->node, p->npos, p->n, p->pitch, p->pstride, p->grows,
-                                                  p->gpitch, r0, G);
+                                                  p->gpitch, r0, 0, G);
         RT_CUDA(e, cudaGetLastError());
+        if (!p->symmetric) {
+            permute_matrix_kernel<<<gp, 256, 0, st>>>(p->cells, p->node, p->npos, p->n, p->pitch, p->pstride, p->grows,
+                                                      p->gpitch, r0, 1, position_matrix_t(p));
+            RT_CUDA(e, cudaGetLastError());
+        }
     }
     return RT_OK;
 }
@@ -371,7 +384,8 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st)
     state_gather_kernel<<<g1, 256, 0, st>>>(p->cells_from_coords ? p->PX : nullptr, p->cells, p->stops, p->node, p->npos,
                                             p->n, p->pitch, p->pstride,
                                             static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale),
-                                            static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale), p->RB, p->E, p->SK);
+                                            static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale), p->RB, p->E, p->SK,
+                                            p->symmetric ? nullptr : p->ER);
     RT_CUDA(e, cudaGetLastError());
     state_routes_kernel<<<p->batch, kScanThreads, 0, st>>>(p->node, p->npos, p->nroutes, p->pstride, p->rstride, p->route,
                                                            p->rstart, p->cost, p->feasible, p->best);

@@ -130,11 +130,17 @@ def _multi_stop(source, destinations, profile_type, driver_details, *, engine=No
         if not distance_matrix:
             return {"error": "ORS matrix returned no distances"}                  # utils.py:104-105
         eng = eng or get_engine()
-        trips, infeasible = eng.greedy_trips(np.asarray(distance_matrix, dtype=np.float64), demand, cap, max_dist)
-        if infeasible:
-            return {"error": _infeasible_message(trips, n)}
         if _wants_extension(destinations, driver_details):
-            return {"error": "time windows / improve need the engine's own matrix (no matrix_fn)"}
+            # windows / improvement on the service's (possibly directional) matrix, integerised like the engine's own
+            res = _solve_on_supplied_matrix(eng, distance_matrix, mres.get("durations"), profile_type, demand, cap,
+                                            max_dist, destinations, driver_details)
+            if "error" in res:
+                return res
+            trips = res["trips"]
+        else:
+            trips, infeasible = eng.greedy_trips(np.asarray(distance_matrix, dtype=np.float64), demand, cap, max_dist)
+            if infeasible:
+                return {"error": _infeasible_message(trips, n)}
     else:
         eng = eng or get_engine()
         res = _solve_on_device(eng, all_points, profile_type, demand, cap, max_dist, destinations, driver_details)
@@ -209,17 +215,10 @@ def _solve_on_device(eng, all_points, profile_type, demand, cap, max_dist, desti
         pr.build_matrix(ds, ts)
         md_units = min(max_dist * ds, 9e18)
         if extended:
-            horizon = int(driver_details.get("shift_end", 43200))
-            stops = np.zeros((1, n, 4), np.int32)
-            stops[0, 0] = (0, horizon, 0, 0)
-            for i, d in enumerate(destinations, start=1):
-                dem = float(d.get("payload", 0))
-                if dem != int(dem) or dem < 0:
-                    return {"error": "time windows / improve need non-negative integer payloads"}
-                stops[0, i] = (int(d.get("tw_start", 0)), int(d.get("tw_end", horizon)), int(d.get("service_time", 0)),
-                               int(dem))
-            icap = int(min(cap, 2 ** 31 - 1))
-            pr.set_stops(stops, [icap], [int(min(md_units, 2 ** 62))])
+            stops = _stop_records(n, destinations, driver_details, demand)
+            if stops is None:
+                return {"error": "time windows / improve need non-negative integer payloads"}
+            pr.set_stops(stops, [int(min(cap, 2 ** 28))], [int(min(md_units, 2 ** 62))])
         trips, status = pr.greedy(demand[None, :], [cap], [md_units], use_tw=extended)
         if status[0] == N.RT_ERR_INFEASIBLE_STOP:
             return {"error": _infeasible_message(trips[0], n)}
@@ -232,6 +231,51 @@ def _solve_on_device(eng, all_points, profile_type, demand, cap, max_dist, desti
     finally:
         pr.close()
     return {"trips": trips, "offline": _OfflineDirections(eng, profile_type, lat=lat, lon=lon, D=D, T=T, ds=ds)}
+
+
+def _stop_records(n, destinations, driver_details, demand):
+    horizon = int(driver_details.get("shift_end", 43200))
+    stops = np.zeros((1, n, 4), np.int32)
+    stops[0, 0] = (0, horizon, 0, 0)
+    for i, d in enumerate(destinations, start=1):
+        dem = float(demand[i])
+        if dem != int(dem) or dem < 0:
+            return None
+        stops[0, i] = (int(d.get("tw_start", 0)), int(d.get("tw_end", horizon)), int(d.get("service_time", 0)), int(dem))
+    return stops
+
+
+def _solve_on_supplied_matrix(eng, distance_matrix, durations, profile_type, demand, cap, max_dist, destinations,
+                              driver_details):
+    """Windows / local search on a matrix a service answered with (utils.py:97-103): metres -> integer distance units
+    (x10, like the engine's own matrix), seconds from `durations` when the service sent them, else distance / profile
+    speed.  The matrix may be directional."""
+    D = np.asarray(distance_matrix, dtype=np.float64)
+    n = D.shape[0]
+    ds = DEFAULT_DIST_SCALE
+    Di = np.rint(D * ds)
+    Ti = np.rint(np.asarray(durations, dtype=np.float64)) if durations else np.rint(D * time_scale_for_profile(profile_type))
+    if D.shape != (n, n) or Ti.shape != (n, n) or not np.isfinite(Di).all() or Di.min() < 0 or Di.max() >= 2 ** 29:
+        return {"error": "matrix not usable: need a square matrix of finite, non-negative distances below 53,000 km"}
+    stops = _stop_records(n, destinations, driver_details, demand)
+    if stops is None:
+        return {"error": "time windows / improve need non-negative integer payloads"}
+    pr = eng.problem(n, 1)
+    try:
+        pr.set_matrix(0, Di.astype(np.int32), Ti.astype(np.int32))
+        md_units = min(max_dist * ds, 9e18)
+        pr.set_stops(stops, [int(min(cap, 2 ** 28))], [int(min(md_units, 2 ** 62))])
+        trips, status = pr.greedy(demand[None, :], [cap], [md_units], use_tw=True)
+        if status[0] == N.RT_ERR_INFEASIBLE_STOP:
+            return {"error": _infeasible_message(trips[0], n)}
+        trips = trips[0]
+        if driver_details.get("improve"):
+            pr.set_routes([trips])
+            pr.local_search()
+            trips = [t for t in pr.get_routes()[0] if t]
+    finally:
+        pr.close()
+    return {"trips": trips}
 
 
 class _OfflineDirections:

@@ -90,28 +90,49 @@ def test_distance_limit_flags(engine):
             assert np.array_equal(f, fr) and np.array_equal(d[fr != 2], dr[fr != 2])
 
 
-def test_caller_supplied_symmetric_matrix(engine):
-    """A matrix that is not great-circle (the ORS case): installed through rt_problem_set_matrix."""
-    inst, node, raw = synth_vrptw(8, 40, 4)
-    rng = np.random.default_rng(8)
+def _perturbed(inst, seed, asymmetric):
+    rng = np.random.default_rng(seed)
     bump = rng.integers(0, 300, inst.D.shape).astype(np.int32)
-    bump = np.triu(bump, 1)
-    D = inst.D + bump + bump.T
-    T = inst.T + (bump + bump.T) // 10
-    alt = O.Instance(D, T, inst.stops, inst.cap)
-    if not O.route_state(alt, node)["feasible"]:
-        pytest.skip("perturbed instance lost feasibility of the start")
+    if asymmetric:
+        np.fill_diagonal(bump, 0)
+        D, T = inst.D + bump, inst.T + bump // 10
+    else:
+        bump = np.triu(bump, 1)
+        D, T = inst.D + bump + bump.T, inst.T + (bump + bump.T) // 10
+    return O.Instance(D, T, inst.stops, inst.cap, inst.max_dist)
+
+
+@pytest.mark.parametrize("asymmetric", [False, True], ids=["symmetric", "asymmetric"])
+def test_caller_supplied_matrix(engine, asymmetric):
+    """A matrix that is not great-circle (the ORS case: road distances, directional), installed through
+    rt_problem_set_matrix: every candidate straight against brute force, then the search against the oracle."""
+    inst, node, raw = synth_vrptw(8, 60, 5)
+    alt = _perturbed(inst, 8, asymmetric)
+    assert (alt.D != alt.D.T).any() == asymmetric
+    # a feasible start on the new matrix: the oracle's window-aware greedy
+    rc, trips = O.greedy_trips(alt.D, raw["demand"].astype(float), float(raw["cap"]), 9e12, T=alt.T, tw=raw["tw"])
+    assert rc == 0
+    node = O.build_positions(trips, alt.n)
+    assert O.route_state(alt, node)["feasible"]
     with _load(engine, [(alt, node, raw)]) as pr:
-        pr.set_matrix(0, D, T)
-        pr.set_routes([O.positions_to_trips(node)])
+        pr.set_matrix(0, alt.D, alt.T)
+        d, t = pr.get_matrix(0)
+        assert np.array_equal(d, alt.D) and np.array_equal(t, alt.T)
+        g_trips, status = pr.greedy(raw["demand"][None].astype(float), [float(raw["cap"])], use_tw=True)
+        assert status[0] == 0 and g_trips[0] == trips          # construction reads the matrix in the right direction
+        pr.set_routes([trips])
+        st = pr.get_state(0)
+        ref = O.route_state(alt, node)
+        assert st["cost"] == ref["cost"] and np.array_equal(st["B"], ref["B"]) and np.array_equal(st["Z"], ref["Z"])
         for fam in (0, 1, 2):
-            d, f = pr.eval_dump(0, fam, node.size)
+            dd, ff = pr.eval_dump(0, fam, node.size)
             dr, fr = O.eval_bruteforce(alt, node, fam)
-            assert np.array_equal(f, fr) and np.array_equal(d[fr != 2], dr[fr != 2])
-        from routest_b200 import EngineError
-        D[1, 2] += 1
-        with pytest.raises(EngineError):
-            pr.set_matrix(0, D, T)
+            assert np.array_equal(ff, fr), f"flags, family {fam}"
+            assert np.array_equal(dd[fr != 2], dr[fr != 2]), f"deltas, family {fam}"
+        final, keys, cost = O.local_search(alt, node, threads=O.num_threads())
+        moves, gcost, gkeys = pr.local_search(keys_capacity=4 * alt.n)
+        assert moves[0] == len(keys) and np.array_equal(gkeys[0], keys) and gcost[0] == cost
+        assert np.array_equal(pr.get_state(0)["node"], final)
 
 
 def test_best_move_batched_and_sharded(engine):

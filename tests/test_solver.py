@@ -117,3 +117,34 @@ def test_time_windows_and_improve_extension(engine):
         stops[i] = (d["tw_start"], d["tw_end"], d["service_time"])
     rc, trips = O.greedy_trips(m["dist"], demand.astype(float), float(cap), 9e13, T=m["time"], tw=stops)
     assert rc == 0 and base["properties"]["optimized_order"] == [i - 1 for t in trips for i in t]
+
+
+@pytest.mark.gpu
+def test_improve_on_a_directional_service_matrix(engine):
+    """Optional fields with a matrix hook: the service's (asymmetric) matrix is integerised, windows are honoured
+    and the local search runs on it; same trips as the oracle on the same integer matrix."""
+    rng = np.random.default_rng(3)
+    n = 41
+    base = rng.uniform(500, 12000, (n, n))
+    D = np.round(base + rng.uniform(0, 900, (n, n)), 1)        # directional
+    np.fill_diagonal(D, 0.0)
+    body = {"source_point": {"lat": 14.58, "lon": 121.04},
+            "destination_points": [{"lat": 14.40 + 0.005 * i, "lon": 120.97 + 0.003 * i, "payload": int(rng.integers(1, 5)),
+                                    "tw_start": 0, "tw_end": 43200, "service_time": 120} for i in range(n - 1)],
+            "driver_details": {"vehicle_type": "car", "vehicle_capacity": 18, "improve": True}}
+    hooks = dict(matrix_fn=lambda coords, profile: {"distances": D.tolist()},
+                 directions_fn=lambda coords, profile: stub_directions(coords))
+    res = S.optimize_route(json.loads(json.dumps(body)), engine=engine, **hooks)
+    assert "error" not in res and sorted(res["properties"]["optimized_order"]) == list(range(n - 1))
+    Di = np.rint(D * 10).astype(np.int32)
+    Ti = np.rint(D * TS_CAR).astype(np.int32)
+    demand = np.array([0] + [d["payload"] for d in body["destination_points"]])
+    stops = np.zeros((n, 4), np.int32)
+    stops[:, 1] = 43200
+    stops[1:, 2] = 120
+    stops[:, 3] = demand
+    rc, trips = O.greedy_trips(Di, demand.astype(float), 18.0, 9e13, T=Ti, tw=stops[:, :3])
+    inst = O.Instance(Di, Ti, stops, 18)
+    final, _, _ = O.local_search(inst, O.build_positions(trips, n))
+    want = [i - 1 for t in O.positions_to_trips(final) if t for i in t]
+    assert rc == 0 and res["properties"]["optimized_order"] == want
