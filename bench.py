@@ -328,6 +328,8 @@ def run_engine(args, rank, world):
         e2e_s = float(t.item())
     same = bool(np.array_equal(h[7].view(np.int64) ^ np.int64(-2 ** 63), keys_ref.cpu().numpy()))
 
+    extra = secondary_figures(eng, torch, stream) if (rank == 0 and not args.no_extra) else None
+
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(peaks_path):
@@ -374,9 +376,11 @@ def run_engine(args, rank, world):
                     "move_evals_per_s": evals_step * world * args.steps / e2e_s,
                     "call": "rt_problem_plan via Problem.plan_call (pinned host buffers in, best keys out; matrices stay in HBM)",
                     "keys_equal_device_path": same},
-            "gpu_launches": 9 * args.steps,
+            "gpu_launches": 11 * args.steps,
             "clocks": clocks,
         }
+        if extra:
+            line["extra"] = extra
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(stops, args.vehicles)
         print(json.dumps(line))
@@ -384,6 +388,80 @@ def run_engine(args, rank, world):
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def secondary_figures(eng, torch, stream):
+    """Quick figures for the other BASELINE configs (not the headline): the matrix kernel at 10,001 nodes, the host
+    matrix API, one 10,000-stop pass on this GPU, and ETA scoring of 1M pairs on a synthetic 200-tree ensemble."""
+    import struct
+
+    out = {}
+
+    def timed(fn, reps=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    # config 4, matrix only: 10,001 nodes device-resident
+    n = 10001
+    lat, lon, _, _ = synth_coords(4567, n - 1, 100)
+    lat_d, lon_d = torch.tensor(lat, device="cuda"), torch.tensor(lon, device="cuda")
+    xyz = torch.empty((3, n), dtype=torch.float64, device="cuda")
+    pitch = eng.matrix_pitch(n)
+    cells = torch.empty((n, pitch, 2), dtype=torch.int32, device="cuda")
+    eng.unit_vectors_dev(lat_d.data_ptr(), lon_d.data_ptr(), n, 1, xyz.data_ptr(), stream)
+    ms = timed(lambda: eng.matrix_cells_dev(xyz.data_ptr(), n, 1, cells.data_ptr(), dist_scale=DIST_SCALE,
+                                            time_scale=TS_CAR, stream=stream))
+    out["matrix_10001_nodes"] = {"ms": ms, "cells_per_s": n * n / ms * 1e3, "GBs": n * n * 8 / ms / 1e6}
+    del cells
+    # host API (rt_matrix_build): 5,001 nodes, dense int32 planes back to pinned host memory
+    n5 = 5001
+    t_d = torch.empty((n5, n5), dtype=torch.int32).pin_memory()
+    t_t = torch.empty((n5, n5), dtype=torch.int32).pin_memory()
+    outb = {"dist": t_d.numpy(), "time": t_t.numpy()}
+    t0 = time.perf_counter()
+    for _ in range(3):
+        eng.matrix_build(lat[:n5], lon[:n5], dist_scale=DIST_SCALE, time_scale=TS_CAR, out=outb)
+    dt = (time.perf_counter() - t0) / 3
+    out["matrix_host_api_5001_nodes"] = {"ms": dt * 1e3, "cells_per_s": n5 * n5 / dt, "d2h_GBs": n5 * n5 * 8 / dt / 1e9}
+    # ETA: 1M pairs, synthetic ensemble of 200 depth-6 trees (complete trees, random splits)
+    rng = np.random.default_rng(3456)
+    trees, depth = 200, 6
+    nodes = bytearray()
+    offs = [0]
+    for _ in range(trees):
+        cnt = 2 ** (depth + 1) - 1
+        for k in range(cnt):
+            if k < 2 ** depth - 1:
+                f = int(rng.integers(0, 12))
+                thr = float(rng.uniform(0, 40) if f == 10 else rng.uniform(20, 40) if f == 11 else rng.uniform(0, 23) if f == 9
+                            else rng.uniform(0, 6) if f == 8 else 0.5)
+                nodes += struct.pack("<fHBB", thr, 2 * k + 1, f, 0)
+            else:
+                nodes += struct.pack("<fHBB", float(rng.normal(0, 0.2)), 0, 0, 1)
+        offs.append(offs[-1] + cnt)
+    blob = b"RTE1" + struct.pack("<IIf", trees, 12, 25.0) + struct.pack(f"<{len(offs)}I", *offs) + bytes(nodes)
+    eng.eta_load_model(blob)
+    m = 1_000_000
+    cols = dict(d=torch.tensor(rng.uniform(0, 45000, m), device="cuda"),
+                w=torch.tensor(rng.integers(0, 4, m).astype(np.uint8), device="cuda"),
+                t=torch.tensor(rng.integers(0, 4, m).astype(np.uint8), device="cuda"),
+                wd=torch.tensor(rng.integers(0, 7, m).astype(np.uint8), device="cuda"),
+                h=torch.tensor(rng.integers(0, 24, m).astype(np.uint8), device="cuda"),
+                a=torch.tensor(rng.uniform(20, 40, m).astype(np.float32), device="cuda"))
+    res = torch.empty(m, dtype=torch.float32, device="cuda")
+    ms = timed(lambda: eng.eta_score_dev(cols["d"].data_ptr(), cols["w"].data_ptr(), cols["t"].data_ptr(),
+                                         cols["wd"].data_ptr(), cols["h"].data_ptr(), cols["a"].data_ptr(), m,
+                                         res.data_ptr(), stream))
+    out["eta_1M_pairs_200_trees_depth6"] = {"ms": ms, "pairs_per_s": m / ms * 1e3}
+    return out
 
 
 def main():
@@ -396,6 +474,7 @@ def main():
     ap.add_argument("--stops", type=int, default=1000)
     ap.add_argument("--vehicles", type=int, default=10)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary figures (other BASELINE configs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
