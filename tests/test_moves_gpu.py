@@ -263,3 +263,53 @@ def test_multi_shard_search_through_dev_entry_points(engine):
         st = pr.get_state(0)
     assert done[0] == 1 and moves[0] == len(keys) and gcost[0] == cost
     assert np.array_equal(st["node"], final)
+
+
+def _tiny_instance(stops, tw_due=1000):
+    rng = np.random.default_rng(stops)
+    n = stops + 1
+    lat = np.concatenate([[14.58], 14.58 + 0.01 * rng.uniform(-1, 1, stops)])
+    lon = np.concatenate([[121.04], 121.04 + 0.01 * rng.uniform(-1, 1, stops)])
+    m = O.matrix_rows(O.unit_vectors(lat, lon), 0, n, 10.0, TS_CAR)
+    st = np.zeros((n, 4), np.int32)
+    st[:, 1] = tw_due
+    st[1:, 3] = 1
+    return O.Instance(m["dist"], m["time"], st, 5), dict(lat=lat, lon=lon)
+
+
+@pytest.mark.parametrize("trips", [[[1]], [[1], [2]], [[2, 1]], [[1, 2], [3]], [[3], [1], [2]]], ids=str)
+def test_tiny_instances_and_routes_that_become_empty(engine, trips):
+    """One to three stops, one route each or together: every candidate against brute force, then the search
+    (which may empty a route: two adjacent separators) against the oracle."""
+    stops = sum(len(t) for t in trips)
+    inst, raw = _tiny_instance(stops)
+    node = O.build_positions(trips, inst.n)
+    with _load(engine, [(inst, node, raw)]) as pr:
+        for fam in (0, 1, 2):
+            d, f = pr.eval_dump(0, fam, node.size)
+            dr, fr = O.eval_bruteforce(inst, node, fam)
+            assert np.array_equal(f, fr) and np.array_equal(d[fr != 2], dr[fr != 2])
+        assert int(pr.eval_moves()[0]) == O.best_move(inst, node)
+        final, keys, cost = O.local_search(inst, node)
+        moves, gcost, gkeys = pr.local_search(keys_capacity=16)
+        assert moves[0] == len(keys) and np.array_equal(gkeys[0], keys) and gcost[0] == cost
+        st = pr.get_state(0)
+        assert np.array_equal(st["node"], final) and st["feasible"]
+        # after the search routes may be empty; evaluation on that state still matches
+        for fam in (0, 1, 2):
+            d, f = pr.eval_dump(0, fam, final.size)
+            dr, fr = O.eval_bruteforce(inst, final, fam)
+            assert np.array_equal(f, fr) and np.array_equal(d[fr != 2], dr[fr != 2])
+        assert pr.get_routes()[0] == O.positions_to_trips(final)
+
+
+def test_local_search_with_zero_moves_and_bad_routes(engine):
+    from routest_b200 import EngineError
+    inst, node, raw = synth_vrptw(14, 30, 3)
+    with _load(engine, [(inst, node, raw)]) as pr:
+        moves, cost, _ = pr.local_search(max_moves=0)
+        assert moves[0] == 0 and cost[0] == O.route_state(inst, node)["cost"]
+        with pytest.raises(EngineError):
+            pr.set_routes([[[1, 2, 3]]])                      # not all customers
+        with pytest.raises(EngineError):
+            pr.set_routes([[[1, 1] + list(range(3, 31))]])    # a customer twice
