@@ -208,6 +208,19 @@ int rt_problem_set_shard(rt_problem *p, int shard_index, int shard_count);
 int rt_problem_eval_moves_dev(rt_problem *p, int families, int shard_index, int shard_count, void *best_keys_d,
                               void *stream);
 int rt_problem_apply_moves_dev(rt_problem *p, const void *keys_d, int improving_only, void *stream);
+/* The same exchange without a collective library: every replica (one process per GPU) exports a small slot buffer
+ * through CUDA IPC, maps its peers', and from then on the evaluation step MIN-reduces its best keys straight into
+ * every peer's buffer with system-scope atomics over NVLink, and the apply step waits (bounded: ~2 s, then
+ * done = 3) until all replicas have published before applying the winner.  8 bytes per instance, no NCCL call in the
+ * loop.  Order of calls: rt_problem_exchange_export on every rank -> all-gather the handles (any transport) ->
+ * rt_problem_exchange_connect -> per iteration rt_problem_eval_moves_xchg_dev, rt_problem_apply_moves_xchg_dev.
+ * The replica's shard (rt_problem_set_shard) must be (rank, world) or unset. */
+int rt_problem_exchange_handle_bytes(void);
+int rt_problem_exchange_export(rt_problem *p, void *handle_out);
+int rt_problem_exchange_connect(rt_problem *p, const void *handles, int rank, int world);
+int rt_problem_eval_moves_xchg_dev(rt_problem *p, int families, void *stream);
+int rt_problem_apply_moves_xchg_dev(rt_problem *p, int improving_only, void *stream);
+
 /* Synchronises the device and reads the search bookkeeping: done [batch], moves [batch], cost [batch]. */
 int rt_problem_search_status(rt_problem *p, int32_t *done_out, int32_t *moves_out, int64_t *cost_out);
 

@@ -166,6 +166,9 @@ void rt_problem_destroy(rt_problem *p)
     DeviceGuard dg(e->device);
     cudaStreamSynchronize(e->stream);
     for (int i = 0; i < p->n_allocs; ++i) cudaFree(p->all_allocs[i]);
+    for (int i = 0; i < p->n_xpeer_mapped; ++i) cudaIpcCloseMemHandle(p->xpeer_mapped[i]);
+    if (p->xpeers) cudaFree(p->xpeers);
+    if (p->xbuf) cudaFree(p->xbuf);
     if (p->Gbuf.p) cudaFree(p->Gbuf.p);
     if (p->GTbuf.p) cudaFree(p->GTbuf.p);
     if (p->host_stage) cudaFreeHost(p->host_stage);

@@ -71,6 +71,11 @@ struct rt_problem {
     int *g_order_out = nullptr, *g_trip_off = nullptr, *g_ntrips = nullptr, *g_status = nullptr;
     void *host_stage = nullptr;            // pinned staging for small D2H results
     size_t host_stage_bytes = 0;
+    // peer exchange (exchange.cu)
+    unsigned long long *xbuf = nullptr;        // this replica's slot buffer (IPC-exported)
+    unsigned long long **xpeers = nullptr;     // device table of every replica's slot buffer
+    void *xpeer_mapped[64] = {nullptr};
+    int n_xpeer_mapped = 0, xrank = 0, xworld = 0, xiter = 0;
     void *all_allocs[64] = {nullptr};
     int n_allocs = 0;
 };

@@ -10,6 +10,12 @@ Where the path shards:
   * greedy construction                               -> replicas only (sequential chain).
 The reduce is 8 bytes per instance and latency bound; iterations are enqueued back to back on one stream and the
 host looks at the done flags only every `check_every` iterations.
+
+Two transports for that reduce:
+  exchange="nccl"  one `all_reduce(MIN)` per iteration through torch.distributed;
+  exchange="peer"  no collective call in the loop: the replicas export a slot buffer through CUDA IPC once, and the
+                   evaluation step MIN-reduces its keys straight into every peer's buffer with system-scope atomics
+                   over NVLink (routest_b200/csrc/exchange.cu); torch.distributed only carries the handles at set-up.
 """
 from __future__ import annotations
 
@@ -37,7 +43,8 @@ class DistributedSearch:
     search_status() -> (done, moves, cost).  The engine's Problem provides them; the CPU tests substitute a stand-in
     to exercise this loop under gloo."""
 
-    def __init__(self, problem, batch: int, *, device=None, group=None, families: int = 7, check_every: int = 16):
+    def __init__(self, problem, batch: int, *, device=None, group=None, families: int = 7, check_every: int = 16,
+                 exchange: str = "nccl"):
         self.problem, self.batch, self.group = problem, batch, group
         self.families, self.check_every = families, check_every
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -45,12 +52,29 @@ class DistributedSearch:
         self.keys = torch.full((batch,), INT64_NONE, dtype=torch.int64, device=device)
         if hasattr(problem, "set_shard"):  # the replica then keeps only its shard's rows of the route-order matrix fresh
             problem.set_shard(self.rank, self.world)
+        if exchange not in ("nccl", "peer"):
+            raise ValueError("exchange must be 'nccl' or 'peer'")
+        self.exchange = exchange
+        if exchange == "peer":
+            handle = problem.exchange_export()
+            handles = [None] * self.world
+            if self.world > 1:
+                dist.all_gather_object(handles, handle, group=group)
+            else:
+                handles[0] = handle
+            problem.exchange_connect(handles, self.rank, self.world)
+            if self.world > 1:
+                dist.barrier(group=group)  # nobody publishes into a buffer that is not mapped yet
 
     def _stream(self) -> int:
         return torch.cuda.current_stream().cuda_stream if self.keys.is_cuda else 0
 
     def step(self):
         s = self._stream()
+        if self.exchange == "peer":
+            self.problem.eval_moves_xchg_dev(self.families, s)
+            self.problem.apply_moves_xchg_dev(True, s)
+            return
         self.problem.eval_moves_dev(self.keys.data_ptr(), self.families, (self.rank, self.world), s)
         allreduce_min_keys(self.keys, self.group)
         self.problem.apply_moves_dev(self.keys.data_ptr(), True, s)

@@ -475,6 +475,23 @@ class Problem:
     def apply_moves_dev(self, keys_ptr: int, improving_only: bool = True, stream: int = 0):
         self._check(self._lib.rt_problem_apply_moves_dev(self._p, keys_ptr, int(bool(improving_only)), stream or None))
 
+    # -- peer-memory exchange (multi-GPU search without a collective call per iteration)
+    def exchange_export(self) -> bytes:
+        buf = C.create_string_buffer(int(self._lib.rt_problem_exchange_handle_bytes()))
+        self._check(self._lib.rt_problem_exchange_export(self._p, C.cast(buf, C.c_void_p)))
+        return buf.raw
+
+    def exchange_connect(self, handles, rank: int, world: int):
+        blob = b"".join(handles)
+        buf = C.create_string_buffer(blob, len(blob))
+        self._check(self._lib.rt_problem_exchange_connect(self._p, C.cast(buf, C.c_void_p), int(rank), int(world)))
+
+    def eval_moves_xchg_dev(self, families: int = ALL_FAMILIES, stream: int = 0):
+        self._check(self._lib.rt_problem_eval_moves_xchg_dev(self._p, int(families), stream or None))
+
+    def apply_moves_xchg_dev(self, improving_only: bool = True, stream: int = 0):
+        self._check(self._lib.rt_problem_apply_moves_xchg_dev(self._p, int(bool(improving_only)), stream or None))
+
     def search_status(self):
         done = np.zeros(self.batch, np.int32)
         moves = np.zeros(self.batch, np.int32)

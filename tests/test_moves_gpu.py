@@ -313,3 +313,21 @@ def test_local_search_with_zero_moves_and_bad_routes(engine):
             pr.set_routes([[[1, 2, 3]]])                      # not all customers
         with pytest.raises(EngineError):
             pr.set_routes([[[1, 1] + list(range(3, 31))]])    # a customer twice
+
+
+def test_peer_exchange_entry_points_single_replica(engine):
+    """The exchange path a multi-GPU search uses instead of NCCL (slot buffer, publish with system-scope atomics,
+    bounded wait, re-arm), here with one replica: same moves and routes as the oracle.  The multi-process form is
+    exercised by tools/dist_search_check.py --exchange peer on 2 and 8 GPUs."""
+    inst, node, raw = synth_vrptw(15, 90, 6)
+    final, keys, cost = O.local_search(inst, node, threads=O.num_threads())
+    with _load(engine, [(inst, node, raw)]) as pr:
+        handle = pr.exchange_export()
+        assert len(handle) == 64
+        pr.exchange_connect([handle], 0, 1)
+        for _ in range(len(keys) + 3):
+            pr.eval_moves_xchg_dev()
+            pr.apply_moves_xchg_dev(True)
+        done, moves, gcost = pr.search_status()
+        assert done[0] == 1 and moves[0] == len(keys) and gcost[0] == cost
+        assert np.array_equal(pr.get_state(0)["node"], final)

@@ -45,6 +45,7 @@ def main():
     ap.add_argument("--stops", type=int, default=2000)
     ap.add_argument("--vehicles", type=int, default=20)
     ap.add_argument("--max-moves", type=int, default=1 << 30)
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"])
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -53,7 +54,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = Engine(local)
     pr, trips = build(eng, 5678, a.stops, a.vehicles)
-    search = DistributedSearch(pr, 1, device="cuda", check_every=32)
+    search = DistributedSearch(pr, 1, device="cuda", check_every=32, exchange=a.exchange)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -74,7 +75,7 @@ def main():
         m1, c1, _ = pr1.local_search(max_moves=a.max_moves)
         dt_single = time.perf_counter() - t0
         same = int(m1[0]) == int(moves[0]) and int(c1[0]) == int(cost[0]) and pr1.get_routes()[0] == routes_multi
-        print(json.dumps({"world": world, "stops": a.stops, "moves": int(moves[0]), "cost": int(cost[0]),
+        print(json.dumps({"world": world, "exchange": a.exchange, "stops": a.stops, "moves": int(moves[0]), "cost": int(cost[0]),
                           "ranks_agree": ok, "equals_single_gpu": bool(same), "s_multi": round(dt_multi, 4),
                           "s_single": round(dt_single, 4), "us_per_move_multi": round(1e6 * dt_multi / max(1, int(moves[0])), 1),
                           "us_per_move_single": round(1e6 * dt_single / max(1, int(m1[0])), 1)}))
