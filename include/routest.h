@@ -220,6 +220,8 @@ int rt_problem_exchange_export(rt_problem *p, void *handle_out);
 int rt_problem_exchange_connect(rt_problem *p, const void *handles, int rank, int world);
 int rt_problem_eval_moves_xchg_dev(rt_problem *p, int families, void *stream);
 int rt_problem_apply_moves_xchg_dev(rt_problem *p, int improving_only, void *stream);
+/* The wait alone: the reduced keys (packed, unsigned form) land in keys_d [batch] and nothing is applied. */
+int rt_problem_collect_keys_xchg_dev(rt_problem *p, void *keys_d, void *stream);
 
 /* Synchronises the device and reads the search bookkeeping: done [batch], moves [batch], cost [batch]. */
 int rt_problem_search_status(rt_problem *p, int32_t *done_out, int32_t *moves_out, int64_t *cost_out);

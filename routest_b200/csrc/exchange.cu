@@ -158,6 +158,21 @@ int rt_problem_eval_moves_xchg_dev(rt_problem *p, int families, void *stream)
     return RT_OK;
 }
 
+int rt_problem_collect_keys_xchg_dev(rt_problem *p, void *keys_d, void *stream)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    rt_engine *e = p->e;
+    if (!keys_d) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_collect_keys_xchg_dev: NULL argument");
+    if (!p->has_routes || p->xworld < 1) return fail(e, RT_ERR_STATE, "rt_problem_collect_keys_xchg_dev: routes and exchange first");
+    DeviceGuard dg(e->device);
+    cudaStream_t st = pick_stream(e, stream);
+    xchg_collect_kernel<<<1, 256, 0, st>>>(p->xbuf, p->xworld, p->batch, p->xiter & 1,
+                                           static_cast<unsigned long long *>(keys_d), p->done, 4000000000LL);
+    RT_CUDA(e, cudaGetLastError());
+    ++p->xiter;
+    return RT_OK;
+}
+
 int rt_problem_apply_moves_xchg_dev(rt_problem *p, int improving_only, void *stream)
 {
     if (!p) return RT_ERR_INVALID_ARG;

@@ -492,6 +492,9 @@ class Problem:
     def apply_moves_xchg_dev(self, improving_only: bool = True, stream: int = 0):
         self._check(self._lib.rt_problem_apply_moves_xchg_dev(self._p, int(bool(improving_only)), stream or None))
 
+    def collect_keys_xchg_dev(self, keys_ptr: int, stream: int = 0):
+        self._check(self._lib.rt_problem_collect_keys_xchg_dev(self._p, keys_ptr, stream or None))
+
     def search_status(self):
         done = np.zeros(self.batch, np.int32)
         moves = np.zeros(self.batch, np.int32)

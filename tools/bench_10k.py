@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--vehicles", type=int, default=100)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--cpu", action="store_true", help="rank 0 also times the CPU oracle on the same pass")
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"],
+                    help="nccl: all_reduce(MIN) per pass; peer: system-scope atomics into every replica's slot buffer")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -54,11 +56,26 @@ def main():
     keys = torch.empty(1, dtype=torch.int64, device="cuda")
     s = torch.cuda.current_stream().cuda_stream
 
+    if a.exchange == "peer":
+        handle = pr.exchange_export()
+        handles = [None] * world
+        if world > 1:
+            dist.all_gather_object(handles, handle)
+        else:
+            handles[0] = handle
+        pr.exchange_connect(handles, rank, world)
+        if world > 1:
+            dist.barrier()
+
     def step():
         pr.refresh_dev(3, s)                                   # this rank's rows of the matrix + route state
-        pr.eval_moves_dev(keys.data_ptr(), ALL_FAMILIES, (rank, world), s)
-        if world > 1:
-            dist.all_reduce(keys, op=dist.ReduceOp.MIN)
+        if a.exchange == "peer":
+            pr.eval_moves_xchg_dev(ALL_FAMILIES, s)            # shard + MIN into every replica's slot over NVLink
+            pr.collect_keys_xchg_dev(keys.data_ptr(), s)       # wait until all replicas have published
+        else:
+            pr.eval_moves_dev(keys.data_ptr(), ALL_FAMILIES, (rank, world), s)
+            if world > 1:
+                dist.all_reduce(keys, op=dist.ReduceOp.MIN)
 
     for _ in range(5):
         step()
@@ -77,10 +94,12 @@ def main():
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
     best = int(keys.item())
+    if a.exchange == "peer":
+        best ^= -(2 ** 63)  # the slot holds the unsigned packed key; fold it into the signed-order form used below
     if rank == 0:
         cand = count_candidates(trips[0], n)
         evals = sum(cand.values())
-        line = {"workload": f"one {a.stops}-stop VRPTW instance ({len(trips[0])} routes, P = {P}), rows and neighbourhood "
+        line = {"exchange": a.exchange, "workload": f"one {a.stops}-stop VRPTW instance ({len(trips[0])} routes, P = {P}), rows and neighbourhood "
                             f"sharded over {world} GPU(s), one NCCL MIN all-reduce per pass",
                 "n_gpus": world, "ms_per_pass": ms, "matrix_cells_per_s": P * P / ms * 1e3,
                 "move_evals_per_s": evals / ms * 1e3, "cells_per_pass": P * P, "move_evals_per_pass": evals,
