@@ -493,7 +493,9 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
                       bool signed_keys, cudaStream_t st)
 {
     rt_engine *e = p->e;
-    fill_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, p->batch);
+    // p->best is reset by every state refresh; a second evaluation of the same state has to clear it itself
+    if (!p->best_clean) fill_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, p->batch);
+    p->best_clean = false;
     EvalArgs a = make_args(p, families, shard_index, shard_count, p->best);
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;  // largest P of the batch
     const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
@@ -509,7 +511,8 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
         else eval_intra_kernel<false, true><<<grid, kIntraThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
-    finish_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, best_d, p->batch, signed_keys ? 1 : 0);
+    if (best_d != p->best || signed_keys)
+        finish_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, best_d, p->batch, signed_keys ? 1 : 0);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }

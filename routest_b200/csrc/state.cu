@@ -400,6 +400,7 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st)
                                              p->max_dist, p->RB, p->E, p->SK, p->Bv, p->Zv, p->route, p->rload, p->rdist,
                                              p->RA, p->RC, p->RD, p->H);
     RT_CUDA(e, cudaGetLastError());
+    p->best_clean = true;  // state_routes_kernel reset the best keys
     return RT_OK;
 }
 
