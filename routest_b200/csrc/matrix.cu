@@ -18,7 +18,6 @@ namespace rt {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kColsPerBlock = kThreads * 4;
 constexpr int kMaxRowsPerBlock = 64;
 constexpr int kBlocksPerSM = 4;
 constexpr int kMinWaves = 10;
@@ -194,9 +193,10 @@ __global__ void fast_sqrt_check_kernel(unsigned lo, unsigned hi, unsigned long l
 // Rows per block: the largest strip that still yields >= kMinWaves full waves of blocks, so that the tail wave (the
 // hardware dispatches a new block whenever one retires) costs a few percent at most; never below 8 rows, which
 // keeps the per-block prologue (12 column loads + one barrier) under ~5% of the block's work.
-int pick_rows_per_block(int rows, int col_blocks, int batch)
+int pick_rows_per_block(int rows, int col_blocks, int batch, int threads)
 {
-    const long long want_blocks = static_cast<long long>(kMinWaves) * kNumSMs * kBlocksPerSM;
+    const int blocks_per_sm = std::min(16, 65536 / (64 * threads));  // 64 registers per thread
+    const long long want_blocks = static_cast<long long>(kMinWaves) * kNumSMs * blocks_per_sm;
     int rpb = kMaxRowsPerBlock;
     while (rpb > 8 && static_cast<long long>((rows + rpb - 1) / rpb) * col_blocks * batch < want_blocks) rpb >>= 1;
     return rpb;
@@ -207,12 +207,19 @@ int launch_matrix(rt_engine *e, MatArgs a, int batch, int pitch_cols, cudaStream
 {
     const int rows = a.r1 - a.r0;
     if (rows <= 0 || batch <= 0) return RT_OK;
-    // Column blocks of equal width: a pitch just above a multiple of 1024 (1,040 for 1,000 stops in route order)
-    // must not leave a block with a handful of live threads, so the block shrinks instead (multiples of a warp).
-    const int col_blocks = (pitch_cols + kColsPerBlock - 1) / kColsPerBlock;
-    const int cols_per_block = (pitch_cols + col_blocks - 1) / col_blocks;
-    const int threads = std::min(kThreads, ((cols_per_block + 3) / 4 + 31) & ~31);
-    a.rows_per_block = pick_rows_per_block(rows, col_blocks, batch);
+    // Column blocks of whole warps (128 columns each), at most eight warps per block: pick the split that leaves the
+    // fewest idle warps (1,040 columns = 9 warps -> 3 blocks of 3, not 2 blocks of 5), larger blocks on ties.
+    const int warps = (pitch_cols + 127) / 128;
+    int col_blocks = (warps + 7) / 8, wpb = (warps + col_blocks - 1) / col_blocks;
+    for (int cb = col_blocks + 1; cb <= (warps + 1) / 2; ++cb) {
+        const int w = (warps + cb - 1) / cb;
+        if (cb * w - warps < col_blocks * wpb - warps) {
+            col_blocks = cb;
+            wpb = w;
+        }
+    }
+    const int threads = wpb * 32;
+    a.rows_per_block = pick_rows_per_block(rows, col_blocks, batch, threads);
     const int row_blocks = (rows + a.rows_per_block - 1) / a.rows_per_block;
     if (row_blocks > 65535 || batch > 65535) return fail(e, RT_ERR_INVALID_ARG, "matrix grid too large");
     dim3 grid(col_blocks, row_blocks, batch);

@@ -166,6 +166,12 @@ void rt_problem_destroy(rt_problem *p)
     DeviceGuard dg(e->device);
     cudaStreamSynchronize(e->stream);
     for (int i = 0; i < p->n_allocs; ++i) cudaFree(p->all_allocs[i]);
+    if (p->side_stream) {
+        cudaStreamSynchronize(p->side_stream);
+        cudaStreamDestroy(p->side_stream);
+        cudaEventDestroy(p->ev_fork);
+        cudaEventDestroy(p->ev_join);
+    }
     for (int i = 0; i < p->n_xpeer_mapped; ++i) cudaIpcCloseMemHandle(p->xpeer_mapped[i]);
     if (p->xpeers) cudaFree(p->xpeers);
     if (p->xbuf) cudaFree(p->xbuf);

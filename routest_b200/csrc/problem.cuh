@@ -72,6 +72,8 @@ struct rt_problem {
     int *g_order_out = nullptr, *g_trip_off = nullptr, *g_ntrips = nullptr, *g_status = nullptr;
     void *host_stage = nullptr;            // pinned staging for small D2H results
     size_t host_stage_bytes = 0;
+    cudaStream_t side_stream = nullptr;    // state tables run here underneath the matrix kernel (state.cu)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     // peer exchange (exchange.cu)
     unsigned long long *xbuf = nullptr;        // this replica's slot buffer (IPC-exported)
     unsigned long long **xpeers = nullptr;     // device table of every replica's slot buffer
@@ -88,7 +90,7 @@ inline int2 *position_matrix(const rt_problem *p) { return p->Gbuf.p ? static_ca
 inline int2 *position_matrix_t(const rt_problem *p) { return p->GTbuf.p ? static_cast<int2 *>(p->GTbuf.p) + 16 : nullptr; }
 
 int state_refresh(rt_problem *p, cudaStream_t st);
-int position_matrix_refresh(rt_problem *p, cudaStream_t st);
+int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready = false);
 int state_tables_refresh(rt_problem *p, cudaStream_t st);
 int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d,
                       bool signed_keys, cudaStream_t st);

@@ -343,7 +343,7 @@ int ensure_position_matrix(rt_problem *p)
 
 // node[] -> G (route-order matrix), rows of this replica's shard only (plus the halo rows the move kernels read).
 // Stream-ordered, no allocation (G is sized by ensure_position_matrix when routes are installed).
-int position_matrix_refresh(rt_problem *p, cudaStream_t st)
+int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready)
 {
     rt_engine *e = p->e;
     int2 *G = position_matrix(p);
@@ -357,9 +357,11 @@ int position_matrix_refresh(rt_problem *p, cudaStream_t st)
         r1 = static_cast<int>(std::min<long long>(hi, p->grows));
     }
     if (p->cells_from_coords) {
-        dim3 g0((p->pstride + 255) / 256, p->batch);
-        position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
-        RT_CUDA(e, cudaGetLastError());
+        if (!vectors_ready) {
+            dim3 g0((p->pstride + 255) / 256, p->batch);
+            position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
+            RT_CUDA(e, cudaGetLastError());
+        }
         RT_TRY(launch_matrix_cells_ld(e, p->PX, p->grows, p->pstride, p->batch, r0, r1, p->dist_scale, p->time_scale, G,
                                       p->gpitch, st));
     } else {
@@ -404,10 +406,29 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st)
     return RT_OK;
 }
 
+// Both halves.  The state tables do not read G (state_gather_kernel rebuilds the cells it needs), so their four small
+// latency-bound kernels run on a side stream underneath the matrix kernel and join before anything evaluates moves.
 int state_refresh(rt_problem *p, cudaStream_t st)
 {
-    RT_TRY(position_matrix_refresh(p, st));
-    return state_tables_refresh(p, st);
+    rt_engine *e = p->e;
+    if (!p->side_stream) {
+        RT_CUDA(e, cudaStreamCreateWithFlags(&p->side_stream, cudaStreamNonBlocking));
+        RT_CUDA(e, cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+        RT_CUDA(e, cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+    }
+    if (p->cells_from_coords) {
+        // the position-ordered vectors feed both halves: produce them first, then fork
+        dim3 g0((p->pstride + 255) / 256, p->batch);
+        position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
+        RT_CUDA(e, cudaGetLastError());
+    }
+    RT_CUDA(e, cudaEventRecord(p->ev_fork, st));
+    RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, p->ev_fork, 0));
+    RT_TRY(position_matrix_refresh(p, st, /*vectors_ready=*/true));
+    RT_TRY(state_tables_refresh(p, p->side_stream));
+    RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
+    RT_CUDA(e, cudaStreamWaitEvent(st, p->ev_join, 0));
+    return RT_OK;
 }
 
 int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
