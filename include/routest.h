@@ -175,6 +175,11 @@ int rt_problem_apply_moves(rt_problem *p, const uint64_t *keys);
  * moves_out [batch], cost_out [batch]; keys_out [batch][keys_capacity] receives the applied keys (may be NULL). */
 int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t *moves_out, int64_t *cost_out,
                             uint64_t *keys_out, int keys_capacity);
+/* The same search with every iteration re-scoring the whole neighbourhood on the route-order matrix, i.e. without
+ * the per-route-pair table rt_problem_local_search keeps (it re-scores only what the last move touched; same keys,
+ * same routes).  For cross-checking and for asymmetric matrices / more than 1,024 routes, where the table is not used. */
+int rt_problem_local_search_full(rt_problem *p, int families, int max_moves, int32_t *moves_out, int64_t *cost_out,
+                                 uint64_t *keys_out, int keys_capacity);
 
 /* One pass of the hot path from host inputs to best moves, for every instance: uploads coordinates, stop data
  * and the current solution, builds the matrices (utils.py:94-109) — in route order, G[p][q] = M[node p][node q],

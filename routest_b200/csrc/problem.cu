@@ -175,6 +175,8 @@ void rt_problem_destroy(rt_problem *p)
     for (int i = 0; i < p->n_xpeer_mapped; ++i) cudaIpcCloseMemHandle(p->xpeer_mapped[i]);
     if (p->xpeers) cudaFree(p->xpeers);
     if (p->xbuf) cudaFree(p->xbuf);
+    for (rt::DevBuf *bf : {&p->cache_inter, &p->cache_intra, &p->cache_tiles, &p->cache_misc})
+        if (bf->p) cudaFree(bf->p);
     if (p->Gbuf.p) cudaFree(p->Gbuf.p);
     if (p->GTbuf.p) cudaFree(p->GTbuf.p);
     if (p->host_stage) cudaFreeHost(p->host_stage);
@@ -688,8 +690,23 @@ int rt_problem_search_status(rt_problem *p, int32_t *done_out, int32_t *moves_ou
     return RT_OK;
 }
 
+static int local_search_impl(rt_problem *p, int families, int max_moves, int mode, int32_t *moves_out,
+                             int64_t *cost_out, uint64_t *keys_out, int keys_capacity);
+
 int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t *moves_out, int64_t *cost_out,
                             uint64_t *keys_out, int keys_capacity)
+{
+    return local_search_impl(p, families, max_moves, 0, moves_out, cost_out, keys_out, keys_capacity);
+}
+
+int rt_problem_local_search_full(rt_problem *p, int families, int max_moves, int32_t *moves_out, int64_t *cost_out,
+                                 uint64_t *keys_out, int keys_capacity)
+{
+    return local_search_impl(p, families, max_moves, 1, moves_out, cost_out, keys_out, keys_capacity);
+}
+
+static int local_search_impl(rt_problem *p, int families, int max_moves, int mode, int32_t *moves_out,
+                             int64_t *cost_out, uint64_t *keys_out, int keys_capacity)
 {
     RT_PROBLEM_GUARD(p);
     if (!(families & 7) || max_moves < 0) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_local_search: bad argument");
@@ -699,7 +716,11 @@ int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t 
     int *done_h = static_cast<int *>(p->host_stage);
     reset_search_kernel<<<(p->batch + 255) / 256, 256, 0, e->stream>>>(p->done, p->moves, p->batch);
     RT_CUDA(e, cudaGetLastError());
-    RT_TRY(state_refresh(p, e->stream));
+    // Incremental search (cache.cu: only what a move touched is re-scored) whenever its table applies; otherwise
+    // every iteration re-scores the whole neighbourhood on the route-order matrix.  Same keys either way.
+    const bool cached = !(mode & 1) && cache_usable(p);
+    if (cached) RT_TRY(cache_begin(p, e->stream));
+    else RT_TRY(state_refresh(p, e->stream));
     // The host only paces the loop: kChunk iterations are enqueued blind (an instance that has reached its local
     // optimum turns its own later iterations into no-ops on the device), then one 4-byte-per-instance read decides
     // whether to go on.
@@ -709,8 +730,13 @@ int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t 
     while (!all_done && issued < max_moves) {
         const int todo = std::min(kChunk, max_moves - issued);
         for (int i = 0; i < todo; ++i) {
-            RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, e->stream));
-            RT_TRY(apply_moves_launch(p, p->best, false, true, e->stream));
+            if (cached) {
+                RT_TRY(cache_evaluate(p, families, e->stream));
+                RT_TRY(cache_apply(p, true, e->stream));
+            } else {
+                RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, e->stream));
+                RT_TRY(apply_moves_launch(p, p->best, false, true, e->stream));
+            }
         }
         issued += todo;
         RT_CUDA(e, cudaMemcpyAsync(done_h, p->done, p->batch * 4, cudaMemcpyDeviceToHost, e->stream));
@@ -718,6 +744,7 @@ int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t 
         all_done = true;
         for (int b = 0; b < p->batch; ++b) all_done = all_done && done_h[b] != 0;
     }
+    if (cached) RT_TRY(state_refresh(p, e->stream));  // bring the route-order matrix back in step with the routes
     if (moves_out) RT_CUDA(e, cudaMemcpyAsync(moves_out, p->moves, p->batch * 4, cudaMemcpyDeviceToHost, e->stream));
     if (cost_out) RT_CUDA(e, cudaMemcpyAsync(cost_out, p->cost, p->batch * 8, cudaMemcpyDeviceToHost, e->stream));
     if (keys_out && keys_capacity > 0) {

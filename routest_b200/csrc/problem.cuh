@@ -72,6 +72,9 @@ struct rt_problem {
     int *g_order_out = nullptr, *g_trip_off = nullptr, *g_ntrips = nullptr, *g_status = nullptr;
     void *host_stage = nullptr;            // pinned staging for small D2H results
     size_t host_stage_bytes = 0;
+    // incremental local search (cache.cu)
+    rt::DevBuf cache_inter, cache_intra, cache_tiles, cache_misc;
+    int cache_r = 0, cache_tile_cap = 0;
     cudaStream_t side_stream = nullptr;    // state tables run here underneath the matrix kernel (state.cu)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     // peer exchange (exchange.cu)
@@ -98,6 +101,14 @@ int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsi
 int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
                        cudaStream_t st);
 int greedy_launch(rt_problem *p, bool use_tw, cudaStream_t st);
+int position_vectors_refresh(rt_problem *p, cudaStream_t st);
+int apply_only_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
+                      cudaStream_t st);
+// incremental local search (cache.cu)
+bool cache_usable(const rt_problem *p);
+int cache_begin(rt_problem *p, cudaStream_t st);
+int cache_evaluate(rt_problem *p, int families, cudaStream_t st);
+int cache_apply(rt_problem *p, bool improving_only, cudaStream_t st);
 int ensure_position_matrix(rt_problem *p);  // sizes G for p->pmax (may allocate; not stream-ordered)
 
 }  // namespace rt

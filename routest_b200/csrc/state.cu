@@ -431,13 +431,28 @@ int state_refresh(rt_problem *p, cudaStream_t st)
     return RT_OK;
 }
 
-int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
-                       cudaStream_t st)
+int position_vectors_refresh(rt_problem *p, cudaStream_t st)
+{
+    dim3 g0((p->pstride + 255) / 256, p->batch);
+    position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
+    RT_CUDA(p->e, cudaGetLastError());
+    return RT_OK;
+}
+
+int apply_only_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
+                      cudaStream_t st)
 {
     apply_moves_kernel<<<p->batch, 256, 0, st>>>(keys_d, signed_keys ? 1 : 0, improving_only ? 1 : 0, p->node,
                                                  p->node_tmp, p->npos, p->pstride, p->done, p->moves, p->hist,
                                                  p->hist_cap);
     RT_CUDA(p->e, cudaGetLastError());
+    return RT_OK;
+}
+
+int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
+                       cudaStream_t st)
+{
+    RT_TRY(apply_only_launch(p, keys_d, signed_keys, improving_only, st));
     return state_refresh(p, st);
 }
 

@@ -396,11 +396,15 @@ class Problem:
         keys = self._arr(keys, np.uint64, (self.batch,))
         self._check(self._lib.rt_problem_apply_moves(self._p, _u64(keys)))
 
-    def local_search(self, families: int = ALL_FAMILIES, max_moves: int = 1 << 30, keys_capacity: int = 0):
+    def local_search(self, families: int = ALL_FAMILIES, max_moves: int = 1 << 30, keys_capacity: int = 0,
+                     full: bool = False):
+        """Best-improvement search to a local optimum.  full=True re-scores the whole neighbourhood every iteration
+        (rt_problem_local_search_full) instead of only what the last move touched; the result is the same."""
         moves = np.zeros(self.batch, np.int32)
         cost = np.zeros(self.batch, np.int64)
         keys = np.zeros((self.batch, max(keys_capacity, 1)), np.uint64)
-        self._check(self._lib.rt_problem_local_search(self._p, int(families), int(min(max_moves, 2 ** 31 - 1)),
+        fn = self._lib.rt_problem_local_search_full if full else self._lib.rt_problem_local_search
+        self._check(fn(self._p, int(families), int(min(max_moves, 2 ** 31 - 1)),
                                                       _i32(moves), _i64(cost), _u64(keys) if keys_capacity else None,
                                                       int(keys_capacity)))
         return moves, cost, [keys[b, :min(moves[b], keys_capacity)].copy() for b in range(self.batch)]

@@ -220,12 +220,15 @@ def test_apply_moves_matches_oracle(engine):
             assert st["cost"] == O.route_state(inst, cur)["cost"]
 
 
+@pytest.mark.parametrize("full", [False, True], ids=["incremental", "full"])
 @pytest.mark.parametrize("seed,stops,veh", [(10, 45, 5), (11, 100, 10), (12, 300, 12)])
-def test_local_search_moves_and_final_routes_bit_exact(engine, seed, stops, veh):
+def test_local_search_moves_and_final_routes_bit_exact(engine, seed, stops, veh, full):
+    """Both search drivers — the one that re-scores only what a move touched (per-route-pair table) and the one that
+    re-scores everything on the route-order matrix — apply the oracle's exact sequence of keys."""
     inst, node, raw = synth_vrptw(seed, stops, veh)
     final, keys, cost = O.local_search(inst, node, threads=O.num_threads())
     with _load(engine, [(inst, node, raw)]) as pr:
-        moves, gcost, gkeys = pr.local_search(keys_capacity=4 * inst.n)
+        moves, gcost, gkeys = pr.local_search(keys_capacity=4 * inst.n, full=full)
         st = pr.get_state(0)
         trips = pr.get_routes()[0]
     assert moves[0] == len(keys) and np.array_equal(gkeys[0], keys)
@@ -234,11 +237,12 @@ def test_local_search_moves_and_final_routes_bit_exact(engine, seed, stops, veh)
     assert trips == O.positions_to_trips(final)
 
 
-def test_local_search_batch_and_max_moves(engine):
+@pytest.mark.parametrize("full", [False, True], ids=["incremental", "full"])
+def test_local_search_batch_and_max_moves(engine, full):
     insts = [synth_vrptw(200 + b, 80, 6) for b in range(4)]
     refs = [O.local_search(inst, node, max_moves=25) for inst, node, _ in insts]
     with _load(engine, insts) as pr:
-        moves, cost, keys = pr.local_search(max_moves=25, keys_capacity=64)
+        moves, cost, keys = pr.local_search(max_moves=25, keys_capacity=64, full=full)
         for b in range(4):
             assert moves[b] == len(refs[b][1]) and np.array_equal(keys[b], refs[b][1]) and cost[b] == refs[b][2]
             assert np.array_equal(pr.get_state(b)["node"], refs[b][0])
