@@ -23,7 +23,9 @@ namespace rt {
 
 namespace {
 
-constexpr int kTileRows = 32, kTileCols = 128;
+constexpr int kTileRows = 8, kTileCols = 128;
+constexpr int kTallRows = 64;     // column-band tiles are tall: their row loop is cheap and there are P/8 of them otherwise
+constexpr int kTallFlag = 1 << 30;  // in a packed tile: rows are counted in units of kTallRows
 constexpr int kBandThreads = kTileCols;
 constexpr int kAllDirty = -2;
 
@@ -90,8 +92,9 @@ __global__ void __launch_bounds__(256) cache_prepare_kernel(const CacheArgs a)
     if (d0 == kAllDirty) {
         for (int i = tid; i < R * a.cr; i += blockDim.x) inter[static_cast<size_t>(i / a.cr) * a.cr + i % a.cr] = kNoMove;
         for (int i = tid; i < R; i += blockDim.x) intra[i] = kNoMove;
-        for (int i = tid; i < nrt * nct; i += blockDim.x) tiles[i] = ((i / nct) << 16) | (i % nct);
-        if (tid == 0) a.ntiles[b] = nrt * nct;
+        const int ntall = (P + kTallRows - 1) / kTallRows;
+        for (int i = tid; i < ntall * nct; i += blockDim.x) tiles[i] = kTallFlag | ((i / nct) << 16) | (i % nct);
+        if (tid == 0) a.ntiles[b] = ntall * nct;
         return;
     }
     for (int k = 0; k < 2; ++k) {
@@ -105,7 +108,10 @@ __global__ void __launch_bounds__(256) cache_prepare_kernel(const CacheArgs a)
         // the route's positions, its starting separator included (it is the insertion edge "before the first stop")
         const int lo = rstart[d], hi = rstart[d + 1] - 1;
         const int rt0 = lo / kTileRows, rt1 = hi / kTileRows, ct0 = lo / kTileCols, ct1 = hi / kTileCols;
-        const int nrows = (rt1 - rt0 + 1) * nct, ncols = (ct1 - ct0 + 1) * nrt;
+        // column band: short tiles while there are fewer of them than blocks to run them (latency), tall ones beyond
+        const bool tall = P > 4096;
+        const int ntall = tall ? (P + kTallRows - 1) / kTallRows : nrt;
+        const int nrows = (rt1 - rt0 + 1) * nct, ncols = (ct1 - ct0 + 1) * ntall;
         __shared__ int s_base;
         if (tid == 0) {
             s_base = s_n;
@@ -114,17 +120,25 @@ __global__ void __launch_bounds__(256) cache_prepare_kernel(const CacheArgs a)
         __syncthreads();
         const int base = s_base;
         for (int i = tid; i < nrows; i += blockDim.x) tiles[base + i] = ((rt0 + i / nct) << 16) | (i % nct);
-        for (int i = tid; i < ncols; i += blockDim.x) tiles[base + nrows + i] = ((i / (ct1 - ct0 + 1)) << 16) | (ct0 + i % (ct1 - ct0 + 1));
+        for (int i = tid; i < ncols; i += blockDim.x)
+            tiles[base + nrows + i] = (tall ? kTallFlag : 0) | ((i / (ct1 - ct0 + 1)) << 16) | (ct0 + i % (ct1 - ct0 + 1));
         __syncthreads();
     }
     if (tid == 0) a.ntiles[b] = s_n;
 }
 
-// Re-scores listed tiles: relocate(p -> q) and swap(p, q) for pairs of different routes, straight-line like
-// eval_inter_kernel, cells rebuilt per pair; a thread owns column q and flushes its best key into inter[ra][rb]
-// whenever the row's route changes.
+// Re-scores listed tiles (8 rows x 128 columns): relocate(p -> q) and swap(p, q) for pairs of different routes,
+// straight-line like eval_inter_kernel.  Everything a tile needs is fetched up front in one round of independent
+// loads — the rows' records and unit vectors into shared memory, the column's into registers — and the cells are
+// rebuilt from those vectors, so the row loop itself never waits on memory.  A thread owns column q and flushes its
+// best key into inter[ra][rb] whenever the row's route changes.
+template <bool COMPUTED>
 __global__ void __launch_bounds__(kBandThreads) cache_inter_kernel(const CacheArgs a)
 {
+    __shared__ int4 sH[kTallRows], sA[kTallRows], sB[kTallRows], sC[kTallRows], sD[kTallRows];
+    __shared__ double sPX[3][kTallRows + 2];
+    __shared__ int s_tile;
+
     const int b = blockIdx.y;
     const int P = a.npos[b];
     const size_t po = static_cast<size_t>(b) * a.pstride;
@@ -134,17 +148,56 @@ __global__ void __launch_bounds__(kBandThreads) cache_inter_kernel(const CacheAr
     const int ntiles = a.ntiles[b];
     const int d0 = a.dirty[2 * b], d1 = a.dirty[2 * b + 1];
     const int tid = threadIdx.x;
-    __shared__ int s_tile;
+    const double *px = COMPUTED ? a.PX + static_cast<size_t>(b) * 3 * a.pstride : nullptr;
     for (;;) {
+        __syncthreads();  // the previous tile's shared data is no longer needed
         if (tid == 0) s_tile = atomicAdd(a.cursor + b, 1);
         __syncthreads();
         const int ti = s_tile;
-        __syncthreads();
         if (ti >= ntiles) break;
         const int packed = tiles[ti];
-        const int p0 = (packed >> 16) * kTileRows, q = (packed & 0xFFFF) * kTileCols + tid;
-        if (q >= P) continue;
-        const int4 Hq = a.H[po + q], qA = a.RA[po + q], qB = a.RB[po + q], qC = a.RC[po + q], qD = a.RD[po + q];
+        const int trows = (packed & kTallFlag) ? kTallRows : kTileRows;
+        const int p0 = ((packed & ~kTallFlag) >> 16) * trows, q = (packed & 0xFFFF) * kTileCols + tid;
+        // one round of loads: rows -> shared memory, column -> registers
+        if (tid < trows) {
+            const int p = min(p0 + tid, P - 1);
+            sH[tid] = a.H[po + p];
+            sA[tid] = a.RA[po + p];
+            sB[tid] = a.RB[po + p];
+            sC[tid] = a.RC[po + p];
+            sD[tid] = a.RD[po + p];
+        }
+        if (COMPUTED) {
+            for (int k = tid; k < 3 * (trows + 2); k += kBandThreads) {
+                const int comp = k / (trows + 2), i = k - comp * (trows + 2);
+                sPX[comp][i] = px[static_cast<size_t>(comp) * a.pstride + min(max(p0 - 1 + i, 0), P - 1)];
+            }
+        }
+        const bool q_in = q < P;
+        const int qq = min(q, P - 1);
+        const int4 Hq = a.H[po + qq], qA = a.RA[po + qq], qB = a.RB[po + qq], qC = a.RC[po + qq], qD = a.RD[po + qq];
+        double cx[3] = {0, 0, 0}, cy[3] = {0, 0, 0}, cz[3] = {0, 0, 0};  // unit vectors of q-1, q, q+1
+        if (COMPUTED) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int c = min(max(qq - 1 + k, 0), P - 1);
+                cx[k] = px[c];
+                cy[k] = px[a.pstride + c];
+                cz[k] = px[2 * static_cast<size_t>(a.pstride) + c];
+            }
+        }
+        __syncthreads();
+        if (!q_in) continue;
+        auto cell = [&](int i, int k, int pa, int pb) -> int2 {  // row slot i (0 = p0-1), column slot k (0 = q-1)
+            if (COMPUTED) {
+                const double ax = sPX[0][i], ay = sPX[1][i], az = sPX[2][i];
+                const double dx = ax - cx[k], dy = ay - cy[k], dz = az - cz[k];
+                const double s2 = fma(dx, dx, fma(dy, dy, dz * dz));
+                return __double2hiint(s2) < a.lim_hi ? cell_i32_fast(s2, a.fd, a.ft)
+                                                     : cell_i32(ax, ay, az, cx[k], cy[k], cz[k], a.fd, a.ft);
+            }
+            return pos_cell(a, b, pa, pb);
+        };
         const int rb = Hq.w & 0x7FFF;
         const bool q_cust = (Hq.w >> 30) & 1;
         const bool q_dirty = is_dirty(rb, d0, d1);
@@ -152,9 +205,10 @@ __global__ void __launch_bounds__(kBandThreads) cache_inter_kernel(const CacheAr
         const int qs = rstart[min(rb, P - a.n)];
         int cur_ra = -1;
         unsigned long long best = kNoMove;
-        const int p1 = min(p0 + kTileRows, P);
-        for (int p = p0; p < p1; ++p) {
-            const int4 Hp = a.H[po + p];
+        const int rows = min(trows, P - p0);
+        for (int rr = 0; rr < rows; ++rr) {
+            const int p = p0 + rr;
+            const int4 Hp = sH[rr];
             if (!((Hp.w >> 30) & 1)) continue;  // separators are never moved
             const int ra = Hp.w & 0x7FFF;
             if (ra == rb || !(q_dirty || is_dirty(ra, d0, d1))) continue;
@@ -164,8 +218,8 @@ __global__ void __launch_bounds__(kBandThreads) cache_inter_kernel(const CacheAr
                 cur_ra = ra;
             }
             const int ps = rstart[ra];
-            const int4 pA = a.RA[po + p], pB = a.RB[po + p], pC = a.RC[po + p], pD = a.RD[po + p];
-            const int2 c_cur = pos_cell(a, b, p, q), c_rt = pos_cell(a, b, p, min(q + 1, P - 1));
+            const int4 pA = sA[rr], pB = sB[rr], pC = sC[rr], pD = sD[rr];
+            const int2 c_cur = cell(rr + 1, 1, p, q), c_rt = cell(rr + 1, 2, p, min(q + 1, P - 1));
             if (rel_q) {
                 const int ins = c_cur.x + c_rt.x - Hq.z;
                 const int tu = max(pB.x, qA.x + c_cur.y);
@@ -176,7 +230,7 @@ __global__ void __launch_bounds__(kBandThreads) cache_inter_kernel(const CacheAr
                 }
             }
             if (swap_q && p < q) {
-                const int2 c_up = pos_cell(a, b, p - 1, q), c_dn = pos_cell(a, b, p + 1, q), c_lf = pos_cell(a, b, p, q - 1);
+                const int2 c_up = cell(rr, 1, p - 1, q), c_dn = cell(rr + 2, 1, p + 1, q), c_lf = cell(rr + 1, 0, p, q - 1);
                 const int dA = c_up.x + c_dn.x - Hp.y, dB = c_lf.x + c_rt.x - Hq.y;
                 const int tv = max(qB.x, pC.x + c_up.y), tw = max(pB.x, qC.x + c_lf.y);
                 const bool ok = qB.w - pB.w <= pD.x && pB.w - qB.w <= qD.x && dA <= pD.y && dB <= qD.y && tv <= qB.y &&
@@ -210,117 +264,155 @@ __device__ __forceinline__ bool cseg_fits(const CSeg &m, int t, int tail, int li
     return m.ok && t <= m.L && max(t + m.a, m.b) + tail <= limit;
 }
 
-// Re-sweeps the anchors of touched routes (the sweep of eval_intra_kernel, symmetric matrices, cells per step).
+// Re-sweeps touched routes (the sweep of eval_intra_kernel, symmetric matrices).  One block per route; a touched
+// route's records and unit vectors are staged in shared memory first (when it has at most kStage positions), so
+// the sequential sweeps of its anchors run without a memory round trip per step.
+constexpr int kStage = 384;  // positions of one route held in shared memory (88 B each)
+
 __global__ void __launch_bounds__(128) cache_intra_kernel(const CacheArgs a)
 {
-    const int b = blockIdx.y;
+    __shared__ int4 sA[kStage], sB[kStage], sC[kStage], sD[kStage];
+    __shared__ double sX[kStage], sY[kStage], sZ[kStage];
+    __shared__ int sN[kStage];
+
+    const int b = blockIdx.y, r = blockIdx.x;
     const int P = a.npos[b];
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= P - 1) return;
-    const size_t po = static_cast<size_t>(b) * a.pstride;
-    const int4 *RA = a.RA + po, *RB = a.RB + po, *RC = a.RC + po, *RD = a.RD + po;
-    const int *node = a.node + po;
-    const int r = a.route[po + t];
+    if (r >= P - a.n) return;
     const int d0 = a.dirty[2 * b], d1 = a.dirty[2 * b + 1];
-    if (r >= P - a.n || !is_dirty(r, d0, d1)) return;
-    const int rs = a.rstart[static_cast<size_t>(b) * (a.rstride + 1) + r];
-    const int nt = node[t];
-    const bool t_cust = nt != 0;
-    const int4 tA = RA[t], tB = RB[t], tC = RC[t], tD = RD[t];
-    const int dslack = tD.y;
-    const int2 Et = a.E[po + t], SKt = a.SK[po + t];
-    const int4 t1B = RB[t + 1];
-    const int dep_t = tA.x, dep_tm1 = tC.x;
+    if (!is_dirty(r, d0, d1)) return;
+    const size_t po = static_cast<size_t>(b) * a.pstride;
+    const int *rstart = a.rstart + static_cast<size_t>(b) * (a.rstride + 1);
+    const int rs = rstart[r], re = rstart[r + 1];  // both separators
+    const int lo = max(rs - 1, 0), cnt = re - lo + 1;
+    const bool staged = cnt <= kStage;
+    const double *gx = a.PX ? a.PX + static_cast<size_t>(b) * 3 * a.pstride : nullptr;
+    if (staged) {
+        for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+            const size_t o = po + lo + i;
+            sA[i] = a.RA[o];
+            sB[i] = a.RB[o];
+            sC[i] = a.RC[o];
+            sD[i] = a.RD[o];
+            sN[i] = a.node[o];
+            if (gx) {
+                sX[i] = gx[lo + i];
+                sY[i] = gx[a.pstride + lo + i];
+                sZ[i] = gx[2 * static_cast<size_t>(a.pstride) + lo + i];
+            }
+        }
+        __syncthreads();
+    }
+    // one indexing scheme for both cases: arrays addressed by absolute position
+    const int4 *A = staged ? sA - lo : a.RA + po, *B = staged ? sB - lo : a.RB + po;
+    const int4 *C = staged ? sC - lo : a.RC + po, *D = staged ? sD - lo : a.RD + po;
+    const int *Nd = staged ? sN - lo : a.node + po;
+    const double *X = staged ? sX - lo : gx, *Y = staged ? sY - lo : (gx ? gx + a.pstride : nullptr),
+                 *Z = staged ? sZ - lo : (gx ? gx + 2 * static_cast<size_t>(a.pstride) : nullptr);
+    auto cell = [&](int pa, int pb) -> int2 {
+        if (gx) {
+            const double ax = X[pa], ay = Y[pa], az = Z[pa], bx = X[pb], by = Y[pb], bz = Z[pb];
+            const double dx = ax - bx, dy = ay - by, dz = az - bz;
+            const double s2 = fma(dx, dx, fma(dy, dy, dz * dz));
+            return __double2hiint(s2) < a.lim_hi ? cell_i32_fast(s2, a.fd, a.ft) : cell_i32(ax, ay, az, bx, by, bz, a.fd, a.ft);
+        }
+        return __ldg(&a.cells[static_cast<size_t>(b) * a.n * a.pitch + static_cast<size_t>(Nd[pa]) * a.pitch + Nd[pb]]);
+    };
     const bool f2 = a.families & 1, f_rel = a.families & 2, f_swap = a.families & 4;
-    int2 cm = SKt, c0 = Et, cp = make_int2(0, 0), c0_prev = make_int2(0, 0);
-    CSeg F = CSeg{0, 0, 0, true}, Rv = CSeg{0, 0, 0, true};
-    int svc_xm1 = 0, Et_xm1 = 0;
     unsigned long long best = kNoMove;
-    for (int x = t + 1; x < P; ++x) {
-        if (node[x] == 0) break;
-        const int4 xA = RA[x], xB = RB[x], xC = RC[x], xD = RD[x];
-        const int2 Ex = make_int2(xA.z, xD.z);
-        const int zn = xA.y;
-        const int2 cm1 = t_cust ? pos_cell(a, b, t - 1, x + 1) : make_int2(0, 0);
-        const int2 c01 = pos_cell(a, b, t, x + 1), cp1 = pos_cell(a, b, t + 1, x + 1);
-        const CSeg sx = cseg_single(xB.x, xB.y);
-        Rv = (x == t + 1) ? sx : cseg_concat(sx, xB.z + Et_xm1, Rv);
-        if (f2 && x >= t + 2) {
-            const int d = c0.x + cp1.x - Et.x - Ex.x;
-            if (d <= dslack && cseg_fits(Rv, dep_t + c0.y, t1B.z + cp1.y, zn)) {
-                const unsigned long long k = rel_key(d, 0, t - rs, x - rs);
-                best = k < best ? k : best;
-            }
-        }
-        if (f_rel) {
-            if (t_cust) {
-                CSeg m = (x == t + 1) ? sx : cseg_concat(F, svc_xm1 + Et_xm1, sx);
-                m = cseg_concat(m, xB.z + c0.y, cseg_single(tB.x, tB.y));
-                const int d = tC.y + c0.x + c01.x - Ex.x;
-                if (d <= dslack && cseg_fits(m, dep_tm1 + SKt.y, tB.z + c01.y, zn)) {
-                    const unsigned long long k = rel_key(d, 1, t - rs, x - rs);
+    for (int t = rs + threadIdx.x; t < re - 1; t += blockDim.x) {  // anchors: the start separator and every stop but the last
+        const bool t_cust = t != rs;
+        const int4 tA = A[t], tB = B[t], tC = C[t], tD = D[t];
+        const int dslack = tD.y;
+        const int2 Et = make_int2(tA.z, tD.z);
+        const int2 SKt = t_cust ? a.SK[po + t] : make_int2(0, 0);
+        const int4 t1B = B[t + 1];
+        const int dep_t = tA.x, dep_tm1 = tC.x;
+        int2 cm = SKt, c0 = Et, cp = make_int2(0, 0), c0_prev = make_int2(0, 0);
+        CSeg F = CSeg{0, 0, 0, true}, Rv = CSeg{0, 0, 0, true};
+        int svc_xm1 = 0, Et_xm1 = 0;
+        for (int x = t + 1; x < re; ++x) {
+            const int4 xA = A[x], xB = B[x], xC = C[x], xD = D[x];
+            const int2 Ex = make_int2(xA.z, xD.z);
+            const int zn = xA.y;
+            const int2 cm1 = t_cust ? cell(t - 1, x + 1) : make_int2(0, 0);
+            const int2 c01 = cell(t, x + 1), cp1 = cell(t + 1, x + 1);
+            const CSeg sx = cseg_single(xB.x, xB.y);
+            Rv = (x == t + 1) ? sx : cseg_concat(sx, xB.z + Et_xm1, Rv);
+            if (f2 && x >= t + 2) {
+                const int d = c0.x + cp1.x - Et.x - Ex.x;
+                if (d <= dslack && cseg_fits(Rv, dep_t + c0.y, t1B.z + cp1.y, zn)) {
+                    const unsigned long long k = rel_key(d, 0, t - rs, x - rs);
                     best = k < best ? k : best;
                 }
             }
-            if (x >= t + 2) {
-                const CSeg m = cseg_concat(sx, xB.z + cp.y, F);
-                const int d = xC.y + c0.x + cp.x - Et.x;
-                if (d <= dslack && cseg_fits(m, dep_t + c0.y, svc_xm1 + xD.w, zn)) {
-                    const unsigned long long k = rel_key(d, 1, x - rs, t - rs);
+            if (f_rel) {
+                if (t_cust) {
+                    CSeg m = (x == t + 1) ? sx : cseg_concat(F, svc_xm1 + Et_xm1, sx);
+                    m = cseg_concat(m, xB.z + c0.y, cseg_single(tB.x, tB.y));
+                    const int d = tC.y + c0.x + c01.x - Ex.x;
+                    if (d <= dslack && cseg_fits(m, dep_tm1 + SKt.y, tB.z + c01.y, zn)) {
+                        const unsigned long long k = rel_key(d, 1, t - rs, x - rs);
+                        best = k < best ? k : best;
+                    }
+                }
+                if (x >= t + 2) {
+                    const CSeg m = cseg_concat(sx, xB.z + cp.y, F);
+                    const int d = xC.y + c0.x + cp.x - Et.x;
+                    if (d <= dslack && cseg_fits(m, dep_t + c0.y, svc_xm1 + xD.w, zn)) {
+                        const unsigned long long k = rel_key(d, 1, x - rs, t - rs);
+                        best = k < best ? k : best;
+                    }
+                }
+            }
+            if (f_swap && t_cust) {
+                CSeg m;
+                int d;
+                if (x == t + 1) {
+                    m = cseg_concat(sx, xB.z + Et.y, cseg_single(tB.x, tB.y));
+                    d = cm.x + c01.x - (tC.z - Et.x) - Ex.x;
+                } else {
+                    m = cseg_concat(sx, xB.z + cp.y, F);
+                    m = cseg_concat(m, svc_xm1 + c0_prev.y, cseg_single(tB.x, tB.y));
+                    d = cm.x + cp.x - tC.z + c0_prev.x + c01.x - xC.z;
+                }
+                if (d <= dslack && cseg_fits(m, dep_tm1 + cm.y, tB.z + c01.y, zn)) {
+                    const unsigned long long k = rel_key(d, 2, t - rs, x - rs);
                     best = k < best ? k : best;
                 }
             }
+            F = (x == t + 1) ? sx : cseg_concat(F, svc_xm1 + Et_xm1, sx);
+            svc_xm1 = xB.z;
+            Et_xm1 = Ex.y;
+            c0_prev = c0;
+            cm = cm1;
+            c0 = c01;
+            cp = cp1;
         }
-        if (f_swap && t_cust) {
-            CSeg m;
-            int d;
-            if (x == t + 1) {
-                m = cseg_concat(sx, xB.z + Et.y, cseg_single(tB.x, tB.y));
-                d = cm.x + c01.x - (tC.z - Et.x) - Ex.x;
-            } else {
-                m = cseg_concat(sx, xB.z + cp.y, F);
-                m = cseg_concat(m, svc_xm1 + c0_prev.y, cseg_single(tB.x, tB.y));
-                d = cm.x + cp.x - tC.z + c0_prev.x + c01.x - xC.z;
-            }
-            if (d <= dslack && cseg_fits(m, dep_tm1 + cm.y, tB.z + c01.y, zn)) {
-                const unsigned long long k = rel_key(d, 2, t - rs, x - rs);
-                best = k < best ? k : best;
-            }
-        }
-        F = (x == t + 1) ? sx : cseg_concat(F, svc_xm1 + Et_xm1, sx);
-        svc_xm1 = xB.z;
-        Et_xm1 = Ex.y;
-        c0_prev = c0;
-        cm = cm1;
-        c0 = c01;
-        cp = cp1;
     }
     if (best != kNoMove) atomicMin(a.intra + static_cast<size_t>(b) * a.cr + r, best);
 }
 
-// Minimum over the table with positions made absolute again -> best[b] (packed key of SPEC.md §7).
-__global__ void __launch_bounds__(256) cache_argmin_kernel(const CacheArgs a)
+// Minimum over the table with positions made absolute again -> best[b] (packed key of SPEC.md §7).  One block per
+// source route ra (its row of the table plus its own intra entry); best[b] was reset by the state refresh.
+__global__ void __launch_bounds__(128) cache_argmin_kernel(const CacheArgs a)
 {
-    __shared__ unsigned long long s_best[8];
-    const int b = blockIdx.x, tid = threadIdx.x;
+    __shared__ unsigned long long s_best[4];
+    const int b = blockIdx.y, ra = blockIdx.x, tid = threadIdx.x;
     const int R = a.npos[b] - a.n;
+    if (ra >= R) return;
     const int *rstart = a.rstart + static_cast<size_t>(b) * (a.rstride + 1);
-    const unsigned long long *inter = a.inter + static_cast<size_t>(b) * a.cr * a.cr;
-    const unsigned long long *intra = a.intra + static_cast<size_t>(b) * a.cr;
-    auto absolute = [&](unsigned long long k, int ra, int rb) -> unsigned long long {
-        if (k == kNoMove) return k;
-        const unsigned long long pr = (k >> 15) & 0x7FFF, qr = k & 0x7FFF;
-        return (k & 0xFFFFFFFFC0000000ull) | ((pr + rstart[ra]) << 15) | (qr + rstart[rb]);
-    };
+    const unsigned long long *row = a.inter + (static_cast<size_t>(b) * a.cr + ra) * a.cr;
+    const unsigned long long pa = static_cast<unsigned long long>(rstart[ra]);
     unsigned long long best = kNoMove;
-    for (int i = tid; i < R * R; i += blockDim.x) {
-        const int ra = i / R, rb = i - ra * R;
-        const unsigned long long k = absolute(inter[static_cast<size_t>(ra) * a.cr + rb], ra, rb);
-        best = k < best ? k : best;
-    }
-    for (int r = tid; r < R; r += blockDim.x) {
-        const unsigned long long k = absolute(intra[r], r, r);
-        best = k < best ? k : best;
+    for (int rb = tid; rb <= R; rb += blockDim.x) {
+        // entry R of the row stands for the route's own intra entry
+        const bool self = rb == R;
+        const unsigned long long k = self ? a.intra[static_cast<size_t>(b) * a.cr + ra] : row[rb];
+        if (k == kNoMove) continue;
+        const unsigned long long pr = (k >> 15) & 0x7FFF, qr = k & 0x7FFF;
+        const unsigned long long qa = static_cast<unsigned long long>(rstart[self ? ra : rb]);
+        const unsigned long long abs_k = (k & 0xFFFFFFFFC0000000ull) | ((pr + pa) << 15) | (qr + qa);
+        best = abs_k < best ? abs_k : best;
     }
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
@@ -330,8 +422,8 @@ __global__ void __launch_bounds__(256) cache_argmin_kernel(const CacheArgs a)
     if ((tid & 31) == 0) s_best[tid >> 5] = best;
     __syncthreads();
     if (tid == 0) {
-        for (int w = 1; w < 8; ++w) best = s_best[w] < best ? s_best[w] : best;
-        a.best[b] = best;
+        for (int w = 1; w < 4; ++w) best = s_best[w] < best ? s_best[w] : best;
+        if (best != kNoMove) atomicMin(a.best + b, best);
     }
 }
 
@@ -450,17 +542,22 @@ int cache_evaluate(rt_problem *p, int families, cudaStream_t st)
 {
     rt_engine *e = p->e;
     const CacheArgs a = cache_args(p, families);
+    if (!p->best_clean) {  // the arg-min accumulates into best[]: it must start from "no move"
+        RT_CUDA(e, cudaMemsetAsync(p->best, 0xFF, static_cast<size_t>(p->batch) * 8, st));
+    }
     cache_prepare_kernel<<<p->batch, 256, 0, st>>>(a);
     RT_CUDA(e, cudaGetLastError());
     if (families & 6) {
         dim3 grid(kNumSMs * 4 / std::max(1, std::min(p->batch, kNumSMs * 4)) + 1, p->batch);
-        cache_inter_kernel<<<grid, kBandThreads, 0, st>>>(a);
+        if (a.PX) cache_inter_kernel<true><<<grid, kBandThreads, 0, st>>>(a);
+        else cache_inter_kernel<false><<<grid, kBandThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
-    dim3 gi((p->grows + 127) / 128, p->batch);
+    dim3 gi(p->cache_r, p->batch);
     cache_intra_kernel<<<gi, 128, 0, st>>>(a);
     RT_CUDA(e, cudaGetLastError());
-    cache_argmin_kernel<<<p->batch, 256, 0, st>>>(a);
+    dim3 ga(p->cache_r, p->batch);
+    cache_argmin_kernel<<<ga, 128, 0, st>>>(a);
     RT_CUDA(e, cudaGetLastError());
     p->best_clean = false;
     return RT_OK;
