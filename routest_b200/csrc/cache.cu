@@ -24,7 +24,7 @@ namespace rt {
 namespace {
 
 constexpr int kTileRows = 8, kTileCols = 128;
-constexpr int kTallRows = 64;     // column-band tiles are tall: their row loop is cheap and there are P/8 of them otherwise
+constexpr int kTallRows = 16;     // column-band tiles are tall: their row loop is cheap and there are P/8 of them otherwise
 constexpr int kTallFlag = 1 << 30;  // in a packed tile: rows are counted in units of kTallRows
 constexpr int kBandThreads = kTileCols;
 constexpr int kAllDirty = -2;
