@@ -724,26 +724,53 @@ static int local_search_impl(rt_problem *p, int families, int max_moves, int mod
     // The host only paces the loop: kChunk iterations are enqueued blind (an instance that has reached its local
     // optimum turns its own later iterations into no-ops on the device), then one 4-byte-per-instance read decides
     // whether to go on.
+    auto one_iteration = [&]() -> int {
+        if (cached) {
+            RT_TRY(cache_evaluate(p, families, e->stream));
+            return cache_apply(p, true, e->stream);
+        }
+        RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, e->stream));
+        return apply_moves_launch(p, p->best, false, true, e->stream);
+    };
+    // An iteration is a fixed sequence of a dozen small launches with constant arguments: it is captured once into a
+    // CUDA graph and replayed (the loop is launch-bound at small and medium sizes).  If capture is refused for any
+    // reason the iterations are launched one kernel at a time instead.
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    if (max_moves > 1 && cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+        const int rc_it = one_iteration();
+        const cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
+        if (rc_it != RT_OK || ce != cudaSuccess || !graph ||
+            cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) {
+            if (graph) cudaGraphDestroy(graph);
+            graph = nullptr;
+            exec = nullptr;
+            (void)cudaGetLastError();
+        }
+    }
     const int kChunk = 32;
     int issued = 0;
     bool all_done = false;
-    while (!all_done && issued < max_moves) {
+    int loop_rc = RT_OK;
+    while (!all_done && issued < max_moves && loop_rc == RT_OK) {
         const int todo = std::min(kChunk, max_moves - issued);
-        for (int i = 0; i < todo; ++i) {
-            if (cached) {
-                RT_TRY(cache_evaluate(p, families, e->stream));
-                RT_TRY(cache_apply(p, true, e->stream));
+        for (int i = 0; i < todo && loop_rc == RT_OK; ++i) {
+            if (exec) {
+                if (cudaGraphLaunch(exec, e->stream) != cudaSuccess) loop_rc = fail(e, RT_ERR_CUDA, "cudaGraphLaunch failed");
             } else {
-                RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, e->stream));
-                RT_TRY(apply_moves_launch(p, p->best, false, true, e->stream));
+                loop_rc = one_iteration();
             }
         }
+        if (loop_rc != RT_OK) break;
         issued += todo;
         RT_CUDA(e, cudaMemcpyAsync(done_h, p->done, p->batch * 4, cudaMemcpyDeviceToHost, e->stream));
         RT_CUDA(e, cudaStreamSynchronize(e->stream));
         all_done = true;
         for (int b = 0; b < p->batch; ++b) all_done = all_done && done_h[b] != 0;
     }
+    if (exec) cudaGraphExecDestroy(exec);
+    if (graph) cudaGraphDestroy(graph);
+    RT_TRY(loop_rc);
     if (cached) RT_TRY(state_refresh(p, e->stream));  // bring the route-order matrix back in step with the routes
     if (moves_out) RT_CUDA(e, cudaMemcpyAsync(moves_out, p->moves, p->batch * 4, cudaMemcpyDeviceToHost, e->stream));
     if (cost_out) RT_CUDA(e, cudaMemcpyAsync(cost_out, p->cost, p->batch * 8, cudaMemcpyDeviceToHost, e->stream));
