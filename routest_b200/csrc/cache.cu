@@ -427,30 +427,6 @@ __global__ void __launch_bounds__(128) cache_argmin_kernel(const CacheArgs a)
     }
 }
 
-// Notes which routes the key about to be applied touches (read from the state BEFORE the move).
-__global__ void cache_mark_dirty_kernel(const unsigned long long *__restrict__ keys, const int *__restrict__ route_all,
-                                        const int *__restrict__ done, int pstride, int batch, int improving_only,
-                                        int *__restrict__ dirty)
-{
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= batch) return;
-    const unsigned long long key = keys[b];
-    const int delta = static_cast<int>(static_cast<unsigned>(key >> 32) - 0x80000000u);
-    int d0 = -1, d1 = -1;
-    if (!done[b] && key != kNoMove && !(improving_only && delta >= 0)) {
-        const int family = static_cast<int>((key >> 30) & 3), p = static_cast<int>((key >> 15) & 0x7FFF),
-                  q = static_cast<int>(key & 0x7FFF);
-        const int *route = route_all + static_cast<size_t>(b) * pstride;
-        if (family == 0) d0 = route[p + 1];
-        else {
-            d0 = route[p];
-            d1 = route[q];
-        }
-    }
-    dirty[2 * b] = d0;
-    dirty[2 * b + 1] = d1;
-}
-
 __global__ void cache_all_dirty_kernel(int *dirty, int batch)
 {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -525,8 +501,7 @@ static CacheArgs cache_args(rt_problem *p, int families)
 // Route state without the route-order matrix: position vectors + tables.
 static int cache_state_refresh(rt_problem *p, cudaStream_t st)
 {
-    if (p->cells_from_coords) RT_TRY(position_vectors_refresh(p, st));
-    return state_tables_refresh(p, st);
+    return state_tables_refresh(p, st, /*with_vectors=*/true);
 }
 
 int cache_mark_all_dirty(rt_problem *p, cudaStream_t st)
@@ -565,12 +540,8 @@ int cache_evaluate(rt_problem *p, int families, cudaStream_t st)
 
 int cache_apply(rt_problem *p, bool improving_only, cudaStream_t st)
 {
-    rt_engine *e = p->e;
     int *misc = static_cast<int *>(p->cache_misc.p);
-    cache_mark_dirty_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, p->route, p->done, p->pstride, p->batch,
-                                                                    improving_only ? 1 : 0, misc);
-    RT_CUDA(e, cudaGetLastError());
-    RT_TRY(apply_only_launch(p, p->best, false, improving_only, st));
+    RT_TRY(apply_only_launch(p, p->best, false, improving_only, st, misc));  // also notes the touched routes
     return cache_state_refresh(p, st);
 }
 

@@ -94,7 +94,7 @@ inline int2 *position_matrix_t(const rt_problem *p) { return p->GTbuf.p ? static
 
 int state_refresh(rt_problem *p, cudaStream_t st);
 int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready = false);
-int state_tables_refresh(rt_problem *p, cudaStream_t st);
+int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors = false);
 int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d,
                       bool signed_keys, cudaStream_t st);
 int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsigned char *feas_d, cudaStream_t st);
@@ -103,7 +103,7 @@ int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool sig
 int greedy_launch(rt_problem *p, bool use_tw, cudaStream_t st);
 int position_vectors_refresh(rt_problem *p, cudaStream_t st);
 int apply_only_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
-                      cudaStream_t st);
+                      cudaStream_t st, int *dirty_d = nullptr);
 // incremental local search (cache.cu)
 bool cache_usable(const rt_problem *p);
 int cache_begin(rt_problem *p, cudaStream_t st);

@@ -62,13 +62,41 @@ __global__ void __launch_bounds__(256) state_gather_kernel(const double *__restr
                                                            const int *__restrict__ npos, int n, int pitch, int pstride,
                                                            float fd, float ft, int4 *__restrict__ RB,
                                                            int2 *__restrict__ E, int2 *__restrict__ SK,
-                                                           int2 *__restrict__ ER)
+                                                           int2 *__restrict__ ER, const double *__restrict__ xyz,
+                                                           double *__restrict__ PX_out)
 {
     const int b = blockIdx.y;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     const int P = npos[b];
-    if (p >= P) return;
     const int *nd = node + static_cast<size_t>(b) * pstride;
+    if (xyz && p < pstride) {
+        // fused position_vectors_kernel (the incremental search has no matrix kernel between the two): the vectors
+        // of p-1, p, p+1 are read straight from the node-order array, p's own is also written out in route order
+        const int cur = p < P ? nd[p] : 0;
+        const double *v = xyz + static_cast<size_t>(b) * 3 * n;
+        double *px = PX_out + static_cast<size_t>(b) * 3 * pstride;
+        const double cx = v[cur], cy = v[n + cur], cz = v[2 * n + cur];
+        px[p] = cx;
+        px[pstride + p] = cy;
+        px[2 * pstride + p] = cz;
+        if (p >= P) return;
+        const size_t o = static_cast<size_t>(b) * pstride + p;
+        RB[o] = stops[static_cast<size_t>(b) * n + cur];
+        int2 e = make_int2(0, 0), sk = make_int2(0, 0);
+        if (p + 1 < P) {
+            const int nx = nd[p + 1];
+            const double nxx = v[nx], nxy = v[n + nx], nxz = v[2 * n + nx];
+            e = cell_i32(cx, cy, cz, nxx, nxy, nxz, fd, ft);
+            if (cur != 0) {
+                const int pv = nd[p - 1];
+                sk = cell_i32(v[pv], v[n + pv], v[2 * n + pv], nxx, nxy, nxz, fd, ft);
+            }
+        }
+        E[o] = e;
+        SK[o] = sk;
+        return;
+    }
+    if (p >= P) return;
     const int cur = nd[p];
     const size_t o = static_cast<size_t>(b) * pstride + p;
     RB[o] = stops[static_cast<size_t>(b) * n + cur];
@@ -274,11 +302,16 @@ __global__ void __launch_bounds__(256) apply_moves_kernel(const unsigned long lo
                                                           int improving_only, int *__restrict__ node_all,
                                                           int *__restrict__ tmp_all, const int *__restrict__ npos,
                                                           int pstride, int *__restrict__ done, int *__restrict__ moves,
-                                                          unsigned long long *__restrict__ hist, int hist_cap)
+                                                          unsigned long long *__restrict__ hist, int hist_cap,
+                                                          const int *__restrict__ route_all, int *__restrict__ dirty)
 {
     const int b = blockIdx.x, tid = threadIdx.x;
     unsigned long long key = keys[b];
     if (signed_keys) key ^= 0x8000000000000000ull;
+    if (dirty && tid == 0) {  // incremental search: which routes this move touches (none if nothing is applied)
+        dirty[2 * b] = -1;
+        dirty[2 * b + 1] = -1;
+    }
     if (done[b]) return;
     const int delta = static_cast<int>(static_cast<unsigned>(key >> 32) - 0x80000000u);
     if (key == kNoMove || (improving_only && delta >= 0)) {
@@ -293,6 +326,11 @@ __global__ void __launch_bounds__(256) apply_moves_kernel(const unsigned long lo
     if (p >= P || q >= P) {  // malformed key: refuse
         if (tid == 0) done[b] = 2;
         return;
+    }
+    if (dirty && tid == 0) {  // route ids of the state BEFORE the move (the tables are refreshed afterwards)
+        const int *route = route_all + static_cast<size_t>(b) * pstride;
+        dirty[2 * b] = family == 0 ? route[p + 1] : route[p];
+        dirty[2 * b + 1] = family == 0 ? -1 : route[q];
     }
     if (family == 2) {
         if (tid == 0) {
@@ -379,15 +417,17 @@ int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready)
 }
 
 // G -> E/SK/RB, B/Z/load/dist, the packed records; resets the best keys.
-int state_tables_refresh(rt_problem *p, cudaStream_t st)
+int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors)
 {
     rt_engine *e = p->e;
     dim3 g1((p->grows + 255) / 256, p->batch);
-    state_gather_kernel<<<g1, 256, 0, st>>>(p->cells_from_coords ? p->PX : nullptr, p->cells, p->stops, p->node, p->npos,
+    const bool fused = with_vectors && p->cells_from_coords;  // also produce the position-ordered vectors
+    dim3 gg(fused ? (p->pstride + 255) / 256 : g1.x, p->batch);
+    state_gather_kernel<<<gg, 256, 0, st>>>(p->cells_from_coords ? p->PX : nullptr, p->cells, p->stops, p->node, p->npos,
                                             p->n, p->pitch, p->pstride,
                                             static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale),
                                             static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale), p->RB, p->E, p->SK,
-                                            p->symmetric ? nullptr : p->ER);
+                                            p->symmetric ? nullptr : p->ER, fused ? p->xyz : nullptr, p->PX);
     RT_CUDA(e, cudaGetLastError());
     state_routes_kernel<<<p->batch, kScanThreads, 0, st>>>(p->node, p->npos, p->nroutes, p->pstride, p->rstride, p->route,
                                                            p->rstart, p->cost, p->feasible, p->best);
@@ -440,11 +480,11 @@ int position_vectors_refresh(rt_problem *p, cudaStream_t st)
 }
 
 int apply_only_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
-                      cudaStream_t st)
+                      cudaStream_t st, int *dirty_d)
 {
     apply_moves_kernel<<<p->batch, 256, 0, st>>>(keys_d, signed_keys ? 1 : 0, improving_only ? 1 : 0, p->node,
                                                  p->node_tmp, p->npos, p->pstride, p->done, p->moves, p->hist,
-                                                 p->hist_cap);
+                                                 p->hist_cap, p->route, dirty_d);
     RT_CUDA(p->e, cudaGetLastError());
     return RT_OK;
 }
