@@ -6,9 +6,10 @@
 //   * a stop is accepted iff load+demand <= cap and trip_dist + (D[cur][idx] + D[idx][0]) <= max_dist, in FP64 and
 //     with this association (utils.py:126-129); a rejected stop does not end the trip;
 //   * accepted: load += demand, trip_dist += D[cur][idx], cur = idx (utils.py:130-133).
-// The chain is sequential, so one warp per instance walks it: the 32 lanes test the next 32 candidates against the
-// current (load, trip_dist, cur); the first lane that fits is accepted, lanes before it are rejected for this trip
-// (exactly what the sequential loop would have decided), lanes after it re-read D[cur][.] and are tested again.
+// The chain is sequential, so one warp per instance walks it.  A pass fetches the next 128 candidates (four per lane,
+// all loads in flight together), then tests them 32 at a time against the current (load, trip_dist, cur): the first
+// lane that fits is accepted, lanes before it are rejected for this trip (exactly what the sequential loop would
+// have decided), lanes after it — and the later chunks of the pass — re-read D[cur][.] and are tested again.
 // Deviation, documented in SPEC.md §4: where the reference would loop forever (a stop that fits no trip on its
 // own) the kernel stops with RT_ERR_INFEASIBLE_STOP.
 #include "problem.cuh"
@@ -102,57 +103,74 @@ __global__ void __launch_bounds__(32) greedy_trips_kernel(const GreedyArgs a)
 
     int m = n - 1, done = 0, trips = 0, status = RT_OK;
     if (lane == 0) trip_off[0] = 0;
+    constexpr int kChunks = 4;  // 128 candidates per pass: their loads are issued together, then tested chunk by chunk
     while (m > 0) {
         double load = 0.0, trip_dist = 0.0;
         int cur = 0, accepted = 0;
         long long clock = static_cast<long long>(depot.x) + depot.z;
-        for (int pos = 0; pos < m; pos += 32) {
-            const int k = pos + lane;
-            int idx = k < m ? order[k] : -1;
-            double dem = 0.0, dback = 0.0, dcur = 0.0;
-            int tcur = 0, tback = 0;
-            int4 st = make_int4(0, 0, 0, 0);
-            if (idx > 0) {
-                dem = demand[idx];
-                dback = dist(idx, 0);
-                dcur = dist(cur, idx);
-                if (tw) {
-                    st = stops[idx];
-                    tcur = M[static_cast<size_t>(cur) * a.pitch + idx].y;
-                    tback = M[static_cast<size_t>(idx) * a.pitch].y;
-                }
-            }
-            unsigned alive = __ballot_sync(0xffffffffu, idx > 0);
-            while (alive) {
-                bool ok = false;
-                long long arr = 0;
-                if ((alive >> lane) & 1u) {
-                    ok = (load + dem) <= cap && (trip_dist + (dcur + dback)) <= maxd;
-                    if (ok && tw) {
-                        arr = clock + tcur;
-                        if (arr < st.x) arr = st.x;
-                        ok = arr <= st.y && arr + st.z + tback <= depot.y;
+        for (int pos = 0; pos < m; pos += 32 * kChunks) {
+            int idx[kChunks], tcur[kChunks], tback[kChunks];
+            double dem[kChunks], dback[kChunks], dcur[kChunks];
+            int4 st[kChunks];
+            const int cur_at_load = cur;
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                const int k = pos + 32 * c + lane;
+                idx[c] = k < m ? order[k] : -1;
+                dem[c] = dback[c] = dcur[c] = 0.0;
+                tcur[c] = tback[c] = 0;
+                st[c] = make_int4(0, 0, 0, 0);
+                if (idx[c] > 0) {
+                    dem[c] = demand[idx[c]];
+                    dback[c] = dist(idx[c], 0);
+                    dcur[c] = dist(cur, idx[c]);
+                    if (tw) {
+                        st[c] = stops[idx[c]];
+                        tcur[c] = M[static_cast<size_t>(cur) * a.pitch + idx[c]].y;
+                        tback[c] = M[static_cast<size_t>(idx[c]) * a.pitch].y;
                     }
                 }
-                const unsigned mask = __ballot_sync(0xffffffffu, ok);
-                if (!mask) break;
-                const int f = __ffs(mask) - 1;
-                const int idx_f = __shfl_sync(0xffffffffu, idx, f);
-                const double dem_f = __shfl_sync(0xffffffffu, dem, f), dcur_f = __shfl_sync(0xffffffffu, dcur, f);
-                const long long arr_f = __shfl_sync(0xffffffffu, arr, f);
-                const int svc_f = __shfl_sync(0xffffffffu, st.z, f);
-                if (lane == 0) order_out[done] = idx_f;
-                ++done;
-                ++accepted;
-                load += dem_f;
-                trip_dist += dcur_f;
-                cur = idx_f;
-                clock = arr_f + svc_f;
-                if (lane == f) order[k] = -idx;  // visited
-                alive &= ~((2u << f) - 1u);       // lanes up to f are decided for this trip
-                if ((alive >> lane) & 1u) {
-                    dcur = dist(cur, idx);
-                    if (tw) tcur = M[static_cast<size_t>(cur) * a.pitch + idx].y;
+            }
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                const int k = pos + 32 * c + lane;
+                if (pos + 32 * c >= m) break;
+                if (cur != cur_at_load && idx[c] > 0) {  // an earlier chunk of this pass accepted a stop
+                    dcur[c] = dist(cur, idx[c]);
+                    if (tw) tcur[c] = M[static_cast<size_t>(cur) * a.pitch + idx[c]].y;
+                }
+                unsigned alive = __ballot_sync(0xffffffffu, idx[c] > 0);
+                while (alive) {
+                    bool ok = false;
+                    long long arr = 0;
+                    if ((alive >> lane) & 1u) {
+                        ok = (load + dem[c]) <= cap && (trip_dist + (dcur[c] + dback[c])) <= maxd;
+                        if (ok && tw) {
+                            arr = clock + tcur[c];
+                            if (arr < st[c].x) arr = st[c].x;
+                            ok = arr <= st[c].y && arr + st[c].z + tback[c] <= depot.y;
+                        }
+                    }
+                    const unsigned mask = __ballot_sync(0xffffffffu, ok);
+                    if (!mask) break;
+                    const int f = __ffs(mask) - 1;
+                    const int idx_f = __shfl_sync(0xffffffffu, idx[c], f);
+                    const double dem_f = __shfl_sync(0xffffffffu, dem[c], f), dcur_f = __shfl_sync(0xffffffffu, dcur[c], f);
+                    const long long arr_f = __shfl_sync(0xffffffffu, arr, f);
+                    const int svc_f = __shfl_sync(0xffffffffu, st[c].z, f);
+                    if (lane == 0) order_out[done] = idx_f;
+                    ++done;
+                    ++accepted;
+                    load += dem_f;
+                    trip_dist += dcur_f;
+                    cur = idx_f;
+                    clock = arr_f + svc_f;
+                    if (lane == f) order[k] = -idx[c];  // visited
+                    alive &= ~((2u << f) - 1u);          // lanes up to f are decided for this trip
+                    if ((alive >> lane) & 1u) {
+                        dcur[c] = dist(cur, idx[c]);
+                        if (tw) tcur[c] = M[static_cast<size_t>(cur) * a.pitch + idx[c]].y;
+                    }
                 }
             }
         }
