@@ -499,17 +499,30 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     EvalArgs a = make_args(p, families, shard_index, shard_count, p->best);
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;  // largest P of the batch
     const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
+    // The sweep kernel is latency bound (a sequential walk per anchor, a few warps per SM) and the tile kernel is ALU
+    // bound: they only share the best[] atomics, so the sweep runs on the side stream underneath the tile kernel.
+    const bool overlap = (families & 6) && p->side_stream;
+    cudaStream_t st_intra = st;
+    if (overlap) {
+        RT_CUDA(e, cudaEventRecord(p->ev_fork, st));
+        RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, p->ev_fork, 0));
+        st_intra = p->side_stream;
+    }
+    {
+        dim3 grid((shard_rows + kIntraThreads - 1) / kIntraThreads, p->batch);
+        if (p->symmetric) eval_intra_kernel<false, false><<<grid, kIntraThreads, 0, st_intra>>>(a);
+        else eval_intra_kernel<false, true><<<grid, kIntraThreads, 0, st_intra>>>(a);
+        RT_CUDA(e, cudaGetLastError());
+    }
     if (families & 6) {
         dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + kStripRows - 1) / kStripRows, p->batch);
         if (p->symmetric) eval_inter_kernel<false, false><<<grid, kInterThreads, 0, st>>>(a);
         else eval_inter_kernel<false, true><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
-    {
-        dim3 grid((shard_rows + kIntraThreads - 1) / kIntraThreads, p->batch);
-        if (p->symmetric) eval_intra_kernel<false, false><<<grid, kIntraThreads, 0, st>>>(a);
-        else eval_intra_kernel<false, true><<<grid, kIntraThreads, 0, st>>>(a);
-        RT_CUDA(e, cudaGetLastError());
+    if (overlap) {
+        RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
+        RT_CUDA(e, cudaStreamWaitEvent(st, p->ev_join, 0));
     }
     if (best_d != p->best || signed_keys)
         finish_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, best_d, p->batch, signed_keys ? 1 : 0);
