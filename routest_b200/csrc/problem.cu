@@ -519,13 +519,18 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
             node[b * PS + npos[b] - 1] != 0)
             return fail(e, RT_ERR_INVALID_ARG, "instance %zu: malformed position array", b);
     cudaStream_t st = e->stream;
+    // What the matrix needs (coordinates, routes) goes first on the compute stream; the stop records and limits, which
+    // only the state tables read, travel on the copy stream underneath the unit-vector and matrix kernels.
     RT_CUDA(e, cudaMemcpyAsync(p->lat, lat, B * N * 8, cudaMemcpyHostToDevice, st));
     RT_CUDA(e, cudaMemcpyAsync(p->lon, lon, B * N * 8, cudaMemcpyHostToDevice, st));
-    RT_CUDA(e, cudaMemcpyAsync(p->stops, stops, B * N * 16, cudaMemcpyHostToDevice, st));
-    RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, B * 4, cudaMemcpyHostToDevice, st));
-    RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, B * 8, cudaMemcpyHostToDevice, st));
     RT_CUDA(e, cudaMemcpyAsync(p->node, node, B * PS * 4, cudaMemcpyHostToDevice, st));
     RT_CUDA(e, cudaMemcpyAsync(p->npos, npos, B * 4, cudaMemcpyHostToDevice, st));
+    RT_CUDA(e, cudaEventRecord(e->ev[0], st));                       // earlier work on the buffers has been ordered
+    RT_CUDA(e, cudaStreamWaitEvent(e->copy_stream, e->ev[0], 0));
+    RT_CUDA(e, cudaMemcpyAsync(p->stops, stops, B * N * 16, cudaMemcpyHostToDevice, e->copy_stream));
+    RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, B * 4, cudaMemcpyHostToDevice, e->copy_stream));
+    RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, B * 8, cudaMemcpyHostToDevice, e->copy_stream));
+    RT_CUDA(e, cudaEventRecord(e->ev[1], e->copy_stream));
     // Coordinates are range-checked by the unit-vector kernel (off the host's critical path); stop records are taken
     // as they are (rt_problem_set_stops is the validating entry point) — out-of-range values cannot fault a kernel.
     int *bad_flag = p->coord_flag;
@@ -545,7 +550,7 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     RT_TRY(ensure_position_matrix(p));
-    RT_TRY(state_refresh(p, st));
+    RT_TRY(state_refresh(p, st, e->ev[1]));
     RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, st));
     RT_TRY(stage(p, 8));
     int *flag_h = static_cast<int *>(p->host_stage);

@@ -92,7 +92,7 @@ namespace rt {
 inline int2 *position_matrix(const rt_problem *p) { return p->Gbuf.p ? static_cast<int2 *>(p->Gbuf.p) + 16 : nullptr; }
 inline int2 *position_matrix_t(const rt_problem *p) { return p->GTbuf.p ? static_cast<int2 *>(p->GTbuf.p) + 16 : nullptr; }
 
-int state_refresh(rt_problem *p, cudaStream_t st);
+int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for = nullptr);
 int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready = false);
 int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors = false);
 int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d,

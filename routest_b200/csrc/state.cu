@@ -448,7 +448,7 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors)
 
 // Both halves.  The state tables do not read G (state_gather_kernel rebuilds the cells it needs), so their four small
 // latency-bound kernels run on a side stream underneath the matrix kernel and join before anything evaluates moves.
-int state_refresh(rt_problem *p, cudaStream_t st)
+int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for)
 {
     rt_engine *e = p->e;
     if (!p->side_stream) {
@@ -464,6 +464,7 @@ int state_refresh(rt_problem *p, cudaStream_t st)
     }
     RT_CUDA(e, cudaEventRecord(p->ev_fork, st));
     RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, p->ev_fork, 0));
+    if (tables_wait_for) RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, tables_wait_for, 0));  // e.g. stop records still in flight
     RT_TRY(position_matrix_refresh(p, st, /*vectors_ready=*/true));
     RT_TRY(state_tables_refresh(p, p->side_stream));
     RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
