@@ -3,7 +3,7 @@
 `predict_eta_minutes` keeps the reference's keyword-only signature, defaults and return convention
 (ml.py:23-58): `(minutes, iso_completion_time)` or `(None, None)` when no model is available.  The model is not a
 pickle (ml.py:6-21) but an ensemble in the engine's tree format (SPEC.md §9.2); `export_sklearn` and
-`export_xgboost_json` write that format.  `ETA_MODEL_PATH` names the file, as in the reference (ml.py:7).
+`export_xgboost_json` (XGBoost `.json` and `.ubj` dumps) write that format.  `ETA_MODEL_PATH` names the file, as in the reference (ml.py:7).
 """
 from __future__ import annotations
 
@@ -146,21 +146,159 @@ def export_sklearn(model) -> bytes:
     return pack_model(trees, base, model.n_features_in_)
 
 
+_IDENTITY_OBJECTIVES = {"reg:squarederror", "reg:linear", "reg:absoluteerror", "reg:pseudohubererror",
+                        "reg:quantileerror", "reg:squaredlogerror"}   # prediction = base_score + sum of leaves
+
+
+def read_ubjson(buf: bytes):
+    """Minimal Universal Binary JSON reader (the container XGBoost's `save_model('*.ubj')` writes): big-endian
+    scalars, strings, arrays and objects, including the strongly typed `[$type#count` containers it uses for the
+    per-tree arrays.  Returns the same dict/list structure `json.load` gives for the `.json` dump."""
+    pos = 0
+    scalar = {b"i": ">b", b"U": ">B", b"I": ">h", b"l": ">i", b"L": ">q", b"d": ">f", b"D": ">d"}
+
+    def take(n):
+        nonlocal pos
+        if pos + n > len(buf):
+            raise ValueError("UBJSON: truncated input")
+        out = buf[pos:pos + n]
+        pos += n
+        return out
+
+    def value(marker=None):
+        m = marker or take(1)
+        while m == b"N":
+            m = take(1)
+        if m in scalar:
+            fmt = scalar[m]
+            return struct.unpack(fmt, take(struct.calcsize(fmt)))[0]
+        if m == b"Z":
+            return None
+        if m == b"T":
+            return True
+        if m == b"F":
+            return False
+        if m == b"C":
+            return take(1).decode("latin-1")
+        if m in (b"S", b"H"):
+            return take(length()).decode("utf-8")
+        if m == b"[":
+            typ, count = header()
+            if typ in scalar and count is not None:      # typed numeric array: one bulk unpack
+                fmt = scalar[typ]
+                return list(struct.unpack(f">{count}{fmt[1]}", take(count * struct.calcsize(fmt))))
+            out = []
+            while count is None or len(out) < count:
+                if count is None:
+                    nxt = take(1)
+                    if nxt == b"]":
+                        break
+                    out.append(value(nxt))
+                else:
+                    out.append(value(typ))
+            return out
+        if m == b"{":
+            typ, count = header()
+            out = {}
+            while count is None or len(out) < count:
+                if count is None:
+                    nxt = take(1)
+                    if nxt == b"}":
+                        break
+                    key = take(length(nxt)).decode("utf-8")
+                else:
+                    key = take(length()).decode("utf-8")
+                out[key] = value(typ)
+            return out
+        raise ValueError(f"UBJSON: unknown marker {m!r} at byte {pos - 1}")
+
+    def length(marker=None):
+        n = value(marker)
+        if not isinstance(n, int) or isinstance(n, bool) or n < 0:
+            raise ValueError("UBJSON: bad length")
+        return n
+
+    def header():
+        nonlocal pos
+        typ = count = None
+        if buf[pos:pos + 1] == b"$":
+            pos += 1
+            typ = take(1)
+            if buf[pos:pos + 1] != b"#":
+                raise ValueError("UBJSON: '$' without '#'")
+        if buf[pos:pos + 1] == b"#":
+            pos += 1
+            count = length()
+        return typ, count
+
+    doc = value()
+    return doc
+
+
+def load_xgboost_dump(path: str) -> dict:
+    """`.json` or `.ubj` model file -> the document `export_xgboost_json` takes (XGBoost picks the container by
+    file extension; so does this, falling back to sniffing: a JSON object's first key starts with a quote)."""
+    with open(path, "rb") as f:
+        raw = f.read()
+    if path.endswith(".ubj") or (not path.endswith(".json") and raw[:1] == b"{" and raw[1:2] not in (b'"', b" ", b"\n", b"}")):
+        return read_ubjson(raw)
+    return json.loads(raw.decode("utf-8"))
+
+
+def _xgb_scalar(v) -> float:
+    """XGBoost writes model parameters as strings: "5E-1", and since 3.x "[5E-1]" (one value per target)."""
+    if isinstance(v, (list, tuple)):
+        if len(v) != 1:
+            raise ValueError("multi-target XGBoost models are not supported")
+        v = v[0]
+    if isinstance(v, str):
+        v = v.strip()
+        if v.startswith("["):
+            parts = [x for x in v.strip("[]").split(",") if x.strip()]
+            if len(parts) != 1:
+                raise ValueError("multi-target XGBoost models are not supported")
+            v = parts[0]
+    return float(v)
+
+
 def export_xgboost_json(path_or_dict) -> bytes:
-    """XGBoost `save_model('*.json')` dump (gbtree, reg:* objective) -> RTE1.  XGBoost already goes left on
-    `x < split_condition` with float32 x and routes missing values by `default_left`."""
-    doc = path_or_dict if isinstance(path_or_dict, dict) else json.load(open(path_or_dict))
+    """XGBoost `save_model('*.json' | '*.ubj')` dump (gbtree or dart, identity-link regression objective) -> RTE1.
+    XGBoost already goes left on `x < split_condition` with float32 x and routes missing values by `default_left`.
+    What the engine's format cannot express is refused with ValueError rather than exported wrongly: categorical
+    splits, multi-target trees, objectives whose prediction is a transform of the margin (logistic, gamma, ...)."""
+    doc = path_or_dict if isinstance(path_or_dict, dict) else load_xgboost_dump(path_or_dict)
     learner = doc["learner"]
-    base = float(learner["learner_model_param"]["base_score"])
-    n_feat = int(learner["learner_model_param"]["num_feature"])
+    objective = (learner.get("objective") or {}).get("name")
+    if objective is not None and objective not in _IDENTITY_OBJECTIVES:
+        raise ValueError(f"objective {objective!r} transforms the margin; only identity-link regression is supported")
+    base = _xgb_scalar(learner["learner_model_param"]["base_score"])
+    n_feat = int(_xgb_scalar(learner["learner_model_param"]["num_feature"]))
+    if int(_xgb_scalar(learner["learner_model_param"].get("num_target", 1))) != 1:
+        raise ValueError("multi-target XGBoost models are not supported")
+    booster = learner["gradient_booster"]
+    weights = None
+    if booster.get("name") == "dart":                    # dart = gbtree + one output weight per tree
+        weights = [float(w) for w in booster["weight_drop"]]
+        booster = booster["gbtree"]
+    elif booster.get("name") not in (None, "gbtree"):
+        raise ValueError(f"booster {booster.get('name')!r} is not a tree ensemble")
     trees = []
-    for tr in learner["gradient_booster"]["model"]["trees"]:
+    for ti, tr in enumerate(booster["model"]["trees"]):
         L, R = tr["left_children"], tr["right_children"]
         cond, feat, dl = tr["split_conditions"], tr["split_indices"], tr["default_left"]
+        if any(int(t) != 0 for t in tr.get("split_type", ())):
+            raise ValueError(f"tree {ti}: categorical splits are not supported")
+        if len(L) > 65535:
+            raise ValueError(f"tree {ti}: {len(L)} nodes exceed the format's 65535 per tree")
+        w = 1.0 if weights is None else weights[ti]
 
-        def emit(k, new_left, L=L, cond=cond, feat=feat, dl=dl):
+        def emit(k, new_left, L=L, cond=cond, feat=feat, dl=dl, w=w):
             if L[k] < 0:
-                return (float(cond[k]), 0, 0, 1)     # leaves keep their value in split_conditions
+                # leaves keep their value in split_conditions; a dart weight multiplies in float32 as XGBoost does
+                leaf = np.float32(cond[k]) if w == 1.0 else np.float32(cond[k]) * np.float32(w)
+                return (float(leaf), 0, 0, 1)
+            if not 0 <= int(feat[k]) < n_feat:
+                raise ValueError(f"tree {ti}: split on feature {feat[k]} outside 0..{n_feat - 1}")
             return (float(cond[k]), new_left, int(feat[k]), 2 if dl[k] else 0)
         trees.append(_relabel(L, R, emit))
     return pack_model(trees, base, n_feat)

@@ -80,6 +80,94 @@ def test_xgboost_json_export():
     assert np.allclose(O.eta_eval(blob, rows), [0.5 + 1.25 + 0.125, 0.5 - 2.0 + 0.125, 0.5 + 7.5 + 0.125, 0.5 - 2.0 + 0.125])
 
 
+def _ubj(v, typed=True):
+    """Test-side UBJSON writer in the style XGBoost uses: numeric lists become typed `[$t#L n` containers."""
+    import struct
+
+    def ilen(n):
+        return b"L" + struct.pack(">q", n)
+    if v is None:
+        return b"Z"
+    if isinstance(v, bool):
+        return b"T" if v else b"F"
+    if isinstance(v, int):
+        return b"l" + struct.pack(">i", v) if -2**31 <= v < 2**31 else b"L" + struct.pack(">q", v)
+    if isinstance(v, float):
+        return b"d" + struct.pack(">f", v)
+    if isinstance(v, str):
+        b = v.encode()
+        return b"S" + ilen(len(b)) + b
+    if isinstance(v, list):
+        if typed and v and all(isinstance(x, int) and not isinstance(x, bool) for x in v):
+            return b"[$l#" + ilen(len(v)) + struct.pack(f">{len(v)}i", *v)
+        if typed and v and all(isinstance(x, float) for x in v):
+            return b"[$d#" + ilen(len(v)) + struct.pack(f">{len(v)}f", *v)
+        return b"[" + b"".join(_ubj(x, typed) for x in v) + b"]"
+    if isinstance(v, dict):
+        out = b"{"
+        for k, x in v.items():
+            kb = k.encode()
+            out += b"U" + bytes([len(kb)]) + kb + _ubj(x, typed)
+        return out + b"}"
+    raise TypeError(type(v))
+
+
+def _xgb_doc(**learner_extra):
+    doc = {"learner": {"learner_model_param": {"base_score": "5E-1", "num_feature": "12", "num_target": "1"},
+                       "objective": {"name": "reg:squarederror"},
+                       "gradient_booster": {"name": "gbtree", "model": {"trees": [
+                           {"left_children": [1, -1, 3, -1, -1], "right_children": [2, -1, 4, -1, -1],
+                            "split_indices": [10, 0, 5, 0, 0], "split_conditions": [5.0, 1.25, 0.5, -2.0, 7.5],
+                            "default_left": [0, 0, 1, 0, 0], "split_type": [0, 0, 0, 0, 0]},
+                           {"left_children": [-1], "right_children": [-1], "split_indices": [0],
+                            "split_conditions": [0.125], "default_left": [0], "split_type": [0]}]}}},
+           "version": [2, 1, 1]}
+    doc["learner"].update(learner_extra)
+    return doc
+
+
+@pytest.mark.parametrize("typed", [True, False], ids=["typed-arrays", "plain-arrays"])
+def test_xgboost_ubj_dump_reads_like_the_json_dump(tmp_path, typed):
+    """XGBoost 2.1.1 (requirements.txt:24) writes `.ubj` by default: same schema, binary container."""
+    doc = _xgb_doc()
+    assert M.read_ubjson(_ubj(doc, typed)) == doc
+    (tmp_path / "m.ubj").write_bytes(_ubj(doc, typed))
+    (tmp_path / "m.json").write_text(__import__("json").dumps(doc))
+    (tmp_path / "m.bin").write_bytes(_ubj(doc, typed))                # no telling extension: sniffed
+    want = M.export_xgboost_json(doc)
+    for name in ("m.ubj", "m.json", "m.bin"):
+        assert M.export_xgboost_json(str(tmp_path / name)) == want
+    with pytest.raises(ValueError):
+        M.read_ubjson(_ubj(doc, typed)[:-9])
+
+
+def test_xgboost_export_refuses_what_the_format_cannot_express():
+    with pytest.raises(ValueError, match="objective"):
+        M.export_xgboost_json(_xgb_doc(objective={"name": "reg:gamma"}))
+    doc = _xgb_doc()
+    doc["learner"]["gradient_booster"]["model"]["trees"][0]["split_type"][2] = 1
+    with pytest.raises(ValueError, match="categorical"):
+        M.export_xgboost_json(doc)
+    doc = _xgb_doc()
+    doc["learner"]["gradient_booster"]["model"]["trees"][0]["split_indices"][0] = 12
+    with pytest.raises(ValueError, match="feature 12"):
+        M.export_xgboost_json(doc)
+    doc = _xgb_doc()
+    doc["learner"]["learner_model_param"]["base_score"] = "[5E-1]"      # 3.x spelling
+    assert M.export_xgboost_json(doc) == M.export_xgboost_json(_xgb_doc())
+
+
+def test_xgboost_dart_weights_scale_the_leaves():
+    doc = _xgb_doc()
+    gb = doc["learner"]["gradient_booster"]
+    doc["learner"]["gradient_booster"] = {"name": "dart", "gbtree": gb, "weight_drop": [0.5, 2.0]}
+    rows = np.zeros((2, 12), np.float32)
+    rows[0, 10] = 4.9
+    rows[1, 10], rows[1, 5] = 9.0, 1.0
+    got = O.eta_eval(M.export_xgboost_json(doc), rows)
+    assert np.allclose(got, [0.5 + 0.5 * 1.25 + 2.0 * 0.125, 0.5 + 0.5 * 7.5 + 2.0 * 0.125])
+
+
 def test_predict_without_model_returns_none_pair(monkeypatch, tmp_path):
     """ml.py:25-26: no usable model => (None, None), remembered without retrying."""
     monkeypatch.setenv("ETA_MODEL_PATH", str(tmp_path / "missing.rte"))
