@@ -383,7 +383,8 @@ int rt_problem_set_routes(rt_problem *p, const int32_t *order, const int32_t *tr
         int *nd = node.data() + b * PS, P = 0;
         nd[P++] = 0;
         for (int k = 0; k < R; ++k) {
-            if (off[k + 1] < off[k]) return fail(e, RT_ERR_INVALID_ARG, "instance %zu: trip offsets must not decrease", b);
+            if (off[k + 1] < off[k] || off[k + 1] > static_cast<int>(N) - 1)
+                return fail(e, RT_ERR_INVALID_ARG, "instance %zu: trip offsets must not decrease or pass %zu", b, N - 1);
             for (int i = off[k]; i < off[k + 1]; ++i) {
                 const int c = ord[i];
                 if (c < 1 || c >= static_cast<int>(N) || seen[c])
@@ -531,6 +532,23 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, B * 4, cudaMemcpyHostToDevice, e->copy_stream));
     RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, B * 8, cudaMemcpyHostToDevice, e->copy_stream));
     RT_CUDA(e, cudaEventRecord(e->ev[1], e->copy_stream));
+    // While those copies are in flight the host checks what the kernels index with: every position holds a node id
+    // below n and there are exactly n-1 customers among them (so the route count is P - n and every table fits).
+    // That a customer is not repeated is not checked here: a repeat gives a meaningless plan, not a fault.
+    for (size_t b = 0; b < B; ++b) {
+        const int32_t *nd = node + b * PS;
+        const int P = npos[b];
+        unsigned bad = 0;
+        int zeros = 0;
+        for (int q = 0; q < P; ++q) {
+            bad |= static_cast<unsigned>(nd[q]) >= static_cast<unsigned>(N);
+            zeros += nd[q] == 0;
+        }
+        if (bad || zeros != P - static_cast<int>(N) + 1) {
+            p->has_routes = false;  // the copy above has already replaced the previous routes
+            return fail(e, RT_ERR_INVALID_ARG, "instance %zu: position array must hold node ids below %zu with %zu customers", b, N, N - 1);
+        }
+    }
     // Coordinates are range-checked by the unit-vector kernel (off the host's critical path); stop records are taken
     // as they are (rt_problem_set_stops is the validating entry point) — out-of-range values cannot fault a kernel.
     int *bad_flag = p->coord_flag;

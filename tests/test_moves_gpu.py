@@ -176,6 +176,15 @@ def test_plan_from_host_buffers(engine):
         assert "coordinate" in str(ei.value)
         lat[2, 7] = insts[2][2]["lat"][7]
         assert np.array_equal(call(), keys)
+        # what the kernels index with is checked before any of them runs: ids below n, exactly n-1 customers
+        keep = node[1, 5]
+        for bad in (n, -3, 0):
+            node[1, 5] = bad
+            with pytest.raises(EngineError) as ei:
+                call()
+            assert "position array" in str(ei.value)
+        node[1, 5] = keep
+        assert np.array_equal(call(), keys)
 
 
 def test_replica_with_a_shard_keeps_only_its_rows_fresh(engine):
