@@ -169,7 +169,10 @@ int rt_problem_eval_moves(rt_problem *p, int families, int shard_index, int shar
 /* Every candidate of one family for one instance: delta_out int32[P*P], feas_out uint8[P*P] indexed [p*P+q];
  * feas 0 = infeasible, 1 = feasible, 2 = not a candidate.  For tests and diagnostics. */
 int rt_problem_eval_dump(rt_problem *p, int instance, int family, int32_t *delta_out, uint8_t *feas_out);
-/* Applies one move per instance (keys [batch]; 2^64-1 = leave unchanged) and refreshes the state. */
+/* Applies one move per instance (keys [batch]; 2^64-1 = leave unchanged) and refreshes the state.  A key that is
+ * not a move of the instance's current routes (wrong family bits, positions outside the routes, a depot where a
+ * customer is needed) leaves that instance unchanged and makes the call return RT_ERR_INVALID_ARG after the other
+ * instances' moves have been applied. */
 int rt_problem_apply_moves(rt_problem *p, const uint64_t *keys);
 /* Best-improvement local search to a local optimum or max_moves applied moves per instance (SPEC.md §8).
  * moves_out [batch], cost_out [batch]; keys_out [batch][keys_capacity] receives the applied keys (may be NULL). */

@@ -685,9 +685,18 @@ int rt_problem_apply_moves(rt_problem *p, const uint64_t *keys)
     RT_PROBLEM_GUARD(p);
     if (!keys) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_apply_moves: NULL argument");
     if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_apply_moves: no routes set");
+    // the per-instance "search finished" flags belong to the search loops; a direct apply neither obeys nor leaves them
+    RT_TRY(stage(p, static_cast<size_t>(p->batch) * 4));
+    int *done_h = static_cast<int *>(p->host_stage);
+    RT_CUDA(e, cudaMemsetAsync(p->done, 0, p->batch * 4, e->stream));
     RT_CUDA(e, cudaMemcpyAsync(p->best, keys, p->batch * 8, cudaMemcpyHostToDevice, e->stream));
     RT_TRY(apply_moves_launch(p, p->best, false, false, e->stream));
+    RT_CUDA(e, cudaMemcpyAsync(done_h, p->done, p->batch * 4, cudaMemcpyDeviceToHost, e->stream));
+    RT_CUDA(e, cudaMemsetAsync(p->done, 0, p->batch * 4, e->stream));
     RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    for (int b = 0; b < p->batch; ++b)
+        if (done_h[b] == 2)
+            return fail(e, RT_ERR_INVALID_ARG, "rt_problem_apply_moves: the key of instance %d is not a move of its current routes (left unchanged)", b);
     return RT_OK;
 }
 

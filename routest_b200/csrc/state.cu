@@ -323,7 +323,16 @@ __global__ void __launch_bounds__(256) apply_moves_kernel(const unsigned long lo
     const int P = npos[b];
     int *node = node_all + static_cast<size_t>(b) * pstride;
     int *tmp = tmp_all + static_cast<size_t>(b) * pstride;
-    if (p >= P || q >= P) {  // malformed key: refuse
+    // A key that is not a move of SPEC.md §7 is refused (done = 2) rather than applied: whatever the caller hands in,
+    // the first and last positions stay the depot and the number of separators does not change, which is what every
+    // other kernel's indexing relies on.
+    bool good = family != 3 && p < P && q < P;
+    if (good) {
+        if (family == 2) good = node[p] != 0 && node[q] != 0;
+        else if (family == 1) good = node[p] != 0 && q != p && q <= P - 2;
+        else good = p < q && q <= P - 2;
+    }
+    if (!good) {
         if (tid == 0) done[b] = 2;
         return;
     }

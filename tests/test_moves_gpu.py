@@ -229,6 +229,34 @@ def test_apply_moves_matches_oracle(engine):
             assert st["cost"] == O.route_state(inst, cur)["cost"]
 
 
+def test_apply_moves_refuses_keys_that_are_not_moves(engine):
+    """rt_problem_apply_moves: a key that is no move of the current routes leaves the instance as it is and is
+    reported; 'no move' is accepted and does not block a later apply; the search flags are left alone."""
+    from routest_b200 import EngineError
+    inst, node, raw = synth_vrptw(19, 60, 5)
+    P = node.size
+
+    def key(fam, p, q):
+        return (2 ** 31 << 32) | (fam << 30) | (p << 15) | q
+
+    with _load(engine, [(inst, node, raw)]) as pr:
+        pr.local_search()                                      # leaves every instance marked finished
+        after = pr.get_state(0)["node"][:P].copy()
+        sep = int(np.flatnonzero(after == 0)[1])               # an inner depot separator
+        cust = int(np.flatnonzero(after != 0)[0])
+        pr.apply_moves(np.array([O.NO_MOVE], np.uint64))
+        for bad in (key(3, cust, cust + 1), key(2, 0, cust), key(2, cust, sep), key(1, sep, cust), key(1, cust, P - 1),
+                    key(1, cust, cust), key(0, cust + 2, cust), key(0, cust, P - 1), key(2, cust, P + 3)):
+            with pytest.raises(EngineError) as ei:
+                pr.apply_moves(np.array([bad], np.uint64))
+            assert "not a move" in str(ei.value)
+            assert np.array_equal(pr.get_state(0)["node"][:P], after)
+        a, b = [int(x) for x in np.flatnonzero(after != 0)[[1, 4]]]
+        pr.apply_moves(np.array([key(2, a, b)], np.uint64))     # a real swap still goes through
+        want = O.apply_move(after, 2, a, b)
+        assert np.array_equal(pr.get_state(0)["node"][:P], want)
+
+
 @pytest.mark.parametrize("full", [False, True], ids=["incremental", "full"])
 @pytest.mark.parametrize("seed,stops,veh", [(10, 45, 5), (11, 100, 10), (12, 300, 12)])
 def test_local_search_moves_and_final_routes_bit_exact(engine, seed, stops, veh, full):
