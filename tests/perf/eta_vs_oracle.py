@@ -1,8 +1,9 @@
 """ETA scorer micro-benchmark (BASELINE config 3: 1M synthetic stop pairs; development aid)."""
 import json, os, sys, time
 import numpy as np, torch
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 from routest_b200 import Engine
 from test_eta import synth_model, synth_pairs
 from oracle import oracle as O

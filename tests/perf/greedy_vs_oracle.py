@@ -1,7 +1,9 @@
-"""Greedy construction time: engine (device matrix) vs the CPU oracle (development aid)."""
+"""Greedy construction time: engine (device matrix) vs the CPU oracle (development aid).
+Lives under tests/ because it runs the CPU oracle as the checker and the baseline beside the engine."""
 import json, os, sys, time
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
 from bench import DIST_SCALE, TS_CAR, synth_coords, synth_windows
 from routest_b200 import Engine
 from oracle import oracle as O

@@ -5,13 +5,13 @@ ranks, one NCCL MIN all-reduce of the best-move key per pass (BASELINE.json conf
       tools/bench_10k.py --stops 10000 --steps 20
 A pass = every rank rebuilds its rows of the route-order matrix (+ the replicated route state), scores its shard
 of the full 2-opt/relocate/swap neighbourhood, and the ranks all-reduce one int64 key.  Timed with CUDA events on
-the launching stream, max over ranks.  Rank 0 also times the CPU oracle on the same instance (all host threads).
+the launching stream, max over ranks.  tests/perf/cpu_pass_10k.py times the CPU oracle on the same instance and prints
+the same best key.
 """
 import argparse
 import json
 import os
 import sys
-import time
 
 import numpy as np
 import torch
@@ -28,7 +28,6 @@ def main():
     ap.add_argument("--stops", type=int, default=10000)
     ap.add_argument("--vehicles", type=int, default=100)
     ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--cpu", action="store_true", help="rank 0 also times the CPU oracle on the same pass")
     ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"],
                     help="nccl: all_reduce(MIN) per pass; peer: system-scope atomics into every replica's slot buffer")
     a = ap.parse_args()
@@ -104,20 +103,6 @@ def main():
                 "n_gpus": world, "ms_per_pass": ms, "matrix_cells_per_s": P * P / ms * 1e3,
                 "move_evals_per_s": evals / ms * 1e3, "cells_per_pass": P * P, "move_evals_per_pass": evals,
                 "best_key": best & (2 ** 64 - 1)}
-        if a.cpu:
-            from oracle import oracle as O
-            th = O.num_threads()
-            t0 = time.perf_counter()
-            m = O.matrix_rows(O.unit_vectors(lat, lon), 0, n, DIST_SCALE, TS_CAR, threads=th)
-            t1 = time.perf_counter()
-            inst = O.Instance(m["dist"], m["time"], st[0], cap)
-            node = O.build_positions(trips[0], n)
-            k = O.best_move(inst, node, threads=th)
-            t2 = time.perf_counter()
-            line["cpu"] = {"threads": th, "matrix_s": t1 - t0, "best_move_s": t2 - t1,
-                           "matrix_cells_per_s": n * n / (t1 - t0), "move_evals_per_s": evals / (t2 - t1),
-                           "same_best_move": (k ^ (1 << 63)) == (best & (2 ** 64 - 1))}
-            line["speedup_vs_cpu"] = {"pass": (t2 - t0) / (ms / 1e3)}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
