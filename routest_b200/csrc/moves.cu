@@ -102,7 +102,7 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
 // some lane in the slow path; computing delta AND feasibility for every candidate without a branch is cheaper.
 // Per row three broadcast LDS.128 bring everything about p; everything about q lives in registers.
 template <bool DUMP, bool ASYM>
-__global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 8) eval_inter_kernel(const EvalArgs a)
+__global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel(const EvalArgs a)
 {
     __shared__ int4 sH[kStripRows];   // {rem_delta, oe, -, route | customer << 30 | rem_ok << 29}
     __shared__ int4 sP1[kStripRows];  // {ready, due, service, demand}
