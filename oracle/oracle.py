@@ -37,6 +37,8 @@ def lib() -> C.CDLL:
         _LIB.or_route_state.restype = C.c_int
         _LIB.or_best_move.restype = C.c_uint64
         _LIB.or_local_search.restype = C.c_int
+        _LIB.or_select_batch.restype = C.c_int
+        _LIB.or_local_search_batched.restype = C.c_int
     return _LIB
 
 
@@ -252,6 +254,41 @@ def local_search(inst, node, families=ALL_FAMILIES, max_moves=1 << 30, threads=1
     m = lib().or_local_search(*inst._args(), _p(node, C.c_int32), C.c_int(node.size), C.c_int(families),
                               C.c_int(cap_keys), C.c_int(threads), _p(keys, C.c_uint64), C.byref(cost))
     return node, keys[:m].copy(), int(cost.value)
+
+
+BATCH_ROUNDS = 3   # SPEC §8.1
+
+
+def select_batch(inst, node, families=ALL_FAMILIES, threads=1, rounds=BATCH_ROUNDS):
+    """SPEC §8.1: (round-1 per-route minimum keys m[R], selected keys round after round)."""
+    node = np.ascontiguousarray(node, dtype=np.int32)
+    R = node.size - inst.n
+    m = np.zeros(R, np.uint64)
+    keys = np.zeros(max(R, 1), np.uint64)
+    c = lib().or_select_batch(*inst._args(), _p(node, C.c_int32), C.c_int(node.size), C.c_int(families),
+                              C.c_int(rounds), C.c_int(threads), _p(m, C.c_uint64), _p(keys, C.c_uint64))
+    return m, keys[:c].copy()
+
+
+def apply_batch(inst, node, keys):
+    node = np.array(node, dtype=np.int32)
+    keys = np.ascontiguousarray(keys, dtype=np.uint64)
+    lib().or_apply_batch(C.c_int(inst.n), _p(node, C.c_int32), C.c_int(node.size), _p(keys, C.c_uint64),
+                         C.c_int(keys.size))
+    return node
+
+
+def local_search_batched(inst, node, families=ALL_FAMILIES, max_iters=1 << 30, threads=1, rounds=BATCH_ROUNDS):
+    """SPEC §8.1.  Returns (final node[], applied keys batch after batch, batch sizes, final cost)."""
+    node = np.array(node, dtype=np.int32)
+    cap = 1 << 20
+    keys = np.zeros(cap, np.uint64)
+    sizes = np.zeros(cap, np.int32)
+    iters, cost = C.c_int32(0), C.c_int64(0)
+    m = lib().or_local_search_batched(*inst._args(), _p(node, C.c_int32), C.c_int(node.size), C.c_int(families),
+                                      C.c_int(rounds), C.c_int(min(max_iters, cap)), C.c_int(threads), _p(keys, C.c_uint64),
+                                      C.c_int(cap), _p(sizes, C.c_int32), C.c_int(cap), C.byref(iters), C.byref(cost))
+    return node, keys[:m].copy(), sizes[:iters.value].copy(), int(cost.value)
 
 
 # ----------------------------------------------------------------------------------------------- SPEC §9

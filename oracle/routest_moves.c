@@ -471,3 +471,141 @@ int or_local_search(int n, const int32_t *D, const int32_t *T, const int32_t *st
     }
     return moves;
 }
+
+/* ------------------------------------------------------------------ §8.1 batched iterations */
+
+typedef struct { uint64_t *m; const int32_t *route; const uint8_t *taken; } rmin_ctx;
+
+static inline void rmin_note(rmin_ctx *c, uint64_t k, int p, int q)
+{
+    const int ra = c->route[p], rb = c->route[q];
+    if (c->taken[ra] || c->taken[rb]) return; /* a route already claimed by an earlier round of this batch */
+    if (k < c->m[ra]) c->m[ra] = k;
+    if (k < c->m[rb]) c->m[rb] = k;
+}
+
+static void emit_rmin(void *c, int family, int p, int q, int32_t delta, int feas)
+{
+    if (feas) rmin_note((rmin_ctx *)c, or_key(delta, family, p, q), p, q);
+}
+
+/*
+ * One batch of SPEC §8.1.  Round 1: m[r] (r < R = P - n) = minimum key over the valid feasible candidates that touch
+ * route r; every candidate with delta < 0 that is the minimum of all its routes is selected and its routes are
+ * claimed.  Rounds 2..rounds repeat that over the candidates whose routes are all still unclaimed.  keys_out receives
+ * the batch round after round, ascending route[p] within a round (at most R keys); m_out (may be NULL) the round-1
+ * minima.  Returns the batch size.
+ */
+int or_select_batch(int n, const int32_t *D, const int32_t *T, const int32_t *stops, int32_t cap, int64_t max_dist,
+                    const int32_t *node, int P, int families, int rounds, int threads, uint64_t *m_out, uint64_t *keys_out)
+{
+    or_inst I = {n, D, T, stops, cap, max_dist};
+    or_scratch s = or_scratch_new(P);
+    or_route_state(n, D, T, stops, cap, max_dist, node, P, s.route, s.B, s.Z, s.rload, s.rdist, NULL);
+    or_view V = {&I, node, s.route, s.B, s.Z, s.rload, s.rdist, P};
+    const int R = P - n;
+    uint64_t *m = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(R + 1)); /* +1: the closing separator's pseudo route */
+    uint8_t *taken = (uint8_t *)calloc((size_t)(R + 1), 1);
+    int count = 0;
+    (void)threads;
+    for (int round = 0; round < rounds; ++round) {
+        for (int r = 0; r <= R; ++r) m[r] = OR_NO_MOVE;
+#pragma omp parallel num_threads(threads > 0 ? threads : 1)
+        {
+            uint64_t *mine = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(R + 1));
+            for (int r = 0; r <= R; ++r) mine[r] = OR_NO_MOVE;
+            rmin_ctx ctx = {mine, s.route, taken};
+#pragma omp for schedule(dynamic, 16) nowait
+            for (int t = 0; t < P; ++t) sweep_anchor(&V, t, families, emit_rmin, &ctx);
+#pragma omp for schedule(dynamic, 16) nowait
+            for (int p = 0; p < P; ++p) {
+                if (node[p] == 0) continue;
+                for (int q = 0; q < P; ++q) {
+                    int32_t d;
+                    if ((families & 2) && s.route[p] != s.route[q] && or_valid(node, s.route, P, 1, p, q) &&
+                        eval_relocate_inter(&V, p, q, &d))
+                        rmin_note(&ctx, or_key(d, 1, p, q), p, q);
+                    if ((families & 4) && q > p && node[q] != 0 && s.route[p] != s.route[q] && eval_swap_inter(&V, p, q, &d))
+                        rmin_note(&ctx, or_key(d, 2, p, q), p, q);
+                }
+            }
+#pragma omp critical
+            for (int r = 0; r <= R; ++r)
+                if (mine[r] < m[r]) m[r] = mine[r];
+            free(mine);
+        }
+        if (round == 0 && m_out && R > 0) memcpy(m_out, m, sizeof(uint64_t) * (size_t)R);
+        const int before = count;
+        for (int r = 0; r < R; ++r) {
+            const uint64_t k = m[r];
+            if (k == OR_NO_MOVE || (int32_t)((uint32_t)(k >> 32) - 0x80000000u) >= 0) continue;
+            const int p = (int)((k >> 15) & 0x7FFF), q = (int)(k & 0x7FFF);
+            if (s.route[p] != r) continue; /* reported once, at the route of p */
+            if (m[s.route[q]] != k) continue;
+            keys_out[count++] = k;
+        }
+        if (count == before) break;
+        for (int i = before; i < count; ++i) {
+            taken[s.route[(keys_out[i] >> 15) & 0x7FFF]] = 1;
+            taken[s.route[keys_out[i] & 0x7FFF]] = 1;
+        }
+    }
+    free(m);
+    free(taken);
+    or_scratch_free(&s);
+    return count;
+}
+
+/* Applies a batch selected on the state node[] currently holds (disjoint routes), in the order given. */
+void or_apply_batch(int n, int32_t *node, int P, const uint64_t *keys, int count)
+{
+    const int R = P - n;
+    int32_t *route = (int32_t *)malloc(sizeof(int32_t) * (size_t)P);
+    int32_t *start = (int32_t *)malloc(sizeof(int32_t) * (size_t)(R + 2));
+    int32_t *rel = (int32_t *)malloc(sizeof(int32_t) * 4 * (size_t)(count > 0 ? count : 1));
+    int r = -1;
+    for (int p = 0; p < P; ++p) { if (node[p] == 0) { ++r; start[r] = p; } route[p] = r; }
+    for (int i = 0; i < count; ++i) { /* route-relative form on the state the batch was selected on */
+        const int p = (int)((keys[i] >> 15) & 0x7FFF), q = (int)(keys[i] & 0x7FFF);
+        rel[4 * i] = route[p]; rel[4 * i + 1] = p - start[route[p]];
+        rel[4 * i + 2] = route[q]; rel[4 * i + 3] = q - start[route[q]];
+    }
+    for (int i = 0; i < count; ++i) {
+        r = -1;
+        for (int p = 0; p < P; ++p) if (node[p] == 0) start[++r] = p;
+        or_apply_move(node, (int)((keys[i] >> 30) & 3), start[rel[4 * i]] + rel[4 * i + 1], start[rel[4 * i + 2]] + rel[4 * i + 3]);
+    }
+    free(route); free(start); free(rel);
+}
+
+/*
+ * §8.1 to a local optimum or max_iters batches.  keys_out (capacity keys_cap, may be NULL) receives the applied keys
+ * batch after batch; batch_sizes_out (capacity max_iters or until done, may be NULL) the size of every batch.
+ * Returns the number of moves applied; *iters_out the number of non-empty batches.
+ */
+int or_local_search_batched(int n, const int32_t *D, const int32_t *T, const int32_t *stops, int32_t cap, int64_t max_dist,
+                            int32_t *node, int P, int families, int rounds, int max_iters, int threads, uint64_t *keys_out,
+                            int keys_cap, int32_t *batch_sizes_out, int sizes_cap, int32_t *iters_out, int64_t *cost_out)
+{
+    const int R = P - n;
+    uint64_t *batch = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(R > 0 ? R : 1));
+    int moves = 0, iters = 0;
+    while (iters < max_iters) {
+        const int c = or_select_batch(n, D, T, stops, cap, max_dist, node, P, families, rounds, threads, NULL, batch);
+        if (c == 0) break;
+        or_apply_batch(n, node, P, batch, c);
+        for (int i = 0; i < c; ++i)
+            if (keys_out && moves + i < keys_cap) keys_out[moves + i] = batch[i];
+        if (batch_sizes_out && iters < sizes_cap) batch_sizes_out[iters] = c;
+        moves += c;
+        ++iters;
+    }
+    free(batch);
+    if (iters_out) *iters_out = iters;
+    if (cost_out) {
+        or_scratch s = or_scratch_new(P);
+        or_route_state(n, D, T, stops, cap, max_dist, node, P, s.route, s.B, s.Z, s.rload, s.rdist, cost_out);
+        or_scratch_free(&s);
+    }
+    return moves;
+}
