@@ -183,6 +183,14 @@ int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t 
  * same routes).  For cross-checking and for asymmetric matrices / more than 1,024 routes, where the table is not used. */
 int rt_problem_local_search_full(rt_problem *p, int families, int max_moves, int32_t *moves_out, int64_t *cost_out,
                                  uint64_t *keys_out, int keys_capacity);
+/* Batched iterations (SPEC.md §8.1): every iteration applies a whole set of improving moves that touch pairwise
+ * disjoint routes (selected in three rounds from the per-route-pair table of a full evaluation; the best move is
+ * always among them), so a local optimum of the same neighbourhood — in general a different one — is reached in
+ * about a tenth of the iterations.  max_iterations bounds the iterations, not the moves; moves_out counts moves;
+ * keys_out receives them batch after batch (positions are those of the state the batch was selected on).  At most
+ * 1,024 routes per instance.  No reference counterpart (utils.py:111-139 has no improvement phase). */
+int rt_problem_local_search_batched(rt_problem *p, int families, int max_iterations, int32_t *moves_out,
+                                    int64_t *cost_out, uint64_t *keys_out, int keys_capacity);
 
 /* One pass of the hot path from host inputs to best moves, for every instance: uploads coordinates, stop data
  * and the current solution, builds the matrices (utils.py:94-109) — in route order, G[p][q] = M[node p][node q],

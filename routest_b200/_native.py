@@ -72,6 +72,7 @@ SIGNATURES = {
     "rt_problem_plan_dev": (C.c_int, [c_problem_p, C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_problem_set_shard": (C.c_int, [c_problem_p, C.c_int, C.c_int]),
     "rt_problem_local_search_full": (C.c_int, [c_problem_p, C.c_int, C.c_int, c_i32_p, c_i64_p, c_u64_p, C.c_int]),
+    "rt_problem_local_search_batched": (C.c_int, [c_problem_p, C.c_int, C.c_int, c_i32_p, c_i64_p, c_u64_p, C.c_int]),
     "rt_problem_eval_moves_dev": (C.c_int, [c_problem_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_problem_apply_moves_dev": (C.c_int, [c_problem_p, C.c_void_p, C.c_int, C.c_void_p]),
     "rt_problem_exchange_handle_bytes": (C.c_int, []),

@@ -84,6 +84,9 @@ struct EvalArgs {
     int families;            // bit 0 = 2-opt, 1 = relocate, 2 = swap
     int shard_index, shard_count;
     unsigned long long *best;  // [batch]
+    // table mode (batched iterations, batch.cu): best key per ordered route pair / per route, absolute positions
+    unsigned long long *inter, *intra;  // [batch][cr][cr], [batch][cr]
+    int cr;
     // dump mode (one instance, one family)
     int dump_instance, dump_family;
     int *dump_delta;
@@ -101,9 +104,14 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
 // feasible one while being infeasible (capacity, windows), so pruning on the delta leaves almost every warp with
 // some lane in the slow path; computing delta AND feasibility for every candidate without a branch is cheaper.
 // Per row three broadcast LDS.128 bring everything about p; everything about q lives in registers.
-template <bool DUMP, bool ASYM>
+// MODE: kBest = one key per instance, kDump = every candidate of one family (tests), kTable = one key per ordered
+// route pair (the thread's column fixes the second route; its best is flushed whenever the row's route changes).
+enum { kBest = 0, kDump = 1, kTable = 2 };
+
+template <int MODE, bool ASYM>
 __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel(const EvalArgs a)
 {
+    constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
     __shared__ int4 sH[kStripRows];   // {rem_delta, oe, -, route | customer << 30 | rem_ok << 29}
     __shared__ int4 sP1[kStripRows];  // {ready, due, service, demand}
     __shared__ int4 sP2[kStripRows];  // {Z[p+1], B[p-1]+service[p-1], capacity slack, distance slack} of p's route
@@ -157,6 +165,15 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
 
     int best_d = INT_MAX;
     unsigned best_i = 0xFFFFFFFFu;  // family << 30 | p << 15 | q
+    int cur_ra = -1;                // table mode: the route the running best belongs to
+    unsigned long long *trow = TABLE ? a.inter + static_cast<size_t>(b) * a.cr * a.cr + q_route : nullptr;
+    auto flush = [&]() {
+        if (best_i != 0xFFFFFFFFu)
+            atomicMin(trow + static_cast<size_t>(cur_ra) * a.cr,
+                      (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i);
+        best_d = INT_MAX;
+        best_i = 0xFFFFFFFFu;
+    };
     const int rows = min(kStripRows, p_hi - p0);
     // Register window over three rows of G, loaded two rows ahead of use.  G carries a pad cell in front and a dozen
     // pad rows behind (ensure_position_matrix), so q-1 / q+1 / p+2 need no clamping: whatever an out-of-range
@@ -198,6 +215,10 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
         if ((Hp.w >> 30) & 1) {  // p is a customer (warp-uniform)
             const int4 p1 = sP1[rr], p2 = sP2[rr];
             const bool other = (Hp.w & 0x7FFF) != q_route;
+            if (TABLE && (Hp.w & 0x7FFF) != cur_ra) {  // warp-uniform: p is the same for the whole block
+                flush();
+                cur_ra = Hp.w & 0x7FFF;
+            }
             // relocate(p -> between q and q+1): a -> u -> b replaces a -> b in route[q]
             const int ins = fadd(fadd(a_cur.x, c_rt.x), -Hq.z);
             const int d_rel = fadd(Hp.x, ins);
@@ -255,7 +276,9 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
         tn_lf = tm_lf;
         tn_cur = tm_cur;
     }
-    if (!DUMP) {
+    if (TABLE) {
+        flush();
+    } else if (!DUMP) {
         const unsigned long long best =
             best_i == 0xFFFFFFFFu
                 ? kNoMove
@@ -292,15 +315,17 @@ __device__ __forceinline__ bool seg_fits(const Seg &m, int t, int tail, int limi
 
 constexpr int kIntraThreads = 128;
 
-template <bool DUMP, bool ASYM>
+template <int MODE, bool ASYM>
 __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArgs a)
 {
+    constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
     const int b = DUMP ? a.dump_instance : blockIdx.y;
     const int P = a.npos[b];
     int t_lo, t_hi;
     shard_range(P, a.shard_index, a.shard_count, t_lo, t_hi);  // same-route work is sharded by anchor
     const int t = t_lo + blockIdx.x * kIntraThreads + threadIdx.x;
     unsigned long long best = kNoMove;
+    int t_route = 0;
 
     if (t < t_hi && t < P - 1) {
         const size_t po = static_cast<size_t>(b) * a.pstride;
@@ -312,6 +337,7 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
         const int nt = node[t];
         const bool t_cust = nt != 0;
         const int4 tA = RA[t], tB = RB[t], tC = RC[t], tD = RD[t];
+        t_route = tA.w;                    // every candidate of this sweep lies inside the anchor's route
         const int dslack = tD.y;           // max_dist - rdist of this route (clamped)
         const int2 Et = E[t];              // cell(node t, node t+1)
         const int4 t1B = RB[t + 1];        // stop data of node t+1 (first node of F)
@@ -442,7 +468,11 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
             rp = rp1;
         }
     }
-    if (!DUMP) block_min_to_global<kIntraThreads>(best, a.best + b);
+    if (TABLE) {
+        if (best != kNoMove) atomicMin(a.intra + static_cast<size_t>(b) * a.cr + t_route, best);
+    } else if (!DUMP) {
+        block_min_to_global<kIntraThreads>(best, a.best + b);
+    }
 }
 
 EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d)
@@ -510,14 +540,14 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     }
     {
         dim3 grid((shard_rows + kIntraThreads - 1) / kIntraThreads, p->batch);
-        if (p->symmetric) eval_intra_kernel<false, false><<<grid, kIntraThreads, 0, st_intra>>>(a);
-        else eval_intra_kernel<false, true><<<grid, kIntraThreads, 0, st_intra>>>(a);
+        if (p->symmetric) eval_intra_kernel<kBest, false><<<grid, kIntraThreads, 0, st_intra>>>(a);
+        else eval_intra_kernel<kBest, true><<<grid, kIntraThreads, 0, st_intra>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     if (families & 6) {
         dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + kStripRows - 1) / kStripRows, p->batch);
-        if (p->symmetric) eval_inter_kernel<false, false><<<grid, kInterThreads, 0, st>>>(a);
-        else eval_inter_kernel<false, true><<<grid, kInterThreads, 0, st>>>(a);
+        if (p->symmetric) eval_inter_kernel<kBest, false><<<grid, kInterThreads, 0, st>>>(a);
+        else eval_inter_kernel<kBest, true><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     if (overlap) {
@@ -527,6 +557,45 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     if (best_d != p->best || signed_keys)
         finish_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, best_d, p->batch, signed_keys ? 1 : 0);
     RT_CUDA(e, cudaGetLastError());
+    return RT_OK;
+}
+
+// Full evaluation into the per-route-pair table (batch.cu): inter[ra][rb] and intra[r] of every instance, absolute
+// positions in the keys.  The state must be fresh; the table buffers are those of the incremental search (cache.cu).
+int eval_table_launch(rt_problem *p, int families, cudaStream_t st)
+{
+    rt_engine *e = p->e;
+    EvalArgs a = make_args(p, families, 0, 1, p->best);
+    a.inter = static_cast<unsigned long long *>(p->cache_inter.p);
+    a.intra = static_cast<unsigned long long *>(p->cache_intra.p);
+    a.cr = p->cache_r;
+    const size_t B = p->batch, cr = p->cache_r;
+    RT_CUDA(e, cudaMemsetAsync(a.inter, 0xFF, B * cr * cr * 8, st));
+    RT_CUDA(e, cudaMemsetAsync(a.intra, 0xFF, B * cr * 8, st));
+    const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
+    const bool overlap = (families & 6) && p->side_stream;
+    cudaStream_t st_intra = st;
+    if (overlap) {
+        RT_CUDA(e, cudaEventRecord(p->ev_fork, st));
+        RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, p->ev_fork, 0));
+        st_intra = p->side_stream;
+    }
+    {
+        dim3 grid((pmax + kIntraThreads - 1) / kIntraThreads, p->batch);
+        if (p->symmetric) eval_intra_kernel<kTable, false><<<grid, kIntraThreads, 0, st_intra>>>(a);
+        else eval_intra_kernel<kTable, true><<<grid, kIntraThreads, 0, st_intra>>>(a);
+        RT_CUDA(e, cudaGetLastError());
+    }
+    if (families & 6) {
+        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (pmax + kStripRows - 1) / kStripRows, p->batch);
+        if (p->symmetric) eval_inter_kernel<kTable, false><<<grid, kInterThreads, 0, st>>>(a);
+        else eval_inter_kernel<kTable, true><<<grid, kInterThreads, 0, st>>>(a);
+        RT_CUDA(e, cudaGetLastError());
+    }
+    if (overlap) {
+        RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
+        RT_CUDA(e, cudaStreamWaitEvent(st, p->ev_join, 0));
+    }
     return RT_OK;
 }
 
@@ -541,13 +610,13 @@ int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsi
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
     if (family != 0) {
         dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (pmax + kStripRows - 1) / kStripRows, 1);
-        if (p->symmetric) eval_inter_kernel<true, false><<<grid, kInterThreads, 0, st>>>(a);
-        else eval_inter_kernel<true, true><<<grid, kInterThreads, 0, st>>>(a);
+        if (p->symmetric) eval_inter_kernel<kDump, false><<<grid, kInterThreads, 0, st>>>(a);
+        else eval_inter_kernel<kDump, true><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     dim3 grid((pmax + kIntraThreads - 1) / kIntraThreads, 1);
-    if (p->symmetric) eval_intra_kernel<true, false><<<grid, kIntraThreads, 0, st>>>(a);
-    else eval_intra_kernel<true, true><<<grid, kIntraThreads, 0, st>>>(a);
+    if (p->symmetric) eval_intra_kernel<kDump, false><<<grid, kIntraThreads, 0, st>>>(a);
+    else eval_intra_kernel<kDump, true><<<grid, kIntraThreads, 0, st>>>(a);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }

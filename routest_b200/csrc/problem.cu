@@ -175,7 +175,7 @@ void rt_problem_destroy(rt_problem *p)
     for (int i = 0; i < p->n_xpeer_mapped; ++i) cudaIpcCloseMemHandle(p->xpeer_mapped[i]);
     if (p->xpeers) cudaFree(p->xpeers);
     if (p->xbuf) cudaFree(p->xbuf);
-    for (rt::DevBuf *bf : {&p->cache_inter, &p->cache_intra, &p->cache_tiles, &p->cache_misc})
+    for (rt::DevBuf *bf : {&p->cache_inter, &p->cache_intra, &p->cache_tiles, &p->cache_misc, &p->batch_buf})
         if (bf->p) cudaFree(bf->p);
     if (p->Gbuf.p) cudaFree(p->Gbuf.p);
     if (p->GTbuf.p) cudaFree(p->GTbuf.p);
@@ -737,6 +737,12 @@ int rt_problem_local_search_full(rt_problem *p, int families, int max_moves, int
     return local_search_impl(p, families, max_moves, 1, moves_out, cost_out, keys_out, keys_capacity);
 }
 
+int rt_problem_local_search_batched(rt_problem *p, int families, int max_iterations, int32_t *moves_out,
+                                    int64_t *cost_out, uint64_t *keys_out, int keys_capacity)
+{
+    return local_search_impl(p, families, max_iterations, 2, moves_out, cost_out, keys_out, keys_capacity);
+}
+
 static int local_search_impl(rt_problem *p, int families, int max_moves, int mode, int32_t *moves_out,
                              int64_t *cost_out, uint64_t *keys_out, int keys_capacity)
 {
@@ -750,13 +756,18 @@ static int local_search_impl(rt_problem *p, int families, int max_moves, int mod
     RT_CUDA(e, cudaGetLastError());
     // Incremental search (cache.cu: only what a move touched is re-scored) whenever its table applies; otherwise
     // every iteration re-scores the whole neighbourhood on the route-order matrix.  Same keys either way.
-    const bool cached = !(mode & 1) && cache_usable(p);
-    if (cached) RT_TRY(cache_begin(p, e->stream));
+    const bool batched = mode & 2;  // SPEC.md §8.1: max_moves counts iterations, each applies a batch of moves
+    if (batched && !batch_usable(p))
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_local_search_batched handles at most 1024 routes per instance");
+    const bool cached = !batched && !(mode & 1) && cache_usable(p);
+    if (batched) RT_TRY(batch_begin(p, e->stream));
+    else if (cached) RT_TRY(cache_begin(p, e->stream));
     else RT_TRY(state_refresh(p, e->stream));
     // The host only paces the loop: kChunk iterations are enqueued blind (an instance that has reached its local
     // optimum turns its own later iterations into no-ops on the device), then one 4-byte-per-instance read decides
     // whether to go on.
     auto one_iteration = [&]() -> int {
+        if (batched) return batch_iteration(p, families, e->stream);
         if (cached) {
             RT_TRY(cache_evaluate(p, families, e->stream));
             return cache_apply(p, true, e->stream);
@@ -780,7 +791,7 @@ static int local_search_impl(rt_problem *p, int families, int max_moves, int mod
             (void)cudaGetLastError();
         }
     }
-    const int kChunk = 32;
+    const int kChunk = batched ? 8 : 32;  // a batched iteration is a full evaluation: overshoot less
     int issued = 0;
     bool all_done = false;
     int loop_rc = RT_OK;

@@ -75,6 +75,7 @@ struct rt_problem {
     // incremental local search (cache.cu)
     rt::DevBuf cache_inter, cache_intra, cache_tiles, cache_misc;
     int cache_r = 0, cache_tile_cap = 0;
+    rt::DevBuf batch_buf;                  // batched iterations (batch.cu): route minima, selection, claims
     cudaStream_t side_stream = nullptr;    // state tables run here underneath the matrix kernel (state.cu)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     // peer exchange (exchange.cu)
@@ -109,6 +110,12 @@ bool cache_usable(const rt_problem *p);
 int cache_begin(rt_problem *p, cudaStream_t st);
 int cache_evaluate(rt_problem *p, int families, cudaStream_t st);
 int cache_apply(rt_problem *p, bool improving_only, cudaStream_t st);
+int cache_ensure(rt_problem *p);
+// batched iterations (batch.cu, SPEC.md §8.1)
+bool batch_usable(const rt_problem *p);
+int batch_begin(rt_problem *p, cudaStream_t st);
+int batch_iteration(rt_problem *p, int families, cudaStream_t st);
+int eval_table_launch(rt_problem *p, int families, cudaStream_t st);
 int ensure_position_matrix(rt_problem *p);  // sizes G for p->pmax (may allocate; not stream-ordered)
 
 }  // namespace rt

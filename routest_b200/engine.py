@@ -397,16 +397,19 @@ class Problem:
         self._check(self._lib.rt_problem_apply_moves(self._p, _u64(keys)))
 
     def local_search(self, families: int = ALL_FAMILIES, max_moves: int = 1 << 30, keys_capacity: int = 0,
-                     full: bool = False):
+                     full: bool = False, batched: bool = False):
         """Best-improvement search to a local optimum.  full=True re-scores the whole neighbourhood every iteration
-        (rt_problem_local_search_full) instead of only what the last move touched; the result is the same."""
+        (rt_problem_local_search_full) instead of only what the last move touched; the result is the same.
+        batched=True applies a set of independent improving moves per iteration (SPEC.md §8.1,
+        rt_problem_local_search_batched): max_moves then bounds the iterations, and the local optimum reached is in
+        general a different one."""
         moves = np.zeros(self.batch, np.int32)
         cost = np.zeros(self.batch, np.int64)
         keys = np.zeros((self.batch, max(keys_capacity, 1)), np.uint64)
-        fn = self._lib.rt_problem_local_search_full if full else self._lib.rt_problem_local_search
-        self._check(fn(self._p, int(families), int(min(max_moves, 2 ** 31 - 1)),
-                                                      _i32(moves), _i64(cost), _u64(keys) if keys_capacity else None,
-                                                      int(keys_capacity)))
+        fn = (self._lib.rt_problem_local_search_batched if batched else
+              self._lib.rt_problem_local_search_full if full else self._lib.rt_problem_local_search)
+        self._check(fn(self._p, int(families), int(min(max_moves, 2 ** 31 - 1)), _i32(moves), _i64(cost),
+                       _u64(keys) if keys_capacity else None, int(keys_capacity)))
         return moves, cost, [keys[b, :min(moves[b], keys_capacity)].copy() for b in range(self.batch)]
 
     def plan(self, lat, lon, stops, cap, max_dist, node, npos, *, dist_scale=DEFAULT_DIST_SCALE, time_scale=None,

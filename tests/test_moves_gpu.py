@@ -285,6 +285,52 @@ def test_local_search_batch_and_max_moves(engine, full):
             assert np.array_equal(pr.get_state(b)["node"], refs[b][0])
 
 
+@pytest.mark.parametrize("seed,stops,veh", [(10, 45, 5), (11, 100, 10), (12, 300, 12), (14, 500, 40)])
+def test_batched_local_search_applies_the_oracles_batches(engine, seed, stops, veh):
+    """SPEC §8.1 (rt_problem_local_search_batched): every iteration's set of independent moves, key for key, the
+    final routes and the cost equal the oracle's; the end state is a local optimum of the full neighbourhood."""
+    inst, node, raw = synth_vrptw(seed, stops, veh)
+    final, keys, sizes, cost = O.local_search_batched(inst, node, threads=O.num_threads())
+    with _load(engine, [(inst, node, raw)]) as pr:
+        moves, gcost, gkeys = pr.local_search(keys_capacity=4 * inst.n, batched=True)
+        st = pr.get_state(0)
+        best_after = int(pr.eval_moves()[0])
+    assert sizes.max() > 1 and sizes.size < keys.size
+    assert moves[0] == len(keys) and np.array_equal(gkeys[0], keys)
+    assert gcost[0] == cost and st["cost"] == cost and st["feasible"]
+    assert np.array_equal(st["node"], final)
+    assert O.key_unpack(best_after)[0] >= 0
+
+
+def test_batched_local_search_batch_of_instances_max_iterations_and_supplied_matrix(engine):
+    insts = [synth_vrptw(210 + b, 90, 5 + b) for b in range(4)]          # same size, different route counts
+    refs = [O.local_search_batched(inst, node, max_iters=3) for inst, node, _ in insts]
+    ends = [O.local_search_batched(inst, node) for inst, node, _ in insts]
+    with _load(engine, insts) as pr:
+        moves, cost, keys = pr.local_search(max_moves=3, keys_capacity=256, batched=True)
+        for b in range(4):
+            assert moves[b] == len(refs[b][1]) and np.array_equal(keys[b], refs[b][1]) and cost[b] == refs[b][3]
+            assert np.array_equal(pr.get_state(b)["node"], refs[b][0])
+        moves, cost, _ = pr.local_search(batched=True)                   # resumes to the oracle's end state
+        for b in range(4):
+            assert cost[b] == ends[b][3] and np.array_equal(pr.get_state(b)["node"], ends[b][0])
+    # a caller-supplied asymmetric matrix goes through the same path
+    inst, node, raw = insts[0]
+    rng = np.random.default_rng(5)
+    D = inst.D + rng.integers(0, 300, inst.D.shape).astype(np.int32)
+    T = inst.T + rng.integers(0, 30, inst.T.shape).astype(np.int32)
+    np.fill_diagonal(D, 0)
+    np.fill_diagonal(T, 0)
+    asym = O.Instance(D, T, inst.stops, inst.cap)
+    if O.route_state(asym, node)["feasible"]:
+        want = O.local_search_batched(asym, node)
+        with _load(engine, [(inst, node, raw)]) as pr:
+            pr.set_matrix(0, D, T)
+            moves, cost, keys = pr.local_search(keys_capacity=1024, batched=True)
+            assert np.array_equal(keys[0], want[1]) and cost[0] == want[3]
+            assert np.array_equal(pr.get_state(0)["node"], want[0])
+
+
 def test_multi_shard_search_through_dev_entry_points(engine):
     """The two _dev steps a multi-GPU search is made of, with the NCCL MIN replaced by torch.minimum over the
     shards' key tensors (one GPU here): same applied moves and final routes as the oracle."""
