@@ -110,6 +110,10 @@ def test_time_windows_and_improve_extension(engine):
     assert sorted(base["properties"]["optimized_order"]) == list(range(120))
     assert sorted(better["properties"]["optimized_order"]) == list(range(120))
     assert better["properties"]["summary"]["distance"] < base["properties"]["summary"]["distance"]
+    body["driver_details"]["improve"] = "batched"                      # SPEC §8.1: sets of independent moves
+    batched = S.optimize_route(json.loads(json.dumps(body)), engine=engine)
+    assert sorted(batched["properties"]["optimized_order"]) == list(range(120))
+    assert batched["properties"]["summary"]["distance"] < base["properties"]["summary"]["distance"]
     # the greedy with windows equals the oracle's
     stops = np.zeros((121, 3), np.int32)
     stops[0] = (0, 43200, 0)
