@@ -224,6 +224,18 @@ int rt_problem_set_shard(rt_problem *p, int shard_index, int shard_count);
 int rt_problem_eval_moves_dev(rt_problem *p, int families, int shard_index, int shard_count, void *best_keys_d,
                               void *stream);
 int rt_problem_apply_moves_dev(rt_problem *p, const void *keys_d, int improving_only, void *stream);
+/* Batched iterations (SPEC.md §8.1) over replicas: every rank scores its shard into a table of best keys per ordered
+ * route pair (followed by one key per route for the same-route families), rt_problem_table_entries int64 values in
+ * order-preserving signed form; the ranks combine their tables with ONE int64 MIN all-reduce; every rank then selects
+ * the same batch from the combined table, applies it and refreshes its state.  table_d: device int64
+ * [rt_problem_table_entries] owned by the caller (e.g. a torch tensor, so the collective can run on it directly).
+ * rt_problem_table_entries returns 0 when no routes are installed or an instance has more than 1,024 routes; call
+ * it once before the loop (it sizes the internal selection buffers).  An instance whose batch comes out empty is
+ * marked done (rt_problem_search_status). */
+int64_t rt_problem_table_entries(rt_problem *p);
+int rt_problem_eval_table_dev(rt_problem *p, int families, int shard_index, int shard_count, void *table_d,
+                              void *stream);
+int rt_problem_apply_batch_dev(rt_problem *p, const void *table_d, void *stream);
 /* The same exchange without a collective library: every replica (one process per GPU) exports a small slot buffer
  * through CUDA IPC, maps its peers', and from then on the evaluation step MIN-reduces its best keys straight into
  * every peer's buffer with system-scope atomics over NVLink, and the apply step waits (bounded: ~2 s, then

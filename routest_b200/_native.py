@@ -75,6 +75,9 @@ SIGNATURES = {
     "rt_problem_local_search_batched": (C.c_int, [c_problem_p, C.c_int, C.c_int, c_i32_p, c_i64_p, c_u64_p, C.c_int]),
     "rt_problem_eval_moves_dev": (C.c_int, [c_problem_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_problem_apply_moves_dev": (C.c_int, [c_problem_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "rt_problem_table_entries": (C.c_int64, [c_problem_p]),
+    "rt_problem_eval_table_dev": (C.c_int, [c_problem_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "rt_problem_apply_batch_dev": (C.c_int, [c_problem_p, C.c_void_p, C.c_void_p]),
     "rt_problem_exchange_handle_bytes": (C.c_int, []),
     "rt_problem_exchange_export": (C.c_int, [c_problem_p, C.c_void_p]),
     "rt_problem_exchange_connect": (C.c_int, [c_problem_p, C.c_void_p, C.c_int, C.c_int]),

@@ -25,6 +25,7 @@ constexpr int kRounds = 3;            // SPEC.md §8.1
 
 struct BatchArgs {
     const unsigned long long *inter, *intra;  // [batch][cr][cr], [batch][cr]
+    unsigned long long xmask;                 // 2^63 when the table is in signed-order form (multi-GPU), else 0
     int cr;
     const int *npos, *route, *rstart;
     int n, pstride, rstride;
@@ -69,13 +70,13 @@ __global__ void __launch_bounds__(128) batch_rowmin_kernel(const BatchArgs a)
     unsigned long long best = kNoMove;
     for (int rb = tid; rb < R; rb += blockDim.x) {
         if (taken[rb]) continue;
-        const unsigned long long k = row[rb];
+        const unsigned long long k = row[rb] ^ a.xmask;
         if (k == kNoMove) continue;
         best = k < best ? k : best;
         if (k < m[rb]) atomicMin(m + rb, k);  // m[] only ever decreases: a stale read costs one redundant atomic
     }
     if (tid == 0) {
-        const unsigned long long k = a.intra[ro + ra];
+        const unsigned long long k = a.intra[ro + ra] ^ a.xmask;
         best = k < best ? k : best;
     }
 #pragma unroll
@@ -219,19 +220,30 @@ __global__ void __launch_bounds__(kSelectThreads) batch_apply_kernel(const Batch
 
 bool batch_usable(const rt_problem *p) { return std::max(1, p->grows - p->n) <= kSelectThreads; }
 
-static int batch_ensure(rt_problem *p)
+// the search's own table: inter and intra back to back in the incremental search's buffer
+static unsigned long long *own_table(rt_problem *p) { return static_cast<unsigned long long *>(p->cache_inter.p); }
+
+size_t batch_table_entries(const rt_problem *p)
 {
-    RT_TRY(cache_ensure(p));  // the table itself
+    const size_t B = p->batch, cr = std::max(1, p->grows - p->n);
+    return B * (cr * cr + cr);
+}
+
+int batch_ensure(rt_problem *p)
+{
+    RT_TRY(cache_ensure(p));  // sizes the table (cache_r) and, for the single-GPU driver, provides its memory
     const size_t B = p->batch, cr = p->cache_r;
+    RT_TRY(reserve(p->e, p->cache_inter, batch_table_entries(p) * 8));
     return reserve(p->e, p->batch_buf, B * cr * (3 * 8 + 4) + B * 4 + 64);
 }
 
-static BatchArgs batch_args(rt_problem *p)
+static BatchArgs batch_args(rt_problem *p, const unsigned long long *table, bool signed_keys)
 {
     BatchArgs a{};
     const size_t B = p->batch, cr = p->cache_r;
-    a.inter = static_cast<unsigned long long *>(p->cache_inter.p);
-    a.intra = static_cast<unsigned long long *>(p->cache_intra.p);
+    a.inter = table;
+    a.intra = table + B * cr * cr;
+    a.xmask = signed_keys ? 0x8000000000000000ull : 0ull;
     a.cr = p->cache_r;
     a.npos = p->npos;
     a.route = p->route;
@@ -260,12 +272,11 @@ int batch_begin(rt_problem *p, cudaStream_t st)
     return state_refresh(p, st);
 }
 
-// One batched iteration on a fresh state; leaves the state fresh again.
-int batch_iteration(rt_problem *p, int families, cudaStream_t st)
+// Table (complete: every shard's minima combined) -> selection rounds -> apply -> state refresh.
+int batch_select_apply(rt_problem *p, const unsigned long long *table, bool signed_keys, cudaStream_t st)
 {
     rt_engine *e = p->e;
-    RT_TRY(eval_table_launch(p, families, st));
-    const BatchArgs a = batch_args(p);
+    const BatchArgs a = batch_args(p, table, signed_keys);
     batch_reset_kernel<<<p->batch, 256, 0, st>>>(a);
     RT_CUDA(e, cudaGetLastError());
     for (int round = 0; round < kRounds; ++round) {
@@ -278,6 +289,13 @@ int batch_iteration(rt_problem *p, int families, cudaStream_t st)
     batch_apply_kernel<<<p->batch, kSelectThreads, 0, st>>>(a);
     RT_CUDA(e, cudaGetLastError());
     return state_refresh(p, st);
+}
+
+// One batched iteration on a fresh state; leaves the state fresh again.
+int batch_iteration(rt_problem *p, int families, cudaStream_t st)
+{
+    RT_TRY(eval_table_launch(p, families, 0, 1, own_table(p), false, st));
+    return batch_select_apply(p, own_table(p), false, st);
 }
 
 }  // namespace rt

@@ -515,6 +515,12 @@ __global__ void fill_keys_kernel(unsigned long long *dst, int batch)
     if (i < batch) dst[i] = kNoMove;
 }
 
+__global__ void flip_keys_kernel(unsigned long long *keys, size_t count)
+{
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < count) keys[i] ^= 0x8000000000000000ull;
+}
+
 }  // namespace
 
 // Evaluates this shard's candidates of every instance and leaves one key per instance in best_d (device),
@@ -560,19 +566,22 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     return RT_OK;
 }
 
-// Full evaluation into the per-route-pair table (batch.cu): inter[ra][rb] and intra[r] of every instance, absolute
-// positions in the keys.  The state must be fresh; the table buffers are those of the incremental search (cache.cu).
-int eval_table_launch(rt_problem *p, int families, cudaStream_t st)
+// Full evaluation of this shard's candidates into a per-route-pair table (batch.cu): inter[ra][rb] for every ordered
+// pair of routes followed by intra[r], [batch][cr][cr] + [batch][cr] keys with absolute positions.  The state must
+// be fresh.  signed_keys: leave the table in order-preserving signed form (key ^ 2^63) so that replicas can combine
+// their shards with an int64 MIN all-reduce.
+int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *table_d,
+                      bool signed_keys, cudaStream_t st)
 {
     rt_engine *e = p->e;
-    EvalArgs a = make_args(p, families, 0, 1, p->best);
-    a.inter = static_cast<unsigned long long *>(p->cache_inter.p);
-    a.intra = static_cast<unsigned long long *>(p->cache_intra.p);
-    a.cr = p->cache_r;
+    EvalArgs a = make_args(p, families, shard_index, shard_count, p->best);
     const size_t B = p->batch, cr = p->cache_r;
-    RT_CUDA(e, cudaMemsetAsync(a.inter, 0xFF, B * cr * cr * 8, st));
-    RT_CUDA(e, cudaMemsetAsync(a.intra, 0xFF, B * cr * 8, st));
+    a.inter = table_d;
+    a.intra = table_d + B * cr * cr;
+    a.cr = p->cache_r;
+    RT_CUDA(e, cudaMemsetAsync(table_d, 0xFF, B * (cr * cr + cr) * 8, st));
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
+    const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
     const bool overlap = (families & 6) && p->side_stream;
     cudaStream_t st_intra = st;
     if (overlap) {
@@ -581,13 +590,13 @@ int eval_table_launch(rt_problem *p, int families, cudaStream_t st)
         st_intra = p->side_stream;
     }
     {
-        dim3 grid((pmax + kIntraThreads - 1) / kIntraThreads, p->batch);
+        dim3 grid((shard_rows + kIntraThreads - 1) / kIntraThreads, p->batch);
         if (p->symmetric) eval_intra_kernel<kTable, false><<<grid, kIntraThreads, 0, st_intra>>>(a);
         else eval_intra_kernel<kTable, true><<<grid, kIntraThreads, 0, st_intra>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     if (families & 6) {
-        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (pmax + kStripRows - 1) / kStripRows, p->batch);
+        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + kStripRows - 1) / kStripRows, p->batch);
         if (p->symmetric) eval_inter_kernel<kTable, false><<<grid, kInterThreads, 0, st>>>(a);
         else eval_inter_kernel<kTable, true><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
@@ -595,6 +604,11 @@ int eval_table_launch(rt_problem *p, int families, cudaStream_t st)
     if (overlap) {
         RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
         RT_CUDA(e, cudaStreamWaitEvent(st, p->ev_join, 0));
+    }
+    if (signed_keys) {
+        const size_t count = B * (cr * cr + cr);
+        flip_keys_kernel<<<static_cast<unsigned>((count + 255) / 256), 256, 0, st>>>(table_d, count);
+        RT_CUDA(e, cudaGetLastError());
     }
     return RT_OK;
 }

@@ -711,6 +711,45 @@ int rt_problem_apply_moves_dev(rt_problem *p, const void *keys_d, int improving_
                               pick_stream(e, stream));
 }
 
+int64_t rt_problem_table_entries(rt_problem *p)
+{
+    if (!p) return 0;
+    rt_engine *e = p->e;
+    std::lock_guard<std::mutex> lk(e->mu);
+    DeviceGuard dg(e->device);
+    if (!p->has_routes || !batch_usable(p) || batch_ensure(p) != RT_OK) return 0;
+    return static_cast<int64_t>(batch_table_entries(p));
+}
+
+int rt_problem_eval_table_dev(rt_problem *p, int families, int shard_index, int shard_count, void *table_d, void *stream)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    rt_engine *e = p->e;
+    if (!table_d || shard_count < 1 || shard_index < 0 || shard_index >= shard_count || !(families & 7))
+        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_eval_table_dev: bad argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_eval_table_dev: no routes set");
+    if (!batch_usable(p)) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_eval_table_dev handles at most 1024 routes per instance");
+    if (!shard_covered(p, shard_index, shard_count))
+        return fail(e, RT_ERR_STATE, "rt_problem_eval_table_dev: shard %d/%d is not the one set by rt_problem_set_shard",
+                    shard_index, shard_count);
+    DeviceGuard dg(e->device);
+    RT_TRY(batch_ensure(p));  // no-op after rt_problem_table_entries
+    return eval_table_launch(p, families, shard_index, shard_count, static_cast<unsigned long long *>(table_d), true,
+                             pick_stream(e, stream));
+}
+
+int rt_problem_apply_batch_dev(rt_problem *p, const void *table_d, void *stream)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    rt_engine *e = p->e;
+    if (!table_d) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_apply_batch_dev: NULL argument");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_apply_batch_dev: no routes set");
+    if (!batch_usable(p)) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_apply_batch_dev handles at most 1024 routes per instance");
+    DeviceGuard dg(e->device);
+    RT_TRY(batch_ensure(p));
+    return batch_select_apply(p, static_cast<const unsigned long long *>(table_d), true, pick_stream(e, stream));
+}
+
 int rt_problem_search_status(rt_problem *p, int32_t *done_out, int32_t *moves_out, int64_t *cost_out)
 {
     RT_PROBLEM_GUARD(p);

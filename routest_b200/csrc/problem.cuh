@@ -115,7 +115,11 @@ int cache_ensure(rt_problem *p);
 bool batch_usable(const rt_problem *p);
 int batch_begin(rt_problem *p, cudaStream_t st);
 int batch_iteration(rt_problem *p, int families, cudaStream_t st);
-int eval_table_launch(rt_problem *p, int families, cudaStream_t st);
+int batch_ensure(rt_problem *p);
+size_t batch_table_entries(const rt_problem *p);
+int batch_select_apply(rt_problem *p, const unsigned long long *table, bool signed_keys, cudaStream_t st);
+int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *table_d,
+                      bool signed_keys, cudaStream_t st);
 int ensure_position_matrix(rt_problem *p);  // sizes G for p->pmax (may allocate; not stream-ordered)
 
 }  // namespace rt

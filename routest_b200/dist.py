@@ -7,6 +7,9 @@ Where the path shards:
     of the candidate space, and the ranks all-reduce ONE int64 key per instance with MIN; every rank then applies
     the same winning move (`DistributedSearch`).  Keys travel in order-preserving signed form (packed key XOR 2^63),
     so `ReduceOp.MIN` on int64 picks the lowest (delta, family, p, q) and INT64_MAX means "no move".
+    With `batched=True` an iteration applies a whole set of independent moves (SPEC.md §8.1): every rank scores
+    its shard into a table of best keys per ordered route pair, the ranks MIN-reduce that table (R^2 + R int64 per
+    instance) in one all-reduce, and every rank selects and applies the same batch.
   * greedy construction                               -> replicas only (sequential chain).
 The reduce is 8 bytes per instance and latency bound; iterations are enqueued back to back on one stream and the
 host looks at the done flags only every `check_every` iterations.
@@ -44,7 +47,7 @@ class DistributedSearch:
     to exercise this loop under gloo."""
 
     def __init__(self, problem, batch: int, *, device=None, group=None, families: int = 7, check_every: int = 16,
-                 exchange: str = "nccl"):
+                 exchange: str = "nccl", batched: bool = False):
         self.problem, self.batch, self.group = problem, batch, group
         self.families, self.check_every = families, check_every
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -54,7 +57,11 @@ class DistributedSearch:
             problem.set_shard(self.rank, self.world)
         if exchange not in ("nccl", "peer"):
             raise ValueError("exchange must be 'nccl' or 'peer'")
+        if batched and exchange != "nccl":
+            raise ValueError("batched iterations exchange their table through the collective (exchange='nccl')")
         self.exchange = exchange
+        self.batched = batched
+        self.table = (torch.empty(problem.table_entries(), dtype=torch.int64, device=device) if batched else None)
         if exchange == "peer":
             handle = problem.exchange_export()
             handles = [None] * self.world
@@ -71,6 +78,11 @@ class DistributedSearch:
 
     def step(self):
         s = self._stream()
+        if self.batched:
+            self.problem.eval_table_dev(self.table.data_ptr(), self.families, (self.rank, self.world), s)
+            allreduce_min_keys(self.table, self.group)
+            self.problem.apply_batch_dev(self.table.data_ptr(), s)
+            return
         if self.exchange == "peer":
             self.problem.eval_moves_xchg_dev(self.families, s)
             self.problem.apply_moves_xchg_dev(True, s)
@@ -80,7 +92,8 @@ class DistributedSearch:
         self.problem.apply_moves_dev(self.keys.data_ptr(), True, s)
 
     def run(self, max_moves: int = 1 << 30):
-        """Runs to a local optimum (or max_moves).  Returns (moves, cost) per instance — identical on every rank."""
+        """Runs to a local optimum (or max_moves iterations).  Returns (moves, cost) per instance — identical on
+        every rank."""
         issued = 0
         while issued < max_moves:
             todo = min(self.check_every, max_moves - issued)

@@ -482,6 +482,20 @@ class Problem:
     def apply_moves_dev(self, keys_ptr: int, improving_only: bool = True, stream: int = 0):
         self._check(self._lib.rt_problem_apply_moves_dev(self._p, keys_ptr, int(bool(improving_only)), stream or None))
 
+    # -- batched iterations over replicas (SPEC.md §8.1): table per rank -> MIN all-reduce -> same batch everywhere
+    def table_entries(self) -> int:
+        n = int(self._lib.rt_problem_table_entries(self._p))
+        if n <= 0:
+            raise EngineError(N.RT_ERR_STATE, "no routes installed, or more than 1024 routes in an instance")
+        return n
+
+    def eval_table_dev(self, table_ptr: int, families: int = ALL_FAMILIES, shard=(0, 1), stream: int = 0):
+        self._check(self._lib.rt_problem_eval_table_dev(self._p, int(families), int(shard[0]), int(shard[1]), table_ptr,
+                                                        stream or None))
+
+    def apply_batch_dev(self, table_ptr: int, stream: int = 0):
+        self._check(self._lib.rt_problem_apply_batch_dev(self._p, table_ptr, stream or None))
+
     # -- peer-memory exchange (multi-GPU search without a collective call per iteration)
     def exchange_export(self) -> bytes:
         buf = C.create_string_buffer(int(self._lib.rt_problem_exchange_handle_bytes()))

@@ -58,6 +58,99 @@ class OracleProblem:
         return [self.done], [self.moves], [self.O.route_state(self.inst, self.node)["cost"]]
 
 
+class OracleBatchProblem(OracleProblem):
+    """Stand-in for the batched steps (SPEC §8.1): the shard's table of best keys per ordered route pair comes from
+    the oracle's candidate dumps, the selection from the MIN-reduced table is restated here in numpy."""
+
+    NONE = np.uint64(2 ** 64 - 1)
+    FLIP = np.uint64(1 << 63)
+
+    def table_entries(self):
+        R = self.node.size - self.inst.n
+        return R * R + R
+
+    def _view(self, ptr):
+        import ctypes
+        n = self.table_entries()
+        return np.frombuffer((ctypes.c_uint64 * n).from_address(ptr), dtype=np.uint64)
+
+    def eval_table_dev(self, table_ptr, families, shard, stream):
+        O, P, R = self.O, self.node.size, self.node.size - self.inst.n
+        route = O.route_state(self.inst, self.node)["route"]
+        i, cnt = shard
+        p0, p1 = P * i // cnt, P * (i + 1) // cnt
+        inter = np.full((R, R), self.NONE, np.uint64)
+        intra = np.full(R, self.NONE, np.uint64)
+        for fam in (0, 1, 2):
+            if not families & (1 << fam):
+                continue
+            d, f = O.eval_fast(self.inst, self.node, fam)
+            for p, q in zip(*np.nonzero(f == 1)):
+                if not p0 <= p < p1:
+                    continue
+                k = np.uint64(((int(d[p, q]) + 2 ** 31) << 32) | (fam << 30) | (int(p) << 15) | int(q))
+                ra, rb = route[p], route[q]
+                if ra == rb:
+                    intra[ra] = min(intra[ra], k)
+                else:
+                    inter[ra, rb] = min(inter[ra, rb], k)
+        self._view(table_ptr)[:] = np.concatenate([inter.ravel(), intra]) ^ self.FLIP
+
+    def apply_batch_dev(self, table_ptr, stream):
+        if self.done:
+            return
+        O, R = self.O, self.node.size - self.inst.n
+        route = O.route_state(self.inst, self.node)["route"]
+        t = self._view(table_ptr) ^ self.FLIP
+        inter, intra = t[:R * R].reshape(R, R), t[R * R:]
+        taken, batch = np.zeros(R, bool), []
+        for _ in range(O.BATCH_ROUNDS):
+            m = np.full(R, self.NONE, np.uint64)
+            for ra in range(R):
+                if taken[ra]:
+                    continue
+                m[ra] = min(m[ra], intra[ra])
+                for rb in range(R):
+                    if not taken[rb]:
+                        m[ra], m[rb] = min(m[ra], inter[ra, rb]), min(m[rb], inter[ra, rb])
+            sel = []
+            for r in range(R):
+                k = int(m[r])
+                if k == O.NO_MOVE or O.key_unpack(k)[0] >= 0:
+                    continue
+                _, _, pp, qq = O.key_unpack(k)
+                if route[pp] == r and int(m[route[qq]]) == k:
+                    sel.append(k)
+            if not sel:
+                break
+            for k in sel:
+                taken[route[O.key_unpack(k)[2]]] = taken[route[O.key_unpack(k)[3]]] = True
+            batch += sel
+        if not batch:
+            self.done = 1
+            return
+        self.node = O.apply_batch(self.inst, self.node, np.array(batch, np.uint64))
+        self.moves += len(batch)
+
+
+def _worker_batched(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch.distributed as dist
+    from conftest import synth_vrptw
+    from routest_b200.dist import DistributedSearch
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        inst, node, _ = synth_vrptw(32, 50, 5)
+        prob = OracleBatchProblem(inst, node)
+        search = DistributedSearch(prob, 1, device="cpu", check_every=4, batched=True)
+        moves, cost = search.run()
+        out[rank] = (int(moves[0]), int(cost[0]), prob.node.tolist())
+    finally:
+        dist.destroy_process_group()
+
+
 def _worker(rank, world, port, out):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -88,4 +181,21 @@ def test_replicated_search_under_gloo_matches_oracle():
     mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
     inst, node, _ = synth_vrptw(31, 60, 5)
     final, keys, cost = O.local_search(inst, node)
+    assert out[0] == out[1] == (len(keys), cost, final.tolist())
+
+
+@pytest.mark.timeout(300)
+def test_batched_replicated_search_under_gloo_matches_oracle():
+    """SPEC §8.1 over two ranks: shard tables MIN-reduced through gloo, both ranks apply the oracle's batches."""
+    from oracle import oracle as O
+    from conftest import synth_vrptw
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_batched, args=(2, port, out), nprocs=2, join=True)
+    inst, node, _ = synth_vrptw(32, 50, 5)
+    final, keys, sizes, cost = O.local_search_batched(inst, node)
+    assert sizes.max() > 1
     assert out[0] == out[1] == (len(keys), cost, final.tolist())

@@ -331,6 +331,27 @@ def test_batched_local_search_batch_of_instances_max_iterations_and_supplied_mat
             assert np.array_equal(pr.get_state(0)["node"], want[0])
 
 
+def test_batched_search_through_sharded_table_entry_points(engine):
+    """The _dev steps of a multi-GPU batched search (rt_problem_eval_table_dev / rt_problem_apply_batch_dev) with the
+    int64 MIN all-reduce replaced by torch.minimum over the shards' tables: the oracle's batches, for two instances."""
+    import torch
+    insts = [synth_vrptw(15 + b, 140, 7 + b) for b in range(2)]
+    ends = [O.local_search_batched(inst, node, threads=O.num_threads()) for inst, node, _ in insts]
+    shards = 3
+    with _load(engine, insts) as pr:
+        s = torch.cuda.current_stream().cuda_stream
+        tabs = [torch.empty(pr.table_entries(), dtype=torch.int64, device="cuda") for _ in range(shards)]
+        for it in range(max(e[2].size for e in ends) + 3):
+            for i in range(shards):
+                pr.eval_table_dev(tabs[i].data_ptr(), shard=(i, shards), stream=s)
+            combined = torch.stack(tabs).min(dim=0).values.contiguous()
+            pr.apply_batch_dev(combined.data_ptr(), stream=s)
+        done, moves, gcost = pr.search_status()
+        for b in range(2):
+            assert done[b] == 1 and moves[b] == ends[b][1].size and gcost[b] == ends[b][3]
+            assert np.array_equal(pr.get_state(b)["node"], ends[b][0])
+
+
 def test_multi_shard_search_through_dev_entry_points(engine):
     """The two _dev steps a multi-GPU search is made of, with the NCCL MIN replaced by torch.minimum over the
     shards' key tensors (one GPU here): same applied moves and final routes as the oracle."""

@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--vehicles", type=int, default=20)
     ap.add_argument("--max-moves", type=int, default=1 << 30)
     ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"])
+    ap.add_argument("--batched", action="store_true", help="SPEC.md 8.1: a set of independent moves per iteration")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -54,7 +55,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = Engine(local)
     pr, trips = build(eng, 5678, a.stops, a.vehicles)
-    search = DistributedSearch(pr, 1, device="cuda", check_every=32, exchange=a.exchange)
+    search = DistributedSearch(pr, 1, device="cuda", check_every=4 if a.batched else 32, exchange=a.exchange,
+                               batched=a.batched)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -72,10 +74,10 @@ def main():
     if rank == 0:
         pr1, _ = build(eng, 5678, a.stops, a.vehicles)
         t0 = time.perf_counter()
-        m1, c1, _ = pr1.local_search(max_moves=a.max_moves)
+        m1, c1, _ = pr1.local_search(max_moves=a.max_moves, batched=a.batched)
         dt_single = time.perf_counter() - t0
         same = int(m1[0]) == int(moves[0]) and int(c1[0]) == int(cost[0]) and pr1.get_routes()[0] == routes_multi
-        print(json.dumps({"world": world, "exchange": a.exchange, "stops": a.stops, "moves": int(moves[0]), "cost": int(cost[0]),
+        print(json.dumps({"world": world, "exchange": a.exchange, "batched": a.batched, "stops": a.stops, "moves": int(moves[0]), "cost": int(cost[0]),
                           "ranks_agree": ok, "equals_single_gpu": bool(same), "s_multi": round(dt_multi, 4),
                           "s_single": round(dt_single, 4), "us_per_move_multi": round(1e6 * dt_multi / max(1, int(moves[0])), 1),
                           "us_per_move_single": round(1e6 * dt_single / max(1, int(m1[0])), 1)}))
