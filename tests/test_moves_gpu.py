@@ -285,11 +285,13 @@ def test_local_search_batch_and_max_moves(engine, full):
             assert np.array_equal(pr.get_state(b)["node"], refs[b][0])
 
 
-@pytest.mark.parametrize("seed,stops,veh", [(10, 45, 5), (11, 100, 10), (12, 300, 12), (14, 500, 40)])
+@pytest.mark.parametrize("seed,stops,veh", [(10, 45, 5), (11, 100, 10), (12, 300, 12), (14, 500, 40), (16, 640, 300)])
 def test_batched_local_search_applies_the_oracles_batches(engine, seed, stops, veh):
     """SPEC §8.1 (rt_problem_local_search_batched): every iteration's set of independent moves, key for key, the
-    final routes and the cost equal the oracle's; the end state is a local optimum of the full neighbourhood."""
+    final routes and the cost equal the oracle's; the end state is a local optimum of the full neighbourhood.  Up to
+    128 routes the selection and the apply step are one kernel, beyond that one kernel per step (last case)."""
     inst, node, raw = synth_vrptw(seed, stops, veh)
+    assert (node.size - inst.n > 128) == (veh > 128)
     final, keys, sizes, cost = O.local_search_batched(inst, node, threads=O.num_threads())
     with _load(engine, [(inst, node, raw)]) as pr:
         moves, gcost, gkeys = pr.local_search(keys_capacity=4 * inst.n, batched=True)
