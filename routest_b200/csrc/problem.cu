@@ -1,6 +1,8 @@
 // problem.cu — extern "C" entry points around rt_problem: a batch of device-resident instances on which the
 // matrix build, the greedy construction, move evaluation and local search run without the matrix ever leaving HBM.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -830,6 +832,9 @@ static int local_search_impl(rt_problem *p, int families, int max_moves, int mod
             (void)cudaGetLastError();
         }
     }
+    if (getenv("ROUTEST_DEBUG"))
+        fprintf(stderr, "[routest] local search (%s): iterations %s\n", batched ? "batched" : cached ? "incremental" : "full",
+                exec ? "replayed from a CUDA graph" : "launched kernel by kernel");
     const int kChunk = batched ? 8 : 32;  // a batched iteration is a full evaluation: overshoot less
     int issued = 0;
     bool all_done = false;
