@@ -304,6 +304,19 @@ def test_batched_local_search_applies_the_oracles_batches(engine, seed, stops, v
     assert O.key_unpack(best_after)[0] >= 0
 
 
+@pytest.mark.parametrize("seed,stops,veh", [(1, 12, 3), (2, 6, 1), (3, 2, 1), (4, 1, 1)])
+def test_batched_local_search_on_tiny_instances(engine, seed, stops, veh):
+    """Edge sizes: a handful of stops, a single route, nothing to improve at all."""
+    inst, node, raw = synth_vrptw(seed, stops, veh)
+    final, keys, sizes, cost = O.local_search_batched(inst, node)
+    with _load(engine, [(inst, node, raw)]) as pr:
+        moves, gcost, gkeys = pr.local_search(keys_capacity=64, batched=True)
+        assert moves[0] == keys.size and np.array_equal(gkeys[0], keys) and gcost[0] == cost
+        assert np.array_equal(pr.get_state(0)["node"], final)
+        moves, gcost, _ = pr.local_search(batched=True)          # already a local optimum: nothing happens
+        assert moves[0] == 0 and gcost[0] == cost
+
+
 def test_batched_local_search_batch_of_instances_max_iterations_and_supplied_matrix(engine):
     insts = [synth_vrptw(210 + b, 90, 5 + b) for b in range(4)]          # same size, different route counts
     refs = [O.local_search_batched(inst, node, max_iters=3) for inst, node, _ in insts]
