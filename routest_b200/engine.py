@@ -7,6 +7,7 @@ handle and never synchronise — torch supplies device memory, streams and NCCL,
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -70,10 +71,13 @@ class Engine:
             self._h = None
             raise EngineError(rc, (msg or b"rt_create failed").decode())
         self.device = int(device)
+        self._problems = weakref.WeakSet()   # closed before the engine: a problem's handle points into it
 
     # -- lifetime -----------------------------------------------------------------------------------------------
     def close(self):
         if getattr(self, "_h", None):
+            for pr in list(getattr(self, "_problems", ())):
+                pr.close()
             self._lib.rt_destroy(self._h)
             self._h = None
 
@@ -260,6 +264,7 @@ class Problem:
         engine._check(self._lib.rt_problem_create(engine.handle, int(n), int(batch), C.byref(self._p)))
         self.n, self.batch = int(n), int(batch)
         self.pstride = int(self._lib.rt_problem_position_stride(self._p))
+        engine._problems.add(self)
 
     def close(self):
         if getattr(self, "_p", None):

@@ -123,3 +123,19 @@ def test_fast_sqrt_is_ieee_on_the_whole_admitted_range(engine):
     lo = int(np.float32(2.0 ** -100).view(np.uint32))
     hi = int(np.float32(4.0).view(np.uint32)) + 1
     assert engine.selftest_fast_sqrt(lo, hi) == 0
+
+
+def test_closing_the_engine_closes_its_problems_first():
+    """A problem's handle points into its engine: Engine.close() destroys the problems it handed out, and a call on
+    a closed problem is an error, not a crash."""
+    from routest_b200 import Engine, EngineError
+    eng = Engine(0)
+    pr = eng.problem(11, 2)
+    rng = np.random.default_rng(0)
+    pr.set_coords(rng.uniform(14.4, 14.6, (2, 11)), rng.uniform(120.9, 121.1, (2, 11)))
+    eng.close()
+    assert pr.handle is None
+    with pytest.raises(EngineError):
+        pr.build_matrix(10.0, 0.09)
+    pr.close()
+    eng.close()
