@@ -44,7 +44,8 @@ typedef struct rt_engine rt_engine;
 int rt_version(void);
 
 /* Engine lifetime.  `device` is a CUDA ordinal.  Replaces nothing in the reference (it holds no state besides the
- * lazily loaded model global, ml.py:4,11-21, whose unlocked initialisation this handle makes explicit). */
+ * lazily loaded model global, ml.py:4,11-21, whose unlocked initialisation this handle makes explicit).
+ * Problems (rt_problem_create) point into their engine: destroy them before rt_destroy. */
 int rt_create(int device, rt_engine **out);
 void rt_destroy(rt_engine *e);
 const char *rt_last_error(const rt_engine *e);
