@@ -3,8 +3,13 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <ctime>
 #include <new>
 #include <vector>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 #include "problem.cuh"
 
@@ -62,6 +67,38 @@ __global__ void cells_to_planes_kernel(const int2 *__restrict__ cells, int n, in
     const int2 c = cells[static_cast<size_t>(i) * pitch + j];
     dist[static_cast<size_t>(i) * n + j] = c.x;
     tim[static_cast<size_t>(i) * n + j] = c.y;
+}
+
+// Host side of rt_problem_plan: every id in [0, n) and exactly n-1 customers among the P positions.  On the call's
+// critical path (the GPU is only busy with the input copies meanwhile), hence four ids per step: the sign bit of
+// v | (n-1 - v) is set iff v is negative or above n-1.
+bool positions_well_formed(const int32_t *nd, int P, int n)
+{
+    const int32_t top = n - 1;
+    int32_t acc = 0, zeros = 0;
+    int q = 0;
+#if defined(__SSE2__)
+    __m128i vacc = _mm_setzero_si128(), vz = _mm_setzero_si128();
+    const __m128i vtop = _mm_set1_epi32(top), zero = _mm_setzero_si128();
+    for (; q + 8 <= P; q += 8) {
+        const __m128i v0 = _mm_loadu_si128(reinterpret_cast<const __m128i *>(nd + q));
+        const __m128i v1 = _mm_loadu_si128(reinterpret_cast<const __m128i *>(nd + q + 4));
+        vacc = _mm_or_si128(vacc, _mm_or_si128(_mm_or_si128(v0, _mm_sub_epi32(vtop, v0)),
+                                               _mm_or_si128(v1, _mm_sub_epi32(vtop, v1))));
+        vz = _mm_sub_epi32(vz, _mm_add_epi32(_mm_cmpeq_epi32(v0, zero), _mm_cmpeq_epi32(v1, zero)));
+    }
+    alignas(16) int32_t t[4];
+    _mm_store_si128(reinterpret_cast<__m128i *>(t), vacc);
+    acc = t[0] | t[1] | t[2] | t[3];
+    _mm_store_si128(reinterpret_cast<__m128i *>(t), vz);
+    zeros = t[0] + t[1] + t[2] + t[3];
+#endif
+    for (; q < P; ++q) {
+        const int32_t v = nd[q];
+        acc |= v | (top - v);
+        zeros += v == 0;
+    }
+    return acc >= 0 && zeros == P - n + 1;
 }
 
 __global__ void reset_search_kernel(int *done, int *moves, int batch)
@@ -137,10 +174,9 @@ int rt_problem_create(rt_engine *e, int n, int batch, rt_problem **out)
     A(dev_alloc(p, p->rdist, B * RS));
     A(dev_alloc(p, p->cost, B));
     A(dev_alloc(p, p->feasible, B));
-    A(dev_alloc(p, p->best, B));
+    A(dev_alloc(p, p->best, B + 1));  // + the coordinate flag of rt_problem_plan: keys and flag leave in one copy
     A(dev_alloc(p, p->done, B));
     A(dev_alloc(p, p->moves, B));
-    A(dev_alloc(p, p->coord_flag, 1));
     A(dev_alloc(p, p->hist, B * p->hist_cap));
     A(dev_alloc(p, p->gkeys, B * n2));
     A(dev_alloc(p, p->gorder, B * n2));
@@ -151,6 +187,11 @@ int rt_problem_create(rt_engine *e, int n, int batch, rt_problem **out)
     A(dev_alloc(p, p->g_trip_off, B * (N + 1)));
     A(dev_alloc(p, p->g_ntrips, B));
     A(dev_alloc(p, p->g_status, B));
+    if (rc == RT_OK) {
+        p->coord_flag = reinterpret_cast<int *>(p->best + B);
+        if (cudaMemset(p->coord_flag, 0, sizeof(unsigned long long)) != cudaSuccess)
+            rc = fail(e, RT_ERR_CUDA, "rt_problem_create: cudaMemset failed");
+    }
     if (rc != RT_OK) {
         for (int i = 0; i < p->n_allocs; ++i) cudaFree(p->all_allocs[i]);
         delete p;
@@ -500,11 +541,11 @@ int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int
     RT_TRY(check_scales(e, dist_scale, time_scale));
     DeviceGuard dg(e->device);
     cudaStream_t st = pick_stream(e, stream);
-    RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, st));
+    RT_TRY(position_unit_vectors_launch(p, st));  // unit vectors, already in route order
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     p->cells_from_coords = true;
-    RT_TRY(state_refresh(p, st));
+    RT_TRY(state_refresh(p, st, nullptr, /*vectors_ready=*/true));
     return eval_moves_launch(p, families, 0, 1, static_cast<unsigned long long *>(best_keys_d), true, st);
 }
 
@@ -522,6 +563,10 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
             node[b * PS + npos[b] - 1] != 0)
             return fail(e, RT_ERR_INVALID_ARG, "instance %zu: malformed position array", b);
     cudaStream_t st = e->stream;
+    static const bool dbg = getenv("ROUTEST_DEBUG_PLAN") != nullptr;  // prints where the call's host time goes
+    auto now = []() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; };
+    const double t_begin = dbg ? now() : 0;
+    double t_copies = 0, t_valid = 0, t_issued = 0;
     // What the matrix needs (coordinates, routes) goes first on the compute stream; the stop records and limits, which
     // only the state tables read, travel on the copy stream underneath the unit-vector and matrix kernels.
     RT_CUDA(e, cudaMemcpyAsync(p->lat, lat, B * N * 8, cudaMemcpyHostToDevice, st));
@@ -534,28 +579,26 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, B * 4, cudaMemcpyHostToDevice, e->copy_stream));
     RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, B * 8, cudaMemcpyHostToDevice, e->copy_stream));
     RT_CUDA(e, cudaEventRecord(e->ev[1], e->copy_stream));
-    // While those copies are in flight the host checks what the kernels index with: every position holds a node id
-    // below n and there are exactly n-1 customers among them (so the route count is P - n and every table fits).
-    // That a customer is not repeated is not checked here: a repeat gives a meaningless plan, not a fault.
+    if (dbg) t_copies = now();
+    // The unit vectors go out first (the kernel itself falls back to the depot for a node id it cannot index), so the
+    // GPU has work while the host checks what every other kernel indexes with: each position holds a node id below n
+    // and there are exactly n-1 customers among them (so the route count is P - n and every table fits).  That a
+    // customer is not repeated is not checked here: a repeat gives a meaningless plan, not a fault.  Coordinates
+    // are range-checked by that kernel (off the host's critical path); stop records are taken as they are
+    // (rt_problem_set_stops is the validating entry point) — out-of-range values cannot fault a kernel.
+    int *bad_flag = p->coord_flag;
+    const int seq = ++p->plan_seq;  // the flag is written with this call's number: no reset launch needed
+    RT_TRY(position_unit_vectors_launch(p, st, bad_flag, seq));
+    const double t_launch1 = dbg ? now() : 0;
     for (size_t b = 0; b < B; ++b) {
-        const int32_t *nd = node + b * PS;
-        const int P = npos[b];
-        unsigned bad = 0;
-        int zeros = 0;
-        for (int q = 0; q < P; ++q) {
-            bad |= static_cast<unsigned>(nd[q]) >= static_cast<unsigned>(N);
-            zeros += nd[q] == 0;
-        }
-        if (bad || zeros != P - static_cast<int>(N) + 1) {
+        if (!positions_well_formed(node + b * PS, npos[b], static_cast<int>(N))) {
             p->has_routes = false;  // the copy above has already replaced the previous routes
+            cudaStreamSynchronize(st);  // the caller's buffers are still being read
+            cudaStreamSynchronize(e->copy_stream);
             return fail(e, RT_ERR_INVALID_ARG, "instance %zu: position array must hold node ids below %zu with %zu customers", b, N, N - 1);
         }
     }
-    // Coordinates are range-checked by the unit-vector kernel (off the host's critical path); stop records are taken
-    // as they are (rt_problem_set_stops is the validating entry point) — out-of-range values cannot fault a kernel.
-    int *bad_flag = p->coord_flag;
-    RT_CUDA(e, cudaMemsetAsync(bad_flag, 0, 4, st));
-    RT_TRY(launch_unit_vectors(e, p->lat, p->lon, p->n, p->batch, p->xyz, st, bad_flag));
+    if (dbg) t_valid = now();
     // the matrix of this pass is built in route order by the refresh below (state.cu); the node-order copy that
     // rt_problem_build_matrix keeps for the greedy and for rt_problem_get_matrix is not needed here
     p->has_coords = p->has_stops = p->has_routes = true;
@@ -570,14 +613,28 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     RT_TRY(ensure_position_matrix(p));
-    RT_TRY(state_refresh(p, st, e->ev[1]));
+    RT_TRY(state_refresh(p, st, e->ev[1], /*vectors_ready=*/true));
     RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, st));
-    RT_TRY(stage(p, 8));
-    int *flag_h = static_cast<int *>(p->host_stage);
-    RT_CUDA(e, cudaMemcpyAsync(flag_h, bad_flag, 4, cudaMemcpyDeviceToHost, st));
-    RT_CUDA(e, cudaMemcpyAsync(best_keys_out, p->best, B * 8, cudaMemcpyDeviceToHost, st));
+    RT_TRY(stage(p, (B + 1) * 8));
+    unsigned long long *res_h = static_cast<unsigned long long *>(p->host_stage);
+    int *flag_h = reinterpret_cast<int *>(res_h + B);
+    RT_CUDA(e, cudaMemcpyAsync(res_h, p->best, (B + 1) * 8, cudaMemcpyDeviceToHost, st));  // keys + flag, one copy
+    if (dbg) t_issued = now();
     RT_CUDA(e, cudaStreamSynchronize(st));
-    if (*flag_h) {
+    if (dbg) {
+        static double acc[5];
+        acc[4] += t_launch1 - t_copies;
+        static int calls;
+        const double t_end = now();
+        acc[0] += t_copies - t_begin, acc[1] += t_valid - t_copies, acc[2] += t_issued - t_valid, acc[3] += t_end - t_issued;
+        if (++calls % 50 == 0) {
+            fprintf(stderr, "[routest] plan: copies issued %.1f us, validation %.1f (first launch %.1f), launches issued %.1f, wait %.1f\n",
+                    acc[0] / 50, acc[1] / 50, acc[4] / 50, acc[2] / 50, acc[3] / 50);
+            acc[0] = acc[1] = acc[2] = acc[3] = acc[4] = 0;
+        }
+    }
+    memcpy(best_keys_out, res_h, B * 8);
+    if (*flag_h == seq) {
         p->has_coords = p->has_routes = false;
         return fail(e, RT_ERR_INVALID_ARG, "a coordinate is out of range or not finite");
     }

@@ -61,7 +61,8 @@ struct rt_problem {
     int *feasible = nullptr;               // [batch]
     unsigned long long *best = nullptr;    // [batch] packed keys (SPEC §7)
     int *done = nullptr, *moves = nullptr; // [batch] local-search bookkeeping
-    int *coord_flag = nullptr;             // [1] set by the unit-vector kernel on a bad coordinate (rt_problem_plan)
+    int *coord_flag = nullptr;             // [1] set to plan_seq by the vector kernel on a bad coordinate (rt_problem_plan)
+    int plan_seq = 0;                      // rt_problem_plan calls so far: the flag needs no reset between calls
     unsigned long long *hist = nullptr;    // [batch][hist_cap] applied keys
     int hist_cap = 0;
     // greedy scratch
@@ -93,7 +94,10 @@ namespace rt {
 inline int2 *position_matrix(const rt_problem *p) { return p->Gbuf.p ? static_cast<int2 *>(p->Gbuf.p) + 16 : nullptr; }
 inline int2 *position_matrix_t(const rt_problem *p) { return p->GTbuf.p ? static_cast<int2 *>(p->GTbuf.p) + 16 : nullptr; }
 
-int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for = nullptr);
+int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for = nullptr, bool vectors_ready = false);
+// unit vectors of the current coordinates straight into route order (and node order): replaces the unit-vector kernel
+// plus the position gather on the plan path
+int position_unit_vectors_launch(rt_problem *p, cudaStream_t st, int *bad_flag = nullptr, int bad_value = 1);
 int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready = false);
 int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors = false);
 int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d,

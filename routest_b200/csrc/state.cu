@@ -35,6 +35,43 @@ __global__ void __launch_bounds__(256) position_vectors_kernel(const double *__r
     px[2 * pstride + p] = v[2 * n + cur];
 }
 
+// Unit vectors straight into route order (SPEC.md §1 per position): PX[c][p] = unit vector of node[p], and, as every
+// node occupies at least one position, the node-order array xyz on the side.  One launch instead of two on the plan
+// path.  A node id outside [0, n) reads the depot instead (the host rejects such input, but only after this launch);
+// a coordinate out of range is neutralised and reported through bad_flag = bad_value.
+__global__ void __launch_bounds__(256) position_unit_vectors_kernel(const double *__restrict__ lat,
+                                                                    const double *__restrict__ lon,
+                                                                    const int *__restrict__ node,
+                                                                    const int *__restrict__ npos, int n, int pstride,
+                                                                    double *__restrict__ xyz, double *__restrict__ PX,
+                                                                    int *__restrict__ bad_flag, int bad_value)
+{
+    const double DEG = 0.017453292519943295;
+    const int b = blockIdx.y;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pstride) return;
+    int cur = p < npos[b] ? node[static_cast<size_t>(b) * pstride + p] : 0;
+    if (static_cast<unsigned>(cur) >= static_cast<unsigned>(n)) cur = 0;
+    double la = lat[static_cast<size_t>(b) * n + cur], lo = lon[static_cast<size_t>(b) * n + cur];
+    if (bad_flag && (!(la >= -90.0 && la <= 90.0) || !(lo >= -180.0 && lo <= 180.0))) {
+        *bad_flag = bad_value;
+        la = 0.0;
+        lo = 0.0;
+    }
+    double sp, cp, sl, cl;
+    det_sincos(la * DEG, sp, cp);
+    det_sincos(lo * DEG, sl, cl);
+    const double x = cp * cl, y = cp * sl;
+    double *px = PX + static_cast<size_t>(b) * 3 * pstride;
+    px[p] = x;
+    px[pstride + p] = y;
+    px[2 * pstride + p] = sp;
+    double *v = xyz + static_cast<size_t>(b) * 3 * n;  // duplicates (the depot) write identical values
+    v[cur] = x;
+    v[n + cur] = y;
+    v[2 * n + cur] = sp;
+}
+
 // G[p][q] = M[node p][node q] for a stored (caller-supplied) matrix: coalesced writes, scattered reads within a row.
 __global__ void __launch_bounds__(256) permute_matrix_kernel(const int2 *__restrict__ cells,
                                                              const int *__restrict__ node,
@@ -457,7 +494,16 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors)
 
 // Both halves.  The state tables do not read G (state_gather_kernel rebuilds the cells it needs), so their four small
 // latency-bound kernels run on a side stream underneath the matrix kernel and join before anything evaluates moves.
-int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for)
+int position_unit_vectors_launch(rt_problem *p, cudaStream_t st, int *bad_flag, int bad_value)
+{
+    dim3 g0((p->pstride + 255) / 256, p->batch);
+    position_unit_vectors_kernel<<<g0, 256, 0, st>>>(p->lat, p->lon, p->node, p->npos, p->n, p->pstride, p->xyz, p->PX,
+                                                     bad_flag, bad_value);
+    RT_CUDA(p->e, cudaGetLastError());
+    return RT_OK;
+}
+
+int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for, bool vectors_ready)
 {
     rt_engine *e = p->e;
     if (!p->side_stream) {
@@ -465,7 +511,7 @@ int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for)
         RT_CUDA(e, cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
         RT_CUDA(e, cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
     }
-    if (p->cells_from_coords) {
+    if (p->cells_from_coords && !vectors_ready) {
         // the position-ordered vectors feed both halves: produce them first, then fork
         dim3 g0((p->pstride + 255) / 256, p->batch);
         position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
