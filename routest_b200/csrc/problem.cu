@@ -514,6 +514,8 @@ int rt_problem_build_matrix_dev(rt_problem *p, double dist_scale, double time_sc
     p->time_scale = time_scale;
     p->has_matrix = true;
     p->cells_from_coords = true;
+    p->symmetric = true;
+    p->supplied = 0;
     return RT_OK;
 }
 
@@ -545,6 +547,8 @@ int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     p->cells_from_coords = true;
+    p->symmetric = true;  // whatever matrix was installed before, this pass runs on SPEC §2 cells
+    p->supplied = 0;
     RT_TRY(state_refresh(p, st, nullptr, /*vectors_ready=*/true));
     return eval_moves_launch(p, families, 0, 1, static_cast<unsigned long long *>(best_keys_d), true, st);
 }
@@ -604,6 +608,8 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     p->has_coords = p->has_stops = p->has_routes = true;
     p->has_matrix = false;
     p->cells_from_coords = true;
+    p->symmetric = true;
+    p->supplied = 0;
     p->pmax = 0;
     p->pmin = npos[0];
     for (size_t b = 0; b < B; ++b) {

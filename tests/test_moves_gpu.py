@@ -170,6 +170,10 @@ def test_plan_from_host_buffers(engine):
         out = np.zeros(B, np.uint64)
         call = pr.plan_call(lat, lon, stops, cap, md, node, npos, out, dist_scale=10.0, time_scale=TS_CAR)
         assert np.array_equal(call(), keys) and call() is out
+        # a directional matrix installed earlier does not leak into a pass that builds its own cells
+        asym = insts[0][0].D + np.triu(np.full_like(insts[0][0].D, 50), 1)
+        pr.set_matrix(0, asym, insts[0][0].T)
+        assert np.array_equal(call(), keys)
         lat[2, 7] = 91.0
         with pytest.raises(EngineError) as ei:
             call()
