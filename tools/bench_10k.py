@@ -23,11 +23,54 @@ from bench import DIST_SCALE, TS_CAR, count_candidates, synth_coords, synth_wind
 from routest_b200 import ALL_FAMILIES, Engine  # noqa: E402
 
 
+def matrix_only(a, eng, rank, world, n, lat, lon):
+    """Rank r builds rows [n*r/world, n*(r+1)/world) of the {dist,time} matrix into its own HBM (every rank holds the
+    n unit vectors: 240 KB at 10,001 nodes).  Nothing is exchanged: a consumer that wants a full replica per GPU would
+    all-gather 800 MB, the move kernels here rebuild their route-order rows instead."""
+    r0, r1 = n * rank // world, n * (rank + 1) // world
+    s = torch.cuda.current_stream().cuda_stream
+    lat_d, lon_d = torch.tensor(lat, device="cuda"), torch.tensor(lon, device="cuda")
+    xyz = torch.empty((3, n), dtype=torch.float64, device="cuda")
+    cells = torch.empty((r1 - r0, eng.matrix_pitch(n), 2), dtype=torch.int32, device="cuda")
+
+    def step():
+        eng.unit_vectors_dev(lat_d.data_ptr(), lon_d.data_ptr(), n, 1, xyz.data_ptr(), s)
+        eng.matrix_cells_dev(xyz.data_ptr(), n, 1, cells.data_ptr(), rows=(r0, r1), dist_scale=DIST_SCALE,
+                             time_scale=TS_CAR, stream=s)
+
+    for _ in range(5):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / a.steps], device="cuda")
+    check = cells[:, :n, 0].sum(dtype=torch.int64)      # a checksum of checksums: independent of the partition
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(check)
+    if rank == 0:
+        ms = float(ms.item())
+        print(json.dumps({"workload": f"{n} x {n} distance/time matrix, rows sharded over {world} GPU(s), no collective",
+                          "n_gpus": world, "ms": ms, "matrix_cells_per_s": n * n / ms * 1e3,
+                          "GBs_aggregate": n * n * 8 / ms / 1e6, "sum_of_distances": int(check.item())}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--stops", type=int, default=10000)
     ap.add_argument("--vehicles", type=int, default=100)
     ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--matrix-only", action="store_true",
+                    help="BASELINE config 4: only the node-order matrix, contiguous row blocks per rank, no collective")
     ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"],
                     help="nccl: all_reduce(MIN) per pass; peer: system-scope atomics into every replica's slot buffer")
     a = ap.parse_args()
@@ -39,6 +82,8 @@ def main():
     eng = Engine(local)
     n = a.stops + 1
     lat, lon, demand, cap = synth_coords(4567, a.stops, a.vehicles)
+    if a.matrix_only:
+        return matrix_only(a, eng, rank, world, n, lat, lon)
     pr = eng.problem(n, 1)
     pr.set_coords(lat, lon)
     pr.build_matrix(DIST_SCALE, TS_CAR)
