@@ -30,7 +30,7 @@ import threading
 import numpy as np
 
 from . import _native as N
-from .engine import DEFAULT_DIST_SCALE, Engine, profile_for_vehicle, time_scale_for_profile
+from .engine import DEFAULT_DIST_SCALE, Engine, EngineError, profile_for_vehicle, time_scale_for_profile
 
 ENGINE_LABEL = "backend:b200"
 
@@ -61,6 +61,15 @@ def optimize_route(input_data: dict, *, engine: Engine | None = None, matrix_fn=
     destinations = input_data["destination_points"]
     hooks = dict(engine=engine, matrix_fn=matrix_fn, directions_fn=directions_fn)
 
+    # What the reference does for a failed ORS request (utils.py:63-66, 106-109, 157-160: the exception becomes an
+    # {"error": ...} dict) is done here for a failed engine call: no GPU, a coordinate out of range, a size limit.
+    try:
+        return _optimize(source, destinations, profile_type, driver_details, vehicle_type, engine_label, hooks)
+    except EngineError as exc:
+        return {"error": f"route engine failed: {exc.message}"}
+
+
+def _optimize(source, destinations, profile_type, driver_details, vehicle_type, engine_label, hooks):
     if len(destinations) == 1:                                                     # utils.py:34-43
         feature = _point_to_point(source, destinations[0], profile_type, driver_details, **hooks)
         if "error" in feature:
@@ -235,7 +244,10 @@ def _solve_on_device(eng, all_points, profile_type, demand, cap, max_dist, desti
 
 def _improve(pr, trips, driver_details):
     pr.set_routes([trips])
-    pr.local_search(batched=driver_details.get("improve") == "batched")
+    if driver_details.get("improve") == "batched" and len(trips) <= 1024:   # the batched driver's route limit
+        pr.local_search(batched=True)
+    else:
+        pr.local_search()
     return [t for t in pr.get_routes()[0] if t]
 
 

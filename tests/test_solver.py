@@ -152,3 +152,13 @@ def test_improve_on_a_directional_service_matrix(engine):
     final, _, _ = O.local_search(inst, O.build_positions(trips, n))
     want = [i - 1 for t in O.positions_to_trips(final) if t for i in t]
     assert rc == 0 and res["properties"]["optimized_order"] == want
+
+
+@pytest.mark.gpu
+def test_engine_failures_come_back_as_error_dicts(engine):
+    """utils.py:63-66,106-109: a failed matrix/directions call is returned as {"error": ...}, never raised; the same
+    holds for a failed engine call (here: a latitude the engine refuses)."""
+    body, *_ = _request(99, 12, 3)
+    body["destination_points"][4]["lat"] = 123.0
+    res = S.optimize_route(body, engine=engine)
+    assert set(res) == {"error"} and "route engine failed" in res["error"] and "coordinate" in res["error"]
