@@ -357,6 +357,15 @@ def run_engine(args, rank, world):
                 "note": "algorithmic bytes per SURVEY.md §8(d): 8 B per matrix cell; 16/24/32 B of matrix reads per "
                         "2-opt/relocate/swap candidate (tile reuse makes real DRAM traffic much smaller than that)",
                 "matrix_kernel": {"achieved": kern["matrix_kernel"]["GBs"], "frac": kern["matrix_kernel"]["GBs"] / peak}}
+        # Neither kernel of this step is purely HBM-bound at 1,040-wide instances: both sit near the issue limit.  The
+        # instruction counts are fixed by the workload (ncu, profiles/traffic.json); the rates use the live durations.
+        winst = (traffic or {}).get("warp_instructions") or {}
+        if winst and clocks.get("sm_mhz"):
+            peak_issue = 148 * 4 * float(clocks["sm_mhz"]) * 1e6            # one warp instruction per SMSP per clock
+            roof["issue"] = {k: {"warp_inst_per_launch": winst[k], "achieved_Ginst_s": winst[k] / kern[k]["ms"] / 1e6,
+                                 "frac_of_issue_peak": winst[k] / (kern[k]["ms"] / 1e3) / peak_issue}
+                             for k in ("matrix_kernel", "eval_moves(inter+intra)") if k in winst}
+            roof["issue"]["peak_Ginst_s"] = peak_issue / 1e9
         total_cells = cells_step * world
         line = {
             "metric": METRIC, "value": total_cells * args.steps / (ms / 1e3), "unit": "cells/s",
