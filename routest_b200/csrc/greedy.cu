@@ -181,15 +181,24 @@ __global__ void __launch_bounds__(32) greedy_trips_kernel(const GreedyArgs a)
         ++trips;
         if (lane == 0) trip_off[trips] = done;
         // drop the visited stops from the candidate list (utils.py:138-139)
+        // (128 entries per step: the four loads are in flight together — one memory round trip per step instead of
+        // four; writes land at or below the lowest index read, so reading ahead of them is safe)
         __syncwarp();
         int w = 0;
-        for (int pos = 0; pos < m; pos += 32) {
-            const int k = pos + lane;
-            const int v = k < m ? order[k] : -1;
-            const unsigned keep = __ballot_sync(0xffffffffu, v > 0);
+        for (int pos = 0; pos < m; pos += 32 * kChunks) {
+            int v[kChunks];
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                const int k = pos + 32 * c + lane;
+                v[c] = k < m ? order[k] : -1;
+            }
             __syncwarp();
-            if (v > 0) order[w + __popc(keep & ((1u << lane) - 1u))] = v;
-            w += __popc(keep);
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                const unsigned keep = __ballot_sync(0xffffffffu, v[c] > 0);
+                if (v[c] > 0) order[w + __popc(keep & ((1u << lane) - 1u))] = v[c];
+                w += __popc(keep);
+            }
             __syncwarp();
         }
         m = w;
