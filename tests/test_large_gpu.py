@@ -34,6 +34,18 @@ def test_config5_5000_stops_50_vehicles(engine):
         assert end["feasible"] and np.array_equal(end["node"], final)
         assert sorted(end["node"][end["node"] != 0].tolist()) == list(range(1, inst.n))
         assert cost[0] == ref["cost"] + sum(O.key_unpack(k)[0] for k in okeys)
+        # SPEC §8.1 from the same start: three batched iterations, then on to a local optimum
+        pr.set_routes(trips)
+        bmoves, bcost, bkeys = pr.local_search(max_moves=3, keys_capacity=1024, batched=True)
+        bfinal, obkeys, sizes, obcost = O.local_search_batched(inst, node, max_iters=3, threads=O.num_threads())
+        assert sizes.size == 3 and sizes.min() > 5
+        assert bmoves[0] == obkeys.size and np.array_equal(bkeys[0], obkeys) and bcost[0] == obcost
+        assert np.array_equal(pr.get_state(0)["node"], bfinal)
+        pr.local_search(batched=True)
+        end = pr.get_state(0)
+        assert end["feasible"] and sorted(end["node"][end["node"] != 0].tolist()) == list(range(1, inst.n))
+        assert O.key_unpack(int(pr.eval_moves()[0]))[0] >= 0        # no improving move is left
+        assert end["cost"] < 0.25 * ref["cost"]
 
 
 @pytest.mark.timeout(600)
@@ -50,3 +62,8 @@ def test_config4_10000_stops_best_move_and_shards(engine):
         idx = np.array([0, 1, 2, 77, P // 2, P - 2, P - 1])
         assert np.array_equal(d[idx], inst.D[node[idx]][:, node]) and np.array_equal(t[idx], inst.T[node[idx]][:, node])
         assert np.array_equal(d, d.T)
+        # one batched iteration at this size (262 routes: the multi-kernel selection path)
+        bmoves, bcost, bkeys = pr.local_search(max_moves=1, keys_capacity=1024, batched=True)
+        bfinal, obkeys, sizes, obcost = O.local_search_batched(inst, node, max_iters=1, threads=O.num_threads())
+        assert sizes[0] > 20 and np.array_equal(bkeys[0], obkeys) and bcost[0] == obcost
+        assert np.array_equal(pr.get_state(0)["node"], bfinal)
