@@ -119,6 +119,15 @@ class ClockSampler:
 
 # ----------------------------------------------------------------------------------------------- CPU side
 
+def host_threads() -> int:
+    """Threads for the CPU legs: every core this process may run on.  Not OMP_NUM_THREADS — torchrun sets that to 1
+    for its workers, which would time a single-threaded baseline at N > 1."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def oracle_instances(seeds, stops, vehicles):
     """Instances + greedy start on the CPU oracle (used by the cpu_baseline leg and by --impl reference only)."""
     from oracle import oracle as O
@@ -127,7 +136,7 @@ def oracle_instances(seeds, stops, vehicles):
         lat, lon, demand, cap = synth_coords(seed, stops, vehicles)
         n = stops + 1
         xyz = O.unit_vectors(lat, lon)
-        m = O.matrix_rows(xyz, 0, n, DIST_SCALE, TS_CAR, threads=O.num_threads())
+        m = O.matrix_rows(xyz, 0, n, DIST_SCALE, TS_CAR, threads=host_threads())
         tw = synth_windows(seed, m["time"][0, 1:], m["time"][1:, 0])
         st = np.zeros((n, 4), np.int32)
         st[:, :3] = tw
@@ -141,7 +150,7 @@ def oracle_instances(seeds, stops, vehicles):
 def oracle_step(insts):
     """One pass of the hot path on the CPU oracle with all host threads; returns (cells, evals)."""
     from oracle import oracle as O
-    th = O.num_threads()
+    th = host_threads()
     cells = evals = 0
     for it in insts:
         n = it["lat"].size
@@ -163,10 +172,10 @@ def cpu_baseline(stops, vehicles, budget_s=8.0, max_inst=4):
         c, e = oracle_step(insts)
         cells, evals, reps = cells + c, evals + e, reps + 1
     dt = time.perf_counter() - t0
-    return {"value": cells / dt, "unit": "cells/s", "move_evals_per_s": evals / dt, "cores": O.num_threads(),
+    return {"value": cells / dt, "unit": "cells/s", "move_evals_per_s": evals / dt, "cores": host_threads(),
             "kind": "port",
             "sample": f"{reps} passes over {max_inst} of the workload's instances ({stops} stops each): oracle matrix "
-                      f"build + full-neighbourhood best move, {O.num_threads()} OpenMP threads, {dt:.1f} s"}
+                      f"build + full-neighbourhood best move, {host_threads()} OpenMP threads, {dt:.1f} s"}
 
 
 def run_reference(args, rank):
@@ -192,7 +201,7 @@ def run_reference(args, rank):
                                "step on the host CPU (bounded sample of the engine arm's batch)",
                    "stops": args.stops, "instances_per_step": per_step},
         "move_evals_per_s": evals / dt,
-        "cpu_baseline": {"value": val, "unit": "cells/s", "cores": O.num_threads(), "kind": "port",
+        "cpu_baseline": {"value": val, "unit": "cells/s", "cores": host_threads(), "kind": "port",
                          "sample": f"{args.steps} steps x {per_step} instances, CPU oracle (the reference itself has no "
                                    "code for matrix build or move evaluation: SURVEY.md §0)"},
         "e2e": {"value": val, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
