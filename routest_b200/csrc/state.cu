@@ -94,17 +94,35 @@ __global__ void __launch_bounds__(256) permute_matrix_kernel(const int2 *__restr
 // successor, predecessor -> successor) are rebuilt from the position-ordered unit vectors (same cell function as the
 // matrix kernel) or, for a caller-supplied matrix, gathered from it; either way not from G, so a replica that builds
 // only its shard's rows of G still gets the state of every route.
-__global__ void __launch_bounds__(256) state_gather_kernel(const double *__restrict__ PX, const int2 *__restrict__ cells,
-                                                           const int4 *__restrict__ stops, const int *__restrict__ node,
-                                                           const int *__restrict__ npos, int n, int pitch, int pstride,
-                                                           float fd, float ft, int4 *__restrict__ RB,
-                                                           int2 *__restrict__ E, int2 *__restrict__ SK,
-                                                           int2 *__restrict__ ER, const double *__restrict__ xyz,
-                                                           double *__restrict__ PX_out)
+// (The bodies of K1..K2c are device functions: the kernels below run them with the whole grid, state_fused_kernel runs
+// all four for one instance in a single block.  No __restrict__ / read-only loads here: in the fused form the arrays a
+// phase reads were written by the previous phase of the same kernel.)
+struct GatherArgs {
+    const double *PX;
+    const int2 *cells;
+    const int4 *stops;
+    const int *node, *npos;
+    int n, pitch, pstride;
+    float fd, ft;
+    int4 *RB;
+    int2 *E, *SK, *ER;
+    const double *xyz;
+    double *PX_out;
+};
+
+__device__ __forceinline__ void gather_position(const GatherArgs &a, int b, int p)
 {
-    const int b = blockIdx.y;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    const int P = npos[b];
+    const double *PX = a.PX;
+    const int2 *cells = a.cells;
+    const int4 *stops = a.stops;
+    const int n = a.n, pitch = a.pitch, pstride = a.pstride;
+    const float fd = a.fd, ft = a.ft;
+    int4 *RB = a.RB;
+    int2 *E = a.E, *SK = a.SK, *ER = a.ER;
+    const double *xyz = a.xyz;
+    double *PX_out = a.PX_out;
+    const int *node = a.node;
+    const int P = a.npos[b];
     const int *nd = node + static_cast<size_t>(b) * pstride;
     if (xyz && p < pstride) {
         // fused position_vectors_kernel (the incremental search has no matrix kernel between the two): the vectors
@@ -158,20 +176,36 @@ __global__ void __launch_bounds__(256) state_gather_kernel(const double *__restr
     SK[o] = sk;
 }
 
+__global__ void __launch_bounds__(256) state_gather_kernel(const GatherArgs a)
+{
+    gather_position(a, blockIdx.y, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
 // K2a: one block per instance — route ids by a block scan over the separators; resets the per-instance results.
 constexpr int kScanThreads = 1024;
 
-__global__ void __launch_bounds__(kScanThreads) state_routes_kernel(const int *__restrict__ node_all,
-                                                                    const int *__restrict__ npos,
-                                                                    int *__restrict__ nroutes_out, int pstride,
-                                                                    int rstride, int *__restrict__ route_all,
-                                                                    int *__restrict__ rstart_all,
-                                                                    long long *__restrict__ cost_all,
-                                                                    int *__restrict__ feasible_all,
-                                                                    unsigned long long *__restrict__ best_all)
+struct RoutesArgs {
+    const int *node, *npos;
+    int *nroutes;
+    int pstride, rstride;
+    int *route, *rstart;
+    long long *cost;
+    int *feasible;
+    unsigned long long *best;
+};
+
+// all kScanThreads threads of the block
+__device__ __forceinline__ void routes_block(const RoutesArgs &a, int b)
 {
     __shared__ int s_scan[kScanThreads];
-    const int b = blockIdx.x, tid = threadIdx.x;
+    const int *node_all = a.node, *npos = a.npos;
+    int *nroutes_out = a.nroutes;
+    const int pstride = a.pstride, rstride = a.rstride;
+    int *route_all = a.route, *rstart_all = a.rstart;
+    long long *cost_all = a.cost;
+    int *feasible_all = a.feasible;
+    unsigned long long *best_all = a.best;
+    const int tid = threadIdx.x;
     const int P = npos[b];
     const int *node = node_all + static_cast<size_t>(b) * pstride;
     int *route = route_all + static_cast<size_t>(b) * pstride;
@@ -205,20 +239,42 @@ __global__ void __launch_bounds__(kScanThreads) state_routes_kernel(const int *_
     }
 }
 
+__global__ void __launch_bounds__(kScanThreads) state_routes_kernel(const RoutesArgs a) { routes_block(a, blockIdx.x); }
+
 // K2b: one warp per route.  The recurrences for B (forwards) and Z (backwards) are sequential, but their inputs are
 // not: each lane loads one position of a 32-position chunk (coalesced), then the warp replays the chunk in order
 // from registers via shuffles — no dependent memory round trip per position.
 constexpr int kWalkWarps = 4;
 
-__global__ void __launch_bounds__(kWalkWarps * 32) state_walk_kernel(
-    const int *__restrict__ npos, int n, int pstride, int rstride, const int4 *__restrict__ stops_all,
-    const int *__restrict__ cap_all, const long long *__restrict__ maxd_all, const int4 *__restrict__ RB_all,
-    const int2 *__restrict__ E_all, int *__restrict__ Bv_all, int *__restrict__ Zv_all,
-    const int *__restrict__ rstart_all, long long *__restrict__ rload_all, long long *__restrict__ rdist_all,
-    long long *__restrict__ cost_all, int *__restrict__ feasible_all)
+struct WalkArgs {
+    const int *npos;
+    int n, pstride, rstride;
+    const int4 *stops;
+    const int *cap;
+    const long long *maxd;
+    const int4 *RB;
+    const int2 *E;
+    int *Bv, *Zv;
+    const int *rstart;
+    long long *rload, *rdist, *cost;
+    int *feasible;
+};
+
+// one warp: route rr of instance b
+__device__ __forceinline__ void walk_route(const WalkArgs &a, int b, int rr)
 {
-    const int b = blockIdx.y, lane = threadIdx.x & 31;
-    const int rr = blockIdx.x * kWalkWarps + (threadIdx.x >> 5);
+    const int *npos = a.npos;
+    const int n = a.n, pstride = a.pstride, rstride = a.rstride;
+    const int4 *stops_all = a.stops;
+    const int *cap_all = a.cap;
+    const long long *maxd_all = a.maxd;
+    const int4 *RB_all = a.RB;
+    const int2 *E_all = a.E;
+    int *Bv_all = a.Bv, *Zv_all = a.Zv;
+    const int *rstart_all = a.rstart;
+    long long *rload_all = a.rload, *rdist_all = a.rdist, *cost_all = a.cost;
+    int *feasible_all = a.feasible;
+    const int lane = threadIdx.x & 31;
     const int P = npos[b];
     const int R = P - n;
     if (rr >= R) return;
@@ -289,17 +345,37 @@ __global__ void __launch_bounds__(kWalkWarps * 32) state_walk_kernel(
     }
 }
 
-// K2c: the packed per-position records, one thread per position.
-__global__ void __launch_bounds__(256) state_records_kernel(
-    const int *__restrict__ node_all, const int *__restrict__ npos, int n, int pstride, int rstride,
-    const int4 *__restrict__ stops_all, const int *__restrict__ cap_all, const long long *__restrict__ maxd_all,
-    const int4 *__restrict__ RB_all, const int2 *__restrict__ E_all, const int2 *__restrict__ SK_all,
-    const int *__restrict__ Bv_all, const int *__restrict__ Zv_all, const int *__restrict__ route_all,
-    const long long *__restrict__ rload_all, const long long *__restrict__ rdist_all, int4 *__restrict__ RA_all,
-    int4 *__restrict__ RC_all, int4 *__restrict__ RD_all, int4 *__restrict__ H_all)
+__global__ void __launch_bounds__(kWalkWarps * 32) state_walk_kernel(const WalkArgs a)
 {
-    const int b = blockIdx.y;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    walk_route(a, blockIdx.y, blockIdx.x * kWalkWarps + (threadIdx.x >> 5));
+}
+
+// K2c: the packed per-position records, one thread per position.
+struct RecordsArgs {
+    const int *node, *npos;
+    int n, pstride, rstride;
+    const int4 *stops;
+    const int *cap;
+    const long long *maxd;
+    const int4 *RB;
+    const int2 *E, *SK;
+    const int *Bv, *Zv, *route;
+    const long long *rload, *rdist;
+    int4 *RA, *RC, *RD, *H;
+};
+
+__device__ __forceinline__ void records_position(const RecordsArgs &a, int b, int p)
+{
+    const int *node_all = a.node, *npos = a.npos;
+    const int n = a.n, pstride = a.pstride, rstride = a.rstride;
+    const int4 *stops_all = a.stops;
+    const int *cap_all = a.cap;
+    const long long *maxd_all = a.maxd;
+    const int4 *RB_all = a.RB;
+    const int2 *E_all = a.E, *SK_all = a.SK;
+    const int *Bv_all = a.Bv, *Zv_all = a.Zv, *route_all = a.route;
+    const long long *rload_all = a.rload, *rdist_all = a.rdist;
+    int4 *RA_all = a.RA, *RC_all = a.RC, *RD_all = a.RD, *H_all = a.H;
     const int P = npos[b];
     if (p >= P) return;
     const int R = P - n;
@@ -332,6 +408,35 @@ __global__ void __launch_bounds__(256) state_records_kernel(
         H_all[o] = make_int4(0, 0, ed.x, rt_);
     }
 }
+
+__global__ void __launch_bounds__(256) state_records_kernel(const RecordsArgs a)
+{
+    records_position(a, blockIdx.y, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
+// All four phases for one instance in one block (kScanThreads threads): what the four launches above do, minus three
+// launch latencies — the tables of a small instance are a few microseconds of work behind ~20 µs of dependent launches.
+struct StateArgs {
+    GatherArgs g;
+    RoutesArgs r;
+    WalkArgs w;
+    RecordsArgs c;
+};
+
+__device__ __forceinline__ void state_tables_block(const StateArgs &a, int b)
+{
+    const int tid = threadIdx.x;
+    const int limit = a.g.xyz ? a.g.pstride : a.g.npos[b];
+    for (int p = tid; p < limit; p += kScanThreads) gather_position(a.g, b, p);
+    routes_block(a.r, b);  // reads node[] only; ends with every thread past its last barrier
+    __syncthreads();
+    const int P = a.g.npos[b], R = P - a.w.n;
+    for (int rr = tid >> 5; rr < R; rr += kScanThreads / 32) walk_route(a.w, b, rr);
+    __syncthreads();
+    for (int p = tid; p < P; p += kScanThreads) records_position(a.c, b, p);
+}
+
+__global__ void __launch_bounds__(kScanThreads) state_fused_kernel(const StateArgs a) { state_tables_block(a, blockIdx.x); }
 
 // Applies one move per instance (SPEC.md §8).  keys are the packed keys of SPEC.md §7, optionally in the
 // order-preserving signed form (key ^ 2^63) that the _dev entry points exchange with NCCL.
@@ -462,33 +567,47 @@ int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready)
     return RT_OK;
 }
 
-// G -> E/SK/RB, B/Z/load/dist, the packed records; resets the best keys.
+// E/SK/RB, B/Z/load/dist, the packed records; resets the best keys.  Up to kFusedStatePositions positions per instance
+// one block per instance does it all in a single launch.
+constexpr int kFusedStatePositions = 4096;
+
+static StateArgs state_args(rt_problem *p, bool fused_vectors)
+{
+    StateArgs a{};
+    a.g = GatherArgs{p->cells_from_coords ? p->PX : nullptr, p->cells, p->stops, p->node, p->npos, p->n, p->pitch, p->pstride,
+                     static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale), static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale),
+                     p->RB, p->E, p->SK, p->symmetric ? nullptr : p->ER, fused_vectors ? p->xyz : nullptr, p->PX};
+    a.r = RoutesArgs{p->node, p->npos, p->nroutes, p->pstride, p->rstride, p->route, p->rstart, p->cost, p->feasible, p->best};
+    a.w = WalkArgs{p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap, p->max_dist, p->RB, p->E, p->Bv, p->Zv, p->rstart,
+                   p->rload, p->rdist, p->cost, p->feasible};
+    a.c = RecordsArgs{p->node, p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap, p->max_dist, p->RB, p->E, p->SK, p->Bv,
+                      p->Zv, p->route, p->rload, p->rdist, p->RA, p->RC, p->RD, p->H};
+    return a;
+}
+
 int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors)
 {
     rt_engine *e = p->e;
-    dim3 g1((p->grows + 255) / 256, p->batch);
     const bool fused = with_vectors && p->cells_from_coords;  // also produce the position-ordered vectors
+    const StateArgs a = state_args(p, fused);
+    p->best_clean = true;  // the route scan resets the best keys
+    if (p->grows <= kFusedStatePositions) {
+        state_fused_kernel<<<p->batch, kScanThreads, 0, st>>>(a);
+        RT_CUDA(e, cudaGetLastError());
+        return RT_OK;
+    }
+    dim3 g1((p->grows + 255) / 256, p->batch);
     dim3 gg(fused ? (p->pstride + 255) / 256 : g1.x, p->batch);
-    state_gather_kernel<<<gg, 256, 0, st>>>(p->cells_from_coords ? p->PX : nullptr, p->cells, p->stops, p->node, p->npos,
-                                            p->n, p->pitch, p->pstride,
-                                            static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale),
-                                            static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale), p->RB, p->E, p->SK,
-                                            p->symmetric ? nullptr : p->ER, fused ? p->xyz : nullptr, p->PX);
+    state_gather_kernel<<<gg, 256, 0, st>>>(a.g);
     RT_CUDA(e, cudaGetLastError());
-    state_routes_kernel<<<p->batch, kScanThreads, 0, st>>>(p->node, p->npos, p->nroutes, p->pstride, p->rstride, p->route,
-                                                           p->rstart, p->cost, p->feasible, p->best);
+    state_routes_kernel<<<p->batch, kScanThreads, 0, st>>>(a.r);
     RT_CUDA(e, cudaGetLastError());
     const int rmax = std::max(1, p->grows - p->n);  // most routes of any instance
     dim3 gw((rmax + kWalkWarps - 1) / kWalkWarps, p->batch);
-    state_walk_kernel<<<gw, kWalkWarps * 32, 0, st>>>(p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap, p->max_dist,
-                                                      p->RB, p->E, p->Bv, p->Zv, p->rstart, p->rload, p->rdist, p->cost,
-                                                      p->feasible);
+    state_walk_kernel<<<gw, kWalkWarps * 32, 0, st>>>(a.w);
     RT_CUDA(e, cudaGetLastError());
-    state_records_kernel<<<g1, 256, 0, st>>>(p->node, p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap,
-                                             p->max_dist, p->RB, p->E, p->SK, p->Bv, p->Zv, p->route, p->rload, p->rdist,
-                                             p->RA, p->RC, p->RD, p->H);
+    state_records_kernel<<<g1, 256, 0, st>>>(a.c);
     RT_CUDA(e, cudaGetLastError());
-    p->best_clean = true;  // state_routes_kernel reset the best keys
     return RT_OK;
 }
 
