@@ -394,7 +394,7 @@ def run_engine(args, rank, world):
                     "move_evals_per_s": evals_step * world * args.steps / e2e_s,
                     "call": "rt_problem_plan via Problem.plan_call (pinned host buffers in, best keys out; matrices stay in HBM)",
                     "keys_equal_device_path": same},
-            "gpu_launches": 9 * args.steps,  # kernels per step, counted in profiles/r1_launches_bench_steps2.csv
+            "gpu_launches": 6 * args.steps,  # kernels per step, counted in profiles/r1_launches_bench_steps2.csv
             "clocks": clocks,
         }
         if extra:
