@@ -354,7 +354,7 @@ def run_engine(args, rank, world):
                               "GBs": cells_step * 8 / ms_matrix / 1e6, "bytes_written": cells_built * 8,
                               "GBs_written": cells_built * 8 / ms_matrix / 1e6,
                               "note": "position_vectors_kernel + matrix_kernel<0> on the route-ordered stops"},
-            "state_tables(2 kernels)": {"ms": ms_refresh},
+            "state_tables": {"ms": ms_refresh},
             "eval_moves(inter+intra)": {"ms": ms_eval, "algorithmic_bytes": eval_bytes,
                                         "GBs": eval_bytes / ms_eval / 1e6, "move_evals_per_s": evals_step / ms_eval * 1e3},
         }
