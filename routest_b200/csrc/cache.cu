@@ -268,6 +268,7 @@ __device__ __forceinline__ bool cseg_fits(const CSeg &m, int t, int tail, int li
 // route's records and unit vectors are staged in shared memory first (when it has at most kStage positions), so
 // the sequential sweeps of its anchors run without a memory round trip per step.
 constexpr int kStage = 384;  // positions of one route held in shared memory (88 B each)
+constexpr int kTable = 64;   // routes up to this many positions also get their cell block in shared memory (32 KB)
 
 __global__ void __launch_bounds__(128) cache_intra_kernel(const CacheArgs a)
 {
@@ -308,7 +309,23 @@ __global__ void __launch_bounds__(128) cache_intra_kernel(const CacheArgs a)
     const int *Nd = staged ? sN - lo : a.node + po;
     const double *X = staged ? sX - lo : gx, *Y = staged ? sY - lo : (gx ? gx + a.pstride : nullptr),
                  *Z = staged ? sZ - lo : (gx ? gx + 2 * static_cast<size_t>(a.pstride) : nullptr);
+    // A short route (at most kTable positions with its two neighbours) gets its whole block of cells computed once,
+    // by all threads in parallel, into shared memory: the sweeps below are a single warp's dependent chain, and three
+    // cell evaluations per step (FP64 chord, sqrt, series) were two thirds of that chain.
+    extern __shared__ int2 s_tab[];
+    const bool tabled = gx && staged && cnt <= kTable;
+    if (tabled) {
+        for (int i = threadIdx.x; i < cnt * cnt; i += blockDim.x) {
+            const int ia = i / cnt, ib = i - ia * cnt;
+            const double ax = sX[ia], ay = sY[ia], az = sZ[ia], bx = sX[ib], by = sY[ib], bz = sZ[ib];
+            const double dx = ax - bx, dy = ay - by, dz = az - bz;
+            const double s2 = fma(dx, dx, fma(dy, dy, dz * dz));
+            s_tab[i] = __double2hiint(s2) < a.lim_hi ? cell_i32_fast(s2, a.fd, a.ft) : cell_i32(ax, ay, az, bx, by, bz, a.fd, a.ft);
+        }
+        __syncthreads();
+    }
     auto cell = [&](int pa, int pb) -> int2 {
+        if (tabled) return s_tab[(pa - lo) * cnt + (pb - lo)];
         if (gx) {
             const double ax = X[pa], ay = Y[pa], az = Z[pa], bx = X[pb], by = Y[pb], bz = Z[pb];
             const double dx = ax - bx, dy = ay - by, dz = az - bz;
@@ -458,6 +475,9 @@ int cache_ensure(rt_problem *p)
     RT_TRY(reserve(e, p->cache_misc, B * 4 * 4));  // dirty[2], ntiles, cursor per instance
     p->cache_r = cr;
     p->cache_tile_cap = tile_cap;
+    // the sweep kernel's cell table is dynamic shared memory on top of 35 KB of static arrays: past the 48 KB default
+    RT_CUDA(e, cudaFuncSetAttribute(cache_intra_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    static_cast<int>(kTable * kTable * sizeof(int2))));
     return RT_OK;
 }
 
@@ -529,7 +549,7 @@ int cache_evaluate(rt_problem *p, int families, cudaStream_t st)
         RT_CUDA(e, cudaGetLastError());
     }
     dim3 gi(p->cache_r, p->batch);
-    cache_intra_kernel<<<gi, 128, 0, st>>>(a);
+    cache_intra_kernel<<<gi, 128, kTable * kTable * sizeof(int2), st>>>(a);
     RT_CUDA(e, cudaGetLastError());
     dim3 ga(p->cache_r, p->batch);
     cache_argmin_kernel<<<ga, 128, 0, st>>>(a);
