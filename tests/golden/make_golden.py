@@ -224,6 +224,20 @@ def optimize_route_cases():
         d.pop("payload")
     run("eight_stops_defaults_missing_payloads", body2, M.tolist())
     run("matrix_missing", body, [])
+    body3 = json.loads(json.dumps(body))                      # unknown vehicle type -> default profile (utils.py:22-29)
+    body3["driver_details"] = {"vehicle_type": "Hovercraft", "vehicle_capacity": 9, "driver_name": None}
+    run("eight_stops_unknown_vehicle", body3, M.tolist())
+    body4 = json.loads(json.dumps(body))                      # nothing to carry, nothing to carry it in: 0 <= 0 holds
+    for d in body4["destination_points"]:
+        d["payload"] = 0
+    body4["driver_details"] = {"vehicle_type": "bike", "vehicle_capacity": 0}
+    run("eight_stops_zero_payload_zero_capacity", body4, M.tolist())
+    Mi = np.round(M)                                          # limits met with equality: both tests are "<=" (utils.py:127-129)
+    body5 = json.loads(json.dumps(body))
+    far = float(max(Mi[0, i] + Mi[i, 0] for i in range(1, n)))   # the longest there-and-back alone exactly fits
+    body5["driver_details"] = {"vehicle_type": "car", "maximum_distance": far,
+                               "vehicle_capacity": max(d["payload"] for d in body5["destination_points"])}
+    run("eight_stops_limits_met_with_equality", body5, Mi.tolist())
     return out
 
 

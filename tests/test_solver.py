@@ -37,7 +37,9 @@ def test_matrix_service_without_distances():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["ref_fixture", "eight_stops_float_matrix", "eight_stops_defaults_missing_payloads"])
+@pytest.mark.parametrize("name", ["ref_fixture", "eight_stops_float_matrix", "eight_stops_defaults_missing_payloads",
+                                  "eight_stops_unknown_vehicle", "eight_stops_zero_payload_zero_capacity",
+                                  "eight_stops_limits_met_with_equality"])
 def test_multi_stop_equals_reference_whole_feature(engine, name):
     """Same request, same matrix answer, same directions answers => the reference's complete return dict."""
     case = CASES[name]
