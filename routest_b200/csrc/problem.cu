@@ -903,7 +903,9 @@ static int local_search_impl(rt_problem *p, int families, int max_moves, int mod
     bool all_done = false;
     int loop_rc = RT_OK;
     while (!all_done && issued < max_moves && loop_rc == RT_OK) {
-        const int todo = std::min(kChunk, max_moves - issued);
+        // the blind run grows with the search (a quarter of what has been issued, between 4 and kChunk): a short
+        // search overshoots its end by a few iterations instead of kChunk, a long one is not paced more often
+        const int todo = std::min(std::max(4, std::min(kChunk, issued / 4)), max_moves - issued);
         for (int i = 0; i < todo && loop_rc == RT_OK; ++i) {
             if (exec) {
                 if (cudaGraphLaunch(exec, e->stream) != cudaSuccess) loop_rc = fail(e, RT_ERR_CUDA, "cudaGraphLaunch failed");
