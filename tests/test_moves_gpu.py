@@ -263,9 +263,11 @@ def test_apply_moves_refuses_keys_that_are_not_moves(engine):
 
 @pytest.mark.parametrize("full", [False, True], ids=["incremental", "full"])
 @pytest.mark.parametrize("seed,stops,veh", [(10, 45, 5), (11, 100, 10), (12, 300, 12)])
-def test_local_search_moves_and_final_routes_bit_exact(engine, seed, stops, veh, full):
+def test_local_search_moves_and_final_routes_bit_exact(engine, seed, stops, veh, full, monkeypatch):
     """Both search drivers — the one that re-scores only what a move touched (per-route-pair table) and the one that
-    re-scores everything on the route-order matrix — apply the oracle's exact sequence of keys."""
+    re-scores everything on the route-order matrix — apply the oracle's exact sequence of keys.  (By default the
+    incremental driver only takes over above ~1,500 positions; the environment switch forces it here.)"""
+    monkeypatch.setenv("ROUTEST_LS_INCREMENTAL_FROM", "0")
     inst, node, raw = synth_vrptw(seed, stops, veh)
     final, keys, cost = O.local_search(inst, node, threads=O.num_threads())
     with _load(engine, [(inst, node, raw)]) as pr:
@@ -279,7 +281,8 @@ def test_local_search_moves_and_final_routes_bit_exact(engine, seed, stops, veh,
 
 
 @pytest.mark.parametrize("full", [False, True], ids=["incremental", "full"])
-def test_local_search_batch_and_max_moves(engine, full):
+def test_local_search_batch_and_max_moves(engine, full, monkeypatch):
+    monkeypatch.setenv("ROUTEST_LS_INCREMENTAL_FROM", "0")
     insts = [synth_vrptw(200 + b, 80, 6) for b in range(4)]
     refs = [O.local_search(inst, node, max_moves=25) for inst, node, _ in insts]
     with _load(engine, insts) as pr:
