@@ -337,6 +337,34 @@ def run_engine(args, rank, world):
         e2e_s = float(t.item())
     same = bool(np.array_equal(h[7].view(np.int64) ^ np.int64(-2 ** 63), keys_ref.cpu().numpy()))
 
+    # ---- the same requests with two in flight (rt_problem_plan_begin / _end on two problems used in turn): every step
+    # still uploads its inputs from pinned host memory and reads its keys back, but the upload of step k+1 runs under
+    # the kernels of step k.  Reported next to the synchronous figure, not instead of it.
+    pr2 = eng.problem(n, B)
+    out2 = pinned(np.zeros(B, np.uint64))
+    pipes = [p_.plan_pipeline_calls(h[0], h[1], h[2], h[3], h[4], h[5], h[6], o_, dist_scale=DIST_SCALE, time_scale=TS_CAR)
+             for p_, o_ in ((pr, h[7]), (pr2, out2[1]))]
+
+    def pipelined(steps):
+        pipes[0][0]()
+        for k in range(1, steps):
+            pipes[k % 2][0]()
+            pipes[(k - 1) % 2][1]()
+        return pipes[(steps - 1) % 2][1]()
+
+    pipelined(max(args.warmup, 2))
+    barrier()
+    t0 = time.perf_counter()
+    last = pipelined(args.steps)
+    barrier()
+    pipe_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([pipe_s], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        pipe_s = float(t.item())
+    same_pipe = bool(np.array_equal(last.view(np.int64) ^ np.int64(-2 ** 63), keys_ref.cpu().numpy()))
+    pr2.close()
+
     extra = secondary_figures(eng, torch, stream) if (rank == 0 and not args.no_extra) else None
 
     if rank == 0:
@@ -393,7 +421,12 @@ def run_engine(args, rank, world):
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * e2e_s / args.steps,
                     "move_evals_per_s": evals_step * world * args.steps / e2e_s,
                     "call": "rt_problem_plan via Problem.plan_call (pinned host buffers in, best keys out; matrices stay in HBM)",
-                    "keys_equal_device_path": same},
+                    "keys_equal_device_path": same,
+                    "two_requests_in_flight": {"value": total_cells * args.steps / pipe_s, "unit": "cells/s",
+                                               "ms_per_step": 1e3 * pipe_s / args.steps,
+                                               "call": "rt_problem_plan_begin / rt_problem_plan_end on two problems used in "
+                                                       "turn: the upload of one request runs under the kernels of the other",
+                                               "keys_equal_device_path": same_pipe}},
             "gpu_launches": 6 * args.steps,  # kernels per step, counted in profiles/r1_launches_bench_steps2.csv
             "clocks": clocks,
         }

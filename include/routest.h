@@ -204,6 +204,18 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
                     const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
                     double time_scale, int families, uint64_t *best_keys_out);
 
+/* The same pass in two halves, for a caller that keeps requests in flight (a service between two of its requests):
+ * rt_problem_plan_begin enqueues the uploads and the kernels and returns; rt_problem_plan_end waits for that pass and
+ * hands out its keys.  All inputs travel on the engine's copy stream, so with two problems of one engine used in
+ * turn, the upload of one request overlaps the kernels of the other and the GPU never waits for PCIe.  The input
+ * buffers must stay unchanged until rt_problem_plan_end returns; one pass per problem may be in flight;
+ * rt_problem_plan_end does not take the engine's lock (other threads can go on enqueueing).  No reference
+ * counterpart (the reference handles one request per thread, synchronously: routes.py:89-127). */
+int rt_problem_plan_begin(rt_problem *p, const double *lat, const double *lon, const int32_t *stops,
+                          const int32_t *cap, const int64_t *max_dist, const int32_t *node, const int32_t *npos,
+                          double dist_scale, double time_scale, int families);
+int rt_problem_plan_end(rt_problem *p, uint64_t *best_keys_out);
+
 /* The same pass for inputs that are already on the device (coordinates, stops and routes installed earlier), on
  * the caller's stream, without synchronisation: unit vectors -> route-order matrix -> route state -> best keys
  * (device int64[batch] in signed-order form, see rt_problem_eval_moves_dev). */

@@ -67,6 +67,9 @@ SIGNATURES = {
     "rt_problem_local_search": (C.c_int, [c_problem_p, C.c_int, C.c_int, c_i32_p, c_i64_p, c_u64_p, C.c_int]),
     "rt_problem_plan": (C.c_int, [c_problem_p, c_f64_p, c_f64_p, c_i32_p, c_i32_p, c_i64_p, c_i32_p, c_i32_p,
                                   C.c_double, C.c_double, C.c_int, c_u64_p]),
+    "rt_problem_plan_begin": (C.c_int, [c_problem_p, c_f64_p, c_f64_p, c_i32_p, c_i32_p, c_i64_p, c_i32_p, c_i32_p,
+                                        C.c_double, C.c_double, C.c_int]),
+    "rt_problem_plan_end": (C.c_int, [c_problem_p, c_u64_p]),
     "rt_problem_build_matrix_dev": (C.c_int, [c_problem_p, C.c_double, C.c_double, C.c_void_p]),
     "rt_problem_refresh_dev": (C.c_int, [c_problem_p, C.c_int, C.c_void_p]),
     "rt_problem_plan_dev": (C.c_int, [c_problem_p, C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p]),

@@ -209,6 +209,8 @@ void rt_problem_destroy(rt_problem *p)
     DeviceGuard dg(e->device);
     cudaStreamSynchronize(e->stream);
     for (int i = 0; i < p->n_allocs; ++i) cudaFree(p->all_allocs[i]);
+    for (cudaEvent_t ev : {p->ev_in[0], p->ev_in[1], p->ev_done})
+        if (ev) cudaEventDestroy(ev);
     if (p->side_stream) {
         cudaStreamSynchronize(p->side_stream);
         cudaStreamDestroy(p->side_stream);
@@ -553,56 +555,64 @@ int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int
     return eval_moves_launch(p, families, 0, 1, static_cast<unsigned long long *>(best_keys_d), true, st);
 }
 
-int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
-                    const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
-                    double time_scale, int families, uint64_t *best_keys_out)
+// Enqueues one pass (inputs -> best keys in the problem's pinned staging buffer).  Synchronous form: what the matrix
+// needs travels on the compute stream, the rest on the copy stream.  Asynchronous form (rt_problem_plan_begin): every
+// input travels on the copy stream, so that the copies of this request overlap whatever an earlier request — of
+// another problem of the same engine — still has running on the compute stream.
+static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
+                        const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
+                        double time_scale, int families, bool async, const char *who)
 {
-    RT_PROBLEM_GUARD(p);
-    if (!lat || !lon || !stops || !cap || !max_dist || !node || !npos || !best_keys_out || !(families & 7))
-        return fail(e, RT_ERR_INVALID_ARG, "rt_problem_plan: bad argument");
+    rt_engine *e = p->e;
+    if (!lat || !lon || !stops || !cap || !max_dist || !node || !npos || !(families & 7))
+        return fail(e, RT_ERR_INVALID_ARG, "%s: bad argument", who);
+    if (p->plan_pending) return fail(e, RT_ERR_STATE, "%s: the previous rt_problem_plan_begin of this problem has not been ended", who);
     RT_TRY(check_scales(e, dist_scale, time_scale));
     const size_t B = p->batch, N = p->n, PS = p->pstride;
     for (size_t b = 0; b < B; ++b)
         if (npos[b] < static_cast<int>(N) + 1 || npos[b] > static_cast<int>(PS) || node[b * PS] != 0 ||
             node[b * PS + npos[b] - 1] != 0)
             return fail(e, RT_ERR_INVALID_ARG, "instance %zu: malformed position array", b);
-    cudaStream_t st = e->stream;
+    if (!p->ev_in[0]) {
+        for (cudaEvent_t *ev : {&p->ev_in[0], &p->ev_in[1], &p->ev_done})
+            RT_CUDA(e, cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+    }
+    cudaStream_t st = e->stream, cs = e->copy_stream;
     static const bool dbg = getenv("ROUTEST_DEBUG_PLAN") != nullptr;  // prints where the call's host time goes
     auto now = []() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; };
-    const double t_begin = dbg ? now() : 0;
-    double t_copies = 0, t_valid = 0, t_issued = 0;
-    // What the matrix needs (coordinates, routes) goes first on the compute stream; the stop records and limits, which
-    // only the state tables read, travel on the copy stream underneath the unit-vector and matrix kernels.
-    RT_CUDA(e, cudaMemcpyAsync(p->lat, lat, B * N * 8, cudaMemcpyHostToDevice, st));
-    RT_CUDA(e, cudaMemcpyAsync(p->lon, lon, B * N * 8, cudaMemcpyHostToDevice, st));
-    RT_CUDA(e, cudaMemcpyAsync(p->node, node, B * PS * 4, cudaMemcpyHostToDevice, st));
-    RT_CUDA(e, cudaMemcpyAsync(p->npos, npos, B * 4, cudaMemcpyHostToDevice, st));
-    RT_CUDA(e, cudaEventRecord(e->ev[0], st));                       // earlier work on the buffers has been ordered
-    RT_CUDA(e, cudaStreamWaitEvent(e->copy_stream, e->ev[0], 0));
-    RT_CUDA(e, cudaMemcpyAsync(p->stops, stops, B * N * 16, cudaMemcpyHostToDevice, e->copy_stream));
-    RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, B * 4, cudaMemcpyHostToDevice, e->copy_stream));
-    RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, B * 8, cudaMemcpyHostToDevice, e->copy_stream));
-    RT_CUDA(e, cudaEventRecord(e->ev[1], e->copy_stream));
-    if (dbg) t_copies = now();
+    p->plan_t[0] = dbg ? now() : 0;
+    // What the matrix needs (coordinates, routes) goes first; the stop records and limits, which only the state tables
+    // read, follow on the copy stream underneath the unit-vector and matrix kernels.
+    cudaStream_t first = async ? cs : st;
+    RT_CUDA(e, cudaMemcpyAsync(p->lat, lat, B * N * 8, cudaMemcpyHostToDevice, first));
+    RT_CUDA(e, cudaMemcpyAsync(p->lon, lon, B * N * 8, cudaMemcpyHostToDevice, first));
+    RT_CUDA(e, cudaMemcpyAsync(p->node, node, B * PS * 4, cudaMemcpyHostToDevice, first));
+    RT_CUDA(e, cudaMemcpyAsync(p->npos, npos, B * 4, cudaMemcpyHostToDevice, first));
+    RT_CUDA(e, cudaEventRecord(p->ev_in[0], first));
+    if (async) RT_CUDA(e, cudaStreamWaitEvent(st, p->ev_in[0], 0));      // the kernels wait for their inputs
+    else RT_CUDA(e, cudaStreamWaitEvent(cs, p->ev_in[0], 0));            // earlier work on the buffers has been ordered
+    RT_CUDA(e, cudaMemcpyAsync(p->stops, stops, B * N * 16, cudaMemcpyHostToDevice, cs));
+    RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, B * 4, cudaMemcpyHostToDevice, cs));
+    RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, B * 8, cudaMemcpyHostToDevice, cs));
+    RT_CUDA(e, cudaEventRecord(p->ev_in[1], cs));
+    p->plan_t[1] = dbg ? now() : 0;
     // The unit vectors go out first (the kernel itself falls back to the depot for a node id it cannot index), so the
     // GPU has work while the host checks what every other kernel indexes with: each position holds a node id below n
     // and there are exactly n-1 customers among them (so the route count is P - n and every table fits).  That a
     // customer is not repeated is not checked here: a repeat gives a meaningless plan, not a fault.  Coordinates
     // are range-checked by that kernel (off the host's critical path); stop records are taken as they are
     // (rt_problem_set_stops is the validating entry point) — out-of-range values cannot fault a kernel.
-    int *bad_flag = p->coord_flag;
-    const int seq = ++p->plan_seq;  // the flag is written with this call's number: no reset launch needed
-    RT_TRY(position_unit_vectors_launch(p, st, bad_flag, seq));
-    const double t_launch1 = dbg ? now() : 0;
+    p->plan_flag_seq = ++p->plan_seq;  // the flag is written with this call's number: no reset launch needed
+    RT_TRY(position_unit_vectors_launch(p, st, p->coord_flag, p->plan_flag_seq));
     for (size_t b = 0; b < B; ++b) {
         if (!positions_well_formed(node + b * PS, npos[b], static_cast<int>(N))) {
             p->has_routes = false;  // the copy above has already replaced the previous routes
             cudaStreamSynchronize(st);  // the caller's buffers are still being read
-            cudaStreamSynchronize(e->copy_stream);
+            cudaStreamSynchronize(cs);
             return fail(e, RT_ERR_INVALID_ARG, "instance %zu: position array must hold node ids below %zu with %zu customers", b, N, N - 1);
         }
     }
-    if (dbg) t_valid = now();
+    p->plan_t[2] = dbg ? now() : 0;
     // the matrix of this pass is built in route order by the refresh below (state.cu); the node-order copy that
     // rt_problem_build_matrix keeps for the greedy and for rt_problem_get_matrix is not needed here
     p->has_coords = p->has_stops = p->has_routes = true;
@@ -619,32 +629,73 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     RT_TRY(ensure_position_matrix(p));
-    RT_TRY(state_refresh(p, st, e->ev[1], /*vectors_ready=*/true));
+    RT_TRY(state_refresh(p, st, p->ev_in[1], /*vectors_ready=*/true));
     RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, st));
     RT_TRY(stage(p, (B + 1) * 8));
-    unsigned long long *res_h = static_cast<unsigned long long *>(p->host_stage);
-    int *flag_h = reinterpret_cast<int *>(res_h + B);
-    RT_CUDA(e, cudaMemcpyAsync(res_h, p->best, (B + 1) * 8, cudaMemcpyDeviceToHost, st));  // keys + flag, one copy
-    if (dbg) t_issued = now();
-    RT_CUDA(e, cudaStreamSynchronize(st));
-    if (dbg) {
-        static double acc[5];
-        acc[4] += t_launch1 - t_copies;
+    RT_CUDA(e, cudaMemcpyAsync(p->host_stage, p->best, (B + 1) * 8, cudaMemcpyDeviceToHost, st));  // keys + flag, one copy
+    RT_CUDA(e, cudaEventRecord(p->ev_done, st));
+    p->plan_t[3] = dbg ? now() : 0;
+    p->plan_pending = true;
+    return RT_OK;
+}
+
+// Waits for the pass enqueued last and hands its keys out.
+static int plan_collect(rt_problem *p, uint64_t *best_keys_out, const char *who)
+{
+    rt_engine *e = p->e;
+    if (!best_keys_out) return fail(e, RT_ERR_INVALID_ARG, "%s: NULL argument", who);
+    if (!p->plan_pending) return fail(e, RT_ERR_STATE, "%s: no pass has been begun on this problem", who);
+    p->plan_pending = false;
+    RT_CUDA(e, cudaEventSynchronize(p->ev_done));
+    if (p->plan_t[0] != 0) {
+        static double acc[4];
         static int calls;
-        const double t_end = now();
-        acc[0] += t_copies - t_begin, acc[1] += t_valid - t_copies, acc[2] += t_issued - t_valid, acc[3] += t_end - t_issued;
+        timespec ts;
+        clock_gettime(CLOCK_MONOTONIC, &ts);
+        const double t_end = ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+        acc[0] += p->plan_t[1] - p->plan_t[0], acc[1] += p->plan_t[2] - p->plan_t[1], acc[2] += p->plan_t[3] - p->plan_t[2];
+        acc[3] += t_end - p->plan_t[3];
         if (++calls % 50 == 0) {
-            fprintf(stderr, "[routest] plan: copies issued %.1f us, validation %.1f (first launch %.1f), launches issued %.1f, wait %.1f\n",
-                    acc[0] / 50, acc[1] / 50, acc[4] / 50, acc[2] / 50, acc[3] / 50);
-            acc[0] = acc[1] = acc[2] = acc[3] = acc[4] = 0;
+            fprintf(stderr, "[routest] plan: copies issued %.1f us, first launch + validation %.1f, launches issued %.1f, wait %.1f\n",
+                    acc[0] / 50, acc[1] / 50, acc[2] / 50, acc[3] / 50);
+            acc[0] = acc[1] = acc[2] = acc[3] = 0;
         }
     }
+    const size_t B = p->batch;
+    const unsigned long long *res_h = static_cast<const unsigned long long *>(p->host_stage);
     memcpy(best_keys_out, res_h, B * 8);
-    if (*flag_h == seq) {
+    if (*reinterpret_cast<const int *>(res_h + B) == p->plan_flag_seq) {
         p->has_coords = p->has_routes = false;
         return fail(e, RT_ERR_INVALID_ARG, "a coordinate is out of range or not finite");
     }
     return RT_OK;
+}
+
+int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
+                    const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
+                    double time_scale, int families, uint64_t *best_keys_out)
+{
+    RT_PROBLEM_GUARD(p);
+    if (!best_keys_out) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_plan: bad argument");
+    RT_TRY(plan_enqueue(p, lat, lon, stops, cap, max_dist, node, npos, dist_scale, time_scale, families, false,
+                        "rt_problem_plan"));
+    return plan_collect(p, best_keys_out, "rt_problem_plan");
+}
+
+int rt_problem_plan_begin(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
+                          const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
+                          double time_scale, int families)
+{
+    RT_PROBLEM_GUARD(p);
+    return plan_enqueue(p, lat, lon, stops, cap, max_dist, node, npos, dist_scale, time_scale, families, true,
+                        "rt_problem_plan_begin");
+}
+
+int rt_problem_plan_end(rt_problem *p, uint64_t *best_keys_out)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    DeviceGuard dg(p->e->device);  // no engine lock: the wait must not keep other requests from being enqueued
+    return plan_collect(p, best_keys_out, "rt_problem_plan_end");
 }
 
 int rt_problem_get_position_matrix(rt_problem *p, int instance, int32_t *dist, int32_t *tim)

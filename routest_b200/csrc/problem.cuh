@@ -63,6 +63,11 @@ struct rt_problem {
     int *done = nullptr, *moves = nullptr; // [batch] local-search bookkeeping
     int *coord_flag = nullptr;             // [1] set to plan_seq by the vector kernel on a bad coordinate (rt_problem_plan)
     int plan_seq = 0;                      // rt_problem_plan calls so far: the flag needs no reset between calls
+    int plan_flag_seq = 0;                 // the number the pass in flight writes into the flag
+    bool plan_pending = false;             // a pass has been enqueued and not collected (rt_problem_plan_begin/_end)
+    cudaEvent_t ev_in[2] = {nullptr, nullptr};  // inputs of the pass in flight are on the device (matrix part / the rest)
+    cudaEvent_t ev_done = nullptr;         // its keys are in the staging buffer
+    double plan_t[4] = {0, 0, 0, 0};       // host timestamps of the pass (ROUTEST_DEBUG_PLAN)
     unsigned long long *hist = nullptr;    // [batch][hist_cap] applied keys
     int hist_cap = 0;
     // greedy scratch

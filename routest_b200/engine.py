@@ -469,6 +469,35 @@ class Problem:
         """what: bit 0 = route-order matrix, bit 1 = route state tables."""
         self._check(self._lib.rt_problem_refresh_dev(self._p, int(what), stream or None))
 
+    def plan_pipeline_calls(self, lat, lon, stops, cap, max_dist, node, npos, out, *, dist_scale=DEFAULT_DIST_SCALE,
+                            time_scale=None, families: int = ALL_FAMILIES):
+        """(begin, end) for callers that keep requests in flight (rt_problem_plan_begin / rt_problem_plan_end): `begin()`
+        enqueues this problem's uploads and kernels and returns at once, `end()` waits for them and returns `out`.
+        With two problems of one engine used in turn the upload of one request overlaps the kernels of the other.
+        Same buffer rules as plan_call; the inputs must stay unchanged between begin() and end()."""
+        if time_scale is None:
+            time_scale = time_scale_for_profile("driving-car")
+        spec = ((lat, np.float64, (self.batch, self.n)), (lon, np.float64, (self.batch, self.n)),
+                (stops, np.int32, (self.batch, self.n, 4)), (cap, np.int32, (self.batch,)),
+                (max_dist, np.int64, (self.batch,)), (node, np.int32, (self.batch, self.pstride)),
+                (npos, np.int32, (self.batch,)), (out, np.uint64, (self.batch,)))
+        for a, dt, shape in spec:
+            if not isinstance(a, np.ndarray) or a.dtype != dt or a.shape != shape or not a.flags.c_contiguous:
+                raise ValueError(f"plan_pipeline_calls needs C-contiguous {np.dtype(dt).name} arrays of shape {shape}")
+        fb, fe, check, handle = self._lib.rt_problem_plan_begin, self._lib.rt_problem_plan_end, self._check, self._p
+        args = (handle, _f64(lat), _f64(lon), _i32(stops), _i32(cap), _i64(max_dist), _i32(node), _i32(npos),
+                C.c_double(dist_scale), C.c_double(time_scale), C.c_int(families))
+        out_p = _u64(out)
+        keep = (lat, lon, stops, cap, max_dist, node, npos, out)
+
+        def begin(_keep=keep):
+            check(fb(*args))
+
+        def end():
+            check(fe(handle, out_p))
+            return out
+        return begin, end
+
     def plan_dev(self, keys_ptr: int, *, dist_scale=DEFAULT_DIST_SCALE, time_scale=None, families: int = ALL_FAMILIES,
                  stream: int = 0):
         if time_scale is None:

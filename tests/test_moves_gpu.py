@@ -191,6 +191,50 @@ def test_plan_from_host_buffers(engine):
         assert np.array_equal(call(), keys)
 
 
+def test_plan_in_two_halves_with_two_problems_in_flight(engine):
+    """rt_problem_plan_begin / rt_problem_plan_end: two problems of one engine used in turn (the upload of one request
+    overlaps the kernels of the other) return what the synchronous call returns; misuse is refused."""
+    from routest_b200 import EngineError
+    B, n = 3, 121
+    sets = [[synth_vrptw(500 + 10 * k + b, 120, 5) for b in range(B)] for k in range(4)]
+    probs = [engine.problem(n, B) for _ in range(2)]
+    try:
+        bufs = []
+        for pr in probs:
+            bufs.append(dict(lat=np.zeros((B, n)), lon=np.zeros((B, n)), stops=np.zeros((B, n, 4), np.int32),
+                             cap=np.zeros(B, np.int32), md=np.full(B, 2 ** 62, np.int64),
+                             node=np.zeros((B, pr.pstride), np.int32), npos=np.zeros(B, np.int32), out=np.zeros(B, np.uint64)))
+        calls = [pr.plan_pipeline_calls(b["lat"], b["lon"], b["stops"], b["cap"], b["md"], b["node"], b["npos"], b["out"],
+                                        dist_scale=10.0, time_scale=TS_CAR) for pr, b in zip(probs, bufs)]
+
+        def fill(b, insts):
+            b["node"][:] = 0
+            for i, (inst, nd, raw) in enumerate(insts):
+                b["lat"][i], b["lon"][i], b["stops"][i], b["cap"][i] = raw["lat"], raw["lon"], inst.stops, inst.cap
+                b["node"][i, :nd.size] = nd
+                b["npos"][i] = nd.size
+
+        want = [[O.best_move(inst, nd) for inst, nd, _ in insts] for insts in sets]
+        got = []
+        fill(bufs[0], sets[0])
+        calls[0][0]()
+        for k in range(1, len(sets)):
+            fill(bufs[k % 2], sets[k])
+            calls[k % 2][0]()                                   # request k goes out ...
+            got.append(calls[(k - 1) % 2][1]().tolist())        # ... before request k-1 is collected
+        got.append(calls[(len(sets) - 1) % 2][1]().tolist())
+        assert got == want
+        with pytest.raises(EngineError):
+            calls[0][1]()                                       # nothing in flight
+        calls[0][0]()
+        with pytest.raises(EngineError):
+            calls[0][0]()                                       # one pass per problem
+        assert calls[0][1]().tolist() == want[2]                # buffers of problem 0 still hold request 2
+    finally:
+        for pr in probs:
+            pr.close()
+
+
 def test_replica_with_a_shard_keeps_only_its_rows_fresh(engine):
     """rt_problem_set_shard: the refresh rebuilds just the shard's rows of the route-order matrix (what each rank of
     a multi-GPU search does); every shard still finds its part of the best move, other shards are refused."""
