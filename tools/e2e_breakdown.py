@@ -35,3 +35,20 @@ print("7 H2D copies (torch, pinned) + sync   ms", round(T(lambda: ([d.copy_(k[0]
 big = torch.empty(sum(x.nbytes for x in h[:7]), dtype=torch.uint8).pin_memory(); bigd = torch.empty_like(big, device="cuda")
 print("1 H2D copy of the same bytes + sync   ms", round(T(lambda: (bigd.copy_(big, non_blocking=True), torch.cuda.synchronize())), 4))
 print("empty sync                            ms", round(T(lambda: torch.cuda.synchronize()), 4))
+# two problems used in turn, inputs already on the device: does alternating cost anything by itself?
+pr2 = eng.problem(n, B); pr2.set_coords(lat, lon); pr2.build_matrix(DIST_SCALE, TS_CAR); pr2.set_stops(st, cap); pr2.set_routes(trips)
+keys2 = torch.empty(B, dtype=torch.int64, device="cuda")
+flip = [0]
+def alt():
+    flip[0] ^= 1
+    (pr2 if flip[0] else pr).plan_dev((keys2 if flip[0] else keys_d).data_ptr(), dist_scale=DIST_SCALE, time_scale=TS_CAR, stream=s)
+print("plan_dev back to back, two problems   ms", round(T(alt, 100), 4))
+outs = [pinned(np.zeros(B, np.uint64)) for _ in range(2)]
+pipes = [p_.plan_pipeline_calls(h[0], h[1], h[2], h[3], h[4], h[5], h[6], o_[1], dist_scale=DIST_SCALE, time_scale=TS_CAR) for p_, o_ in ((pr, outs[0]), (pr2, outs[1]))]
+def pipe(steps):
+    pipes[0][0]()
+    for k in range(1, steps):
+        pipes[k % 2][0](); pipes[(k - 1) % 2][1]()
+    pipes[(steps - 1) % 2][1]()
+pipe(10); torch.cuda.synchronize(); t0 = time.perf_counter(); pipe(200); dt = (time.perf_counter() - t0) / 200 * 1e3
+print("begin/end, two requests in flight     ms", round(dt, 4))
