@@ -29,7 +29,7 @@ namespace rt {
 namespace {
 
 constexpr int kInterThreads = 128;  // one column q per thread
-constexpr int kStripRows = 32;     // rows p per block
+constexpr int kStripRows = 32;     // rows p per block (64 where that still leaves several waves of blocks)
 
 // a + b on the FMA pipe (IMAD with multiplier 1): the move kernels are bound by the ALU pipe (compares, min/max,
 // selects, three-input adds), while the FMA pipe idles — plain sums go there.
@@ -108,9 +108,10 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
 // route pair (the thread's column fixes the second route; its best is flushed whenever the row's route changes).
 enum { kBest = 0, kDump = 1, kTable = 2 };
 
-template <int MODE, bool ASYM>
+template <int MODE, bool ASYM, int ROWS = kStripRows>
 __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel(const EvalArgs a)
 {
+    constexpr int kStripRows = ROWS;  // shadows the default: every use below is this launch's strip height
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
     __shared__ int4 sH[kStripRows];   // {rem_delta, oe, -, route | customer << 30 | rem_ok << 29}
     __shared__ int4 sP1[kStripRows];  // {ready, due, service, demand}
@@ -475,6 +476,18 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
     }
 }
 
+// Taller strips halve the per-block prologue (the column's records, the window's first rows, the block reduction) but
+// also the number of blocks: 64 rows when at least four waves of blocks remain (0.249 -> 0.236 ms on the bench step;
+// 128 rows: 0.231 alone but a slower step, the sweep kernel underneath has fewer blocks to share the SMs with), 32
+// otherwise (a single 5,000-stop instance has 2.4 waves at 64 rows and runs 7 % slower with them).  Symmetric
+// matrices only: the directional variant keeps the 32-row build.
+int pick_strip_rows(int pmax, int rows, int batch)
+{
+    const long long col_blocks = (pmax + kInterThreads - 1) / kInterThreads;
+    const long long blocks64 = col_blocks * ((rows + 63) / 64) * batch;
+    return blocks64 >= 4LL * kNumSMs * 9 ? 64 : kStripRows;
+}
+
 EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d)
 {
     EvalArgs a{};
@@ -551,9 +564,11 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaGetLastError());
     }
     if (families & 6) {
-        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + kStripRows - 1) / kStripRows, p->batch);
-        if (p->symmetric) eval_inter_kernel<kBest, false><<<grid, kInterThreads, 0, st>>>(a);
-        else eval_inter_kernel<kBest, true><<<grid, kInterThreads, 0, st>>>(a);
+        const int sr = pick_strip_rows(pmax, shard_rows, p->batch);
+        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + sr - 1) / sr, p->batch);
+        if (!p->symmetric) eval_inter_kernel<kBest, true><<<grid, kInterThreads, 0, st>>>(a);
+        else if (sr == 64) eval_inter_kernel<kBest, false, 64><<<grid, kInterThreads, 0, st>>>(a);
+        else eval_inter_kernel<kBest, false><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
     if (overlap) {
