@@ -1,29 +1,40 @@
 #!/usr/bin/env python
 """bench.py — one JSON line for the routing hot path on N B200s (contract in the task statement).
 
-A step = one pass of the hot path over one batch of synthetic input: for each of `--batch` independent
-1,000-stop VRPTW instances (BASELINE.json configs[1]) build the 1,001 x 1,001 distance/time matrix from the
-coordinates (in route order: one row per position of the current solution), derive the route state of the current solution and score the full 2-opt/relocate/swap neighbourhood
-(delta + capacity + time-window feasibility per candidate), ending in one best-move key per instance.
+Headline workload (BASELINE.json: the configuration north_star quotes its target on): ONE 10,000-stop VRPTW instance.
+A step = one pass of the hot path over it, partitioned the way north_star names: every rank computes the unit vectors,
+rebuilds ITS rows of the distance/time matrix (in route order: one row per position of the current solution), derives
+the route state and scores ITS shard of the full 2-opt/relocate/swap neighbourhood (delta + capacity + time-window
+feasibility per candidate); the per-shard best-move keys are MIN-reduced over NVLink with NCCL inside the timed region.
+Strong scaling: the instance is fixed, N only changes how it is cut.
 
-  value        matrix cells/s over the whole step, inputs resident in HBM, CUDA events on the launching stream
-  e2e          the same metric through rt_problem_plan with pinned HOST buffers (H2D of coordinates, stops and the
-               current routes, D2H of the best keys, inside the timed region)
-  roofline     the step's dominant kernel, timed alone in the same process
-  cpu_baseline the CPU oracle (a port: the reference has no code for these steps) on this box's cores
-At N > 1 every rank owns its own batch (independent instances, no data-path collective): weak scaling.
+  value        matrix cells/s of the pass (n x n cells of the instance per pass), inputs resident in HBM, CUDA events
+               on the launching stream, max over ranks
+  e2e          the same through the C ABI from pinned HOST buffers (rt_problem_plan_upload_dev: H2D of coordinates,
+               stop records and the current routes, kernels, NCCL MIN, D2H of the key) inside the timed region
+  roofline     the dominant kernel (move evaluation: ALU-pipe bound, against an ALU peak measured in this run) plus
+               the HBM form for the matrix kernel
+  cpu_baseline the CPU oracle (a port: the reference has no code for these steps) on this box's cores,
+               same instance; its best key must equal the engine's reduced key (keys_equal_oracle)
+  extra        the other BASELINE configs at the same N: 10,001^2 matrix rows sharded (C4), 5,000-stop/50-vehicle
+               batched solve over the replicas (C5), 1M ETA pairs x 500 trees sharded (C3); at N = 1 also round 1's
+               64 x 1,000-stop batch (C2) and the request-latency / CPU columns
 
-`--impl reference` times the CPU oracle instead (rank 0 only) and prints the same line with "impl": "reference".
+`--impl reference` times the CPU oracle on the same instance (rank 0 only) and prints the same line with
+"impl": "reference".
 """
 from __future__ import annotations
 
 import argparse
+import datetime
 import json
 import os
+import struct
 import subprocess
 import sys
 import threading
 import time
+import zlib
 
 import numpy as np
 
@@ -36,6 +47,8 @@ TS_CAR = 3.6 / 40.0
 DIST_SCALE = 10.0
 METRIC = "matrix cells/s and VRPTW move-evals/s"
 BYTES_PER_EVAL = {0: 16, 1: 24, 2: 32}  # matrix reads per 2-opt / relocate / swap candidate
+SEED_10K, SEED_5K, SEED_ETA, SEED_BATCH = 4567, 5678, 3456, 2345
+INT64_NONE = 2 ** 63 - 1
 
 
 # ----------------------------------------------------------------------------------------------- workload
@@ -78,6 +91,33 @@ def count_candidates(trips, n):
     P = n + len(trips)
     two_opt = sum(len(t) * (len(t) - 1) // 2 for t in trips)
     return {0: two_opt, 1: ncust * (P - 3), 2: ncust * (ncust - 1) // 2}
+
+
+def eta_model_blob(trees, depth, seed=SEED_ETA):
+    """Synthetic gradient-boosted ensemble in the engine's format (SPEC.md §9.2): complete trees, random splits over
+    the 12 features of ml.py:35-48 with thresholds inside each feature's range."""
+    rng = np.random.default_rng(seed)
+    nodes = bytearray()
+    offs = [0]
+    for _ in range(trees):
+        cnt = 2 ** (depth + 1) - 1
+        for k in range(cnt):
+            if k < 2 ** depth - 1:
+                f = int(rng.integers(0, 12))
+                thr = float(rng.uniform(0, 40) if f == 10 else rng.uniform(20, 40) if f == 11 else rng.uniform(0, 23) if f == 9
+                            else rng.uniform(0, 6) if f == 8 else 0.5)
+                nodes += struct.pack("<fHBB", thr, 2 * k + 1, f, 0)
+            else:
+                nodes += struct.pack("<fHBB", float(rng.normal(0, 0.2)), 0, 0, 1)
+        offs.append(offs[-1] + cnt)
+    return b"RTE1" + struct.pack("<IIf", trees, 12, 25.0) + struct.pack(f"<{len(offs)}I", *offs) + bytes(nodes)
+
+
+def eta_columns(m, seed=SEED_ETA):
+    rng = np.random.default_rng(seed + 1)
+    return (rng.uniform(0, 45000, m), rng.integers(0, 4, m).astype(np.uint8), rng.integers(0, 4, m).astype(np.uint8),
+            rng.integers(0, 7, m).astype(np.uint8), rng.integers(0, 24, m).astype(np.uint8),
+            rng.uniform(20, 40, m).astype(np.float32))
 
 
 # ----------------------------------------------------------------------------------------------- clocks
@@ -128,147 +168,254 @@ def host_threads() -> int:
         return max(1, os.cpu_count() or 1)
 
 
-def oracle_instances(seeds, stops, vehicles):
-    """Instances + greedy start on the CPU oracle (used by the cpu_baseline leg and by --impl reference only)."""
+def oracle_instance(seed, stops, vehicles, threads=None):
+    """The instance + greedy start on the CPU oracle (cpu_baseline leg, key check and --impl reference only)."""
     from oracle import oracle as O
-    out = []
-    for seed in seeds:
-        lat, lon, demand, cap = synth_coords(seed, stops, vehicles)
-        n = stops + 1
-        xyz = O.unit_vectors(lat, lon)
-        m = O.matrix_rows(xyz, 0, n, DIST_SCALE, TS_CAR, threads=host_threads())
-        tw = synth_windows(seed, m["time"][0, 1:], m["time"][1:, 0])
-        st = np.zeros((n, 4), np.int32)
-        st[:, :3] = tw
-        st[:, 3] = demand
-        rc, trips = O.greedy_trips(m["dist"], demand.astype(float), float(cap), 9e12, T=m["time"], tw=tw)
-        assert rc == 0
-        out.append(dict(lat=lat, lon=lon, stops=st, cap=cap, trips=trips, node=O.build_positions(trips, n)))
-    return out
+    th = threads or host_threads()
+    lat, lon, demand, cap = synth_coords(seed, stops, vehicles)
+    n = stops + 1
+    m = O.matrix_rows(O.unit_vectors(lat, lon), 0, n, DIST_SCALE, TS_CAR, threads=th)
+    tw = synth_windows(seed, m["time"][0, 1:], m["time"][1:, 0])
+    st = np.zeros((n, 4), np.int32)
+    st[:, :3] = tw
+    st[:, 3] = demand
+    rc, trips = O.greedy_trips(m["dist"], demand.astype(float), float(cap), 9e12, T=m["time"], tw=tw)
+    assert rc == 0
+    return dict(lat=lat, lon=lon, stops=st, cap=cap, trips=trips, node=O.build_positions(trips, n), n=n,
+                inst=O.Instance(m["dist"], m["time"], st, cap))
 
 
-def oracle_step(insts):
-    """One pass of the hot path on the CPU oracle with all host threads; returns (cells, evals)."""
+def oracle_pass(it, threads):
+    """One pass of the hot path on the CPU oracle: matrix from coordinates + full-neighbourhood best move.
+    Returns (cells, evals, key)."""
     from oracle import oracle as O
+    n = it["n"]
+    m = O.matrix_rows(O.unit_vectors(it["lat"], it["lon"]), 0, n, DIST_SCALE, TS_CAR, threads=threads)
+    inst = O.Instance(m["dist"], m["time"], it["stops"], it["cap"])
+    key = O.best_move(inst, it["node"], threads=threads)
+    return n * n, sum(count_candidates(it["trips"], n).values()), int(key)
+
+
+def cpu_baseline(it, budget_s=10.0):
+    """All host threads on the headline instance for about budget_s, plus a single-thread column on a 1,000-stop one."""
     th = host_threads()
-    cells = evals = 0
-    for it in insts:
-        n = it["lat"].size
-        m = O.matrix_rows(O.unit_vectors(it["lat"], it["lon"]), 0, n, DIST_SCALE, TS_CAR, threads=th)
-        inst = O.Instance(m["dist"], m["time"], it["stops"], it["cap"])
-        O.best_move(inst, it["node"], threads=th)
-        cells += n * n
-        evals += sum(count_candidates(it["trips"], n).values())
-    return cells, evals
-
-
-def cpu_baseline(stops, vehicles, budget_s=8.0, max_inst=4):
-    from oracle import oracle as O
-    insts = oracle_instances([2345 + i for i in range(max_inst)], stops, vehicles)
-    oracle_step(insts[:1])  # warm-up
     t0 = time.perf_counter()
     cells = evals = reps = 0
-    while time.perf_counter() - t0 < budget_s:
-        c, e = oracle_step(insts)
+    while reps < 1 or time.perf_counter() - t0 < budget_s:
+        c, e, key = oracle_pass(it, th)
         cells, evals, reps = cells + c, evals + e, reps + 1
     dt = time.perf_counter() - t0
-    return {"value": cells / dt, "unit": "cells/s", "move_evals_per_s": evals / dt, "cores": host_threads(),
-            "kind": "port",
-            "sample": f"{reps} passes over {max_inst} of the workload's instances ({stops} stops each): oracle matrix "
-                      f"build + full-neighbourhood best move, {host_threads()} OpenMP threads, {dt:.1f} s"}
+    small = oracle_instance(SEED_BATCH, 1000, 10, threads=th)
+    oracle_pass(small, 1)
+    t1 = time.perf_counter()
+    c1 = e1 = r1 = 0
+    while r1 < 1 or time.perf_counter() - t1 < 3.0:
+        c, e, _ = oracle_pass(small, 1)
+        c1, e1, r1 = c1 + c, e1 + e, r1 + 1
+    d1 = time.perf_counter() - t1
+    return {"value": cells / dt, "unit": "cells/s", "move_evals_per_s": evals / dt, "ms_per_pass": 1e3 * dt / reps,
+            "cores": th, "kind": "port",
+            "sample": f"{reps} full passes over the headline instance ({it['n'] - 1} stops): oracle matrix build + "
+                      f"full-neighbourhood best move, {th} OpenMP threads, {dt:.1f} s",
+            "single_thread": {"value": c1 / d1, "unit": "cells/s", "move_evals_per_s": e1 / d1, "cores": 1,
+                              "sample": f"{r1} passes over one 1,000-stop instance, 1 thread, {d1:.1f} s"},
+            "best_key": key}
 
 
 def run_reference(args, rank):
     if rank != 0:
         return
-    from oracle import oracle as O
-    per_step = 2
-    insts = oracle_instances([2345 + i for i in range(per_step)], args.stops, args.vehicles)
-    for _ in range(args.warmup):
-        oracle_step(insts)
+    th = host_threads()
+    it = oracle_instance(SEED_10K, args.stops, args.vehicles, threads=th)
+    for _ in range(min(args.warmup, 1)):   # one warm pass is enough for a CPU loop of ~1 s per pass
+        oracle_pass(it, th)
     t0 = time.perf_counter()
     cells = evals = 0
     for _ in range(args.steps):
-        c, e = oracle_step(insts)
+        c, e, key = oracle_pass(it, th)
         cells, evals = cells + c, evals + e
     dt = time.perf_counter() - t0
     val = cells / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "cells/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64/f32->i32", "data": "synthetic",
-        "config": {"workload": f"{per_step} x ({args.stops}-stop matrix + full 2-opt/relocate/swap neighbourhood) per "
-                               "step on the host CPU (bounded sample of the engine arm's batch)",
-                   "stops": args.stops, "instances_per_step": per_step},
-        "move_evals_per_s": evals / dt,
-        "cpu_baseline": {"value": val, "unit": "cells/s", "cores": host_threads(), "kind": "port",
-                         "sample": f"{args.steps} steps x {per_step} instances, CPU oracle (the reference itself has no "
-                                   "code for matrix build or move evaluation: SURVEY.md §0)"},
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64/f32->i32", "data": "synthetic",
+        "config": workload_config(args.stops, args.vehicles, len(it["trips"]), it["n"] + len(it["trips"]),
+                                  sum(count_candidates(it["trips"], it["n"]).values()), args.gpus),
+        "reference_arm": "host CPU, all threads, the whole instance per step — the same instance, cells and candidates "
+                         "as the engine arm",
+        "move_evals_per_s": evals / dt, "best_key": key,
+        "cpu_baseline": {"value": val, "unit": "cells/s", "cores": th, "kind": "port",
+                         "sample": f"{args.steps} full passes over the instance, CPU oracle, {th} OpenMP threads (the "
+                                   "reference itself has no code for matrix build or move evaluation: SURVEY.md §0)"},
         "e2e": {"value": val, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
 
 
+def workload_config(stops, vehicles, routes, P, evals, world):
+    n = stops + 1
+    parallelism = (f"matrix rows and move neighbourhood sharded over {world} GPUs (one process per GPU); per-shard "
+                   "best-move keys MIN-reduced with one NCCL all_reduce (int64) per pass inside the timed region"
+                   if world > 1 else "1 GPU: the whole instance on one shard, no exchange needed")
+    return {"workload": f"one {stops}-stop / {vehicles}-vehicle VRPTW instance (seed {SEED_10K}): {n} x {n} distance/time "
+                        "matrix in route order + route state + full 2-opt/relocate/swap neighbourhood with capacity "
+                        "and time-window feasibility, best-move key per pass",
+            "stops": stops, "routes": routes, "positions": P, "cells_per_step": n * n, "move_evals_per_step": evals,
+            "l2": f"each pass writes and re-reads {P * ((P + 15) // 16 * 16) * 8 / 1e6:.0f} MB of route-order matrix "
+                  "(> 126 MB L2 up to 4 GPUs; 105 MB per GPU at 8); no flush",
+            "parallelism": parallelism}
+
+
 # ----------------------------------------------------------------------------------------------- engine arm
 
-def run_engine(args, rank, world):
-    import torch
-    import torch.distributed as dist
+class Ctx:
+    """What every block of the engine arm needs."""
 
-    from routest_b200 import ALL_FAMILIES, Engine
+    def __init__(self, args, rank, world):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.args, self.rank, self.world = torch, dist, args, rank, world
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        if world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local),
+                                    timeout=datetime.timedelta(seconds=300))
+        from routest_b200 import Engine
+        self.eng = Engine(self.local)
+        self.stream = torch.cuda.current_stream().cuda_stream
 
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    eng = Engine(local)
-    B, stops, n = args.batch, args.stops, args.stops + 1
-    pr = eng.problem(n, B)
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
 
-    # ---- set-up (untimed): this rank's instances, their windows and a feasible start from the engine's own greedy
-    seeds = [2345 + rank * B + b for b in range(B)]
-    raw = [synth_coords(s, stops, args.vehicles) for s in seeds]
-    lat = np.stack([r[0] for r in raw])
-    lon = np.stack([r[1] for r in raw])
-    demand = np.stack([r[2] for r in raw])
-    cap = np.array([r[3] for r in raw], np.int32)
+    def max_over_ranks(self, v):
+        if self.world == 1:
+            return float(v)
+        t = self.torch.tensor([float(v)], device="cuda", dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def all_agree(self, ok):
+        """True when `ok` holds on every rank (a collective: every rank must call it)."""
+        if self.world == 1:
+            return bool(ok)
+        t = self.torch.tensor([1 if ok else 0], device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MIN)
+        return bool(t.item())
+
+    def timed(self, fn, reps, warm=3):
+        """Average device time of fn() in ms (CUDA events on the launching stream), this rank only."""
+        torch = self.torch
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    def timed_all(self, fn, reps, warm=3):
+        """The same with a barrier in front and the max over ranks behind (multi-GPU figures)."""
+        for _ in range(warm):
+            fn()
+        self.barrier()
+        torch = self.torch
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        self.barrier()
+        return self.max_over_ranks(a.elapsed_time(b) / reps)
+
+
+def build_problem(eng, seed, stops, vehicles):
+    """Instance on the device with a feasible start from the engine's own greedy (set-up, untimed)."""
+    n = stops + 1
+    lat, lon, demand, cap = synth_coords(seed, stops, vehicles)
+    t0 = eng.matrix_build(lat, lon, dist_scale=DIST_SCALE, time_scale=TS_CAR, rows=(0, 1), want=("time",))["time"][0]
+    st = np.zeros((1, n, 4), np.int32)
+    st[0, :, :3] = synth_windows(seed, t0[1:], t0[1:])   # the SPEC §2 matrix is symmetric: t[0][i] == t[i][0]
+    st[0, :, 3] = demand
+    pr = eng.problem(n, 1)
     pr.set_coords(lat, lon)
     pr.build_matrix(DIST_SCALE, TS_CAR)
-    st = np.zeros((B, n, 4), np.int32)
-    for b in range(B):
-        _, t = pr.get_matrix(b)
-        st[b, :, :3] = synth_windows(seeds[b], t[0, 1:], t[1:, 0])
-        st[b, :, 3] = demand[b]
-    pr.set_stops(st, cap)
-    trips, status = pr.greedy(demand.astype(np.float64), cap.astype(np.float64), use_tw=True)
-    assert not status.any(), "greedy failed on the synthetic workload"
+    pr.set_stops(st, [cap])
+    trips, status = pr.greedy(demand[None].astype(np.float64), [float(cap)], use_tw=True)
+    assert status[0] == 0, "greedy failed on the synthetic workload"
     pr.set_routes(trips)
-    cand = [count_candidates(t, n) for t in trips]
-    evals_step = sum(sum(c.values()) for c in cand)
-    eval_bytes = sum(c[f] * BYTES_PER_EVAL[f] for c in cand for f in c)
-    cells_step = B * n * n                       # the metric counts the n x n matrix of the instance ...
-    pmax = max(n + len(t) for t in trips)
-    cells_built = B * pmax * ((pmax + 15) // 16 * 16)   # ... the kernel writes it in route order with one depot row per route
+    return pr, dict(lat=lat, lon=lon, stops=st, cap=cap, demand=demand, trips=trips[0], n=n)
 
-    stream = torch.cuda.current_stream().cuda_stream
-    keys_d = torch.empty(B, dtype=torch.int64, device="cuda")
+
+def capture(torch, fn):
+    """fn(stream) captured once into a CUDA graph; returns (replay callable, True) or (eager callable, False)."""
+    try:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            fn(torch.cuda.current_stream().cuda_stream)
+        return g.replay, True
+    except Exception:
+        torch.cuda.synchronize()
+        return (lambda: fn(torch.cuda.current_stream().cuda_stream)), False
+
+
+def count_kernels(torch, fn):
+    """Kernels one call of fn() launches, counted by the profiler (CUPTI); None when it is unavailable."""
+    try:
+        from torch.profiler import ProfilerActivity, profile
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            fn()
+            torch.cuda.synchronize()
+        names = [ev.name for ev in prof.events() if str(getattr(ev, "device_type", "")).endswith("CUDA")
+                 and "memcpy" not in ev.name.lower() and "memset" not in ev.name.lower()]
+        mine = [nm for nm in names if "nccl" not in nm.lower()]
+        return (len(mine), len(names) - len(mine)) if names else None
+    except Exception:
+        return None
+
+
+def run_engine(args, rank, world):
+    cx = Ctx(args, rank, world)
+    torch, dist, eng, stream = cx.torch, cx.dist, cx.eng, cx.stream
+    from routest_b200 import ALL_FAMILIES
+
+    # ---- set-up (untimed): the instance, a feasible start, this rank's shard
+    pr, w = build_problem(eng, SEED_10K, args.stops, args.vehicles)
+    n, trips = w["n"], w["trips"]
+    pr.set_shard(rank, world)
+    P = n + len(trips)
+    cand = count_candidates(trips, n)
+    evals_step = sum(cand.values())
+    cells_step = n * n
+    keys = torch.full((1,), INT64_NONE, dtype=torch.int64, device="cuda")
+
+    def enqueue_pass(s):
+        # unit vectors -> this rank's rows of the route-order matrix (+ route state underneath) -> this rank's shard of
+        # the neighbourhood -> its best key, signed-order int64 on the device
+        pr.plan_dev(keys.data_ptr(), dist_scale=DIST_SCALE, time_scale=TS_CAR, families=ALL_FAMILIES, stream=s)
+
+    enqueue_pass(stream)                      # lazy set-up (side streams, buffers) stays outside the capture
+    torch.cuda.synchronize()
+    replay, graphed = capture(torch, enqueue_pass)
 
     def step():
-        # unit vectors -> matrix (route order) -> route state -> full neighbourhood -> best keys, all on `stream`
-        pr.plan_dev(keys_d.data_ptr(), dist_scale=DIST_SCALE, time_scale=TS_CAR, families=ALL_FAMILIES, stream=stream)
-
-    def barrier():
-        torch.cuda.synchronize()
+        replay()                              # this rank's kernels, one graph launch
         if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
+            dist.all_reduce(keys, op=dist.ReduceOp.MIN)   # the path's one exchange: 8 bytes over NVLink
 
-    # ---- device-resident timing
+    # ---- device-resident timing: K passes, barrier + sync on both sides, CUDA events, max over ranks
     for _ in range(args.warmup):
         step()
-    barrier()
-    sampler = ClockSampler(local)
+    cx.barrier()
+    sampler = ClockSampler(cx.local)
     if rank == 0:
         sampler.start()
         time.sleep(0.25)
@@ -278,263 +425,422 @@ def run_engine(args, rank, world):
     for _ in range(args.steps):
         step()
     ev1.record()
-    barrier()
-    t_wall1 = time.perf_counter()
-    ms = ev0.elapsed_time(ev1)
-    if world > 1:
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    keys_ref = keys_d.clone()
+    cx.barrier()
+    ms = cx.max_over_ranks(ev0.elapsed_time(ev1))
+    key_device = int(keys.item())
 
-    # ---- per-kernel timing (same process, alone): which one dominates, and its roofline
-    def timed(fn, reps):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        for _ in range(reps):
-            fn()
-        b.record()
-        torch.cuda.synchronize()
-        return a.elapsed_time(b) / reps
-
+    # ---- per-kernel timing, this rank's shard, each alone: which one dominates, and its roofline
     reps = max(args.steps, 10)
-    ms_matrix = timed(lambda: pr.refresh_dev(1, stream), reps)   # position vectors + matrix kernel (route order)
-    ms_refresh = timed(lambda: pr.refresh_dev(2, stream), reps)  # gather + walk
-    ms_eval = timed(lambda: pr.eval_moves_dev(keys_d.data_ptr(), ALL_FAMILIES, (0, 1), stream), reps)
+    ms_matrix = cx.timed(lambda: pr.refresh_dev(1, stream), reps)   # position vectors + matrix kernel (shard rows)
+    ms_state = cx.timed(lambda: pr.refresh_dev(2, stream), reps)    # gather + routes + walk + records
+    ms_eval = cx.timed(lambda: pr.eval_moves_dev(keys.data_ptr(), ALL_FAMILIES, (rank, world), stream), reps)
+    ms_own = cx.timed(replay, reps)                                 # the rank's whole pass without the exchange
+    # a longer loop of the same pass so that the clock sampler sees the GPU under this very load
+    t_load = time.perf_counter()
+    while time.perf_counter() - t_load < 0.6:
+        for _ in range(50):
+            replay()
+        torch.cuda.synchronize()
     clocks = sampler.stop(t_wall0, time.perf_counter()) if rank == 0 else None
+    peak_alu = peak_issue = None
+    if rank == 0:
+        peak_alu, _ = eng.pipe_peak(0, 40000)
+        peak_issue, _ = eng.pipe_peak(2, 40000)
 
-    # ---- end to end through the C ABI with pinned host buffers
+    # ---- end to end through the C ABI with pinned host buffers: upload, kernels, NCCL MIN, key back to the host
     def pinned(a):
         t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
         return t, t.numpy()
 
-    node = np.zeros((B, pr.pstride), np.int32)
-    npos = np.zeros(B, np.int32)
-    for b in range(B):
-        node[b], npos[b] = positions(trips[b], pr.pstride)
-    keep = [pinned(x) for x in (lat, lon, st, cap, np.full(B, 2 ** 62, np.int64), node, npos, np.zeros(B, np.uint64))]
+    node, npos = positions(trips, pr.pstride)
+    keep = [pinned(x) for x in (w["lat"][None], w["lon"][None], w["stops"], np.array([w["cap"]], np.int32),
+                                np.full(1, 2 ** 62, np.int64), node[None], np.array([npos], np.int32))]
     h = [k[1] for k in keep]
-    h2d = sum(x.nbytes for x in h[:7])
-    d2h = h[7].nbytes
+    key_host_t = torch.zeros(1, dtype=torch.int64).pin_memory()
+    h2d, d2h = sum(x.nbytes for x in h), 8
+    upload = pr.plan_upload_call(*h, keys.data_ptr(), dist_scale=DIST_SCALE, time_scale=TS_CAR, stream=stream)
 
-    # the call a service makes per request batch: host buffers (re-filled in place by the caller) in, best keys out
-    e2e_step = pr.plan_call(h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7], dist_scale=DIST_SCALE, time_scale=TS_CAR)
+    def e2e_step():
+        upload()
+        if world > 1:
+            dist.all_reduce(keys, op=dist.ReduceOp.MIN)
+        key_host_t.copy_(keys, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return int(key_host_t[0])
 
     for _ in range(args.warmup):
         e2e_step()
-    barrier()
+    cx.barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        e2e_step()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    same = bool(np.array_equal(h[7].view(np.int64) ^ np.int64(-2 ** 63), keys_ref.cpu().numpy()))
+        key_e2e = e2e_step()
+    cx.barrier()
+    e2e_s = cx.max_over_ranks(time.perf_counter() - t0)
 
-    # ---- the same requests with two in flight (rt_problem_plan_begin / _end on two problems used in turn): every step
-    # still uploads its inputs from pinned host memory and reads its keys back, but the upload of step k+1 runs under
-    # the kernels of step k.  Reported next to the synchronous figure, not instead of it.
-    pr2 = eng.problem(n, B)
-    out2 = pinned(np.zeros(B, np.uint64))
-    pipes = [p_.plan_pipeline_calls(h[0], h[1], h[2], h[3], h[4], h[5], h[6], o_, dist_scale=DIST_SCALE, time_scale=TS_CAR)
-             for p_, o_ in ((pr, h[7]), (pr2, out2[1]))]
+    # ---- the same pass with the peer-memory exchange instead of the collective (exchange.cu), as a secondary figure
+    peer = None if args.no_extra else peer_exchange_pass(cx, pr, reps)
 
-    def pipelined(steps):
-        pipes[0][0]()
-        for k in range(1, steps):
-            pipes[k % 2][0]()
-            pipes[(k - 1) % 2][1]()
-        return pipes[(steps - 1) % 2][1]()
+    # ---- the key must be the oracle's (rank 0; the cpu_baseline leg at N = 1 times the same calls)
+    base = oracle_key = None
+    if rank == 0 and not args.no_cpu:
+        it = oracle_instance(SEED_10K, args.stops, args.vehicles)
+        assert it["trips"] == trips, "greedy start differs from the oracle's"
+        if world == 1:
+            base = cpu_baseline(it)
+            oracle_key = base.pop("best_key")
+        else:
+            oracle_key = oracle_pass(it, host_threads())[2]
 
-    pipelined(max(args.warmup, 2))
-    barrier()
-    t0 = time.perf_counter()
-    last = pipelined(args.steps)
-    barrier()
-    pipe_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([pipe_s], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        pipe_s = float(t.item())
-    same_pipe = bool(np.array_equal(last.view(np.int64) ^ np.int64(-2 ** 63), keys_ref.cpu().numpy()))
-    pr2.close()
-
-    extra = secondary_figures(eng, torch, stream) if (rank == 0 and not args.no_extra) else None
+    extra = None
+    if not args.no_extra:
+        extra = secondary_blocks(cx)
+        if peer is not None:
+            extra["pass_10000_peer_exchange"] = peer
+    # last, so that the profiler cannot disturb any timing: how many kernels one pass launches
+    launches = count_kernels(torch, lambda: enqueue_pass(stream)) if rank == 0 else None
+    pr.close()
 
     if rank == 0:
-        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-        if os.path.exists(peaks_path):
-            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-        else:
-            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            traffic = json.load(open(tp))
-        kern = {
-            "matrix_kernel": {"ms": ms_matrix, "algorithmic_bytes": cells_step * 8,
-                              "GBs": cells_step * 8 / ms_matrix / 1e6, "bytes_written": cells_built * 8,
-                              "GBs_written": cells_built * 8 / ms_matrix / 1e6,
-                              "note": "position_vectors_kernel + matrix_kernel<0> on the route-ordered stops"},
-            "state_tables": {"ms": ms_refresh},
-            "eval_moves(inter+intra)": {"ms": ms_eval, "algorithmic_bytes": eval_bytes,
-                                        "GBs": eval_bytes / ms_eval / 1e6, "move_evals_per_s": evals_step / ms_eval * 1e3},
-        }
-        dom = "matrix_kernel" if ms_matrix >= ms_eval else "eval_moves(inter+intra)"
-        ach = kern[dom]["GBs"]
-        roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "peak_source": peak_src,
-                "traffic": (traffic or {}).get(dom),
-                "note": "algorithmic bytes per SURVEY.md §8(d): 8 B per matrix cell; 16/24/32 B of matrix reads per "
-                        "2-opt/relocate/swap candidate (tile reuse makes real DRAM traffic much smaller than that)",
-                "matrix_kernel": {"achieved": kern["matrix_kernel"]["GBs"], "frac": kern["matrix_kernel"]["GBs"] / peak}}
-        # Neither kernel of this step is purely HBM-bound at 1,040-wide instances: both sit near the issue limit.  The
-        # instruction counts are fixed by the workload (ncu, profiles/traffic.json); the rates use the live durations.
-        winst = (traffic or {}).get("warp_instructions") or {}
-        if winst and clocks.get("sm_mhz"):
-            peak_issue = 148 * 4 * float(clocks["sm_mhz"]) * 1e6            # one warp instruction per SMSP per clock
-            roof["issue"] = {k: {"warp_inst_per_launch": winst[k], "achieved_Ginst_s": winst[k] / kern[k]["ms"] / 1e6,
-                                 "frac_of_issue_peak": winst[k] / (kern[k]["ms"] / 1e3) / peak_issue}
-                             for k in ("matrix_kernel", "eval_moves(inter+intra)") if k in winst}
-            roof["issue"]["peak_Ginst_s"] = peak_issue / 1e9
-        total_cells = cells_step * world
+        to_u64 = lambda k: (int(k) ^ -(2 ** 63)) & (2 ** 64 - 1)   # signed-order form -> packed key (SPEC §7)
+        key_u = to_u64(key_device)
+        keys_ok = None if oracle_key is None else bool(key_u == oracle_key and to_u64(key_e2e) == oracle_key)
+        if keys_ok is False:
+            raise SystemExit(f"best-move key mismatch: engine {key_u:#x} / e2e {to_u64(key_e2e):#x} / oracle {oracle_key:#x}")
         line = {
-            "metric": METRIC, "value": total_cells * args.steps / (ms / 1e3), "unit": "cells/s",
+            "metric": METRIC, "value": cells_step * args.steps / (ms / 1e3), "unit": "cells/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64/f32->i32",
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64/f32->i32",
             "data": "synthetic",
-            "config": {"workload": f"{B} x ({stops}-stop distance/time matrix + route state + full 2-opt/relocate/swap "
-                                   "neighbourhood with capacity and time-window feasibility) per GPU per step",
-                       "stops": stops, "instances_per_gpu": B, "routes_per_instance_mean": float(np.mean([len(t) for t in trips])),
-                       "cells_per_step_per_gpu": cells_step, "move_evals_per_step_per_gpu": evals_step,
-                       "l2": f"each step writes and re-reads {cells_step * 8 / 1e6:.0f} MB of matrix per GPU (> 126 MB L2); no flush needed",
-                       "parallelism": f"{world} x independent batches (no collective)"},
-            "move_evals_per_s": evals_step * world * args.steps / (ms / 1e3),
-            "kernels": kern, "roofline": roof,
-            "e2e": {"value": total_cells * args.steps / e2e_s, "unit": "cells/s", "h2d_bytes_per_step": int(h2d),
+            "config": workload_config(args.stops, args.vehicles, len(trips), P, evals_step, world),
+            "move_evals_per_s": evals_step * args.steps / (ms / 1e3),
+            "best_key": key_u, "keys_equal_oracle": keys_ok,
+            "pass_graph_replayed": graphed,
+            "kernels": kernel_block(ms_matrix, ms_state, ms_eval, ms_own, P, n, world, cand),
+            "roofline": roofline_block(ms_matrix, ms_eval, P, n, world, cand, clocks, peak_alu, peak_issue),
+            "e2e": {"value": cells_step * args.steps / e2e_s, "unit": "cells/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * e2e_s / args.steps,
-                    "move_evals_per_s": evals_step * world * args.steps / e2e_s,
-                    "call": "rt_problem_plan via Problem.plan_call (pinned host buffers in, best keys out; matrices stay in HBM)",
-                    "keys_equal_device_path": same,
-                    "two_requests_in_flight": {"value": total_cells * args.steps / pipe_s, "unit": "cells/s",
-                                               "ms_per_step": 1e3 * pipe_s / args.steps,
-                                               "call": "rt_problem_plan_begin / rt_problem_plan_end on two problems used in "
-                                                       "turn: the upload of one request runs under the kernels of the other",
-                                               "keys_equal_device_path": same_pipe}},
-            "gpu_launches": 6 * args.steps,  # kernels per step, counted in profiles/r1_launches_bench_steps2.csv
+                    "move_evals_per_s": evals_step * args.steps / e2e_s,
+                    "call": "rt_problem_plan_upload_dev (pinned host buffers in, this rank's shard scored) + NCCL "
+                            "all_reduce(MIN) + 8-byte key back to pinned host memory, synchronous per step",
+                    "keys_equal_device_path": bool(key_e2e == key_device)},
+            "gpu_launches": (launches[0] if launches else 10) * args.steps,
+            "gpu_launches_source": ("torch.profiler (CUPTI) count of this library's kernels in one pass: "
+                                    f"{launches[0]} per step, + {1 if world > 1 else 0} NCCL kernel" if launches else
+                                    "constant: 10 kernels per pass (position vectors, matrix, 4 state tables, fill, "
+                                    "intra, inter, finish)"),
             "clocks": clocks,
         }
         if extra:
             line["extra"] = extra
-        if world == 1 and not args.no_cpu:
-            line["cpu_baseline"] = cpu_baseline(stops, args.vehicles)
+        if base:
+            line["cpu_baseline"] = base
         print(json.dumps(line))
-    pr.close()
     eng.close()
     if world > 1:
         dist.destroy_process_group()
 
 
-def secondary_figures(eng, torch, stream):
-    """Quick figures for the other BASELINE configs (not the headline): the matrix kernel at 10,001 nodes, the host
-    matrix API, ETA scoring of 1M pairs on a synthetic 200-tree ensemble, and a full 5,000-stop solve."""
-    import struct
+def kernel_block(ms_matrix, ms_state, ms_eval, ms_own, P, n, world, cand):
+    pitch = (P + 15) // 16 * 16
+    rows = P // world + 3 if world > 1 else P
+    return {
+        "note": f"rank 0's shard (1/{world} of the rows and of the neighbourhood), each timed alone in this process",
+        "position_vectors+matrix_kernel": {"ms": ms_matrix, "rows": rows, "bytes_written": rows * pitch * 8,
+                                           "GBs_written": rows * pitch * 8 / ms_matrix / 1e6},
+        "state_tables": {"ms": ms_state, "note": "replicated on every rank (runs underneath the matrix kernel)"},
+        "eval_moves(inter+intra)": {"ms": ms_eval, "move_evals": sum(cand.values()) // world,
+                                    "move_evals_per_s": sum(cand.values()) / world / ms_eval * 1e3},
+        "whole_pass_without_exchange": {"ms": ms_own},
+    }
 
+
+def roofline_block(ms_matrix, ms_eval, P, n, world, cand, clocks, peak_alu, peak_issue):
+    """Dominant kernel = move evaluation, bound by the ALU pipe: achieved = ALU-pipe warp instructions per launch (ncu
+    counter of the same workload, profiles/r2_counters.json; a shard executes 1/N of them) / live duration, against the
+    ALU-pipe peak measured in this run (rt_selftest_pipe_peak).  The matrix kernel keeps the HBM form."""
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        hbm, hbm_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        hbm, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+    counters = {}
+    cp = os.path.join(ROOT, "profiles", "r2_counters.json")
+    if os.path.exists(cp):
+        counters = json.load(open(cp)).get(f"pass_{n - 1}", {})
+    pitch = (P + 15) // 16 * 16
+    rows = P // world + 3 if world > 1 else P
+    mat_bytes = (n * n * 8) / world                    # algorithmic: 8 B per cell of the instance, this rank's share
+    mat = {"kernel": "matrix_kernel<0> (+ position vectors)", "bound": "hbm", "achieved": mat_bytes / ms_matrix / 1e6,
+           "peak": hbm, "unit": "GB/s", "frac": mat_bytes / ms_matrix / 1e6 / hbm, "peak_source": hbm_src,
+           "bytes_written_incl_route_order_rows_and_pad": rows * pitch * 8,
+           "frac_on_bytes_written": rows * pitch * 8 / ms_matrix / 1e6 / hbm,
+           "traffic": (counters.get("matrix_kernel") or {}).get("dram_bytes")}
+    ev = counters.get("eval_moves") or {}
+    alu_inst, all_inst = ev.get("alu_warp_inst"), ev.get("warp_inst")
+    roof = {"kernel": "eval_inter_kernel + eval_intra_kernel (move evaluation)", "bound": "alu",
+            "unit": "G warp-instructions/s on the ALU pipe", "achieved": None, "peak": None, "frac": None,
+            "traffic": ev.get("dram_bytes"),
+            "note": "move evaluation is not HBM-bound (SURVEY.md §8(d)): every cell is fetched once per strip and "
+                    "re-used from registers; the binding unit is the ALU pipe (compares, min/max, selects)",
+            "matrix_kernel": mat}
+    if peak_alu:
+        roof["peak"] = peak_alu / 1e9
+        roof["peak_source"] = ("measured in this run: rt_selftest_pipe_peak mode 0 (independent LOP3/IMNMX chains, CUDA "
+                               f"events, SM clock {clocks.get('sm_mhz') if clocks else None} MHz)")
+        roof["issue_peak"] = peak_issue / 1e9 if peak_issue else None
+    if alu_inst and peak_alu:
+        ach = alu_inst / world / (ms_eval / 1e3)
+        roof["achieved"] = ach / 1e9
+        roof["frac"] = ach / peak_alu
+        roof["alu_warp_inst_per_launch"] = alu_inst / world
+        roof["counter_source"] = "profiles/r2_counters.json (ncu smsp__inst_executed_pipe_alu.sum, inter + intra)"
+    if all_inst and peak_issue:
+        roof["issue"] = {"achieved": all_inst / world / (ms_eval / 1e3) / 1e9, "peak": peak_issue / 1e9,
+                         "frac": all_inst / world / (ms_eval / 1e3) / peak_issue}
+    roof["algorithmic_matrix_reads"] = {
+        "bytes": sum(cand[f] * BYTES_PER_EVAL[f] for f in cand) // world,
+        "GBs": sum(cand[f] * BYTES_PER_EVAL[f] for f in cand) / world / ms_eval / 1e6,
+        "note": "SURVEY.md §8(d) per-candidate figure (16/24/32 B), for reference only: served from registers/L1, not HBM"}
+    return roof
+
+
+def peer_exchange_pass(cx, pr, reps):
+    """The headline pass with exchange.cu instead of the collective: every rank MIN-reduces its key straight into every
+    replica's slot buffer with system-scope atomics over NVLink; two passes (the two slots) form one graph."""
+    torch, dist, world, rank = cx.torch, cx.dist, cx.world, cx.rank
+    from routest_b200 import ALL_FAMILIES
+    keys = torch.full((1,), INT64_NONE, dtype=torch.int64, device="cuda")
+    try:
+        handle = pr.exchange_export()
+    except Exception:
+        handle = None
+    handles = [handle]
+    if world > 1:
+        handles = [None] * world
+        dist.all_gather_object(handles, handle)
+    ok = all(hd is not None for hd in handles)
+    if ok:
+        try:
+            pr.exchange_connect(handles, rank, world)
+        except Exception:
+            ok = False
+    if not cx.all_agree(ok):
+        return {"unavailable": "CUDA IPC export/connect failed on a rank"}
+    cx.barrier()
+
+    def one(s):
+        pr.refresh_dev(3, s)
+        pr.eval_moves_xchg_dev(ALL_FAMILIES, s)
+        pr.collect_keys_xchg_dev(keys.data_ptr(), s)
+
+    def two(s):
+        one(s)
+        one(s)
+
+    two(cx.stream)
+    torch.cuda.synchronize()
+    replay, graphed = capture(torch, two)
+    ms = cx.timed_all(replay, max(reps // 2, 5)) / 2
+    return {"ms_per_pass": ms, "graph_replayed": graphed, "best_key": int(keys.item()) & (2 ** 64 - 1),
+            "exchange": "system-scope atomicMin into every replica's slot buffer (CUDA IPC over NVLink), no collective call"}
+
+
+# ----------------------------------------------------------------------------------------------- other configs
+
+def secondary_blocks(cx):
+    """BASELINE configs 4, 5 and 3 at the same N (every rank takes part), then the single-GPU extras on rank 0."""
     out = {}
+    out["matrix_10001_rows_sharded"] = block_matrix_rows(cx)
+    out["solve_5000_stops_50_vehicles"] = block_solve(cx)
+    out["eta_1M_pairs_500_trees"] = block_eta(cx)
+    if cx.world == 1:
+        out["batch_64x1000"] = block_batch(cx)
+        out["requests"] = block_requests(cx)
+    return out
 
-    def timed(fn, reps=10):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        for _ in range(reps):
-            fn()
-        b.record()
-        torch.cuda.synchronize()
-        return a.elapsed_time(b) / reps
 
-    # config 4, matrix only: 10,001 nodes device-resident
+def hbm_peak():
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    return float(json.load(open(peaks_path))["hbm_gbs"]) if os.path.exists(peaks_path) else 6650.0
+
+
+def block_matrix_rows(cx):
+    """C4: rank r builds rows [n*r/N, n*(r+1)/N) of the 10,001 x 10,001 {dist,time} matrix into its own HBM; nothing is
+    exchanged.  The sum of all distances is partition independent (a checksum of checksums)."""
+    torch, eng, rank, world, s = cx.torch, cx.eng, cx.rank, cx.world, cx.stream
     n = 10001
-    lat, lon, _, _ = synth_coords(4567, n - 1, 100)
+    lat, lon, _, _ = synth_coords(SEED_10K, n - 1, 100)
+    r0, r1 = n * rank // world, n * (rank + 1) // world
     lat_d, lon_d = torch.tensor(lat, device="cuda"), torch.tensor(lon, device="cuda")
     xyz = torch.empty((3, n), dtype=torch.float64, device="cuda")
     pitch = eng.matrix_pitch(n)
-    cells = torch.empty((n, pitch, 2), dtype=torch.int32, device="cuda")
-    eng.unit_vectors_dev(lat_d.data_ptr(), lon_d.data_ptr(), n, 1, xyz.data_ptr(), stream)
-    ms = timed(lambda: eng.matrix_cells_dev(xyz.data_ptr(), n, 1, cells.data_ptr(), dist_scale=DIST_SCALE,
-                                            time_scale=TS_CAR, stream=stream))
-    out["matrix_10001_nodes"] = {"ms": ms, "cells_per_s": n * n / ms * 1e3, "GBs": n * n * 8 / ms / 1e6}
+    cells = torch.empty((r1 - r0, pitch, 2), dtype=torch.int32, device="cuda")
+
+    def step():
+        eng.unit_vectors_dev(lat_d.data_ptr(), lon_d.data_ptr(), n, 1, xyz.data_ptr(), s)
+        eng.matrix_cells_dev(xyz.data_ptr(), n, 1, cells.data_ptr(), rows=(r0, r1), dist_scale=DIST_SCALE,
+                             time_scale=TS_CAR, stream=s)
+
+    ms = cx.timed_all(step, 20, warm=5)
+    check = cells[:, :n, 0].sum(dtype=torch.int64)
+    if world > 1:
+        cx.dist.all_reduce(check)
+    res = {"ms": ms, "cells_per_s": n * n / ms * 1e3, "GBs_aggregate": n * n * 8 / ms / 1e6, "n_gpus": world,
+           "roofline": {"bound": "hbm", "achieved": n * n * 8 / world / ms / 1e6, "peak": hbm_peak(), "unit": "GB/s per GPU",
+                        "frac": n * n * 8 / world / ms / 1e6 / hbm_peak()},
+           "sum_of_distances": int(check.item())}
     del cells
-    # host API (rt_matrix_build): 5,001 nodes, dense int32 planes back to pinned host memory
-    n5 = 5001
-    t_d = torch.empty((n5, n5), dtype=torch.int32).pin_memory()
-    t_t = torch.empty((n5, n5), dtype=torch.int32).pin_memory()
-    outb = {"dist": t_d.numpy(), "time": t_t.numpy()}
+    if world > 1 and rank == 0:   # the unsharded build on rank 0 must give the same sum
+        full = torch.empty((n, pitch, 2), dtype=torch.int32, device="cuda")
+        eng.matrix_cells_dev(xyz.data_ptr(), n, 1, full.data_ptr(), dist_scale=DIST_SCALE, time_scale=TS_CAR, stream=s)
+        res["sum_equals_unsharded_build"] = bool(int(full[:, :n, 0].sum(dtype=torch.int64).item()) == res["sum_of_distances"])
+        del full
+    return res
+
+
+def block_solve(cx):
+    """C5: 5,000 stops / 50 vehicles, greedy start -> local optimum with batched iterations (SPEC.md §8.1) over the
+    replicas: shard tables, ONE int64 MIN all-reduce per iteration, the same batch applied everywhere."""
+    torch, eng, rank, world = cx.torch, cx.eng, cx.rank, cx.world
+    from routest_b200.dist import DistributedSearch
     t0 = time.perf_counter()
-    for _ in range(3):
-        eng.matrix_build(lat[:n5], lon[:n5], dist_scale=DIST_SCALE, time_scale=TS_CAR, out=outb)
-    dt = (time.perf_counter() - t0) / 3
-    out["matrix_host_api_5001_nodes"] = {"ms": dt * 1e3, "cells_per_s": n5 * n5 / dt, "d2h_GBs": n5 * n5 * 8 / dt / 1e9}
-    # ETA: 1M pairs, synthetic ensemble of 200 depth-6 trees (complete trees, random splits)
-    rng = np.random.default_rng(3456)
-    trees, depth = 200, 6
-    nodes = bytearray()
-    offs = [0]
-    for _ in range(trees):
-        cnt = 2 ** (depth + 1) - 1
-        for k in range(cnt):
-            if k < 2 ** depth - 1:
-                f = int(rng.integers(0, 12))
-                thr = float(rng.uniform(0, 40) if f == 10 else rng.uniform(20, 40) if f == 11 else rng.uniform(0, 23) if f == 9
-                            else rng.uniform(0, 6) if f == 8 else 0.5)
-                nodes += struct.pack("<fHBB", thr, 2 * k + 1, f, 0)
-            else:
-                nodes += struct.pack("<fHBB", float(rng.normal(0, 0.2)), 0, 0, 1)
-        offs.append(offs[-1] + cnt)
-    blob = b"RTE1" + struct.pack("<IIf", trees, 12, 25.0) + struct.pack(f"<{len(offs)}I", *offs) + bytes(nodes)
-    eng.eta_load_model(blob)
-    m = 1_000_000
-    cols = dict(d=torch.tensor(rng.uniform(0, 45000, m), device="cuda"),
-                w=torch.tensor(rng.integers(0, 4, m).astype(np.uint8), device="cuda"),
-                t=torch.tensor(rng.integers(0, 4, m).astype(np.uint8), device="cuda"),
-                wd=torch.tensor(rng.integers(0, 7, m).astype(np.uint8), device="cuda"),
-                h=torch.tensor(rng.integers(0, 24, m).astype(np.uint8), device="cuda"),
-                a=torch.tensor(rng.uniform(20, 40, m).astype(np.float32), device="cuda"))
-    res = torch.empty(m, dtype=torch.float32, device="cuda")
-    ms = timed(lambda: eng.eta_score_dev(cols["d"].data_ptr(), cols["w"].data_ptr(), cols["t"].data_ptr(),
-                                         cols["wd"].data_ptr(), cols["h"].data_ptr(), cols["a"].data_ptr(), m,
-                                         res.data_ptr(), stream))
-    out["eta_1M_pairs_200_trees_depth6"] = {"ms": ms, "pairs_per_s": m / ms * 1e3}
-    # config 5: full solve of 5,000 stops / 50 vehicles, greedy start -> local optimum, batched iterations (SPEC §8.1)
-    n = 5001
-    lat, lon, demand, cap = synth_coords(5678, n - 1, 50)
-    pr = eng.problem(n, 1)
+    pr, w = build_problem(eng, SEED_5K, 5000, 50)
+    t_build = time.perf_counter() - t0
+    cost0 = int(pr.get_state(0)["cost"])
+    search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True)
+    cx.barrier()
+    t0 = time.perf_counter()
+    moves, cost = search.run()
+    torch.cuda.synchronize()
+    dt = cx.max_over_ranks(time.perf_counter() - t0)
+    routes = pr.get_routes()[0]
+    sig = zlib.crc32(json.dumps(routes).encode())
+    agree = True
+    if world > 1:
+        t = torch.tensor([int(moves[0]), int(cost[0]), sig % (2 ** 31)], device="cuda")
+        lo, hi = t.clone(), t.clone()
+        cx.dist.all_reduce(lo, op=cx.dist.ReduceOp.MIN)
+        cx.dist.all_reduce(hi, op=cx.dist.ReduceOp.MAX)
+        agree = bool((lo == hi).all().item())
+    pr.close()
+    res = {"local_search_ms": dt * 1e3, "moves": int(moves[0]), "routes": len(routes), "cost_greedy": cost0,
+           "cost_local_optimum": int(cost[0]), "n_gpus": world, "ranks_agree": agree, "routes_crc32": sig,
+           "graph_replayed": search._graph is not None, "setup_incl_greedy_ms": t_build * 1e3,
+           "driver": "DistributedSearch(batched=True): eval_table_dev -> NCCL MIN all_reduce of R^2+R keys -> apply_batch_dev"}
+    if rank == 0:   # the single-GPU driver on the same instance: same moves, cost and routes
+        pr1, _ = build_problem(eng, SEED_5K, 5000, 50)
+        t0 = time.perf_counter()
+        m1, c1, _ = pr1.local_search(batched=True)
+        res["single_gpu_driver_ms"] = (time.perf_counter() - t0) * 1e3
+        res["equals_single_gpu_driver"] = bool(int(m1[0]) == int(moves[0]) and int(c1[0]) == int(cost[0]) and
+                                               pr1.get_routes()[0] == routes)
+        pr1.close()
+    if world > 1:
+        cx.barrier()
+    return res
+
+
+def block_eta(cx):
+    """C3: 1M stop pairs x 500 depth-6 trees; contiguous pair ranges per rank, model replicated, no collective."""
+    torch, eng, rank, world, s = cx.torch, cx.eng, cx.rank, cx.world, cx.stream
+    from routest_b200.dist import eta_score_shard_dev
+    trees, depth, m = 500, 6, 1_000_000
+    eng.eta_load_model(eta_model_blob(trees, depth))
+    cols = [torch.tensor(c, device="cuda") for c in eta_columns(m)]
+    res_t = torch.zeros(m, dtype=torch.float32, device="cuda")
+    ptrs = [c.data_ptr() for c in cols]
+    ms = cx.timed_all(lambda: eta_score_shard_dev(eng, ptrs, m, res_t.data_ptr(), rank, world, s), 10)
+    lo, hi = eta_score_shard_dev(eng, ptrs, m, res_t.data_ptr(), rank, world, s)
+    part = res_t[lo:hi].double().sum()
+    if world > 1:
+        cx.dist.all_reduce(part)
+    # shared-memory roofline: three conflict-free 4-byte LDS per node visit (value, left|feature|flags, feature row),
+    # one visit per tree level => wavefronts = pairs/32 * trees * depth * 3 against one wavefront per SM per clock
+    wave = (m / world) / 32 * trees * depth * 3
+    lds_peak = 148 * 1.965e9
+    out = {"ms": ms, "pairs_per_s": m / ms * 1e3, "n_gpus": world, "trees": trees, "depth": depth,
+           "sum_of_minutes": float(part.item()),
+           "roofline": {"bound": "shared-memory wavefronts", "achieved": wave / (ms / 1e3) / 1e9, "peak": lds_peak / 1e9,
+                        "unit": "G wavefronts/s per GPU", "frac": wave / (ms / 1e3) / lds_peak,
+                        "peak_source": "148 SMs x 1 LDS wavefront per clock x 1,965 MHz (nominal)",
+                        "hbm_floor_GBs": 16 * m / world / ms / 1e6}}
+    if rank == 0 and world > 1:
+        full = torch.zeros(m, dtype=torch.float32, device="cuda")
+        eng.eta_score_dev(*ptrs, m, full.data_ptr(), s)
+        out["shard_equals_full_on_rank0"] = bool(torch.equal(full[lo:hi], res_t[lo:hi]))
+    return out
+
+
+def block_batch(cx):
+    """C2 (round 1's headline, kept comparable): 64 independent 1,000-stop instances per step on one GPU."""
+    torch, eng, s = cx.torch, cx.eng, cx.stream
+    from routest_b200 import ALL_FAMILIES
+    B, stops = 64, 1000
+    n = stops + 1
+    seeds = [SEED_BATCH + b for b in range(B)]
+    raw = [synth_coords(sd, stops, 10) for sd in seeds]
+    lat, lon = np.stack([r[0] for r in raw]), np.stack([r[1] for r in raw])
+    demand = np.stack([r[2] for r in raw])
+    cap = np.array([r[3] for r in raw], np.int32)
+    pr = eng.problem(n, B)
     pr.set_coords(lat, lon)
     pr.build_matrix(DIST_SCALE, TS_CAR)
-    _, t = pr.get_matrix(0)
-    st = np.zeros((1, n, 4), np.int32)
-    st[0, :, :3] = synth_windows(5678, t[0, 1:], t[1:, 0])
-    st[0, :, 3] = demand
-    pr.set_stops(st, [cap])
-    t0 = time.perf_counter()
-    trips, status = pr.greedy(demand[None, :].astype(float), [float(cap)], use_tw=True)
-    t1 = time.perf_counter()
+    st = np.zeros((B, n, 4), np.int32)
+    for b in range(B):
+        _, t = pr.get_matrix(b)
+        st[b, :, :3] = synth_windows(seeds[b], t[0, 1:], t[1:, 0])
+        st[b, :, 3] = demand[b]
+    pr.set_stops(st, cap)
+    trips, status = pr.greedy(demand.astype(np.float64), cap.astype(np.float64), use_tw=True)
+    assert not status.any()
     pr.set_routes(trips)
-    cost0 = int(pr.get_state(0)["cost"])
-    t2 = time.perf_counter()
-    moves, cost, _ = pr.local_search(batched=True)
-    t3 = time.perf_counter()
-    out["solve_5000_stops_50_vehicles"] = {"greedy_ms": (t1 - t0) * 1e3, "local_search_ms": (t3 - t2) * 1e3,
-                                           "moves": int(moves[0]), "routes": len(trips[0]), "cost_greedy": cost0,
-                                           "cost_local_optimum": int(cost[0]), "driver": "batched iterations (SPEC.md 8.1)"}
+    cand = [count_candidates(t, n) for t in trips]
+    evals = sum(sum(c.values()) for c in cand)
+    cells = B * n * n
+    keys = torch.empty(B, dtype=torch.int64, device="cuda")
+    step = lambda: pr.plan_dev(keys.data_ptr(), dist_scale=DIST_SCALE, time_scale=TS_CAR, families=ALL_FAMILIES, stream=s)
+    ms = cx.timed(step, 20)
+    ms_matrix = cx.timed(lambda: pr.refresh_dev(1, s), 20)
+    ms_eval = cx.timed(lambda: pr.eval_moves_dev(keys.data_ptr(), ALL_FAMILIES, (0, 1), s), 20)
+    step()
+    got = (keys.cpu().numpy() ^ np.int64(-2 ** 63)).view(np.uint64)
+    ok = None
+    if not cx.args.no_cpu:   # the first two instances against the oracle
+        ok = True
+        for b in range(2):
+            it = oracle_instance(seeds[b], stops, 10)
+            ok = ok and it["trips"] == trips[b] and oracle_pass(it, host_threads())[2] == int(got[b])
     pr.close()
+    return {"ms_per_step": ms, "cells_per_s": cells / ms * 1e3, "move_evals_per_s": evals / ms * 1e3,
+            "keys_equal_oracle": ok, "matrix_kernel": {"ms": ms_matrix, "GBs": cells * 8 / ms_matrix / 1e6,
+                                                       "frac_of_hbm_peak": cells * 8 / ms_matrix / 1e6 / hbm_peak()},
+            "eval_moves": {"ms": ms_eval, "move_evals_per_s": evals / ms_eval * 1e3}}
+
+
+def block_requests(cx):
+    """The size the reference actually serves (<= 10 stops, page.jsx:19) and BASELINE config 1: one request through
+    routest_b200.solver.optimize_route (matrix + greedy + offline directions + GeoJSON), median of 20."""
+    from routest_b200 import solver as S
+    out = {}
+    for stops, veh in ((10, 2), (100, 10), (1000, 10)):
+        lat, lon, demand, cap = synth_coords(1234, stops, veh)
+        req = {"source_point": {"lat": float(lat[0]), "lon": float(lon[0])},
+               "destination_points": [{"lat": float(lat[i]), "lon": float(lon[i]), "payload": int(demand[i])}
+                                      for i in range(1, stops + 1)],
+               "driver_details": {"vehicle_type": "car", "vehicle_capacity": int(cap)}}
+        S.optimize_route(json.loads(json.dumps(req)), engine=cx.eng)
+        ts = []
+        for _ in range(20):
+            r = json.loads(json.dumps(req))
+            t0 = time.perf_counter()
+            res = S.optimize_route(r, engine=cx.eng)
+            ts.append(time.perf_counter() - t0)
+        assert "error" not in res
+        out[f"{stops}_stops"] = {"ms_median": 1e3 * float(np.median(ts)), "trips": res["properties"]["summary"]["trips"]}
+    out["reference_python_ms"] = {"100_stops": 1.2, "1000_stops": 26.0, "5000_stops": 600.0,
+                                  "provenance": "Flaskr/utils.py:_multi_stop imported by file path with ORS stubbed, one "
+                                                "Python thread, measured in the build container (8 vCPU) by "
+                                                "tests/perf/reference_greedy_time.py; /root/reference is not on the GPU box"}
     return out
 
 
@@ -544,10 +850,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
-    ap.add_argument("--batch", type=int, default=64)
-    ap.add_argument("--stops", type=int, default=1000)
-    ap.add_argument("--vehicles", type=int, default=10)
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--stops", type=int, default=10000)
+    ap.add_argument("--vehicles", type=int, default=100)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg and the oracle key check")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary figures (other BASELINE configs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

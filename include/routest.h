@@ -198,7 +198,8 @@ int rt_problem_local_search_batched(rt_problem *p, int families, int max_iterati
 /* One pass of the hot path from host inputs to best moves, for every instance: uploads coordinates, stop data
  * and the current solution, builds the matrices (utils.py:94-109) — in route order, G[p][q] = M[node p][node q],
  * which is the layout the move kernels stream — derives the route state and scores the full neighbourhood; only
- * the best keys [batch] come back (the matrices stay on the GPU).  node is the position array
+ * the best keys [batch] come back (the matrices stay on the GPU; with a shard set by rt_problem_set_shard, the best
+ * keys of that shard).  node is the position array
  * of SPEC.md §6, [batch][rt_problem_position_stride()], npos [batch] its used length. */
 int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
                     const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
@@ -216,13 +217,27 @@ int rt_problem_plan_begin(rt_problem *p, const double *lat, const double *lon, c
                           double dist_scale, double time_scale, int families);
 int rt_problem_plan_end(rt_problem *p, uint64_t *best_keys_out);
 
+/* The same pass for a replica of a multi-GPU search (one process per GPU): host inputs in, but every copy and kernel
+ * goes to the CALLER's stream, the replica scores only its own shard (rt_problem_set_shard; default everything), and
+ * the keys stay on the device — best_keys_d is device int64[batch] in signed-order form, ready for the MIN
+ * all-reduce that combines the shards (NCCL through torch.distributed, or the peer exchange below).  Nothing is
+ * synchronised: the host buffers must stay unchanged until the stream has passed the copies (pinned memory makes them
+ * asynchronous).  Coordinates and the position arrays are validated on the host before anything is enqueued.
+ * No reference counterpart (the reference handles one request on one thread: routes.py:89-127). */
+int rt_problem_plan_upload_dev(rt_problem *p, const double *lat, const double *lon, const int32_t *stops,
+                               const int32_t *cap, const int64_t *max_dist, const int32_t *node, const int32_t *npos,
+                               double dist_scale, double time_scale, int families, void *best_keys_d, void *stream);
+
 /* The same pass for inputs that are already on the device (coordinates, stops and routes installed earlier), on
  * the caller's stream, without synchronisation: unit vectors -> route-order matrix -> route state -> best keys
- * (device int64[batch] in signed-order form, see rt_problem_eval_moves_dev). */
+ * (device int64[batch] in signed-order form, see rt_problem_eval_moves_dev).  A replica whose shard was set with
+ * rt_problem_set_shard rebuilds only its rows of the matrix and scores only its shard: the MIN over the replicas'
+ * keys is the best move. */
 int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int families, void *best_keys_d,
                         void *stream);
 /* Its pieces, stream-ordered: the node-order matrix of rt_problem_build_matrix; the refresh (what: bit 0 = rebuild
- * the route-order matrix from the current routes, bit 1 = re-derive the route state tables from it). */
+ * the route-order matrix from the current routes, bit 1 = re-derive the route state tables; either bit works on its
+ * own after a route change, and with both set the tables run on a side stream underneath the matrix kernel). */
 int rt_problem_build_matrix_dev(rt_problem *p, double dist_scale, double time_scale, void *stream);
 int rt_problem_refresh_dev(rt_problem *p, int what, void *stream);
 
@@ -253,11 +268,14 @@ int rt_problem_eval_table_dev(rt_problem *p, int families, int shard_index, int 
 int rt_problem_apply_batch_dev(rt_problem *p, const void *table_d, void *stream);
 /* The same exchange without a collective library: every replica (one process per GPU) exports a small slot buffer
  * through CUDA IPC, maps its peers', and from then on the evaluation step MIN-reduces its best keys straight into
- * every peer's buffer with system-scope atomics over NVLink, and the apply step waits (bounded: ~2 s, then
- * done = 3) until all replicas have published before applying the winner.  8 bytes per instance, no NCCL call in the
+ * every peer's buffer with system-scope atomics over NVLink, and the apply step waits until all replicas have
+ * published before applying the winner.  The wait is bounded (ROUTEST_XCHG_TIMEOUT_MS, default 10 s); a replica that
+ * gives up raises an abort word in every replica's buffer, so ALL replicas stop (done = 3 in
+ * rt_problem_search_status) instead of drifting apart.  8 bytes per instance, no NCCL call in the
  * loop.  Order of calls: rt_problem_exchange_export on every rank -> all-gather the handles (any transport) ->
  * rt_problem_exchange_connect -> per iteration rt_problem_eval_moves_xchg_dev, rt_problem_apply_moves_xchg_dev.
- * The replica's shard (rt_problem_set_shard) must be (rank, world) or unset. */
+ * The replica's shard (rt_problem_set_shard) must be (rank, world) or unset.  rt_problem_exchange_connect may be called
+ * again (it closes the earlier mappings, re-arms the slots and clears the abort word). */
 int rt_problem_exchange_handle_bytes(void);
 int rt_problem_exchange_export(rt_problem *p, void *handle_out);
 int rt_problem_exchange_connect(rt_problem *p, const void *handles, int rank, int world);
@@ -292,6 +310,13 @@ int rt_eta_score_dev(rt_engine *e, const double *distance_m_d, const uint8_t *we
 /* Self-test: counts floats with bit pattern in [lo_bits, hi_bits) for which the matrix kernel's straight-line
  * square root differs from IEEE sqrtf (must be 0; SPEC.md §2 relies on it).  No reference counterpart. */
 int rt_selftest_fast_sqrt(rt_engine *e, uint32_t lo_bits, uint32_t hi_bits, uint64_t *mismatches);
+
+/* On-box instruction-rate peak, the roofline denominator of the integer move-evaluation kernels (SURVEY.md §8(d) asks
+ * for ALU peaks measured on the box): a kernel of independent register chains, timed with CUDA events on the engine's
+ * stream (the call synchronises).  mode 0 = ALU pipe only (LOP3/IMNMX), 1 = FMA pipe only (IMAD), 2 = both interleaved
+ * (the issue limit).  iters = loop trips per thread (32 instructions each); the result is warp instructions per second
+ * over the whole GPU.  No reference counterpart. */
+int rt_selftest_pipe_peak(rt_engine *e, int mode, int iters, double *warp_inst_per_s, double *elapsed_ms);
 
 #ifdef __cplusplus
 }

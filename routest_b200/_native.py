@@ -70,6 +70,8 @@ SIGNATURES = {
     "rt_problem_plan_begin": (C.c_int, [c_problem_p, c_f64_p, c_f64_p, c_i32_p, c_i32_p, c_i64_p, c_i32_p, c_i32_p,
                                         C.c_double, C.c_double, C.c_int]),
     "rt_problem_plan_end": (C.c_int, [c_problem_p, c_u64_p]),
+    "rt_problem_plan_upload_dev": (C.c_int, [c_problem_p, c_f64_p, c_f64_p, c_i32_p, c_i32_p, c_i64_p, c_i32_p, c_i32_p,
+                                             C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_problem_build_matrix_dev": (C.c_int, [c_problem_p, C.c_double, C.c_double, C.c_void_p]),
     "rt_problem_refresh_dev": (C.c_int, [c_problem_p, C.c_int, C.c_void_p]),
     "rt_problem_plan_dev": (C.c_int, [c_problem_p, C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p]),
@@ -97,6 +99,7 @@ SIGNATURES = {
     "rt_eta_score_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_int64, C.c_void_p, C.c_void_p]),
     "rt_selftest_fast_sqrt": (C.c_int, [c_engine_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]),
+    "rt_selftest_pipe_peak": (C.c_int, [c_engine_p, C.c_int, C.c_int, c_f64_p, c_f64_p]),
     "rt_unit_vectors_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_matrix_cells_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
                                       C.c_double, C.c_void_p, C.c_void_p]),

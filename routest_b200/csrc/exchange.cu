@@ -4,6 +4,7 @@
 // Every replica owns a small slot buffer in its own HBM that its peers map through CUDA IPC (one process per GPU):
 //   keys  [2][batch]  packed move keys (SPEC.md §7), initialised to "no move"
 //   count [2]         how many replicas have published into keys[slot]
+//   abort [1]         non-zero once ANY replica has given up waiting (written into every replica's buffer)
 // Iteration i uses slot i & 1.
 //   publish (after the evaluation kernels, same stream): every replica MIN-reduces its shard's best key straight
 //           into keys[slot][b] of EVERY replica with system-scope atomics over NVLink, fences, and bumps every
@@ -13,8 +14,13 @@
 //           apply kernel and re-arms the slot.  A slot is reused two iterations later; by then every peer has
 //           passed its own collect of the iteration in between, which it can only do after this replica's publish
 //           of that iteration, which is stream-ordered after this collect — so the re-arm cannot race a publish.
-// The wait is bounded (a peer that died must not hang this GPU): on timeout every instance is marked done = 3.
+// The wait is bounded (a peer that died must not hang this GPU; ROUTEST_XCHG_TIMEOUT_MS, default 10 s of wall time).
+// Giving up is collective: the replica that times out raises the abort word in EVERY replica's buffer, stops
+// publishing keys (it still bumps the counters so that nobody waits for it) and marks its instances done = 3; every
+// other replica sees the word at its next collect and does the same, so no replica goes on applying keys that were
+// computed from routes another one no longer follows.  DistributedSearch.run turns done = 3 into an exception.
 // No reference counterpart (the reference has no solver state to exchange).
+#include <cstdlib>
 #include <vector>
 
 #include "problem.cuh"
@@ -23,40 +29,59 @@ namespace rt {
 
 namespace {
 
-__global__ void xchg_publish_kernel(const unsigned long long *__restrict__ local_best,
-                                    unsigned long long *const *__restrict__ peers, int world, int batch, int slot)
+__device__ __forceinline__ unsigned long long wall_ns()
 {
-    for (int b = threadIdx.x; b < batch; b += blockDim.x) {
-        const unsigned long long k = local_best[b];
-        if (k != kNoMove)
-            for (int r = 0; r < world; ++r) atomicMin_system(peers[r] + static_cast<size_t>(slot) * batch + b, k);
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x < world)
-        atomicAdd_system(peers[threadIdx.x] + 2 * static_cast<size_t>(batch) + slot, 1ull);
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
 }
 
-__global__ void xchg_collect_kernel(unsigned long long *__restrict__ xbuf, int world, int batch, int slot,
+// slot buffer layout: keys[2][batch] | count[2] | abort
+__device__ __forceinline__ size_t count_at(int batch, int slot) { return 2 * static_cast<size_t>(batch) + slot; }
+__device__ __forceinline__ size_t abort_at(int batch) { return 2 * static_cast<size_t>(batch) + 2; }
+
+__global__ void xchg_publish_kernel(const unsigned long long *__restrict__ local_best,
+                                    unsigned long long *const *__restrict__ peers, int rank, int world, int batch,
+                                    int slot)
+{
+    // a replica that has aborted keeps the counters moving but contributes no keys (its routes are frozen)
+    const bool aborted = *reinterpret_cast<volatile unsigned long long *>(peers[rank] + abort_at(batch)) != 0;
+    if (!aborted)
+        for (int b = threadIdx.x; b < batch; b += blockDim.x) {
+            const unsigned long long k = local_best[b];
+            if (k != kNoMove)
+                for (int r = 0; r < world; ++r) atomicMin_system(peers[r] + static_cast<size_t>(slot) * batch + b, k);
+        }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < world) atomicAdd_system(peers[threadIdx.x] + count_at(batch, slot), 1ull);
+}
+
+__global__ void xchg_collect_kernel(unsigned long long *__restrict__ xbuf,
+                                    unsigned long long *const *__restrict__ peers, int world, int batch, int slot,
                                     unsigned long long *__restrict__ best_out, int *__restrict__ done,
-                                    long long timeout_cycles)
+                                    unsigned long long timeout_ns)
 {
     __shared__ int s_ok;
-    volatile unsigned long long *count = xbuf + 2 * static_cast<size_t>(batch) + slot;
+    volatile unsigned long long *count = xbuf + count_at(batch, slot);
+    volatile unsigned long long *abort_word = xbuf + abort_at(batch);
     if (threadIdx.x == 0) {
-        const long long t0 = clock64();
+        const unsigned long long t0 = wall_ns();
         int ok = 1;
         while (*count < static_cast<unsigned long long>(world)) {
             __nanosleep(200);
-            if (clock64() - t0 > timeout_cycles) {
+            if (*abort_word != 0 || wall_ns() - t0 > timeout_ns) {
                 ok = 0;
                 break;
             }
         }
+        if (*abort_word != 0) ok = 0;
         s_ok = ok;
     }
     __syncthreads();
     __threadfence_system();
+    if (!s_ok && threadIdx.x < world)  // collective abort: every replica learns of it at its next collect at the latest
+        atomicExch_system(peers[threadIdx.x] + abort_at(batch), 1ull);
     const unsigned long long none = 0xFFFFFFFFFFFFFFFFull;
     for (int b = threadIdx.x; b < batch; b += blockDim.x) {
         unsigned long long *cell = xbuf + static_cast<size_t>(slot) * batch + b;
@@ -73,7 +98,15 @@ __global__ void xchg_init_kernel(unsigned long long *xbuf, int batch)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < 2 * batch) xbuf[i] = kNoMove;
-    else if (i < 2 * batch + 2) xbuf[i] = 0;
+    else if (i < 2 * batch + 3) xbuf[i] = 0;
+}
+
+unsigned long long xchg_timeout_ns()
+{
+    long long ms = 10000;
+    if (const char *ev = getenv("ROUTEST_XCHG_TIMEOUT_MS")) ms = atoll(ev);
+    if (ms < 1) ms = 1;
+    return static_cast<unsigned long long>(ms) * 1000000ull;
 }
 
 }  // namespace
@@ -94,7 +127,7 @@ int rt_problem_exchange_export(rt_problem *p, void *handle_out)
     std::lock_guard<std::mutex> lk(e->mu);
     DeviceGuard dg(e->device);
     if (!p->xbuf) {
-        const size_t cnt = 2 * static_cast<size_t>(p->batch) + 2;
+        const size_t cnt = 2 * static_cast<size_t>(p->batch) + 3;
         void *raw = nullptr;
         RT_CUDA(e, cudaMalloc(&raw, cnt * 8));  // plain cudaMalloc: IPC handles cannot refer to pool memory
         p->xbuf = static_cast<unsigned long long *>(raw);
@@ -114,9 +147,21 @@ int rt_problem_exchange_connect(rt_problem *p, const void *handles, int rank, in
     rt_engine *e = p->e;
     if (!handles || world < 1 || world > 64 || rank < 0 || rank >= world)
         return fail(e, RT_ERR_INVALID_ARG, "rt_problem_exchange_connect: bad argument");
-    if (!p->xbuf) return fail(e, RT_ERR_STATE, "rt_problem_exchange_connect: export this replica's handle first");
     std::lock_guard<std::mutex> lk(e->mu);
     DeviceGuard dg(e->device);
+    if (!p->xbuf) return fail(e, RT_ERR_STATE, "rt_problem_exchange_connect: export this replica's handle first");
+    // a second connect (a search constructed again, a reconnect after an abort) starts from a clean slate: earlier
+    // mappings are closed, the slots re-armed and the abort word cleared
+    RT_CUDA(e, cudaDeviceSynchronize());
+    for (int i = 0; i < p->n_xpeer_mapped; ++i) cudaIpcCloseMemHandle(p->xpeer_mapped[i]);
+    p->n_xpeer_mapped = 0;
+    p->xworld = 0;
+    {
+        const size_t cnt = 2 * static_cast<size_t>(p->batch) + 3;
+        xchg_init_kernel<<<static_cast<unsigned>((cnt + 255) / 256), 256, 0, e->stream>>>(p->xbuf, p->batch);
+        RT_CUDA(e, cudaGetLastError());
+        RT_CUDA(e, cudaStreamSynchronize(e->stream));
+    }
     std::vector<unsigned long long *> ptrs(world);
     for (int r = 0; r < world; ++r) {
         if (r == rank) {
@@ -128,6 +173,7 @@ int rt_problem_exchange_connect(rt_problem *p, const void *handles, int rank, in
         void *mapped = nullptr;
         RT_CUDA(e, cudaIpcOpenMemHandle(&mapped, h, cudaIpcMemLazyEnablePeerAccess));
         ptrs[r] = static_cast<unsigned long long *>(mapped);
+        if (p->n_xpeer_mapped >= 64) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_exchange_connect: too many peers");
         p->xpeer_mapped[p->n_xpeer_mapped++] = mapped;
     }
     if (!p->xpeers) {
@@ -153,7 +199,7 @@ int rt_problem_eval_moves_xchg_dev(rt_problem *p, int families, void *stream)
     DeviceGuard dg(e->device);
     cudaStream_t st = pick_stream(e, stream);
     RT_TRY(eval_moves_launch(p, families, p->xrank, p->xworld, p->best, false, st));
-    xchg_publish_kernel<<<1, 256, 0, st>>>(p->best, p->xpeers, p->xworld, p->batch, p->xiter & 1);
+    xchg_publish_kernel<<<1, 256, 0, st>>>(p->best, p->xpeers, p->xrank, p->xworld, p->batch, p->xiter & 1);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }
@@ -166,8 +212,8 @@ int rt_problem_collect_keys_xchg_dev(rt_problem *p, void *keys_d, void *stream)
     if (!p->has_routes || p->xworld < 1) return fail(e, RT_ERR_STATE, "rt_problem_collect_keys_xchg_dev: routes and exchange first");
     DeviceGuard dg(e->device);
     cudaStream_t st = pick_stream(e, stream);
-    xchg_collect_kernel<<<1, 256, 0, st>>>(p->xbuf, p->xworld, p->batch, p->xiter & 1,
-                                           static_cast<unsigned long long *>(keys_d), p->done, 4000000000LL);
+    xchg_collect_kernel<<<1, 256, 0, st>>>(p->xbuf, p->xpeers, p->xworld, p->batch, p->xiter & 1,
+                                           static_cast<unsigned long long *>(keys_d), p->done, xchg_timeout_ns());
     RT_CUDA(e, cudaGetLastError());
     ++p->xiter;
     return RT_OK;
@@ -180,8 +226,9 @@ int rt_problem_apply_moves_xchg_dev(rt_problem *p, int improving_only, void *str
     if (!p->has_routes || p->xworld < 1) return fail(e, RT_ERR_STATE, "rt_problem_apply_moves_xchg_dev: routes and exchange first");
     DeviceGuard dg(e->device);
     cudaStream_t st = pick_stream(e, stream);
-    const long long timeout_cycles = 4000000000LL;  // ~2 s at 1.9 GHz: a dead peer must not hang this GPU
-    xchg_collect_kernel<<<1, 256, 0, st>>>(p->xbuf, p->xworld, p->batch, p->xiter & 1, p->best, p->done, timeout_cycles);
+    // bounded wait: a dead peer must not hang this GPU
+    xchg_collect_kernel<<<1, 256, 0, st>>>(p->xbuf, p->xpeers, p->xworld, p->batch, p->xiter & 1, p->best, p->done,
+                                           xchg_timeout_ns());
     RT_CUDA(e, cudaGetLastError());
     ++p->xiter;
     return apply_moves_launch(p, p->best, false, improving_only != 0, st);

@@ -529,8 +529,11 @@ int rt_problem_refresh_dev(rt_problem *p, int what, void *stream)
     if (!(what & 3)) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_refresh_dev: what must have bit 0 and/or bit 1 set");
     DeviceGuard dg(e->device);
     cudaStream_t st = pick_stream(e, stream);
+    // both: the state tables run on the side stream underneath the matrix kernel; the tables alone re-derive the
+    // position-ordered unit vectors themselves, so bit 1 never depends on an earlier bit-0 refresh
+    if ((what & 3) == 3) return state_refresh(p, st);
     if (what & 1) RT_TRY(position_matrix_refresh(p, st));
-    if (what & 2) RT_TRY(state_tables_refresh(p, st));
+    if (what & 2) RT_TRY(state_tables_refresh(p, st, /*with_vectors=*/true));
     return RT_OK;
 }
 
@@ -552,7 +555,9 @@ int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int
     p->symmetric = true;  // whatever matrix was installed before, this pass runs on SPEC §2 cells
     p->supplied = 0;
     RT_TRY(state_refresh(p, st, nullptr, /*vectors_ready=*/true));
-    return eval_moves_launch(p, families, 0, 1, static_cast<unsigned long long *>(best_keys_d), true, st);
+    // a replica of a multi-GPU search scores the shard set by rt_problem_set_shard (default: everything)
+    return eval_moves_launch(p, families, p->shard_index, p->shard_count, static_cast<unsigned long long *>(best_keys_d),
+                             true, st);
 }
 
 // Enqueues one pass (inputs -> best keys in the problem's pinned staging buffer).  Synchronous form: what the matrix
@@ -561,8 +566,11 @@ int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int
 // another problem of the same engine — still has running on the compute stream.
 static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
                         const int64_t *max_dist, const int32_t *node, const int32_t *npos, double dist_scale,
-                        double time_scale, int families, bool async, const char *who)
+                        double time_scale, int families, bool async, const char *who,
+                        unsigned long long *keys_dev = nullptr, cudaStream_t caller = nullptr)
 {
+    // keys_dev != nullptr: the caller's-stream form (rt_problem_plan_upload_dev) — every copy and kernel goes to
+    // `caller`, the keys stay on the device in signed-order form and nothing is staged for the host.
     rt_engine *e = p->e;
     if (!lat || !lon || !stops || !cap || !max_dist || !node || !npos || !(families & 7))
         return fail(e, RT_ERR_INVALID_ARG, "%s: bad argument", who);
@@ -577,7 +585,7 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
         for (cudaEvent_t *ev : {&p->ev_in[0], &p->ev_in[1], &p->ev_done})
             RT_CUDA(e, cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
     }
-    cudaStream_t st = e->stream, cs = e->copy_stream;
+    cudaStream_t st = keys_dev ? caller : e->stream, cs = keys_dev ? caller : e->copy_stream;
     static const bool dbg = getenv("ROUTEST_DEBUG_PLAN") != nullptr;  // prints where the call's host time goes
     auto now = []() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; };
     p->plan_t[0] = dbg ? now() : 0;
@@ -603,7 +611,7 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
     // are range-checked by that kernel (off the host's critical path); stop records are taken as they are
     // (rt_problem_set_stops is the validating entry point) — out-of-range values cannot fault a kernel.
     p->plan_flag_seq = ++p->plan_seq;  // the flag is written with this call's number: no reset launch needed
-    RT_TRY(position_unit_vectors_launch(p, st, p->coord_flag, p->plan_flag_seq));
+    RT_TRY(position_unit_vectors_launch(p, st, keys_dev ? nullptr : p->coord_flag, p->plan_flag_seq));
     for (size_t b = 0; b < B; ++b) {
         if (!positions_well_formed(node + b * PS, npos[b], static_cast<int>(N))) {
             p->has_routes = false;  // the copy above has already replaced the previous routes
@@ -629,8 +637,10 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     RT_TRY(ensure_position_matrix(p));
-    RT_TRY(state_refresh(p, st, p->ev_in[1], /*vectors_ready=*/true));
-    RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, st));
+    RT_TRY(state_refresh(p, st, keys_dev ? nullptr : p->ev_in[1], /*vectors_ready=*/true));
+    // a replica of a multi-GPU search scores its own shard (rt_problem_set_shard); the default is everything
+    if (keys_dev) return eval_moves_launch(p, families, p->shard_index, p->shard_count, keys_dev, true, st);
+    RT_TRY(eval_moves_launch(p, families, p->shard_index, p->shard_count, p->best, false, st));
     RT_TRY(stage(p, (B + 1) * 8));
     RT_CUDA(e, cudaMemcpyAsync(p->host_stage, p->best, (B + 1) * 8, cudaMemcpyDeviceToHost, st));  // keys + flag, one copy
     RT_CUDA(e, cudaEventRecord(p->ev_done, st));
@@ -696,6 +706,25 @@ int rt_problem_plan_end(rt_problem *p, uint64_t *best_keys_out)
     if (!p) return RT_ERR_INVALID_ARG;
     DeviceGuard dg(p->e->device);  // no engine lock: the wait must not keep other requests from being enqueued
     return plan_collect(p, best_keys_out, "rt_problem_plan_end");
+}
+
+int rt_problem_plan_upload_dev(rt_problem *p, const double *lat, const double *lon, const int32_t *stops,
+                               const int32_t *cap, const int64_t *max_dist, const int32_t *node, const int32_t *npos,
+                               double dist_scale, double time_scale, int families, void *best_keys_d, void *stream)
+{
+    if (!p) return RT_ERR_INVALID_ARG;
+    rt_engine *e = p->e;
+    if (!best_keys_d) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_plan_upload_dev: bad argument");
+    if (lat && lon) {  // checked on the host here: there is no later host step that could report a device-side flag
+        const long long total = static_cast<long long>(p->n) * p->batch;
+        for (long long i = 0; i < total; ++i)
+            if (!(lat[i] >= -90.0 && lat[i] <= 90.0) || !(lon[i] >= -180.0 && lon[i] <= 180.0))
+                return fail(e, RT_ERR_INVALID_ARG, "coordinate %lld out of range or not finite", i);
+    }
+    DeviceGuard dg(e->device);
+    return plan_enqueue(p, lat, lon, stops, cap, max_dist, node, npos, dist_scale, time_scale, families, false,
+                        "rt_problem_plan_upload_dev", static_cast<unsigned long long *>(best_keys_d),
+                        pick_stream(e, stream));
 }
 
 int rt_problem_get_position_matrix(rt_problem *p, int instance, int32_t *dist, int32_t *tim)

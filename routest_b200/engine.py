@@ -142,6 +142,13 @@ class Engine:
         self._check(self._lib.rt_selftest_fast_sqrt(self._h, lo_bits, hi_bits, C.byref(bad)))
         return int(bad.value)
 
+    def pipe_peak(self, mode: int = 0, iters: int = 20000):
+        """Measured instruction-rate peak in warp instructions per second (rt_selftest_pipe_peak): mode 0 = ALU pipe,
+        1 = FMA pipe, 2 = both interleaved (issue limit).  Returns (rate, elapsed_ms)."""
+        rate, ms = C.c_double(0), C.c_double(0)
+        self._check(self._lib.rt_selftest_pipe_peak(self._h, int(mode), int(iters), C.byref(rate), C.byref(ms)))
+        return float(rate.value), float(ms.value)
+
     def unit_vectors_dev(self, lat_ptr: int, lon_ptr: int, n: int, batch: int, xyz_ptr: int, stream: int = 0):
         self._check(self._lib.rt_unit_vectors_dev(self._h, lat_ptr, lon_ptr, int(n), int(batch), xyz_ptr, stream or None))
 
@@ -497,6 +504,30 @@ class Problem:
             check(fe(handle, out_p))
             return out
         return begin, end
+
+    def plan_upload_call(self, lat, lon, stops, cap, max_dist, node, npos, keys_ptr: int, *,
+                         dist_scale=DEFAULT_DIST_SCALE, time_scale=None, families: int = ALL_FAMILIES, stream: int = 0):
+        """rt_problem_plan_upload_dev as a reusable call (same buffer rules as plan_call): host inputs go up on
+        `stream`, this replica's shard is scored, the signed-order keys stay on the device at keys_ptr (int64[batch]);
+        nothing is synchronised.  What a rank of a multi-GPU search does per request before the MIN all-reduce."""
+        if time_scale is None:
+            time_scale = time_scale_for_profile("driving-car")
+        spec = ((lat, np.float64, (self.batch, self.n)), (lon, np.float64, (self.batch, self.n)),
+                (stops, np.int32, (self.batch, self.n, 4)), (cap, np.int32, (self.batch,)),
+                (max_dist, np.int64, (self.batch,)), (node, np.int32, (self.batch, self.pstride)),
+                (npos, np.int32, (self.batch,)))
+        for a, dt, shape in spec:
+            if not isinstance(a, np.ndarray) or a.dtype != dt or a.shape != shape or not a.flags.c_contiguous:
+                raise ValueError(f"plan_upload_call needs C-contiguous {np.dtype(dt).name} arrays of shape {shape}")
+        fn, check = self._lib.rt_problem_plan_upload_dev, self._check
+        args = (self._p, _f64(lat), _f64(lon), _i32(stops), _i32(cap), _i64(max_dist), _i32(node), _i32(npos),
+                C.c_double(dist_scale), C.c_double(time_scale), C.c_int(families), C.c_void_p(keys_ptr),
+                C.c_void_p(stream or None))
+        keep = (lat, lon, stops, cap, max_dist, node, npos)
+
+        def call(_keep=keep):
+            check(fn(*args))
+        return call
 
     def plan_dev(self, keys_ptr: int, *, dist_scale=DEFAULT_DIST_SCALE, time_scale=None, families: int = ALL_FAMILIES,
                  stream: int = 0):

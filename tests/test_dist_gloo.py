@@ -199,3 +199,50 @@ def test_batched_replicated_search_under_gloo_matches_oracle():
     final, keys, sizes, cost = O.local_search_batched(inst, node)
     assert sizes.max() > 1
     assert out[0] == out[1] == (len(keys), cost, final.tolist())
+
+
+class OracleEtaEngine:
+    """Stand-in for Engine.eta_score on the CPU: the scalar evaluator."""
+
+    def __init__(self, blob):
+        self.blob = blob
+
+    def eta_score(self, distance_m, weather, traffic, weekday, hour, age):
+        from oracle import oracle as O
+        return O.eta_eval(self.blob, O.eta_features(distance_m, weather, traffic, weekday, hour, age))
+
+
+def _worker_eta(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch.distributed as dist
+    from test_eta import synth_model, synth_pairs
+    from routest_b200.dist import eta_score_distributed
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        _, blob = synth_model(seed=7, n_estimators=20, depth=4, n=1500)
+        cols = synth_pairs(11, 10_001)   # odd: the two ranges differ in length
+        got = eta_score_distributed(OracleEtaEngine(blob), cols["distance_m"], cols["weather"], cols["traffic"],
+                                    cols["weekday"], cols["hour"], cols["age"])
+        out[rank] = got.numpy().tobytes()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_eta_pairs_sharded_over_two_ranks_equal_the_single_rank_result():
+    """contiguous pair ranges per rank, model replicated; the gathered result is the
+    single-rank result on every rank."""
+    from oracle import oracle as O
+    from test_eta import synth_model, synth_pairs
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_eta, args=(2, port, out), nprocs=2, join=True)
+    _, blob = synth_model(seed=7, n_estimators=20, depth=4, n=1500)
+    cols = synth_pairs(11, 10_001)
+    want = O.eta_eval(blob, O.eta_features(**cols)).astype(np.float32).tobytes()
+    assert out[0] == out[1] == want

@@ -204,6 +204,50 @@ def test_engine_scores_equal_oracle_bitwise_1m_pairs(engine):
                           O.eta_features(**{k: v[:4096] for k, v in cols.items()}), equal_nan=True)
 
 
+def synth_blob_complete(trees, depth, seed=3456):
+    """The bench's ensemble (bench.eta_model_blob): complete trees with random splits, as surveyed for config 3."""
+    import bench
+    return bench.eta_model_blob(trees, depth, seed)
+
+
+def test_bench_ensemble_is_a_valid_model_for_the_oracle():
+    blob = synth_blob_complete(8, 3)
+    cols = synth_pairs(5, 257)
+    out = O.eta_eval(blob, O.eta_features(**cols))
+    assert out.shape == (257,) and np.isfinite(out).all() and np.unique(out).size > 8
+
+
+@pytest.mark.gpu
+def test_config3_as_surveyed_500_trees_depth6_1m_pairs(engine):
+    """1M pairs on a 500-tree depth-6 ensemble (the one bench.py times), bit-exact vs the oracle."""
+    blob = synth_blob_complete(500, 6)
+    engine.eta_load_model(blob)
+    assert engine.eta_model_info() == (500, 500 * 127)
+    cols = synth_pairs(3456, 1_000_000)
+    got = engine.eta_score(**cols)
+    want = O.eta_eval(blob, O.eta_features(**cols), threads=O.num_threads())
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
+def test_eta_pair_ranges_written_by_shards_equal_one_call(engine):
+    """SURVEY.md §8(e) row 4 on one GPU: eight contiguous pair ranges scored one after the other == one call."""
+    import torch
+    from routest_b200.dist import eta_score_shard_dev
+    blob = synth_blob_complete(60, 5)
+    engine.eta_load_model(blob)
+    n = 100_003
+    cols = synth_pairs(17, n)
+    want = engine.eta_score(**cols)
+    dev = [torch.tensor(cols[k], device="cuda") for k in ("distance_m", "weather", "traffic", "weekday", "hour", "age")]
+    out = torch.full((n,), -1.0, dtype=torch.float32, device="cuda")
+    cuts = [eta_score_shard_dev(engine, [d.data_ptr() for d in dev], n, out.data_ptr(), r, 8,
+                                torch.cuda.current_stream().cuda_stream) for r in range(8)]
+    torch.cuda.synchronize()
+    assert cuts[0][0] == 0 and cuts[-1][1] == n and all(a[1] == b[0] for a, b in zip(cuts, cuts[1:]))
+    assert np.array_equal(out.cpu().numpy(), want)
+
+
 @pytest.mark.gpu
 def test_engine_many_chunks_and_ragged_sizes(engine):
     """An ensemble larger than one shared-memory chunk, and pair counts around the block size."""

@@ -505,3 +505,73 @@ def test_peer_exchange_entry_points_single_replica(engine):
         done, moves, gcost = pr.search_status()
         assert done[0] == 1 and moves[0] == len(keys) and gcost[0] == cost
         assert np.array_equal(pr.get_state(0)["node"], final)
+
+
+def test_plan_upload_dev_scores_the_replica_shard(engine):
+    """rt_problem_plan_upload_dev: host inputs in, the keys of THIS replica's shard left on the device in signed-order
+    form; the minimum over the shards (what the NCCL MIN computes across ranks) is the oracle's best move."""
+    import torch
+    inst, node, raw = synth_vrptw(77, 700, 8)
+    s = torch.cuda.current_stream().cuda_stream
+    keys = torch.zeros(1, dtype=torch.int64, device="cuda")
+    found = []
+    for world in (1, 3):
+        for rank in range(world):
+            with engine.problem(inst.n, 1) as pr:
+                pr.set_shard(rank, world)
+                nd = np.zeros((1, pr.pstride), np.int32)
+                nd[0, :node.size] = node
+                call = pr.plan_upload_call(np.ascontiguousarray(raw["lat"][None]), np.ascontiguousarray(raw["lon"][None]),
+                                           np.ascontiguousarray(inst.stops[None]), np.array([inst.cap], np.int32),
+                                           np.full(1, 2 ** 62, np.int64), nd, np.array([node.size], np.int32),
+                                           keys.data_ptr(), dist_scale=10.0, time_scale=TS_CAR, stream=s)
+                call()
+                call()   # a second request on the same problem: nothing left over from the first
+                torch.cuda.synchronize()
+                found.append((world, (int(keys.item()) ^ -(2 ** 63)) & (2 ** 64 - 1)))
+    want = O.best_move(inst, node)
+    assert found[0] == (1, want)
+    assert min(k for w, k in found if w == 3) == want
+    with engine.problem(inst.n, 1) as pr:   # a coordinate out of range is refused before anything is enqueued
+        nd = np.zeros((1, pr.pstride), np.int32)
+        nd[0, :node.size] = node
+        lat = np.ascontiguousarray(raw["lat"][None]).copy()
+        lat[0, 5] = 91.0
+        call = pr.plan_upload_call(lat, np.ascontiguousarray(raw["lon"][None]), np.ascontiguousarray(inst.stops[None]),
+                                   np.array([inst.cap], np.int32), np.full(1, 2 ** 62, np.int64), nd,
+                                   np.array([node.size], np.int32), keys.data_ptr(), dist_scale=10.0, time_scale=TS_CAR, stream=s)
+        from routest_b200 import EngineError
+        with pytest.raises(EngineError):
+            call()
+
+
+def test_state_tables_refresh_alone_follows_a_route_change(engine):
+    """rt_problem_refresh_dev(what=2) on its own after the routes changed: the tables re-derive their unit vectors
+    themselves (they do not depend on an earlier what=1 refresh)."""
+    import torch
+    inst, node, raw = synth_vrptw(78, 300, 4)
+    with _load(engine, [(inst, node, raw)]) as pr:
+        k = int(pr.eval_moves()[0])
+        keys = torch.from_numpy((np.array([k], np.uint64) ^ np.uint64(1 << 63)).view(np.int64)).cuda()
+        s = torch.cuda.current_stream().cuda_stream
+        pr.apply_moves_dev(keys.data_ptr(), improving_only=True, stream=s)   # routes change (and are refreshed)
+        torch.cuda.synchronize()
+        d, f, p, q = O.key_unpack(k)
+        node2 = O.apply_move(node, f, p, q)
+        pr.refresh_dev(2, s)            # tables only
+        torch.cuda.synchronize()
+        st, ref = pr.get_state(0), O.route_state(inst, node2)
+        assert st["cost"] == ref["cost"] and np.array_equal(st["B"], ref["B"]) and np.array_equal(st["Z"], ref["Z"])
+        pr.refresh_dev(3, s)
+        assert int(pr.eval_moves()[0]) == O.best_move(inst, node2)
+
+
+def test_measured_pipe_peaks_are_plausible(engine):
+    """rt_selftest_pipe_peak: the ALU pipe issues one warp instruction every two clocks per scheduler, the issue limit
+    is one per clock — the measured rates must sit just under 148 SMs x 4 schedulers x clock x {1/2, 1}."""
+    alu, _ = engine.pipe_peak(0, 20000)
+    both, _ = engine.pipe_peak(2, 20000)
+    lo, hi = 148 * 4 * 1.0e9, 148 * 4 * 2.1e9
+    assert 0.5 * lo * 0.8 < alu < 0.5 * hi * 1.02, alu
+    assert lo * 0.8 < both < hi * 1.02, both
+    assert 1.6 < both / alu < 2.1

@@ -2,8 +2,8 @@
 a pool, or cudaMalloc's device-wide synchronisation must stay off their request path).  Its scratch is a static device
 array inside the library, so the test checks what such a caller relies on: the same cells as the ordinary entry
 points (rt_unit_vectors_dev + rt_matrix_cells_dev into caller buffers), bit for bit as everywhere in this suite, on
-two calls in a row — the second with fewer nodes, so stale vectors of the first call sit in the shared array — and a
-clear refusal beyond the static size.  Collected last on purpose: a failure here cannot hide any other test."""
+two calls in a row — the second with fewer nodes, so stale vectors of the first call sit in the shared array — the
+same cells as the CPU oracle computes from the coordinates, and a clear refusal beyond the static size.  Collected last on purpose: a failure here cannot hide any other test."""
 import numpy as np
 import pytest
 
@@ -37,6 +37,10 @@ def test_static_scratch_matrix_equals_the_allocating_path_twice_in_a_row(engine)
         got, want = _both_paths(engine, torch, lat, lon)
         assert np.array_equal(got, want)
         assert got[:, :stops + 1, 0].any() and not got[:, stops + 1:, :].any()
+        # and directly against the oracle (not only against the engine's other path)
+        from oracle import oracle as O
+        ref = O.matrix_rows(O.unit_vectors(lat, lon), 0, stops + 1, 10.0, TS_CAR, threads=O.num_threads())
+        assert np.array_equal(got[:, :stops + 1, 0], ref["dist"]) and np.array_equal(got[:, :stops + 1, 1], ref["time"])
 
 
 def test_static_scratch_refuses_sizes_beyond_its_array(engine):
