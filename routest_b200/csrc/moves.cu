@@ -21,6 +21,7 @@
 // row-contiguous; for a symmetric matrix (SPEC.md §2 always is) GT is G and the extra loads disappear at compile
 // time.
 #include <climits>
+#include <cstdlib>
 
 #include "problem.cuh"
 
@@ -29,7 +30,8 @@ namespace rt {
 namespace {
 
 constexpr int kInterThreads = 128;  // one column q per thread
-constexpr int kStripRows = 32;     // rows p per block (64 where that still leaves several waves of blocks)
+constexpr int kStripRows = 32;     // default rows p per block
+constexpr int kMaxStripRows = 64;  // the launcher picks the height per launch (pick_strip_rows)
 
 // a + b on the FMA pipe (IMAD with multiplier 1): the move kernels are bound by the ALU pipe (compares, min/max,
 // selects, three-input adds), while the FMA pipe idles — plain sums go there.
@@ -57,8 +59,10 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
     return v;
 }
 
+// signed_dst: the destination holds keys in order-preserving signed form (key ^ 2^63, "none" = INT64_MAX) — what the
+// replicas exchange — so the minimum is taken with the signed atomic and no conversion pass is needed afterwards.
 template <int THREADS>
-__device__ __forceinline__ void block_min_to_global(unsigned long long best, unsigned long long *dst)
+__device__ __forceinline__ void block_min_to_global(unsigned long long best, unsigned long long *dst, bool signed_dst = false)
 {
     __shared__ unsigned long long s_best[THREADS / 32];
     best = warp_min_u64(best);
@@ -67,7 +71,10 @@ __device__ __forceinline__ void block_min_to_global(unsigned long long best, uns
     if (threadIdx.x < 32) {
         unsigned long long v = threadIdx.x < THREADS / 32 ? s_best[threadIdx.x] : kNoMove;
         v = warp_min_u64(v);
-        if (threadIdx.x == 0 && v != kNoMove) atomicMin(dst, v);
+        if (threadIdx.x == 0 && v != kNoMove) {
+            if (signed_dst) atomicMin(reinterpret_cast<long long *>(dst), static_cast<long long>(v ^ 0x8000000000000000ull));
+            else atomicMin(dst, v);
+        }
     }
 }
 
@@ -80,10 +87,14 @@ struct EvalArgs {
     const int *npos;
     const int4 *RA, *RB, *RC, *RD, *H;
     const int2 *E, *SK;
+    const int *rstart;       // [batch][rstride + 1] separator positions (route r owns rstart[r] .. rstart[r+1]-1)
+    int rstride;
     int n, pitch, pstride;
     int families;            // bit 0 = 2-opt, 1 = relocate, 2 = swap
     int shard_index, shard_count;
     unsigned long long *best;  // [batch]
+    int signed_dst;            // best[] is in signed-order form (see block_min_to_global)
+    int strip_rows;            // rows per block of the tile kernel (<= its ROWS template bound)
     // table mode (batched iterations, batch.cu): best key per ordered route pair / per route, absolute positions
     unsigned long long *inter, *intra;  // [batch][cr][cr], [batch][cr]
     int cr;
@@ -108,14 +119,14 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
 // route pair (the thread's column fixes the second route; its best is flushed whenever the row's route changes).
 enum { kBest = 0, kDump = 1, kTable = 2 };
 
-template <int MODE, bool ASYM, int ROWS = kStripRows>
+template <int MODE, bool ASYM>
 __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel(const EvalArgs a)
 {
-    constexpr int kStripRows = ROWS;  // shadows the default: every use below is this launch's strip height
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
-    __shared__ int4 sH[kStripRows];   // {rem_delta, oe, -, route | customer << 30 | rem_ok << 29}
-    __shared__ int4 sP1[kStripRows];  // {ready, due, service, demand}
-    __shared__ int4 sP2[kStripRows];  // {Z[p+1], B[p-1]+service[p-1], capacity slack, distance slack} of p's route
+    __shared__ int4 sH[kMaxStripRows];   // {rem_delta, oe, -, route | customer << 30 | rem_ok << 29}
+    __shared__ int4 sP1[kMaxStripRows];  // {ready, due, service, demand}
+    __shared__ int4 sP2[kMaxStripRows];  // {Z[p+1], B[p-1]+service[p-1], capacity slack, distance slack} of p's route
+    const int kStripRows = a.strip_rows;  // this launch's strip height (block-uniform)
 
     const int b = DUMP ? a.dump_instance : blockIdx.z;
     const int P = a.npos[b];
@@ -284,7 +295,7 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
             best_i == 0xFFFFFFFFu
                 ? kNoMove
                 : (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i;
-        block_min_to_global<kInterThreads>(best, a.best + b);
+        block_min_to_global<kInterThreads>(best, a.best + b, a.signed_dst != 0);
     }
 }
 
@@ -365,16 +376,26 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
         int Er_xm1 = 0;               // T[node x][node x-1]
         int asym = 0;                 // sum over the inner edges of (reversed - forward) distance, for 2-opt
 
-        for (int x = t + 1; x < P; ++x) {
-            const int nx = node[x];
-            if (nx == 0) break;
-            const int4 xA = RA[x], xB = RB[x], xC = RC[x], xD = RD[x];
+        // The sweep ends at the route's closing separator, known from the route table — no data-dependent exit, so the
+        // records and cells of step x+1 are fetched while step x is being scored (the sweep is a chain of dependent
+        // steps: one memory round trip per step instead of two).
+        const int x_end = a.rstart[static_cast<size_t>(b) * (a.rstride + 1) + t_route + 1];
+        int4 nA = RA[t + 1], nB = t1B, nC = RC[t + 1], nD = RD[t + 1];
+        int2 ncm = __ldg(row_m + t + 2), nc0 = __ldg(row_0 + t + 2), ncp = __ldg(row_p + t + 2);
+        for (int x = t + 1; x < x_end; ++x) {
+            const int4 xA = nA, xB = nB, xC = nC, xD = nD;
             const int2 Ex = make_int2(xA.z, xD.z);  // cell(node x, node x+1)
             const int zn = xA.y;                    // Z[x+1]
             // next column's cells (rows fixed per thread): the only scattered loads of the step
-            const int2 cm1 = __ldg(row_m + x + 1);
-            const int2 c01 = __ldg(row_0 + x + 1);
-            const int2 cp1 = __ldg(row_p + x + 1);
+            const int2 cm1 = ncm, c01 = nc0, cp1 = ncp;
+            // step x+1 (x+1 <= x_end <= P-1 and column x+2 <= P stay inside the padded arrays)
+            nA = RA[x + 1];
+            nB = RB[x + 1];
+            nC = RC[x + 1];
+            nD = RD[x + 1];
+            ncm = __ldg(row_m + x + 2);
+            nc0 = __ldg(row_0 + x + 2);
+            ncp = __ldg(row_p + x + 2);
             const int2 r01 = ASYM ? __ldg(trow_0 + x + 1) : c01;
             const int2 rp1 = ASYM ? __ldg(trow_p + x + 1) : cp1;
             const Seg sx = seg_single(xB.x, xB.y);
@@ -472,20 +493,23 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
     if (TABLE) {
         if (best != kNoMove) atomicMin(a.intra + static_cast<size_t>(b) * a.cr + t_route, best);
     } else if (!DUMP) {
-        block_min_to_global<kIntraThreads>(best, a.best + b);
+        block_min_to_global<kIntraThreads>(best, a.best + b, a.signed_dst != 0);
     }
 }
 
-// Taller strips halve the per-block prologue (the column's records, the window's first rows, the block reduction) but
-// also the number of blocks: 64 rows when at least four waves of blocks remain (0.249 -> 0.236 ms on the bench step;
-// 128 rows: 0.231 alone but a slower step, the sweep kernel underneath has fewer blocks to share the SMs with), 32
-// otherwise (a single 5,000-stop instance has 2.4 waves at 64 rows and runs 7 % slower with them).  Symmetric
-// matrices only: the directional variant keeps the 32-row build.
-int pick_strip_rows(int pmax, int rows, int batch)
+// Strip height of the tile kernel.  Taller strips amortise the per-block prologue (the column's records, the window's
+// first rows, the block reduction: worth about four rows — 0.249 -> 0.236 ms on the 64 x 1,000 batch going from 32 to
+// 64), shorter ones shorten the tail in which the last blocks leave SMs idle.  64 rows where at least four waves of
+// blocks remain, 32 otherwise.  (Measured on a 1/8 shard of the 10,000-stop instance, 2.5 waves at 32 rows: 44 us at
+// 32 rows, 47 us at 41 rows = exactly two full waves — filling whole waves does not pay, the dispatcher back-fills
+// and a half-empty last wave simply runs faster.)  ROUTEST_STRIP_ROWS overrides, for experiments.
+int pick_strip_rows(int pmax, int rows, int batch, bool asym)
 {
+    static const int forced = getenv("ROUTEST_STRIP_ROWS") ? atoi(getenv("ROUTEST_STRIP_ROWS")) : 0;
+    if (forced >= 8 && forced <= kMaxStripRows) return forced;
     const long long col_blocks = (pmax + kInterThreads - 1) / kInterThreads;
     const long long blocks64 = col_blocks * ((rows + 63) / 64) * batch;
-    return blocks64 >= 4LL * kNumSMs * 9 ? 64 : kStripRows;
+    return (!asym && blocks64 >= 4LL * kNumSMs * 9) ? 64 : kStripRows;
 }
 
 EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d)
@@ -505,6 +529,8 @@ EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count
     a.H = p->H;
     a.E = p->E;
     a.SK = p->SK;
+    a.rstart = p->rstart;
+    a.rstride = p->rstride;
     a.n = p->n;
     a.pitch = p->pitch;
     a.pstride = p->pstride;
@@ -512,6 +538,7 @@ EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count
     a.shard_index = shard_index;
     a.shard_count = shard_count;
     a.best = best_d;
+    a.strip_rows = kStripRows;
     return a;
 }
 
@@ -542,10 +569,18 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
                       bool signed_keys, cudaStream_t st)
 {
     rt_engine *e = p->e;
-    // p->best is reset by every state refresh; a second evaluation of the same state has to clear it itself
-    if (!p->best_clean) fill_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, p->batch);
-    p->best_clean = false;
-    EvalArgs a = make_args(p, families, shard_index, shard_count, p->best);
+    // Where the minimum is accumulated.  Normally p->best (reset by every state refresh; a second evaluation of the same
+    // state clears it itself) followed by a small conversion/copy kernel.  When the state refresh that has just run
+    // was told about the caller's buffer (p->ext_best, the plan entry points), that buffer already holds "none" in
+    // signed-order form and the kernels reduce straight into it: no fill, no conversion launch.
+    const bool direct = signed_keys && best_d == p->ext_best && p->ext_best_clean;
+    p->ext_best_clean = false;
+    if (!direct) {
+        if (!p->best_clean) fill_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, p->batch);
+        p->best_clean = false;
+    }
+    EvalArgs a = make_args(p, families, shard_index, shard_count, direct ? best_d : p->best);
+    a.signed_dst = direct ? 1 : 0;
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;  // largest P of the batch
     const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
     // The sweep kernel is latency bound (a sequential walk per anchor, a few warps per SM) and the tile kernel is ALU
@@ -564,10 +599,9 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaGetLastError());
     }
     if (families & 6) {
-        const int sr = pick_strip_rows(pmax, shard_rows, p->batch);
-        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + sr - 1) / sr, p->batch);
+        a.strip_rows = pick_strip_rows(pmax, shard_rows, p->batch, !p->symmetric);
+        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + a.strip_rows - 1) / a.strip_rows, p->batch);
         if (!p->symmetric) eval_inter_kernel<kBest, true><<<grid, kInterThreads, 0, st>>>(a);
-        else if (sr == 64) eval_inter_kernel<kBest, false, 64><<<grid, kInterThreads, 0, st>>>(a);
         else eval_inter_kernel<kBest, false><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
@@ -575,7 +609,7 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
         RT_CUDA(e, cudaStreamWaitEvent(st, p->ev_join, 0));
     }
-    if (best_d != p->best || signed_keys)
+    if (!direct && (best_d != p->best || signed_keys))
         finish_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, best_d, p->batch, signed_keys ? 1 : 0);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
@@ -611,6 +645,7 @@ int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaGetLastError());
     }
     if (families & 6) {
+        a.strip_rows = kStripRows;  // table mode flushes per route change: short strips keep the flush count low
         dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + kStripRows - 1) / kStripRows, p->batch);
         if (p->symmetric) eval_inter_kernel<kTable, false><<<grid, kInterThreads, 0, st>>>(a);
         else eval_inter_kernel<kTable, true><<<grid, kInterThreads, 0, st>>>(a);

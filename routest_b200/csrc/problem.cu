@@ -554,10 +554,15 @@ int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int
     p->cells_from_coords = true;
     p->symmetric = true;  // whatever matrix was installed before, this pass runs on SPEC §2 cells
     p->supplied = 0;
-    RT_TRY(state_refresh(p, st, nullptr, /*vectors_ready=*/true));
+    p->ext_best = static_cast<unsigned long long *>(best_keys_d);  // reset by the refresh, reduced into directly
+    int rc = state_refresh(p, st, nullptr, /*vectors_ready=*/true);
     // a replica of a multi-GPU search scores the shard set by rt_problem_set_shard (default: everything)
-    return eval_moves_launch(p, families, p->shard_index, p->shard_count, static_cast<unsigned long long *>(best_keys_d),
-                             true, st);
+    if (rc == RT_OK)
+        rc = eval_moves_launch(p, families, p->shard_index, p->shard_count, static_cast<unsigned long long *>(best_keys_d),
+                               true, st);
+    p->ext_best = nullptr;
+    p->ext_best_clean = false;
+    return rc;
 }
 
 // Enqueues one pass (inputs -> best keys in the problem's pinned staging buffer).  Synchronous form: what the matrix
@@ -637,9 +642,17 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     RT_TRY(ensure_position_matrix(p));
-    RT_TRY(state_refresh(p, st, keys_dev ? nullptr : p->ev_in[1], /*vectors_ready=*/true));
+    p->ext_best = keys_dev;  // (may be null) reset by the refresh, reduced into directly by the evaluation
+    int rc_refresh = state_refresh(p, st, keys_dev ? nullptr : p->ev_in[1], /*vectors_ready=*/true);
     // a replica of a multi-GPU search scores its own shard (rt_problem_set_shard); the default is everything
-    if (keys_dev) return eval_moves_launch(p, families, p->shard_index, p->shard_count, keys_dev, true, st);
+    if (keys_dev) {
+        if (rc_refresh == RT_OK)
+            rc_refresh = eval_moves_launch(p, families, p->shard_index, p->shard_count, keys_dev, true, st);
+        p->ext_best = nullptr;
+        p->ext_best_clean = false;
+        return rc_refresh;
+    }
+    RT_TRY(rc_refresh);
     RT_TRY(eval_moves_launch(p, families, p->shard_index, p->shard_count, p->best, false, st));
     RT_TRY(stage(p, (B + 1) * 8));
     RT_CUDA(e, cudaMemcpyAsync(p->host_stage, p->best, (B + 1) * 8, cudaMemcpyDeviceToHost, st));  // keys + flag, one copy

@@ -54,6 +54,8 @@ struct rt_problem {
     int pmax = 0, pmin = 0;                // max / min npos over the batch (host copies; size grids and shards)
     int shard_index = 0, shard_count = 1;  // which part of the candidate space this replica evaluates (multi-GPU)
     bool best_clean = false;               // p->best holds "no move" for every instance (set by the state refresh)
+    unsigned long long *ext_best = nullptr;  // caller's key buffer of the plan call in progress: the refresh resets it too
+    bool ext_best_clean = false;           //   ... and it holds "none" in signed-order form right now
     bool cells_from_coords = false;        // the matrix is SPEC §2 of this problem's coordinates
     int *Bv = nullptr, *Zv = nullptr, *route = nullptr, *rstart = nullptr;
     long long *rload = nullptr, *rdist = nullptr;

@@ -176,11 +176,6 @@ __device__ __forceinline__ void gather_position(const GatherArgs &a, int b, int 
     SK[o] = sk;
 }
 
-__global__ void __launch_bounds__(256) state_gather_kernel(const GatherArgs a)
-{
-    gather_position(a, blockIdx.y, blockIdx.x * blockDim.x + threadIdx.x);
-}
-
 // K2a: one block per instance — route ids by a block scan over the separators; resets the per-instance results.
 constexpr int kScanThreads = 1024;
 
@@ -192,6 +187,7 @@ struct RoutesArgs {
     long long *cost;
     int *feasible;
     unsigned long long *best;
+    unsigned long long *ext_best;  // optional: the caller's key buffer (signed-order form), reset alongside
 };
 
 // all kScanThreads threads of the block
@@ -215,14 +211,29 @@ __device__ __forceinline__ void routes_block(const RoutesArgs &a, int b)
     const int c0 = min(P, tid * chunk), c1 = min(P, c0 + chunk);
     int cnt = 0;
     for (int p = c0; p < c1; ++p) cnt += node[p] == 0;
-    s_scan[tid] = cnt;
-    __syncthreads();
-    for (int off = 1; off < kScanThreads; off <<= 1) {  // Hillis-Steele inclusive scan
-        int v = tid >= off ? s_scan[tid - off] : 0;
-        __syncthreads();
-        s_scan[tid] += v;
-        __syncthreads();
+    // inclusive scan of the per-thread counts: shuffles inside a warp, then the 32 warp totals by the first warp
+    const int lane_ = tid & 31, warp_ = tid >> 5;
+    int incl = cnt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane_ >= off) incl += v;
     }
+    __shared__ int s_wtot[kScanThreads / 32];
+    if (lane_ == 31) s_wtot[warp_] = incl;
+    __syncthreads();
+    if (warp_ == 0) {
+        int t = s_wtot[lane_];
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, t, off);
+            if (lane_ >= off) t += v;
+        }
+        s_wtot[lane_] = t;  // inclusive over warps
+    }
+    __syncthreads();
+    s_scan[tid] = incl + (warp_ > 0 ? s_wtot[warp_ - 1] : 0);
+    __syncthreads();
     int r = s_scan[tid] - cnt - 1;  // separators before this chunk, minus 1
     for (int p = c0; p < c1; ++p) {
         if (node[p] == 0) {
@@ -236,6 +247,7 @@ __device__ __forceinline__ void routes_block(const RoutesArgs &a, int b)
         cost_all[b] = 0;
         feasible_all[b] = 1;
         best_all[b] = kNoMove;
+        if (a.ext_best) a.ext_best[b] = kNoMove ^ 0x8000000000000000ull;
     }
 }
 
@@ -244,7 +256,6 @@ __global__ void __launch_bounds__(kScanThreads) state_routes_kernel(const Routes
 // K2b: one warp per route.  The recurrences for B (forwards) and Z (backwards) are sequential, but their inputs are
 // not: each lane loads one position of a 32-position chunk (coalesced), then the warp replays the chunk in order
 // from registers via shuffles — no dependent memory round trip per position.
-constexpr int kWalkWarps = 4;
 
 struct WalkArgs {
     const int *npos;
@@ -345,11 +356,6 @@ __device__ __forceinline__ void walk_route(const WalkArgs &a, int b, int rr)
     }
 }
 
-__global__ void __launch_bounds__(kWalkWarps * 32) state_walk_kernel(const WalkArgs a)
-{
-    walk_route(a, blockIdx.y, blockIdx.x * kWalkWarps + (threadIdx.x >> 5));
-}
-
 // K2c: the packed per-position records, one thread per position.
 struct RecordsArgs {
     const int *node, *npos;
@@ -385,7 +391,9 @@ __device__ __forceinline__ void records_position(const RecordsArgs &a, int b, in
     const int4 rb = RB_all[o];
     const int2 ed = E_all[o], sk = SK_all[o];
     const int dep = Bv_all[o] + rb.z;
-    const int zn = p + 1 < P ? Zv_all[o + 1] : depot.y;
+    // Z of a separator is the depot's due time by definition: not read from memory, so a route's records depend on
+    // nothing another route's warp writes
+    const int zn = (p + 1 < P && node_all[o + 1] != 0) ? Zv_all[o + 1] : depot.y;
     RA_all[o] = make_int4(dep, zn, ed.x, rt_);
     // slacks are clamped to [-2^29, 2^30]: wide enough to compare against any demand / delta (both < 2^30 in
     // magnitude), narrow enough that "slack - value" never overflows in the move kernels
@@ -407,11 +415,6 @@ __device__ __forceinline__ void records_position(const RecordsArgs &a, int b, in
         RC_all[o] = make_int4(0, 0, 0, 0);
         H_all[o] = make_int4(0, 0, ed.x, rt_);
     }
-}
-
-__global__ void __launch_bounds__(256) state_records_kernel(const RecordsArgs a)
-{
-    records_position(a, blockIdx.y, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 // All four phases for one instance in one block (kScanThreads threads): what the four launches above do, minus three
@@ -437,6 +440,110 @@ __device__ __forceinline__ void state_tables_block(const StateArgs &a, int b)
 }
 
 __global__ void __launch_bounds__(kScanThreads) state_fused_kernel(const StateArgs a) { state_tables_block(a, blockIdx.x); }
+
+// K2bc for large instances: ONE warp per route does everything the route needs — the gather of its positions (stop
+// record, edge to the successor, skip edge), the forward/backward walk and the packed records — so that after the
+// route scan a single launch finishes the tables (two dependent launches instead of four: the tables sit on the
+// critical path of a sharded pass, where the matrix rows they used to hide under are 1/N of the work).  A route only
+// reads what its own warp wrote (positions s .. e-1, s its opening separator), in program order behind __syncwarp().
+constexpr int kRouteWarps = 4;
+
+__device__ __forceinline__ void route_tables_warp(const StateArgs &a, int b, int rr)
+{
+    const WalkArgs &w = a.w;
+    const RecordsArgs &c = a.c;
+    const int lane = threadIdx.x & 31;
+    const int P = w.npos[b];
+    const int R = P - w.n;
+    if (rr >= R) return;
+    const size_t po = static_cast<size_t>(b) * w.pstride, ro = static_cast<size_t>(b) * w.rstride;
+    const int *rstart = w.rstart + ro + b;
+    const int s = rstart[rr], e = rstart[rr + 1];
+    const bool last = rr == R - 1;
+    const unsigned full = 0xffffffffu;
+    int *route = a.r.route + po;
+    // gather: this route's positions, plus (last route) the closing depot
+    const int g_end = last ? P : e;
+    for (int p = s + lane; p < g_end; p += 32) {
+        gather_position(a.g, b, p);
+        route[p] = p < e ? rr : R;
+    }
+    // fused-vectors form: the unused tail of the position arrays repeats the depot's vector; spread over all warps
+    if (a.g.xyz)
+        for (int p = P + rr * 32 + lane; p < a.g.pstride; p += 32 * R) gather_position(a.g, b, p);
+    __syncwarp();
+    const int4 *RB = w.RB + po;
+    const int2 *E = w.E + po;
+    int *Bv = w.Bv + po, *Zv = w.Zv + po;
+    const int4 depot = w.stops[static_cast<size_t>(b) * w.n];
+    int Bcur = depot.x, svc_prev = depot.z;
+    long long load = 0, dist = 0;
+    bool feas = true;
+    for (int base = s + 1; base < e; base += 32) {
+        const int p = base + lane;
+        const bool in = p < e;
+        const int4 rb = in ? RB[p] : make_int4(0, 0, 0, 0);
+        const int2 ed = in ? E[p - 1] : make_int2(0, 0);
+        const int cntc = min(32, e - base);
+        int myB = 0;
+        for (int k = 0; k < cntc; ++k) {
+            const int ready = __shfl_sync(full, rb.x, k), due = __shfl_sync(full, rb.y, k);
+            const int svc = __shfl_sync(full, rb.z, k), dem = __shfl_sync(full, rb.w, k);
+            const int ed_d = __shfl_sync(full, ed.x, k), ed_t = __shfl_sync(full, ed.y, k);
+            Bcur = max(ready, Bcur + svc_prev + ed_t);
+            feas = feas && Bcur <= due;
+            if (k == lane) myB = Bcur;
+            svc_prev = svc;
+            load += dem;
+            dist += ed_d;
+        }
+        if (in) Bv[p] = myB;
+    }
+    const int2 lastE = E[e - 1];
+    feas = feas && (Bcur + svc_prev + lastE.y <= depot.y);
+    dist += lastE.x;
+    feas = feas && load <= w.cap[b] && dist <= w.maxd[b];
+    int Zn = depot.y;
+    for (int top = e - 1; top > s; top -= 32) {
+        const int p = top - lane;
+        const bool in = p > s;
+        const int4 rb = in ? RB[p] : make_int4(0, 0, 0, 0);
+        const int2 ed = in ? E[p] : make_int2(0, 0);
+        const int cntc = min(32, top - s);
+        int myZ = 0;
+        for (int k = 0; k < cntc; ++k) {
+            const int due = __shfl_sync(full, rb.y, k), svc = __shfl_sync(full, rb.z, k);
+            const int ed_t = __shfl_sync(full, ed.y, k);
+            Zn = min(due, Zn - ed_t - svc);
+            if (k == lane) myZ = Zn;
+        }
+        if (in) Zv[p] = myZ;
+    }
+    if (lane == 0) {
+        Bv[s] = depot.x;
+        Zv[s] = depot.y;
+        if (last) {
+            Bv[P - 1] = depot.x;
+            Zv[P - 1] = depot.y;
+        }
+        w.rload[ro + rr] = load;
+        w.rdist[ro + rr] = dist;
+        atomicAdd(reinterpret_cast<unsigned long long *>(w.cost + b), static_cast<unsigned long long>(dist));
+        if (!feas) w.feasible[b] = 0;
+    }
+    __syncwarp();
+    // records: position p reads B/Z/E of p-1, p, p+1 — all inside [s, e] (Z of the next separator is the depot's due
+    // time, which records_position takes from the depot record when p + 1 is the last position; for an inner
+    // separator e the next route's warp writes the same constant, so either order gives the same value)
+    const int r_end = last ? P : e;
+    for (int p = s + lane; p < r_end; p += 32) records_position(c, b, p);
+}
+
+__global__ void __launch_bounds__(kRouteWarps * 32) state_route_tables_kernel(const StateArgs a)
+{
+    route_tables_warp(a, blockIdx.y, blockIdx.x * kRouteWarps + (threadIdx.x >> 5));
+}
+
 
 // Applies one move per instance (SPEC.md §8).  keys are the packed keys of SPEC.md §7, optionally in the
 // order-preserving signed form (key ^ 2^63) that the _dev entry points exchange with NCCL.
@@ -577,7 +684,8 @@ static StateArgs state_args(rt_problem *p, bool fused_vectors)
     a.g = GatherArgs{p->cells_from_coords ? p->PX : nullptr, p->cells, p->stops, p->node, p->npos, p->n, p->pitch, p->pstride,
                      static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale), static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale),
                      p->RB, p->E, p->SK, p->symmetric ? nullptr : p->ER, fused_vectors ? p->xyz : nullptr, p->PX};
-    a.r = RoutesArgs{p->node, p->npos, p->nroutes, p->pstride, p->rstride, p->route, p->rstart, p->cost, p->feasible, p->best};
+    a.r = RoutesArgs{p->node, p->npos, p->nroutes, p->pstride, p->rstride, p->route, p->rstart, p->cost, p->feasible, p->best,
+                     p->ext_best};
     a.w = WalkArgs{p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap, p->max_dist, p->RB, p->E, p->Bv, p->Zv, p->rstart,
                    p->rload, p->rdist, p->cost, p->feasible};
     a.c = RecordsArgs{p->node, p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap, p->max_dist, p->RB, p->E, p->SK, p->Bv,
@@ -591,27 +699,23 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors)
     const bool fused = with_vectors && p->cells_from_coords;  // also produce the position-ordered vectors
     const StateArgs a = state_args(p, fused);
     p->best_clean = true;  // the route scan resets the best keys
+    p->ext_best_clean = p->ext_best != nullptr;
     if (p->grows <= kFusedStatePositions) {
         state_fused_kernel<<<p->batch, kScanThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
         return RT_OK;
     }
-    dim3 g1((p->grows + 255) / 256, p->batch);
-    dim3 gg(fused ? (p->pstride + 255) / 256 : g1.x, p->batch);
-    state_gather_kernel<<<gg, 256, 0, st>>>(a.g);
-    RT_CUDA(e, cudaGetLastError());
+    // route scan, then one warp per route: gather + walk + records of its own positions
     state_routes_kernel<<<p->batch, kScanThreads, 0, st>>>(a.r);
     RT_CUDA(e, cudaGetLastError());
     const int rmax = std::max(1, p->grows - p->n);  // most routes of any instance
-    dim3 gw((rmax + kWalkWarps - 1) / kWalkWarps, p->batch);
-    state_walk_kernel<<<gw, kWalkWarps * 32, 0, st>>>(a.w);
-    RT_CUDA(e, cudaGetLastError());
-    state_records_kernel<<<g1, 256, 0, st>>>(a.c);
+    dim3 gw((rmax + kRouteWarps - 1) / kRouteWarps, p->batch);
+    state_route_tables_kernel<<<gw, kRouteWarps * 32, 0, st>>>(a);
     RT_CUDA(e, cudaGetLastError());
     return RT_OK;
 }
 
-// Both halves.  The state tables do not read G (state_gather_kernel rebuilds the cells it needs), so their four small
+// Both halves.  The state tables do not read G (the gather step rebuilds the cells it needs), so their four small
 // latency-bound kernels run on a side stream underneath the matrix kernel and join before anything evaluates moves.
 int position_unit_vectors_launch(rt_problem *p, cudaStream_t st, int *bad_flag, int bad_value)
 {
