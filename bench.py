@@ -263,8 +263,9 @@ def workload_config(stops, vehicles, routes, P, evals, world):
                         "matrix in route order + route state + full 2-opt/relocate/swap neighbourhood with capacity "
                         "and time-window feasibility, best-move key per pass",
             "stops": stops, "routes": routes, "positions": P, "cells_per_step": n * n, "move_evals_per_step": evals,
-            "l2": f"each pass writes and re-reads {P * ((P + 15) // 16 * 16) * 8 / 1e6:.0f} MB of route-order matrix "
-                  "(> 126 MB L2 up to 4 GPUs; 105 MB per GPU at 8); no flush",
+            "l2": "inputs per pass are O(n) (coordinates, stop records, routes: 0.6 MB) and every pass recomputes everything "
+                  f"from them; the route-order matrix ({P * ((P + 15) // 16 * 16) * 8 / 1e6:.0f} MB / N per GPU) is an "
+                  "intermediate written and re-read inside the pass (> 126 MB L2 up to N = 4); no flush",
             "parallelism": parallelism}
 
 
@@ -414,11 +415,11 @@ def run_engine(args, rank, world):
     # ---- device-resident timing: K passes, barrier + sync on both sides, CUDA events, max over ranks
     for _ in range(args.warmup):
         step()
-    cx.barrier()
     sampler = ClockSampler(cx.local)
-    if rank == 0:
+    if rank == 0:                             # before the barrier: no rank may enter the timed loop late
         sampler.start()
         time.sleep(0.25)
+    cx.barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_wall0 = time.perf_counter()
     ev0.record()
