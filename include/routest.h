@@ -318,6 +318,12 @@ int rt_selftest_fast_sqrt(rt_engine *e, uint32_t lo_bits, uint32_t hi_bits, uint
  * over the whole GPU.  No reference counterpart. */
 int rt_selftest_pipe_peak(rt_engine *e, int mode, int iters, double *warp_inst_per_s, double *elapsed_ms);
 
+/* Test and measurement knobs (process-wide, not for production use): "strip_rows" = rows per block of the tile kernel
+ * (0 = let the launcher pick, 8..64), "intra_kernel" = which same-route kernel runs (0 = pick, 1 = one thread per
+ * anchor, 2 = one warp per anchor).  Both choices give the same keys; the tests run them against each other and the
+ * oracle.  No reference counterpart. */
+int rt_debug_set(const char *name, int value);
+
 #ifdef __cplusplus
 }
 #endif

@@ -100,6 +100,7 @@ SIGNATURES = {
                                    C.c_int64, C.c_void_p, C.c_void_p]),
     "rt_selftest_fast_sqrt": (C.c_int, [c_engine_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]),
     "rt_selftest_pipe_peak": (C.c_int, [c_engine_p, C.c_int, C.c_int, c_f64_p, c_f64_p]),
+    "rt_debug_set": (C.c_int, [C.c_char_p, C.c_int]),
     "rt_unit_vectors_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "rt_matrix_cells_dev": (C.c_int, [c_engine_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
                                       C.c_double, C.c_void_p, C.c_void_p]),

@@ -497,19 +497,244 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
     }
 }
 
+
+// ---- same-route candidates, one WARP per anchor ------------------------------------------------------------------
+// The sweep above is a chain of dependent steps: ~0.4 us per position of the route whatever the GPU has left to do,
+// i.e. 35-50 us for routes of a hundred stops — invisible underneath a 270 us tile kernel, but the floor of a pass once
+// the neighbourhood is sharded over several GPUs (a 1/8 shard of the tile kernel takes less).  Segment concatenation is
+// associative, so the forward segment node[t+1..x] and the reversed one node[x..t+1] of EVERY x are two warp scans:
+// lane j owns x = base + j, five shuffle steps build both segments, and all candidates of 32 consecutive x are scored
+// at once; routes longer than 32 positions carry the last lane's segments into the next chunk.  Same candidates, same
+// keys as the sweep (the composition is exact integer max-plus algebra, so the association order cannot change a
+// value).  Symmetric matrices only; the sweep stays for directional ones and for launches with enough anchors to hide
+// its latency (it needs half the instructions).
+struct SegW {  // a segment plus the link weight the next concatenation on its open side needs
+    int a, b, L, ok, w;
+};
+
+__device__ __forceinline__ SegW segw_shfl_up(const SegW &s, int off)
+{
+    SegW r;
+    r.a = __shfl_up_sync(0xffffffffu, s.a, off);
+    r.b = __shfl_up_sync(0xffffffffu, s.b, off);
+    r.L = __shfl_up_sync(0xffffffffu, s.L, off);
+    r.ok = __shfl_up_sync(0xffffffffu, s.ok, off);
+    r.w = __shfl_up_sync(0xffffffffu, s.w, off);
+    return r;
+}
+
+__device__ __forceinline__ Seg seg_of(const SegW &s) { return Seg{s.a, s.b, s.L, s.ok != 0}; }
+
+constexpr int kIntraWarps = 4;
+
+template <int MODE>
+__global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const EvalArgs a)
+{
+    constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
+    const int b = DUMP ? a.dump_instance : blockIdx.y;
+    const int P = a.npos[b];
+    int t_lo, t_hi;
+    shard_range(P, a.shard_index, a.shard_count, t_lo, t_hi);  // same-route work is sharded by anchor
+    const int lane = threadIdx.x & 31;
+    const int t = t_lo + blockIdx.x * kIntraWarps + (threadIdx.x >> 5);
+    unsigned long long best = kNoMove;
+    int t_route = 0;
+
+    if (t < t_hi && t < P - 1) {  // warp-uniform
+        const size_t po = static_cast<size_t>(b) * a.pstride;
+        const int2 *G = a.G + static_cast<size_t>(b) * a.grows * a.gpitch;
+        const int4 *RA = a.RA + po, *RB = a.RB + po, *RC = a.RC + po, *RD = a.RD + po;
+        const int4 tA = RA[t], tB = RB[t], tC = RC[t], tD = RD[t];
+        t_route = tA.w;
+        const int x_end = a.rstart[static_cast<size_t>(b) * (a.rstride + 1) + t_route + 1];
+        const bool t_cust = tC.w & 1;
+        const int dslack = tD.y;
+        const int2 Et = a.E[po + t], SKt = a.SK[po + t];
+        const int svc_t1 = RB[t + 1].z;           // service time of node t+1
+        const int dep_t = tA.x, dep_tm1 = tC.x;
+        const int2 *row_m = G + static_cast<size_t>(max(t - 1, 0)) * a.gpitch;
+        const int2 *row_0 = G + static_cast<size_t>(t) * a.gpitch;
+        const int2 *row_p = G + static_cast<size_t>(t + 1) * a.gpitch;
+        const bool f2 = a.families & 1, f_rel = a.families & 2, f_swap = a.families & 4;
+        const Seg st_single = seg_single(tB.x, tB.y);
+
+        // carries from the previous chunk (positions below `base`): forward segment t+1..base-1, reversed base-1..t+1,
+        // service time and outgoing edge of base-1, cell (t, base-1)
+        Seg Fc = Seg{0, 0, 0, true}, Rc = Fc;
+        int svc_c = 0, et_c = 0;
+        int2 c0_c = make_int2(0, 0);
+        for (int base = t + 1; base < x_end; base += 32) {
+            const int x = base + lane;
+            const bool in = x < x_end;
+            const int xx = in ? x : x_end - 1;     // lanes beyond the route re-read its last position; never reported
+            const int4 xA = RA[xx], xB = RB[xx], xC = RC[xx], xD = RD[xx];
+            const int2 cm = __ldg(row_m + xx), c0 = __ldg(row_0 + xx), c01 = __ldg(row_0 + xx + 1);
+            const int2 cp = __ldg(row_p + xx), cp1 = __ldg(row_p + xx + 1);
+            const int2 Ex = make_int2(xA.z, xD.z);  // cell(node x, node x+1)
+            const int zn = xA.y;                    // Z[x+1]
+            int svc_xm1 = __shfl_up_sync(0xffffffffu, xB.z, 1);
+            int et_xm1 = __shfl_up_sync(0xffffffffu, Ex.y, 1);
+            int2 r0_prev = make_int2(__shfl_up_sync(0xffffffffu, c0.x, 1), __shfl_up_sync(0xffffffffu, c0.y, 1));
+            if (lane == 0) {
+                svc_xm1 = svc_c;
+                et_xm1 = et_c;
+                r0_prev = c0_c;
+            }
+            const Seg sx = seg_single(xB.x, xB.y);
+            // forward: F = node[base..x], open on its low side, link weight service[x-1] + T[x-1][x]
+            // reversed: R = node[x..base], open on its low side too, link weight service[x] + T[x][x-1]
+            SegW F{sx.a, sx.b, sx.L, 1, svc_xm1 + et_xm1};
+            SegW R{sx.a, sx.b, sx.L, 1, xB.z + et_xm1};
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const SegW Fl = segw_shfl_up(F, off), Rl = segw_shfl_up(R, off);
+                if (lane >= off) {
+                    const Seg f = seg_concat(seg_of(Fl), F.w, seg_of(F));
+                    F = SegW{f.a, f.b, f.L, f.ok ? 1 : 0, Fl.w};
+                    const Seg r = seg_concat(seg_of(R), R.w, seg_of(Rl));
+                    R = SegW{r.a, r.b, r.L, r.ok ? 1 : 0, Rl.w};
+                }
+            }
+            Seg Fin = seg_of(F), Rv = seg_of(R);   // node[t+1..x] and node[x..t+1] once the carries are attached
+            if (base > t + 1) {
+                Fin = seg_concat(Fc, F.w, Fin);
+                Rv = seg_concat(Rv, R.w, Rc);
+            }
+            // node[t+1..x-1]: the left neighbour's inclusive segment
+            SegW Fw{Fin.a, Fin.b, Fin.L, Fin.ok ? 1 : 0, 0};
+            const SegW Fp_ = segw_shfl_up(Fw, 1);
+            const Seg Fprev = lane == 0 ? Fc : seg_of(Fp_);
+
+            if (in) {
+                // (A) 2-opt(t, x)
+                if (f2 && x >= t + 2) {
+                    const int d = c0.x + cp1.x - Et.x - Ex.x;
+                    const bool ok = d <= dslack && seg_fits(Rv, dep_t + c0.y, svc_t1 + cp1.y, zn);
+                    if (DUMP) {
+                        if (a.dump_family == 0) {
+                            a.dump_delta[static_cast<size_t>(t) * P + x] = d;
+                            a.dump_feas[static_cast<size_t>(t) * P + x] = ok ? 1 : 0;
+                        }
+                    } else if (ok) {
+                        const unsigned long long k = pack_key(d, 0, t, x);
+                        best = k < best ? k : best;
+                    }
+                }
+                if (f_rel) {
+                    // (B) relocate(t -> after x): prefix(..t-1) + node[t+1..x] + [t] + suffix(x+1..)
+                    if (t_cust) {
+                        const Seg m = seg_concat(Fin, xB.z + c0.y, st_single);
+                        const int d = tC.y + c0.x + c01.x - Ex.x;
+                        const bool ok = d <= dslack && seg_fits(m, dep_tm1 + SKt.y, tB.z + c01.y, zn);
+                        if (DUMP) {
+                            if (a.dump_family == 1) {
+                                a.dump_delta[static_cast<size_t>(t) * P + x] = d;
+                                a.dump_feas[static_cast<size_t>(t) * P + x] = ok ? 1 : 0;
+                            }
+                        } else if (ok) {
+                            const unsigned long long k = pack_key(d, 1, t, x);
+                            best = k < best ? k : best;
+                        }
+                    }
+                    // (C) relocate(x -> after t): prefix(..t) + [x] + node[t+1..x-1] + suffix(x+1..)
+                    if (x >= t + 2) {
+                        const Seg m = seg_concat(sx, xB.z + cp.y, Fprev);
+                        const int d = xC.y + c0.x + cp.x - Et.x;
+                        const bool ok = d <= dslack && seg_fits(m, dep_t + c0.y, svc_xm1 + xD.w, zn);
+                        if (DUMP) {
+                            if (a.dump_family == 1) {
+                                a.dump_delta[static_cast<size_t>(x) * P + t] = d;
+                                a.dump_feas[static_cast<size_t>(x) * P + t] = ok ? 1 : 0;
+                            }
+                        } else if (ok) {
+                            const unsigned long long k = pack_key(d, 1, x, t);
+                            best = k < best ? k : best;
+                        }
+                    }
+                }
+                // (D) swap(t, x)
+                if (f_swap && t_cust) {
+                    Seg m;
+                    int d;
+                    if (x == t + 1) {
+                        m = seg_concat(sx, xB.z + c0.y, st_single);
+                        d = cm.x + c0.x + c01.x - tC.z - Ex.x;
+                    } else {
+                        m = seg_concat(sx, xB.z + cp.y, Fprev);
+                        m = seg_concat(m, svc_xm1 + r0_prev.y, st_single);
+                        d = cm.x + cp.x - tC.z + r0_prev.x + c01.x - xC.z;
+                    }
+                    const bool ok = d <= dslack && seg_fits(m, dep_tm1 + cm.y, tB.z + c01.y, zn);
+                    if (DUMP) {
+                        if (a.dump_family == 2) {
+                            a.dump_delta[static_cast<size_t>(t) * P + x] = d;
+                            a.dump_feas[static_cast<size_t>(t) * P + x] = ok ? 1 : 0;
+                        }
+                    } else if (ok) {
+                        const unsigned long long k = pack_key(d, 2, t, x);
+                        best = k < best ? k : best;
+                    }
+                }
+            }
+            // carries for the next chunk: everything of lane 31 (x = base + 31 < x_end whenever there is a next chunk)
+            Fc = Seg{__shfl_sync(0xffffffffu, Fin.a, 31), __shfl_sync(0xffffffffu, Fin.b, 31),
+                     __shfl_sync(0xffffffffu, Fin.L, 31), __shfl_sync(0xffffffffu, Fin.ok ? 1 : 0, 31) != 0};
+            Rc = Seg{__shfl_sync(0xffffffffu, Rv.a, 31), __shfl_sync(0xffffffffu, Rv.b, 31),
+                     __shfl_sync(0xffffffffu, Rv.L, 31), __shfl_sync(0xffffffffu, Rv.ok ? 1 : 0, 31) != 0};
+            svc_c = __shfl_sync(0xffffffffu, xB.z, 31);
+            et_c = __shfl_sync(0xffffffffu, Ex.y, 31);
+            c0_c = make_int2(__shfl_sync(0xffffffffu, c0.x, 31), __shfl_sync(0xffffffffu, c0.y, 31));
+        }
+    }
+    if (TABLE) {
+        best = warp_min_u64(best);
+        if (lane == 0 && best != kNoMove) atomicMin(a.intra + static_cast<size_t>(b) * a.cr + t_route, best);
+    } else if (!DUMP) {
+        block_min_to_global<kIntraWarps * 32>(best, a.best + b, a.signed_dst != 0);
+    }
+}
+
 // Strip height of the tile kernel.  Taller strips amortise the per-block prologue (the column's records, the window's
 // first rows, the block reduction: worth about four rows — 0.249 -> 0.236 ms on the 64 x 1,000 batch going from 32 to
 // 64), shorter ones shorten the tail in which the last blocks leave SMs idle.  64 rows where at least four waves of
 // blocks remain, 32 otherwise.  (Measured on a 1/8 shard of the 10,000-stop instance, 2.5 waves at 32 rows: 44 us at
 // 32 rows, 47 us at 41 rows = exactly two full waves — filling whole waves does not pay, the dispatcher back-fills
 // and a half-empty last wave simply runs faster.)  ROUTEST_STRIP_ROWS overrides, for experiments.
+int g_strip_rows = 0;    // rt_debug_set("strip_rows", h): 0 = pick, else the height to use
+int g_intra_kernel = 0;  // rt_debug_set("intra_kernel", k): 0 = pick, 1 = one thread per anchor, 2 = one warp per anchor
+
 int pick_strip_rows(int pmax, int rows, int batch, bool asym)
 {
-    static const int forced = getenv("ROUTEST_STRIP_ROWS") ? atoi(getenv("ROUTEST_STRIP_ROWS")) : 0;
+    static const int env = getenv("ROUTEST_STRIP_ROWS") ? atoi(getenv("ROUTEST_STRIP_ROWS")) : 0;
+    const int forced = g_strip_rows ? g_strip_rows : env;
     if (forced >= 8 && forced <= kMaxStripRows) return forced;
     const long long col_blocks = (pmax + kInterThreads - 1) / kInterThreads;
     const long long blocks64 = col_blocks * ((rows + 63) / 64) * batch;
     return (!asym && blocks64 >= 4LL * kNumSMs * 9) ? 64 : kStripRows;
+}
+
+// One warp per anchor while the launch has too few anchors to hide the sweep's latency behind other work (a single
+// instance, a shard of one); one thread per anchor for big batches, where the sweep's lower instruction count wins.
+bool intra_by_warp(const rt_problem *p, int shard_rows)
+{
+    if (!p->symmetric) return false;
+    if (g_intra_kernel) return g_intra_kernel == 2;
+    return static_cast<long long>(shard_rows) * p->batch <= 16384;
+}
+
+template <int MODE>
+int launch_intra(rt_problem *p, const EvalArgs &a, int shard_rows, int batch, cudaStream_t st)
+{
+    if (intra_by_warp(p, shard_rows)) {
+        dim3 grid((shard_rows + kIntraWarps - 1) / kIntraWarps, batch);
+        eval_intra_warp_kernel<MODE><<<grid, kIntraWarps * 32, 0, st>>>(a);
+    } else {
+        dim3 grid((shard_rows + kIntraThreads - 1) / kIntraThreads, batch);
+        if (p->symmetric) eval_intra_kernel<MODE, false><<<grid, kIntraThreads, 0, st>>>(a);
+        else eval_intra_kernel<MODE, true><<<grid, kIntraThreads, 0, st>>>(a);
+    }
+    RT_CUDA(p->e, cudaGetLastError());
+    return RT_OK;
 }
 
 EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d)
@@ -592,12 +817,7 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, p->ev_fork, 0));
         st_intra = p->side_stream;
     }
-    {
-        dim3 grid((shard_rows + kIntraThreads - 1) / kIntraThreads, p->batch);
-        if (p->symmetric) eval_intra_kernel<kBest, false><<<grid, kIntraThreads, 0, st_intra>>>(a);
-        else eval_intra_kernel<kBest, true><<<grid, kIntraThreads, 0, st_intra>>>(a);
-        RT_CUDA(e, cudaGetLastError());
-    }
+    RT_TRY(launch_intra<kBest>(p, a, shard_rows, p->batch, st_intra));
     if (families & 6) {
         a.strip_rows = pick_strip_rows(pmax, shard_rows, p->batch, !p->symmetric);
         dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + a.strip_rows - 1) / a.strip_rows, p->batch);
@@ -638,12 +858,7 @@ int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, p->ev_fork, 0));
         st_intra = p->side_stream;
     }
-    {
-        dim3 grid((shard_rows + kIntraThreads - 1) / kIntraThreads, p->batch);
-        if (p->symmetric) eval_intra_kernel<kTable, false><<<grid, kIntraThreads, 0, st_intra>>>(a);
-        else eval_intra_kernel<kTable, true><<<grid, kIntraThreads, 0, st_intra>>>(a);
-        RT_CUDA(e, cudaGetLastError());
-    }
+    RT_TRY(launch_intra<kTable>(p, a, shard_rows, p->batch, st_intra));
     if (families & 6) {
         a.strip_rows = kStripRows;  // table mode flushes per route change: short strips keep the flush count low
         dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + kStripRows - 1) / kStripRows, p->batch);
@@ -678,11 +893,16 @@ int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsi
         else eval_inter_kernel<kDump, true><<<grid, kInterThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
     }
-    dim3 grid((pmax + kIntraThreads - 1) / kIntraThreads, 1);
-    if (p->symmetric) eval_intra_kernel<kDump, false><<<grid, kIntraThreads, 0, st>>>(a);
-    else eval_intra_kernel<kDump, true><<<grid, kIntraThreads, 0, st>>>(a);
-    RT_CUDA(e, cudaGetLastError());
-    return RT_OK;
+    return launch_intra<kDump>(p, a, pmax, 1, st);
 }
 
 }  // namespace rt
+
+extern "C" int rt_debug_set(const char *name, int value)
+{
+    if (!name) return RT_ERR_INVALID_ARG;
+    if (!strcmp(name, "strip_rows")) rt::g_strip_rows = value;
+    else if (!strcmp(name, "intra_kernel")) rt::g_intra_kernel = value;
+    else return RT_ERR_INVALID_ARG;
+    return RT_OK;
+}

@@ -142,6 +142,10 @@ class Engine:
         self._check(self._lib.rt_selftest_fast_sqrt(self._h, lo_bits, hi_bits, C.byref(bad)))
         return int(bad.value)
 
+    def debug_set(self, name: str, value: int):
+        """rt_debug_set: process-wide test/measurement knob ("strip_rows", "intra_kernel")."""
+        self._check(self._lib.rt_debug_set(name.encode(), int(value)))
+
     def pipe_peak(self, mode: int = 0, iters: int = 20000):
         """Measured instruction-rate peak in warp instructions per second (rt_selftest_pipe_peak): mode 0 = ALU pipe,
         1 = FMA pipe, 2 = both interleaved (issue limit).  Returns (rate, elapsed_ms)."""

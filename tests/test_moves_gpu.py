@@ -575,3 +575,35 @@ def test_measured_pipe_peaks_are_plausible(engine):
     assert 0.5 * lo * 0.8 < alu < 0.5 * hi * 1.02, alu
     assert lo * 0.8 < both < hi * 1.02, both
     assert 1.6 < both / alu < 2.1
+
+
+@pytest.mark.parametrize("kernel", [1, 2], ids=["thread-per-anchor", "warp-per-anchor"])
+@pytest.mark.parametrize("seed,stops,veh,kw", [(11, 40, 6, {}), (12, 150, 4, dict(half_lo=7200, half_hi=20000)),
+                                                (13, 260, 3, dict(half_lo=20000, half_hi=43200))])
+def test_same_route_kernels_agree_with_the_oracle(engine, kernel, seed, stops, veh, kw):
+    """Both same-route kernels (sweep per thread / segment scans per warp; rt_debug_set "intra_kernel") score every
+    candidate like the oracle — routes of 7, ~40 and ~90 positions: no carry, one carry, several carries between the
+    warp's 32-position chunks — and give the same table-mode batches and searches."""
+    inst, node0, raw = synth_vrptw(seed, stops, veh, **kw)
+    engine.debug_set("intra_kernel", kernel)
+    try:
+        for node in (node0, _walk(inst, node0, seed, 10)):
+            with _load(engine, [(inst, node0, raw)], [node]) as pr:
+                for fam in (0, 1, 2):
+                    d, f = pr.eval_dump(0, fam, node.size)
+                    dr, fr = O.eval_fast(inst, node, fam)
+                    assert np.array_equal(f, fr), f"feasibility flags differ in family {fam}"
+                    assert np.array_equal(d[fr != 2], dr[fr != 2]), f"deltas differ in family {fam}"
+                assert int(pr.eval_moves()[0]) == O.best_move(inst, node)
+                parts = [int(pr.eval_moves(shard=(i, 3))[0]) for i in range(3)]
+                assert min(parts) == O.best_move(inst, node)
+        with _load(engine, [(inst, node0, raw)]) as pr:
+            bmoves, bcost, bkeys = pr.local_search(max_moves=3, keys_capacity=512, batched=True)   # table mode
+            bfinal, okeys, _, ocost = O.local_search_batched(inst, node0, max_iters=3)
+            assert np.array_equal(bkeys[0], okeys) and bcost[0] == ocost
+            moves, cost, keys = pr.local_search(max_moves=12, keys_capacity=16, full=True)
+            final, okeys2, ocost2 = O.local_search(inst, bfinal, max_moves=12)
+            assert np.array_equal(keys[0], okeys2) and cost[0] == ocost2
+            assert np.array_equal(pr.get_state(0)["node"], final)
+    finally:
+        engine.debug_set("intra_kernel", 0)
