@@ -236,8 +236,11 @@ int rt_problem_plan_upload_dev(rt_problem *p, const double *lat, const double *l
 int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int families, void *best_keys_d,
                         void *stream);
 /* Its pieces, stream-ordered: the node-order matrix of rt_problem_build_matrix; the refresh (what: bit 0 = rebuild
- * the route-order matrix from the current routes, bit 1 = re-derive the route state tables; either bit works on its
- * own after a route change, and with both set the tables run on a side stream underneath the matrix kernel). */
+ * what the move kernels read of the route-order matrix from the current routes, bit 1 = re-derive the route state
+ * tables; either bit works on its own after a route change, and with both set the tables run on a side stream
+ * underneath the matrix kernel.  Where the matrix is SPEC.md §2 of the problem's own coordinates the move kernels
+ * rebuild their cells from the unit vectors and read no matrix, so bit 0 has nothing to do; bit 2 materialises the
+ * route-order matrix regardless (rt_problem_get_position_matrix does that by itself)). */
 int rt_problem_build_matrix_dev(rt_problem *p, double dist_scale, double time_scale, void *stream);
 int rt_problem_refresh_dev(rt_problem *p, int what, void *stream);
 
@@ -320,8 +323,9 @@ int rt_selftest_pipe_peak(rt_engine *e, int mode, int iters, double *warp_inst_p
 
 /* Test and measurement knobs (process-wide, not for production use): "strip_rows" = rows per block of the tile kernel
  * (0 = let the launcher pick, 8..64), "intra_kernel" = which same-route kernel runs (0 = pick, 1 = one thread per
- * anchor, 2 = one warp per anchor).  Both choices give the same keys; the tests run them against each other and the
- * oracle.  No reference counterpart. */
+ * anchor, 2 = one warp per anchor), "fused_eval" = 1 (default): move kernels rebuild matrix cells from unit vectors
+ * where the matrix is SPEC.md §2 of the problem's coordinates, 0: always write the route-order matrix and read it back.
+ * Every choice gives the same keys; the tests run them against each other and the oracle.  No reference counterpart. */
 int rt_debug_set(const char *name, int value);
 
 #ifdef __cplusplus

@@ -23,9 +23,12 @@
 #include <climits>
 #include <cstdlib>
 
+#include "geometry.cuh"
 #include "problem.cuh"
 
 namespace rt {
+
+int g_fused_eval = 1;  // see problem.cuh
 
 namespace {
 
@@ -87,6 +90,9 @@ struct EvalArgs {
     const int *npos;
     const int4 *RA, *RB, *RC, *RD, *H;
     const int2 *E, *SK;
+    const double *PX;        // [batch][3][pstride] position-ordered unit vectors (the no-G kernels rebuild cells from them)
+    float fd, ft;            // R * dist_scale, R * time_scale
+    int lim_hi;              // fast_path_limit_hi(fd, ft)
     const int *rstart;       // [batch][rstride + 1] separator positions (route r owns rstart[r] .. rstart[r+1]-1)
     int rstride;
     int n, pitch, pstride;
@@ -110,6 +116,73 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
     hi = static_cast<int>(static_cast<long long>(P) * (idx + 1) / cnt);
 }
 
+enum { kBest = 0, kDump = 1, kTable = 2 };
+
+// Everything a thread of the tile kernels knows about its column q.
+struct ColQ {
+    int4 Hq, qB;
+    int dep_q, zn_q, depprev_q, capsl_q, distsl_q;
+    int q, q_route;
+    bool rel_q, swap_q;
+};
+
+// relocate(p -> between q and q+1) and swap(p, q) for one customer row p against column q: delta AND feasibility,
+// straight line.  Cells: c_up = (p-1, q), c_rt = (p, q+1); a_cur = (p, q), a_lf = (p, q-1), a_dn = (p+1, q) in the
+// orientation that leads towards p's side (the same cells when the matrix is symmetric).
+template <int MODE>
+__device__ __forceinline__ void score_pair(const EvalArgs &a, int P, int p, const int4 &Hp, const int4 &p1, const int4 &p2,
+                                           const ColQ &c, bool swap_tile, int2 c_up, int2 c_rt, int2 a_cur, int2 a_lf,
+                                           int2 a_dn, int &best_d, unsigned &best_i)
+{
+    constexpr bool DUMP = MODE == kDump;
+    const int q = c.q;
+    const bool other = (Hp.w & 0x7FFF) != c.q_route;
+    // relocate(p -> between q and q+1): a -> u -> b replaces a -> b in route[q]
+    const int ins = fadd(fadd(a_cur.x, c_rt.x), -c.Hq.z);
+    const int d_rel = fadd(Hp.x, ins);
+    const int tu = max(p1.x, fadd(c.dep_q, a_cur.y));
+    const bool v_rel = c.rel_q && other;
+    const bool ok_rel = v_rel && ((Hp.w >> 29) & 1) && p1.w <= c.capsl_q && ins <= c.distsl_q && tu <= p1.y &&
+                        fadd(fadd(tu, p1.z), c_rt.y) <= c.zn_q;
+    if (DUMP) {
+        if (v_rel && a.dump_family == 1) {
+            a.dump_delta[static_cast<size_t>(p) * P + q] = d_rel;
+            a.dump_feas[static_cast<size_t>(p) * P + q] = ok_rel ? 1 : 0;
+        }
+    } else if (ok_rel && d_rel <= best_d) {  // rarely true: the update stays off the straight-line path
+        const unsigned idx = (1u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q);
+        if (d_rel < best_d || idx < best_i) {
+            best_d = d_rel;
+            best_i = idx;
+        }
+    }
+    if (swap_tile) {
+        // swap(p, q), p < q: pu -> v -> nu in route[p], pw -> u -> nw in route[q]
+        const int d1 = fadd(fadd(c_up.x, a_dn.x), -Hp.y);
+        const int d2 = fadd(fadd(a_lf.x, c_rt.x), -c.Hq.y);
+        const int d_swap = fadd(d1, d2);
+        const int tv = max(c.qB.x, fadd(p2.y, c_up.y));
+        const int tw = max(p1.x, fadd(c.depprev_q, a_lf.y));
+        const int dd = fadd(c.qB.w, -p1.w);
+        const bool v_swap = c.swap_q && other && p < q;
+        const bool ok_swap = v_swap && dd <= p2.z && -dd <= c.capsl_q && d1 <= p2.w && d2 <= c.distsl_q &&
+                             tv <= c.qB.y && fadd(fadd(tv, c.qB.z), a_dn.y) <= p2.x && tw <= p1.y &&
+                             fadd(fadd(tw, p1.z), c_rt.y) <= c.zn_q;
+        if (DUMP) {
+            if (v_swap && a.dump_family == 2) {
+                a.dump_delta[static_cast<size_t>(p) * P + q] = d_swap;
+                a.dump_feas[static_cast<size_t>(p) * P + q] = ok_swap ? 1 : 0;
+            }
+        } else if (ok_swap && d_swap <= best_d) {
+            const unsigned idx = (2u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q);
+            if (d_swap < best_d || idx < best_i) {
+                best_d = d_swap;
+                best_i = idx;
+            }
+        }
+    }
+}
+
 // grid (column strips of 128, row strips of kStripRows within the shard, instances).
 // Straight-line evaluation: in a realistic state a large share of the candidates has a delta below the best
 // feasible one while being infeasible (capacity, windows), so pruning on the delta leaves almost every warp with
@@ -117,8 +190,6 @@ __device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, in
 // Per row three broadcast LDS.128 bring everything about p; everything about q lives in registers.
 // MODE: kBest = one key per instance, kDump = every candidate of one family (tests), kTable = one key per ordered
 // route pair (the thread's column fixes the second route; its best is flushed whenever the row's route changes).
-enum { kBest = 0, kDump = 1, kTable = 2 };
-
 template <int MODE, bool ASYM>
 __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel(const EvalArgs a)
 {
@@ -173,6 +244,7 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
     const bool q_cust = q_in && ((Hq.w >> 30) & 1);
     const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
     const bool swap_q = q_cust && (a.families & 4);
+    const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q};
     const bool swap_tile = (a.families & 4) && p0 < q0 + kInterThreads - 1;  // some pair of the tile has p < q
 
     int best_d = INT_MAX;
@@ -226,55 +298,11 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
         const int4 Hp = sH[rr];
         if ((Hp.w >> 30) & 1) {  // p is a customer (warp-uniform)
             const int4 p1 = sP1[rr], p2 = sP2[rr];
-            const bool other = (Hp.w & 0x7FFF) != q_route;
             if (TABLE && (Hp.w & 0x7FFF) != cur_ra) {  // warp-uniform: p is the same for the whole block
                 flush();
                 cur_ra = Hp.w & 0x7FFF;
             }
-            // relocate(p -> between q and q+1): a -> u -> b replaces a -> b in route[q]
-            const int ins = fadd(fadd(a_cur.x, c_rt.x), -Hq.z);
-            const int d_rel = fadd(Hp.x, ins);
-            const int tu = max(p1.x, fadd(dep_q, a_cur.y));
-            const bool v_rel = rel_q && other;
-            const bool ok_rel = v_rel && ((Hp.w >> 29) & 1) && p1.w <= capsl_q && ins <= distsl_q && tu <= p1.y &&
-                                fadd(fadd(tu, p1.z), c_rt.y) <= zn_q;
-            if (DUMP) {
-                if (v_rel && a.dump_family == 1) {
-                    a.dump_delta[static_cast<size_t>(p) * P + q] = d_rel;
-                    a.dump_feas[static_cast<size_t>(p) * P + q] = ok_rel ? 1 : 0;
-                }
-            } else if (ok_rel && d_rel <= best_d) {  // rarely true: the update stays off the straight-line path
-                const unsigned idx = (1u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q);
-                if (d_rel < best_d || idx < best_i) {
-                    best_d = d_rel;
-                    best_i = idx;
-                }
-            }
-            if (swap_tile) {
-                // swap(p, q), p < q: pu -> v -> nu in route[p], pw -> u -> nw in route[q]
-                const int d1 = fadd(fadd(c_up.x, a_dn.x), -Hp.y);
-                const int d2 = fadd(fadd(a_lf.x, c_rt.x), -Hq.y);
-                const int d_swap = fadd(d1, d2);
-                const int tv = max(qB.x, fadd(p2.y, c_up.y));
-                const int tw = max(p1.x, fadd(depprev_q, a_lf.y));
-                const int dd = fadd(qB.w, -p1.w);
-                const bool v_swap = swap_q && other && p < q;
-                const bool ok_swap = v_swap && dd <= p2.z && -dd <= capsl_q && d1 <= p2.w && d2 <= distsl_q &&
-                                     tv <= qB.y && fadd(fadd(tv, qB.z), a_dn.y) <= p2.x && tw <= p1.y &&
-                                     fadd(fadd(tw, p1.z), c_rt.y) <= zn_q;
-                if (DUMP) {
-                    if (v_swap && a.dump_family == 2) {
-                        a.dump_delta[static_cast<size_t>(p) * P + q] = d_swap;
-                        a.dump_feas[static_cast<size_t>(p) * P + q] = ok_swap ? 1 : 0;
-                    }
-                } else if (ok_swap && d_swap <= best_d) {
-                    const unsigned idx = (2u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q);
-                    if (d_swap < best_d || idx < best_i) {
-                        best_d = d_swap;
-                        best_i = idx;
-                    }
-                }
-            }
+            score_pair<MODE>(a, P, p, Hp, p1, p2, col, swap_tile, c_up, c_rt, a_cur, a_lf, a_dn, best_d, best_i);
         }
         c_up = c_cur;
         c_lf = n_lf;
@@ -287,6 +315,161 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
         t_cur = tn_cur;
         tn_lf = tm_lf;
         tn_cur = tm_cur;
+    }
+    if (TABLE) {
+        flush();
+    } else if (!DUMP) {
+        const unsigned long long best =
+            best_i == 0xFFFFFFFFu
+                ? kNoMove
+                : (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i;
+        block_min_to_global<kInterThreads>(best, a.best + b, a.signed_dst != 0);
+    }
+}
+
+
+// ---- the tile kernel without a matrix --------------------------------------------------------------------------
+// For matrices that are SPEC.md §2 of the problem's own coordinates the route-order matrix need not exist: a cell
+// is ~27 instructions from two unit vectors (6 FP64 ops for the chord, then the FP32 tail of geometry.cuh — the very
+// functions matrix_kernel runs, hence the same bits), mostly on the FP64/FMA/XU pipes, which the ALU-bound scoring
+// leaves idle.  A thread owns column q and keeps q's unit vector in registers; the strip's row vectors sit in shared
+// memory (broadcast LDS); per row it computes ONE new cell, (p+1, q), rotates (p, q) and (p-1, q) down its register
+// window, and gets (p, q-1) and (p, q+1) from its lane neighbours with four shuffles.  Lanes 0 and 31 of a warp only
+// feed their neighbours (a warp scores 30 columns).  No G write, no G read: a pass touches O(n) bytes of HBM.
+constexpr int kFusedCols = 120;  // columns scored per block: 4 warps x 30
+
+__device__ __forceinline__ int2 cell_from_vectors(double ax, double ay, double az, double bx, double by, double bz, float fd,
+                                                  float ft, int lim_hi)
+{
+    const double dx = ax - bx, dy = ay - by, dz = az - bz;
+    const double s2 = fma(dx, dx, fma(dy, dy, dz * dz));
+    return __double2hiint(s2) < lim_hi ? cell_i32_fast(s2, fd, ft) : cell_i32(ax, ay, az, bx, by, bz, fd, ft);
+}
+
+// One shared-memory slot per row of the strip (+2): slot i holds the unit vector of position p0 - 1 + i and, for
+// i < rows, the three records of strip row i.  One array and explicit 32-bit shared addresses: with three separate
+// arrays indexed by the (uniform) loop counter the compiler rebuilt every array's shared-window address in the uniform
+// datapath on every iteration — a quarter of the loop's instructions.
+struct __align__(16) RowSlot {
+    int4 H, P1, P2;
+    double vx, vy, vz, pad;
+};
+static_assert(sizeof(RowSlot) == 80, "row slot layout");
+
+__device__ __forceinline__ int4 lds128(unsigned addr)
+{
+    int4 v;
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
+__device__ __forceinline__ double lds64(unsigned addr)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(const EvalArgs a)
+{
+    constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
+    __shared__ RowSlot slots[kMaxStripRows + 2];
+    const int kStripRows = a.strip_rows;
+
+    const int b = DUMP ? a.dump_instance : blockIdx.z;
+    const int P = a.npos[b];
+    int p_lo, p_hi;
+    shard_range(P, a.shard_index, a.shard_count, p_lo, p_hi);
+    const int p0 = p_lo + blockIdx.y * kStripRows, q0 = blockIdx.x * kFusedCols;
+    if (p0 >= p_hi || q0 >= P) return;
+
+    const size_t po = static_cast<size_t>(b) * a.pstride;
+    const double *__restrict__ PX = a.PX + static_cast<size_t>(b) * 3 * a.pstride;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int q = q0 + (tid >> 5) * 30 + lane - 1;            // lanes 0 and 31 are the warp's halo columns
+    const bool owner = lane >= 1 && lane <= 30;
+    const bool q_in = owner && q < P;
+    const int rows = min(kStripRows, p_hi - p0);
+    if (tid < rows + 2) {
+        RowSlot sl;
+        sl.H = sl.P1 = sl.P2 = make_int4(0, 0, 0, 0);
+        if (tid < rows && p0 + tid < P) {
+            const size_t o = po + p0 + tid;
+            const int4 rA = a.RA[o], rC = a.RC[o], rD = a.RD[o];
+            sl.H = a.H[o];
+            sl.H.w |= (rC.w & 2) << 28;  // rem_ok -> bit 29
+            sl.P1 = a.RB[o];
+            sl.P2 = make_int4(rA.y, rC.x, rD.x, rD.y);
+        }
+        const int pv = min(max(p0 - 1 + tid, 0), a.pstride - 1);
+        sl.vx = PX[pv];
+        sl.vy = PX[a.pstride + pv];
+        sl.vz = PX[2 * static_cast<size_t>(a.pstride) + pv];
+        sl.pad = 0.0;
+        slots[tid] = sl;
+    }
+    int4 Hq = make_int4(0, 0, 0, -1), qB = make_int4(0, 0, 0, 0);
+    int dep_q = 0, zn_q = 0, depprev_q = 0, capsl_q = 0, distsl_q = 0;
+    if (q_in) {
+        const int4 rA = a.RA[po + q], rC = a.RC[po + q], rD = a.RD[po + q];
+        Hq = a.H[po + q];
+        qB = a.RB[po + q];
+        dep_q = rA.x;
+        zn_q = rA.y;
+        depprev_q = rC.x;
+        capsl_q = rD.x;
+        distsl_q = rD.y;
+    }
+    const int qv = min(max(q, 0), a.pstride - 1);   // positions beyond P repeat the depot's vector
+    const double bx = PX[qv], by = PX[a.pstride + qv], bz = PX[2 * static_cast<size_t>(a.pstride) + qv];
+    __syncthreads();
+
+    const int q_route = Hq.w & 0x7FFF;
+    const bool q_cust = q_in && ((Hq.w >> 30) & 1);
+    const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
+    const bool swap_q = q_cust && (a.families & 4);
+    const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q};
+    const bool swap_tile = (a.families & 4) && p0 < q0 + kFusedCols - 1;  // some pair of the tile has p < q
+
+    int best_d = INT_MAX;
+    unsigned best_i = 0xFFFFFFFFu;
+    int cur_ra = -1;
+    unsigned long long *trow = TABLE ? a.inter + static_cast<size_t>(b) * a.cr * a.cr + q_route : nullptr;
+    auto flush = [&]() {
+        if (best_i != 0xFFFFFFFFu)
+            atomicMin(trow + static_cast<size_t>(cur_ra) * a.cr,
+                      (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i);
+        best_d = INT_MAX;
+        best_i = 0xFFFFFFFFu;
+    };
+    // slot address in a per-thread register (the shift is zero for every thread of a 128-thread block; it only keeps
+    // the compiler from proving the address uniform and moving it back into the uniform datapath)
+    unsigned sa = static_cast<unsigned>(__cvta_generic_to_shared(slots)) + (threadIdx.x >> 10);
+    const float fd = a.fd, ft = a.ft;
+    const int lim_hi = a.lim_hi;
+    auto cell_slot = [&](unsigned addr) {  // cell(position of that slot, q)
+        return cell_from_vectors(lds64(addr + 48), lds64(addr + 56), lds64(addr + 64), bx, by, bz, fd, ft, lim_hi);
+    };
+    int2 c_up = cell_slot(sa), c_cur = cell_slot(sa + 80);
+    const unsigned full = 0xffffffffu;
+#pragma unroll 2
+    for (int rr = 0; rr < rows; ++rr, sa += 80) {
+        const int p = p0 + rr;
+        const int2 c_dn = cell_slot(sa + 160);
+        const int4 Hp = lds128(sa);
+        if ((Hp.w >> 30) & 1) {  // p is a customer (block-uniform)
+            const int2 c_lf = make_int2(__shfl_up_sync(full, c_cur.x, 1), __shfl_up_sync(full, c_cur.y, 1));
+            const int2 c_rt = make_int2(__shfl_down_sync(full, c_cur.x, 1), __shfl_down_sync(full, c_cur.y, 1));
+            const int4 p1 = lds128(sa + 16), p2 = lds128(sa + 32);
+            if (TABLE && (Hp.w & 0x7FFF) != cur_ra) {
+                flush();
+                cur_ra = Hp.w & 0x7FFF;
+            }
+            score_pair<MODE>(a, P, p, Hp, p1, p2, col, swap_tile, c_up, c_rt, c_cur, c_lf, c_dn, best_d, best_i);
+        }
+        c_up = c_cur;
+        c_cur = c_dn;
     }
     if (TABLE) {
         flush();
@@ -327,9 +510,10 @@ __device__ __forceinline__ bool seg_fits(const Seg &m, int t, int tail, int limi
 
 constexpr int kIntraThreads = 128;
 
-template <int MODE, bool ASYM>
+template <int MODE, bool ASYM, bool FUSED = false>
 __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArgs a)
 {
+    static_assert(!(ASYM && FUSED), "cells are rebuilt from unit vectors only for the symmetric SPEC 2 matrix");
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
     const int b = DUMP ? a.dump_instance : blockIdx.y;
     const int P = a.npos[b];
@@ -356,10 +540,33 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
         const int dep_t = tA.x;            // B[t] + service[node t]
         const int dep_tm1 = tC.x;          // B[t-1] + service[node t-1]   (customers only)
         const int2 SKt = SK[t];            // cell(node t-1, node t+1)
-        // rows t-1, t, t+1 of the route-order matrix; the sweep reads them at consecutive columns x+1
+        // rows t-1, t, t+1 of the route-order matrix; the sweep reads them at consecutive columns x+1 — or, without a
+        // matrix, rebuilds those cells from the unit vectors of the three rows (registers) and of the column
         const int2 *row_m = G + static_cast<size_t>(max(t - 1, 0)) * a.gpitch;
         const int2 *row_0 = G + static_cast<size_t>(t) * a.gpitch;
         const int2 *row_p = G + static_cast<size_t>(t + 1) * a.gpitch;
+        const double *PXb = a.PX + static_cast<size_t>(b) * 3 * a.pstride;
+        double vm[3] = {0, 0, 0}, v0[3] = {0, 0, 0}, vp[3] = {0, 0, 0};
+        if (FUSED) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                vm[k] = PXb[static_cast<size_t>(k) * a.pstride + max(t - 1, 0)];
+                v0[k] = PXb[static_cast<size_t>(k) * a.pstride + t];
+                vp[k] = PXb[static_cast<size_t>(k) * a.pstride + t + 1];
+            }
+        }
+        auto cells_at = [&](int col, int2 &o_m, int2 &o_0, int2 &o_p) {
+            if (FUSED) {
+                const double cx = PXb[col], cy = PXb[a.pstride + col], cz = PXb[2 * static_cast<size_t>(a.pstride) + col];
+                o_m = cell_from_vectors(vm[0], vm[1], vm[2], cx, cy, cz, a.fd, a.ft, a.lim_hi);
+                o_0 = cell_from_vectors(v0[0], v0[1], v0[2], cx, cy, cz, a.fd, a.ft, a.lim_hi);
+                o_p = cell_from_vectors(vp[0], vp[1], vp[2], cx, cy, cz, a.fd, a.ft, a.lim_hi);
+            } else {
+                o_m = __ldg(row_m + col);
+                o_0 = __ldg(row_0 + col);
+                o_p = __ldg(row_p + col);
+            }
+        };
         // asymmetric matrices: the cells that lead from x back to t / t+1 come from the transposed array
         const int2 *GTb = ASYM ? a.GT + static_cast<size_t>(b) * a.grows * a.gpitch : G;
         const int2 *trow_0 = GTb + static_cast<size_t>(t) * a.gpitch;
@@ -381,7 +588,8 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
         // steps: one memory round trip per step instead of two).
         const int x_end = a.rstart[static_cast<size_t>(b) * (a.rstride + 1) + t_route + 1];
         int4 nA = RA[t + 1], nB = t1B, nC = RC[t + 1], nD = RD[t + 1];
-        int2 ncm = __ldg(row_m + t + 2), nc0 = __ldg(row_0 + t + 2), ncp = __ldg(row_p + t + 2);
+        int2 ncm, nc0, ncp;
+        cells_at(t + 2, ncm, nc0, ncp);
         for (int x = t + 1; x < x_end; ++x) {
             const int4 xA = nA, xB = nB, xC = nC, xD = nD;
             const int2 Ex = make_int2(xA.z, xD.z);  // cell(node x, node x+1)
@@ -393,9 +601,7 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
             nB = RB[x + 1];
             nC = RC[x + 1];
             nD = RD[x + 1];
-            ncm = __ldg(row_m + x + 2);
-            nc0 = __ldg(row_0 + x + 2);
-            ncp = __ldg(row_p + x + 2);
+            cells_at(x + 2, ncm, nc0, ncp);
             const int2 r01 = ASYM ? __ldg(trow_0 + x + 1) : c01;
             const int2 rp1 = ASYM ? __ldg(trow_p + x + 1) : cp1;
             const Seg sx = seg_single(xB.x, xB.y);
@@ -527,7 +733,7 @@ __device__ __forceinline__ Seg seg_of(const SegW &s) { return Seg{s.a, s.b, s.L,
 
 constexpr int kIntraWarps = 4;
 
-template <int MODE>
+template <int MODE, bool FUSED = false>
 __global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const EvalArgs a)
 {
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
@@ -557,6 +763,16 @@ __global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const
         const int2 *row_p = G + static_cast<size_t>(t + 1) * a.gpitch;
         const bool f2 = a.families & 1, f_rel = a.families & 2, f_swap = a.families & 4;
         const Seg st_single = seg_single(tB.x, tB.y);
+        const double *PXb = a.PX + static_cast<size_t>(b) * 3 * a.pstride;
+        double vm[3] = {0, 0, 0}, v0[3] = {0, 0, 0}, vp[3] = {0, 0, 0};  // unit vectors of t-1, t, t+1 (no-G form)
+        if (FUSED) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                vm[k] = PXb[static_cast<size_t>(k) * a.pstride + max(t - 1, 0)];
+                v0[k] = PXb[static_cast<size_t>(k) * a.pstride + t];
+                vp[k] = PXb[static_cast<size_t>(k) * a.pstride + t + 1];
+            }
+        }
 
         // carries from the previous chunk (positions below `base`): forward segment t+1..base-1, reversed base-1..t+1,
         // service time and outgoing edge of base-1, cell (t, base-1)
@@ -568,8 +784,22 @@ __global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const
             const bool in = x < x_end;
             const int xx = in ? x : x_end - 1;     // lanes beyond the route re-read its last position; never reported
             const int4 xA = RA[xx], xB = RB[xx], xC = RC[xx], xD = RD[xx];
-            const int2 cm = __ldg(row_m + xx), c0 = __ldg(row_0 + xx), c01 = __ldg(row_0 + xx + 1);
-            const int2 cp = __ldg(row_p + xx), cp1 = __ldg(row_p + xx + 1);
+            int2 cm, c0, c01, cp, cp1;
+            if (FUSED) {
+                const double ax = PXb[xx], ay = PXb[a.pstride + xx], az = PXb[2 * static_cast<size_t>(a.pstride) + xx];
+                const double ux = PXb[xx + 1], uy = PXb[a.pstride + xx + 1], uz = PXb[2 * static_cast<size_t>(a.pstride) + xx + 1];
+                cm = cell_from_vectors(vm[0], vm[1], vm[2], ax, ay, az, a.fd, a.ft, a.lim_hi);
+                c0 = cell_from_vectors(v0[0], v0[1], v0[2], ax, ay, az, a.fd, a.ft, a.lim_hi);
+                cp = cell_from_vectors(vp[0], vp[1], vp[2], ax, ay, az, a.fd, a.ft, a.lim_hi);
+                c01 = cell_from_vectors(v0[0], v0[1], v0[2], ux, uy, uz, a.fd, a.ft, a.lim_hi);
+                cp1 = cell_from_vectors(vp[0], vp[1], vp[2], ux, uy, uz, a.fd, a.ft, a.lim_hi);
+            } else {
+                cm = __ldg(row_m + xx);
+                c0 = __ldg(row_0 + xx);
+                c01 = __ldg(row_0 + xx + 1);
+                cp = __ldg(row_p + xx);
+                cp1 = __ldg(row_p + xx + 1);
+            }
             const int2 Ex = make_int2(xA.z, xD.z);  // cell(node x, node x+1)
             const int zn = xA.y;                    // Z[x+1]
             int svc_xm1 = __shfl_up_sync(0xffffffffu, xB.z, 1);
@@ -703,12 +933,12 @@ __global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const
 int g_strip_rows = 0;    // rt_debug_set("strip_rows", h): 0 = pick, else the height to use
 int g_intra_kernel = 0;  // rt_debug_set("intra_kernel", k): 0 = pick, 1 = one thread per anchor, 2 = one warp per anchor
 
-int pick_strip_rows(int pmax, int rows, int batch, bool asym)
+int pick_strip_rows(int pmax, int rows, int batch, bool asym, int cols_per_block)
 {
     static const int env = getenv("ROUTEST_STRIP_ROWS") ? atoi(getenv("ROUTEST_STRIP_ROWS")) : 0;
     const int forced = g_strip_rows ? g_strip_rows : env;
     if (forced >= 8 && forced <= kMaxStripRows) return forced;
-    const long long col_blocks = (pmax + kInterThreads - 1) / kInterThreads;
+    const long long col_blocks = (pmax + cols_per_block - 1) / cols_per_block;
     const long long blocks64 = col_blocks * ((rows + 63) / 64) * batch;
     return (!asym && blocks64 >= 4LL * kNumSMs * 9) ? 64 : kStripRows;
 }
@@ -725,14 +955,33 @@ bool intra_by_warp(const rt_problem *p, int shard_rows)
 template <int MODE>
 int launch_intra(rt_problem *p, const EvalArgs &a, int shard_rows, int batch, cudaStream_t st)
 {
+    const bool fused = eval_without_matrix(p);
     if (intra_by_warp(p, shard_rows)) {
         dim3 grid((shard_rows + kIntraWarps - 1) / kIntraWarps, batch);
-        eval_intra_warp_kernel<MODE><<<grid, kIntraWarps * 32, 0, st>>>(a);
+        if (fused) eval_intra_warp_kernel<MODE, true><<<grid, kIntraWarps * 32, 0, st>>>(a);
+        else eval_intra_warp_kernel<MODE, false><<<grid, kIntraWarps * 32, 0, st>>>(a);
     } else {
         dim3 grid((shard_rows + kIntraThreads - 1) / kIntraThreads, batch);
-        if (p->symmetric) eval_intra_kernel<MODE, false><<<grid, kIntraThreads, 0, st>>>(a);
+        if (fused) eval_intra_kernel<MODE, false, true><<<grid, kIntraThreads, 0, st>>>(a);
+        else if (p->symmetric) eval_intra_kernel<MODE, false><<<grid, kIntraThreads, 0, st>>>(a);
         else eval_intra_kernel<MODE, true><<<grid, kIntraThreads, 0, st>>>(a);
     }
+    RT_CUDA(p->e, cudaGetLastError());
+    return RT_OK;
+}
+
+// The tile kernel of this launch: without a matrix where the cells are SPEC 2 of the problem's coordinates, on G
+// (and GT for a directional matrix) otherwise.
+template <int MODE>
+int launch_inter(rt_problem *p, EvalArgs &a, int pmax, int shard_rows, int batch, int strip_rows, cudaStream_t st)
+{
+    const bool fused = eval_without_matrix(p);
+    const int cols = fused ? kFusedCols : kInterThreads;
+    a.strip_rows = strip_rows > 0 ? strip_rows : pick_strip_rows(pmax, shard_rows, batch, !p->symmetric, cols);
+    dim3 grid((pmax + cols - 1) / cols, (shard_rows + a.strip_rows - 1) / a.strip_rows, batch);
+    if (fused) eval_inter_fused_kernel<MODE><<<grid, kInterThreads, 0, st>>>(a);
+    else if (p->symmetric) eval_inter_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
+    else eval_inter_kernel<MODE, true><<<grid, kInterThreads, 0, st>>>(a);
     RT_CUDA(p->e, cudaGetLastError());
     return RT_OK;
 }
@@ -754,6 +1003,10 @@ EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count
     a.H = p->H;
     a.E = p->E;
     a.SK = p->SK;
+    a.PX = p->PX;
+    a.fd = static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale);
+    a.ft = static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale);
+    a.lim_hi = fast_path_limit_hi(a.fd, a.ft);
     a.rstart = p->rstart;
     a.rstride = p->rstride;
     a.n = p->n;
@@ -818,13 +1071,7 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
         st_intra = p->side_stream;
     }
     RT_TRY(launch_intra<kBest>(p, a, shard_rows, p->batch, st_intra));
-    if (families & 6) {
-        a.strip_rows = pick_strip_rows(pmax, shard_rows, p->batch, !p->symmetric);
-        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + a.strip_rows - 1) / a.strip_rows, p->batch);
-        if (!p->symmetric) eval_inter_kernel<kBest, true><<<grid, kInterThreads, 0, st>>>(a);
-        else eval_inter_kernel<kBest, false><<<grid, kInterThreads, 0, st>>>(a);
-        RT_CUDA(e, cudaGetLastError());
-    }
+    if (families & 6) RT_TRY(launch_inter<kBest>(p, a, pmax, shard_rows, p->batch, 0, st));
     if (overlap) {
         RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
         RT_CUDA(e, cudaStreamWaitEvent(st, p->ev_join, 0));
@@ -859,13 +1106,8 @@ int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_co
         st_intra = p->side_stream;
     }
     RT_TRY(launch_intra<kTable>(p, a, shard_rows, p->batch, st_intra));
-    if (families & 6) {
-        a.strip_rows = kStripRows;  // table mode flushes per route change: short strips keep the flush count low
-        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (shard_rows + kStripRows - 1) / kStripRows, p->batch);
-        if (p->symmetric) eval_inter_kernel<kTable, false><<<grid, kInterThreads, 0, st>>>(a);
-        else eval_inter_kernel<kTable, true><<<grid, kInterThreads, 0, st>>>(a);
-        RT_CUDA(e, cudaGetLastError());
-    }
+    // table mode flushes per route change: short strips keep the flush count low
+    if (families & 6) RT_TRY(launch_inter<kTable>(p, a, pmax, shard_rows, p->batch, kStripRows, st));
     if (overlap) {
         RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
         RT_CUDA(e, cudaStreamWaitEvent(st, p->ev_join, 0));
@@ -880,19 +1122,13 @@ int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_co
 
 int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsigned char *feas_d, cudaStream_t st)
 {
-    rt_engine *e = p->e;
     EvalArgs a = make_args(p, 1 << family, 0, 1, p->best);
     a.dump_instance = instance;
     a.dump_family = family;
     a.dump_delta = delta_d;
     a.dump_feas = feas_d;
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
-    if (family != 0) {
-        dim3 grid((pmax + kInterThreads - 1) / kInterThreads, (pmax + kStripRows - 1) / kStripRows, 1);
-        if (p->symmetric) eval_inter_kernel<kDump, false><<<grid, kInterThreads, 0, st>>>(a);
-        else eval_inter_kernel<kDump, true><<<grid, kInterThreads, 0, st>>>(a);
-        RT_CUDA(e, cudaGetLastError());
-    }
+    if (family != 0) RT_TRY(launch_inter<kDump>(p, a, pmax, pmax, 1, kStripRows, st));
     return launch_intra<kDump>(p, a, pmax, 1, st);
 }
 
@@ -903,6 +1139,7 @@ extern "C" int rt_debug_set(const char *name, int value)
     if (!name) return RT_ERR_INVALID_ARG;
     if (!strcmp(name, "strip_rows")) rt::g_strip_rows = value;
     else if (!strcmp(name, "intra_kernel")) rt::g_intra_kernel = value;
+    else if (!strcmp(name, "fused_eval")) rt::g_fused_eval = value;
     else return RT_ERR_INVALID_ARG;
     return RT_OK;
 }

@@ -526,9 +526,16 @@ int rt_problem_refresh_dev(rt_problem *p, int what, void *stream)
     if (!p) return RT_ERR_INVALID_ARG;
     rt_engine *e = p->e;
     if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_refresh_dev: no routes set");
-    if (!(what & 3)) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_refresh_dev: what must have bit 0 and/or bit 1 set");
+    if (!(what & 7)) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_refresh_dev: what must have bit 0, 1 or 2 set");
     DeviceGuard dg(e->device);
     cudaStream_t st = pick_stream(e, stream);
+    if (what & 4) {  // the route-order matrix itself, whether or not the move kernels read one
+        RT_TRY(position_matrix_refresh(p, st));
+        what &= ~1;
+        if (!(what & 3)) return RT_OK;
+    }
+    if (eval_without_matrix(p)) what &= ~1;  // bit 0: "what the move kernels need of the matrix" — nothing here
+    if (!(what & 3)) return RT_OK;
     // both: the state tables run on the side stream underneath the matrix kernel; the tables alone re-derive the
     // position-ordered unit vectors themselves, so bit 1 never depends on an earlier bit-0 refresh
     if ((what & 3) == 3) return state_refresh(p, st);
@@ -745,8 +752,9 @@ int rt_problem_get_position_matrix(rt_problem *p, int instance, int32_t *dist, i
     RT_PROBLEM_GUARD(p);
     if (!dist || !tim || instance < 0 || instance >= p->batch)
         return fail(e, RT_ERR_INVALID_ARG, "rt_problem_get_position_matrix: bad argument");
-    if (!p->has_routes || !p->Gbuf.p) return fail(e, RT_ERR_STATE, "rt_problem_get_position_matrix: no routes set");
+    if (!p->has_routes) return fail(e, RT_ERR_STATE, "rt_problem_get_position_matrix: no routes set");
     if (p->shard_count != 1) return fail(e, RT_ERR_STATE, "rt_problem_get_position_matrix needs shard 0/1");
+    if (eval_without_matrix(p)) RT_TRY(position_matrix_refresh(p, e->stream));  // not kept fresh when nothing reads it
     int P = 0;
     RT_CUDA(e, cudaMemcpy(&P, p->npos + instance, 4, cudaMemcpyDeviceToHost));
     const size_t cnt = static_cast<size_t>(P) * P;

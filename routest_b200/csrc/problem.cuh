@@ -97,6 +97,12 @@ struct rt_problem {
 
 namespace rt {
 
+// rt_debug_set("fused_eval", v): 1 (default) = the move kernels rebuild matrix cells from the position-ordered unit
+// vectors wherever the matrix is SPEC 2 of the problem's own coordinates, so no route-order matrix is written or read;
+// 0 = always materialise G and read it (the write-then-read form, kept for measurement and for supplied matrices).
+extern int g_fused_eval;
+inline bool eval_without_matrix(const rt_problem *p) { return g_fused_eval != 0 && p->cells_from_coords && p->symmetric; }
+
 // first cell of G (the buffer starts with 16 pad cells)
 inline int2 *position_matrix(const rt_problem *p) { return p->Gbuf.p ? static_cast<int2 *>(p->Gbuf.p) + 16 : nullptr; }
 inline int2 *position_matrix_t(const rt_problem *p) { return p->GTbuf.p ? static_cast<int2 *>(p->GTbuf.p) + 16 : nullptr; }
@@ -131,6 +137,6 @@ size_t batch_table_entries(const rt_problem *p);
 int batch_select_apply(rt_problem *p, const unsigned long long *table, bool signed_keys, cudaStream_t st);
 int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *table_d,
                       bool signed_keys, cudaStream_t st);
-int ensure_position_matrix(rt_problem *p);  // sizes G for p->pmax (may allocate; not stream-ordered)
+int ensure_position_matrix(rt_problem *p, bool need_buffer = false);  // sizes G for p->pmax (may allocate; not stream-ordered)
 
 }  // namespace rt

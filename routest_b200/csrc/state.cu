@@ -624,12 +624,15 @@ __global__ void __launch_bounds__(256) apply_moves_kernel(const unsigned long lo
 
 }  // namespace
 
-int ensure_position_matrix(rt_problem *p)
+int ensure_position_matrix(rt_problem *p, bool need_buffer)
 {
     const int rows = p->pmax > 0 ? p->pmax : p->pstride;
     const int pitch = (rows + 15) & ~15;
     p->grows = rows;
     p->gpitch = pitch;
+    // Where the move kernels rebuild their cells from the unit vectors no buffer is needed until somebody asks for the
+    // matrix itself (rt_problem_get_position_matrix, rt_problem_refresh_dev bit 2): 843 MB at 10,000 stops.
+    if (!need_buffer && eval_without_matrix(p)) return RT_OK;
     // 16 pad cells in front and pad rows behind: the move kernels read q-1, q+1 and p+2 without clamping and
     // prefetch up to ten rows ahead
     if (!p->symmetric)
@@ -642,8 +645,9 @@ int ensure_position_matrix(rt_problem *p)
 int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready)
 {
     rt_engine *e = p->e;
+    if (p->grows <= 0) return fail(e, RT_ERR_STATE, "route state refresh before routes were installed");
+    RT_TRY(ensure_position_matrix(p, /*need_buffer=*/true));  // a no-op once the buffer has its size
     int2 *G = position_matrix(p);
-    if (!p->Gbuf.p || p->grows <= 0) return fail(e, RT_ERR_STATE, "route state refresh before routes were installed");
     // rows any instance of the batch can need: shard [P*i/c, P*(i+1)/c) over P in [pmin, pmax], one halo row each side
     int r0 = 0, r1 = p->grows;
     if (p->shard_count > 1) {
@@ -739,6 +743,11 @@ int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for, b
         dim3 g0((p->pstride + 255) / 256, p->batch);
         position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
         RT_CUDA(e, cudaGetLastError());
+    }
+    if (eval_without_matrix(p)) {
+        // no route-order matrix to rebuild: the kernels that follow read the unit vectors and the tables only
+        if (tables_wait_for) RT_CUDA(e, cudaStreamWaitEvent(st, tables_wait_for, 0));
+        return state_tables_refresh(p, st);
     }
     RT_CUDA(e, cudaEventRecord(p->ev_fork, st));
     RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, p->ev_fork, 0));

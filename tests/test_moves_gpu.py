@@ -577,15 +577,19 @@ def test_measured_pipe_peaks_are_plausible(engine):
     assert 1.6 < both / alu < 2.1
 
 
+@pytest.mark.parametrize("fused", [1, 0], ids=["cells-from-vectors", "route-order-matrix"])
 @pytest.mark.parametrize("kernel", [1, 2], ids=["thread-per-anchor", "warp-per-anchor"])
 @pytest.mark.parametrize("seed,stops,veh,kw", [(11, 40, 6, {}), (12, 150, 4, dict(half_lo=7200, half_hi=20000)),
                                                 (13, 260, 3, dict(half_lo=20000, half_hi=43200))])
-def test_same_route_kernels_agree_with_the_oracle(engine, kernel, seed, stops, veh, kw):
-    """Both same-route kernels (sweep per thread / segment scans per warp; rt_debug_set "intra_kernel") score every
-    candidate like the oracle — routes of 7, ~40 and ~90 positions: no carry, one carry, several carries between the
-    warp's 32-position chunks — and give the same table-mode batches and searches."""
+def test_kernel_variants_agree_with_the_oracle(engine, fused, kernel, seed, stops, veh, kw):
+    """Every variant of the move kernels scores every candidate like the oracle: the same-route kernels (sweep per
+    thread / segment scans per warp; rt_debug_set "intra_kernel") on routes of 7, ~40 and ~90 positions — no carry,
+    one carry, several carries between the warp's 32-position chunks — and both sources of matrix cells ("fused_eval":
+    rebuilt from the unit vectors inside the kernels / read from the route-order matrix); same table-mode batches and
+    searches too."""
     inst, node0, raw = synth_vrptw(seed, stops, veh, **kw)
     engine.debug_set("intra_kernel", kernel)
+    engine.debug_set("fused_eval", fused)
     try:
         for node in (node0, _walk(inst, node0, seed, 10)):
             with _load(engine, [(inst, node0, raw)], [node]) as pr:
@@ -605,5 +609,10 @@ def test_same_route_kernels_agree_with_the_oracle(engine, kernel, seed, stops, v
             final, okeys2, ocost2 = O.local_search(inst, bfinal, max_moves=12)
             assert np.array_equal(keys[0], okeys2) and cost[0] == ocost2
             assert np.array_equal(pr.get_state(0)["node"], final)
+            P = node0.size   # the route-order matrix itself is still there for whoever asks
+            d, t = pr.get_position_matrix(0, pr.get_state(0)["P"])
+            nd = pr.get_state(0)["node"]
+            assert np.array_equal(d, inst.D[np.ix_(nd, nd)]) and np.array_equal(t, inst.T[np.ix_(nd, nd)])
     finally:
         engine.debug_set("intra_kernel", 0)
+        engine.debug_set("fused_eval", 1)

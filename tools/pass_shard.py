@@ -23,8 +23,12 @@ def main():
     ap.add_argument("--rank", type=int, default=3)
     ap.add_argument("--reps", type=int, default=50)
     ap.add_argument("--once", action="store_true")
+    ap.add_argument("--fused", type=int, default=1, help="0: write the route-order matrix and read it back")
+    ap.add_argument("--strip", type=int, default=0)
     a = ap.parse_args()
     eng = Engine(0)
+    eng.debug_set("fused_eval", a.fused)
+    eng.debug_set("strip_rows", a.strip)
     pr, w = bench.build_problem(eng, bench.SEED_10K, a.stops, a.vehicles)
     pr.set_shard(a.rank, a.world)
     keys = torch.zeros(1, dtype=torch.int64, device="cuda")
@@ -51,9 +55,9 @@ def main():
         return e0.elapsed_time(e1) / reps * 1e3
 
     replay, graphed = bench.capture(torch, one)
-    out = {"stops": a.stops, "shard": [a.rank, a.world], "graphed": graphed,
-           "us_matrix": timed(lambda: pr.refresh_dev(1, s)), "us_state": timed(lambda: pr.refresh_dev(2, s)),
-           "us_refresh_forked": timed(lambda: pr.refresh_dev(3, s)),
+    out = {"stops": a.stops, "shard": [a.rank, a.world], "fused": a.fused, "strip": a.strip, "graphed": graphed,
+           "us_matrix": timed(lambda: pr.refresh_dev(4, s)), "us_state": timed(lambda: pr.refresh_dev(2, s)),
+           "us_refresh": timed(lambda: pr.refresh_dev(3, s)),
            "us_eval": timed(lambda: pr.eval_moves_dev(keys.data_ptr(), ALL_FAMILIES, (a.rank, a.world), s)),
            "us_pass_eager": timed(lambda: one(s)), "us_pass_graph": timed(replay)}
     print(json.dumps(out))
