@@ -264,8 +264,8 @@ def workload_config(stops, vehicles, routes, P, evals, world):
                         "and time-window feasibility, best-move key per pass",
             "stops": stops, "routes": routes, "positions": P, "cells_per_step": n * n, "move_evals_per_step": evals,
             "l2": "inputs per pass are O(n) (coordinates, stop records, routes: 0.6 MB) and every pass recomputes everything "
-                  f"from them; the route-order matrix ({P * ((P + 15) // 16 * 16) * 8 / 1e6:.0f} MB / N per GPU) is an "
-                  "intermediate written and re-read inside the pass (> 126 MB L2 up to N = 4); no flush",
+                  "from them — unit vectors, route tables, every matrix cell (inside the move kernels, never stored) "
+                  "and every candidate; nothing a pass produces is reused by the next, no flush needed",
             "parallelism": parallelism}
 
 
@@ -432,10 +432,22 @@ def run_engine(args, rank, world):
 
     # ---- per-kernel timing, this rank's shard, each alone: which one dominates, and its roofline
     reps = max(args.steps, 10)
-    ms_matrix = cx.timed(lambda: pr.refresh_dev(1, stream), reps)   # position vectors + matrix kernel (shard rows)
-    ms_state = cx.timed(lambda: pr.refresh_dev(2, stream), reps)    # gather + routes + walk + records
+    ms_state = cx.timed(lambda: pr.refresh_dev(2, stream), reps)    # route scan + one warp per route
     ms_eval = cx.timed(lambda: pr.eval_moves_dev(keys.data_ptr(), ALL_FAMILIES, (rank, world), stream), reps)
     ms_own = cx.timed(replay, reps)                                 # the rank's whole pass without the exchange
+    # the matrix kernel on its own (this rank's rows of the route-order matrix, materialised: what the pass no longer
+    # does), and the whole pass in the write-then-read form it replaced — both timings kept side by side
+    ms_matrix = cx.timed(lambda: pr.refresh_dev(4, stream), reps)
+    eng.debug_set("fused_eval", 0)
+    enqueue_pass(stream)
+    torch.cuda.synchronize()
+    replay_wtr, _ = capture(torch, enqueue_pass)
+    ms_wtr = cx.timed(replay_wtr, reps)
+    key_wtr = int(keys.item())
+    eng.debug_set("fused_eval", 1)
+    replay()
+    torch.cuda.synchronize()
+    assert int(keys.item()) == key_wtr, "the two forms of the pass disagree"
     # a longer loop of the same pass so that the clock sampler sees the GPU under this very load
     t_load = time.perf_counter()
     while time.perf_counter() - t_load < 0.6:
@@ -443,10 +455,12 @@ def run_engine(args, rank, world):
             replay()
         torch.cuda.synchronize()
     clocks = sampler.stop(t_wall0, time.perf_counter()) if rank == 0 else None
-    peak_alu = peak_issue = None
+    peaks = None
     if rank == 0:
-        peak_alu, _ = eng.pipe_peak(0, 40000)
-        peak_issue, _ = eng.pipe_peak(2, 40000)
+        mixes = {m: eng.pipe_peak(m, 40000)[0] for m in (2, 3, 4)}
+        sm_hz = 1e6 * float((clocks or {}).get("sm_mhz") or 1965.0)
+        peaks = {"alu": eng.pipe_peak(0, 40000)[0], "issue_limit": 148 * 4 * sm_hz,
+                 "issue_measured_mixes": {"alu+imad": mixes[2], "alu+ffma_imm": mixes[3], "alu+imad+ffma_imm": mixes[4]}}
 
     # ---- end to end through the C ABI with pinned host buffers: upload, kernels, NCCL MIN, key back to the host
     def pinned(a):
@@ -516,19 +530,19 @@ def run_engine(args, rank, world):
             "move_evals_per_s": evals_step * args.steps / (ms / 1e3),
             "best_key": key_u, "keys_equal_oracle": keys_ok,
             "pass_graph_replayed": graphed,
-            "kernels": kernel_block(ms_matrix, ms_state, ms_eval, ms_own, P, n, world, cand),
-            "roofline": roofline_block(ms_matrix, ms_eval, P, n, world, cand, clocks, peak_alu, peak_issue),
+            "kernels": kernel_block(ms_matrix, ms_state, ms_eval, ms_own, ms_wtr, P, n, world, cand),
+            "roofline": roofline_block(ms_matrix, ms_eval, P, n, world, cand, clocks, peaks),
             "e2e": {"value": cells_step * args.steps / e2e_s, "unit": "cells/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * e2e_s / args.steps,
                     "move_evals_per_s": evals_step * args.steps / e2e_s,
                     "call": "rt_problem_plan_upload_dev (pinned host buffers in, this rank's shard scored) + NCCL "
                             "all_reduce(MIN) + 8-byte key back to pinned host memory, synchronous per step",
                     "keys_equal_device_path": bool(key_e2e == key_device)},
-            "gpu_launches": (launches[0] if launches else 10) * args.steps,
+            "gpu_launches": (launches[0] if launches else 5) * args.steps,
             "gpu_launches_source": ("torch.profiler (CUPTI) count of this library's kernels in one pass: "
                                     f"{launches[0]} per step, + {1 if world > 1 else 0} NCCL kernel" if launches else
-                                    "constant: 10 kernels per pass (position vectors, matrix, 4 state tables, fill, "
-                                    "intra, inter, finish)"),
+                                    "constant: 5 kernels per pass (position unit vectors, route scan, route tables, "
+                                    "same-route kernel, tile kernel)"),
             "clocks": clocks,
         }
         if extra:
@@ -541,29 +555,36 @@ def run_engine(args, rank, world):
         dist.destroy_process_group()
 
 
-def kernel_block(ms_matrix, ms_state, ms_eval, ms_own, P, n, world, cand):
+def kernel_block(ms_matrix, ms_state, ms_eval, ms_own, ms_wtr, P, n, world, cand):
     pitch = (P + 15) // 16 * 16
     rows = P // world + 3 if world > 1 else P
     return {
         "note": f"rank 0's shard (1/{world} of the rows and of the neighbourhood), each timed alone in this process",
-        "position_vectors+matrix_kernel": {"ms": ms_matrix, "rows": rows, "bytes_written": rows * pitch * 8,
-                                           "GBs_written": rows * pitch * 8 / ms_matrix / 1e6},
-        "state_tables": {"ms": ms_state, "note": "replicated on every rank (runs underneath the matrix kernel)"},
-        "eval_moves(inter+intra)": {"ms": ms_eval, "move_evals": sum(cand.values()) // world,
-                                    "move_evals_per_s": sum(cand.values()) / world / ms_eval * 1e3},
-        "whole_pass_without_exchange": {"ms": ms_own},
+        "state_tables": {"ms": ms_state, "note": "route scan + one warp per route; replicated on every rank"},
+        "eval_moves(tile kernel without a matrix + same-route kernel)": {
+            "ms": ms_eval, "move_evals": sum(cand.values()) // world,
+            "move_evals_per_s": sum(cand.values()) / world / ms_eval * 1e3,
+            "matrix_cells_rebuilt_per_s": rows * P / ms_eval * 1e3},
+        "whole_pass_without_exchange": {"ms": ms_own, "form": "cells rebuilt from unit vectors inside the move kernels"},
+        "whole_pass_write_then_read": {"ms": ms_wtr, "form": "matrix kernel writes the route-order rows, move kernels "
+                                                            "read them back (rt_debug_set fused_eval = 0): the form "
+                                                            "this pass replaced, same key"},
+        "matrix_kernel_alone": {"ms": ms_matrix, "rows": rows, "bytes_written": rows * pitch * 8,
+                                "GBs_written": rows * pitch * 8 / ms_matrix / 1e6,
+                                "note": "position vectors + matrix_kernel<0>, route-order rows materialised "
+                                        "(rt_problem_refresh_dev bit 2); not part of the pass any more"},
     }
 
 
-def roofline_block(ms_matrix, ms_eval, P, n, world, cand, clocks, peak_alu, peak_issue):
-    """Dominant kernel = move evaluation, bound by the ALU pipe: achieved = ALU-pipe warp instructions per launch (ncu
-    counter of the same workload, profiles/r2_counters.json; a shard executes 1/N of them) / live duration, against the
-    ALU-pipe peak measured in this run (rt_selftest_pipe_peak).  The matrix kernel keeps the HBM form."""
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        hbm, hbm_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-    else:
-        hbm, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+def roofline_block(ms_matrix, ms_eval, P, n, world, cand, clocks, peaks):
+    """Dominant kernel = move evaluation (tile kernel that rebuilds its cells from unit vectors).  It touches O(n) bytes
+    of HBM, so its roofline is an instruction rate: achieved = warp instructions per launch (ncu counter of the same
+    workload, profiles/r2_counters.json; a shard executes 1/N of them) / live duration, against the issue peak measured
+    in this run (rt_selftest_pipe_peak); the ALU-pipe share is given the same way.  The matrix kernel, which the pass
+    no longer needs, keeps its HBM form (measured on this rank's rows)."""
+    hbm = hbm_peak()
+    hbm_src = ("measured (MEASURED_PEAKS.json hbm_gbs)" if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json"))
+               else "fallback (B200_PROFILING.md)")
     counters = {}
     cp = os.path.join(ROOT, "profiles", "r2_counters.json")
     if os.path.exists(cp):
@@ -571,37 +592,40 @@ def roofline_block(ms_matrix, ms_eval, P, n, world, cand, clocks, peak_alu, peak
     pitch = (P + 15) // 16 * 16
     rows = P // world + 3 if world > 1 else P
     mat_bytes = (n * n * 8) / world                    # algorithmic: 8 B per cell of the instance, this rank's share
-    mat = {"kernel": "matrix_kernel<0> (+ position vectors)", "bound": "hbm", "achieved": mat_bytes / ms_matrix / 1e6,
-           "peak": hbm, "unit": "GB/s", "frac": mat_bytes / ms_matrix / 1e6 / hbm, "peak_source": hbm_src,
-           "bytes_written_incl_route_order_rows_and_pad": rows * pitch * 8,
+    mat = {"kernel": "matrix_kernel<0> (+ position vectors), materialising this rank's route-order rows", "bound": "hbm",
+           "achieved": mat_bytes / ms_matrix / 1e6, "peak": hbm, "unit": "GB/s", "frac": mat_bytes / ms_matrix / 1e6 / hbm,
+           "peak_source": hbm_src, "bytes_written_incl_route_order_rows_and_pad": rows * pitch * 8,
            "frac_on_bytes_written": rows * pitch * 8 / ms_matrix / 1e6 / hbm,
            "traffic": (counters.get("matrix_kernel") or {}).get("dram_bytes")}
     ev = counters.get("eval_moves") or {}
     alu_inst, all_inst = ev.get("alu_warp_inst"), ev.get("warp_inst")
-    roof = {"kernel": "eval_inter_kernel + eval_intra_kernel (move evaluation)", "bound": "alu",
-            "unit": "G warp-instructions/s on the ALU pipe", "achieved": None, "peak": None, "frac": None,
+    roof = {"kernel": "eval_inter_fused_kernel + same-route kernel (move evaluation, cells rebuilt from unit vectors)",
+            "bound": "issue", "unit": "G warp-instructions/s", "achieved": None, "peak": None, "frac": None,
             "traffic": ev.get("dram_bytes"),
-            "note": "move evaluation is not HBM-bound (SURVEY.md §8(d)): every cell is fetched once per strip and "
-                    "re-used from registers; the binding unit is the ALU pipe (compares, min/max, selects)",
+            "note": "no matrix is written or read: HBM traffic is O(n) per pass, so the bound is the instruction issue "
+                    "rate (ncu: issue slots ~85 % busy, ALU pipe ~70 %); SURVEY.md §8(d) already rules HBM out for this kernel",
             "matrix_kernel": mat}
-    if peak_alu:
-        roof["peak"] = peak_alu / 1e9
-        roof["peak_source"] = ("measured in this run: rt_selftest_pipe_peak mode 0 (independent LOP3/IMNMX chains, CUDA "
-                               f"events, SM clock {clocks.get('sm_mhz') if clocks else None} MHz)")
-        roof["issue_peak"] = peak_issue / 1e9 if peak_issue else None
-    if alu_inst and peak_alu:
-        ach = alu_inst / world / (ms_eval / 1e3)
+    if peaks:
+        roof["peak"] = peaks["issue_limit"] / 1e9
+        roof["peak_source"] = ("issue limit: 148 SMs x 4 schedulers x 1 warp instruction per clock at the SM clock sampled in "
+                               f"this run ({clocks.get('sm_mhz') if clocks else None} MHz) - what ncu's issue-active is a "
+                               "percentage of; instruction mixes measured in this run (rt_selftest_pipe_peak) beside it")
+        roof["measured_mixes_Ginst_s"] = {k: v / 1e9 for k, v in peaks["issue_measured_mixes"].items()}
+    if all_inst and peaks:
+        ach = all_inst / world / (ms_eval / 1e3)
         roof["achieved"] = ach / 1e9
-        roof["frac"] = ach / peak_alu
-        roof["alu_warp_inst_per_launch"] = alu_inst / world
-        roof["counter_source"] = "profiles/r2_counters.json (ncu smsp__inst_executed_pipe_alu.sum, inter + intra)"
-    if all_inst and peak_issue:
-        roof["issue"] = {"achieved": all_inst / world / (ms_eval / 1e3) / 1e9, "peak": peak_issue / 1e9,
-                         "frac": all_inst / world / (ms_eval / 1e3) / peak_issue}
+        roof["frac"] = ach / peaks["issue_limit"]
+        roof["warp_inst_per_launch"] = all_inst / world
+        roof["counter_source"] = "profiles/r2_counters.json (ncu smsp__inst_executed.sum, tile + same-route kernel, N = 1)"
+    if alu_inst and peaks:
+        roof["alu_pipe"] = {"achieved": alu_inst / world / (ms_eval / 1e3) / 1e9, "peak": peaks["alu"] / 1e9,
+                            "frac": alu_inst / world / (ms_eval / 1e3) / peaks["alu"],
+                            "unit": "G warp-instructions/s on the ALU pipe",
+                            "peak_source": "rt_selftest_pipe_peak mode 0 (LOP3/IMNMX chains), this run"}
     roof["algorithmic_matrix_reads"] = {
         "bytes": sum(cand[f] * BYTES_PER_EVAL[f] for f in cand) // world,
         "GBs": sum(cand[f] * BYTES_PER_EVAL[f] for f in cand) / world / ms_eval / 1e6,
-        "note": "SURVEY.md §8(d) per-candidate figure (16/24/32 B), for reference only: served from registers/L1, not HBM"}
+        "note": "SURVEY.md §8(d) per-candidate figure (16/24/32 B), for reference only: those cells never exist in memory"}
     return roof
 
 
@@ -801,8 +825,11 @@ def block_batch(cx):
     keys = torch.empty(B, dtype=torch.int64, device="cuda")
     step = lambda: pr.plan_dev(keys.data_ptr(), dist_scale=DIST_SCALE, time_scale=TS_CAR, families=ALL_FAMILIES, stream=s)
     ms = cx.timed(step, 20)
-    ms_matrix = cx.timed(lambda: pr.refresh_dev(1, s), 20)
+    ms_matrix = cx.timed(lambda: pr.refresh_dev(4, s), 20)   # route-order matrices materialised (not part of the step)
     ms_eval = cx.timed(lambda: pr.eval_moves_dev(keys.data_ptr(), ALL_FAMILIES, (0, 1), s), 20)
+    cx.eng.debug_set("fused_eval", 0)
+    ms_wtr = cx.timed(step, 20)                               # the write-then-read form of round 1
+    cx.eng.debug_set("fused_eval", 1)
     step()
     got = (keys.cpu().numpy() ^ np.int64(-2 ** 63)).view(np.uint64)
     ok = None
@@ -813,6 +840,7 @@ def block_batch(cx):
             ok = ok and it["trips"] == trips[b] and oracle_pass(it, host_threads())[2] == int(got[b])
     pr.close()
     return {"ms_per_step": ms, "cells_per_s": cells / ms * 1e3, "move_evals_per_s": evals / ms * 1e3,
+            "ms_per_step_write_then_read": ms_wtr,
             "keys_equal_oracle": ok, "matrix_kernel": {"ms": ms_matrix, "GBs": cells * 8 / ms_matrix / 1e6,
                                                        "frac_of_hbm_peak": cells * 8 / ms_matrix / 1e6 / hbm_peak()},
             "eval_moves": {"ms": ms_eval, "move_evals_per_s": evals / ms_eval * 1e3}}

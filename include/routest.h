@@ -316,8 +316,9 @@ int rt_selftest_fast_sqrt(rt_engine *e, uint32_t lo_bits, uint32_t hi_bits, uint
 
 /* On-box instruction-rate peak, the roofline denominator of the integer move-evaluation kernels (SURVEY.md §8(d) asks
  * for ALU peaks measured on the box): a kernel of independent register chains, timed with CUDA events on the engine's
- * stream (the call synchronises).  mode 0 = ALU pipe only (LOP3/IMNMX), 1 = FMA pipe only (IMAD), 2 = both interleaved
- * (the issue limit).  iters = loop trips per thread (32 instructions each); the result is warp instructions per second
+ * stream (the call synchronises).  mode 0 = ALU pipe only (LOP3/IMNMX), 1 = FMA pipe only (IMAD), 2 = ALU + IMAD
+ * interleaved, 3 = ALU + immediate-form FFMA interleaved, 4 = ALU + IMAD + FFMA (2:1:1, three pipes: the closest to the
+ * issue limit of one warp instruction per scheduler per clock).  iters = loop trips per thread (32 instructions each); the result is warp instructions per second
  * over the whole GPU.  No reference counterpart. */
 int rt_selftest_pipe_peak(rt_engine *e, int mode, int iters, double *warp_inst_per_s, double *elapsed_ms);
 

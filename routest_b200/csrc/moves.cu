@@ -22,6 +22,7 @@
 // time.
 #include <climits>
 #include <cstdlib>
+#include <cstring>
 
 #include "geometry.cuh"
 #include "problem.cuh"
@@ -129,12 +130,17 @@ struct ColQ {
 // relocate(p -> between q and q+1) and swap(p, q) for one customer row p against column q: delta AND feasibility,
 // straight line.  Cells: c_up = (p-1, q), c_rt = (p, q+1); a_cur = (p, q), a_lf = (p, q-1), a_dn = (p+1, q) in the
 // orientation that leads towards p's side (the same cells when the matrix is symmetric).
+// thr: the delta a candidate has to reach to matter.  In best-key mode it is the smallest best delta any lane of the
+// warp holds (the block's minimum is all that leaves the kernel, so a candidate above another lane's best can never be
+// it): new records then become rare — a handful per warp and strip instead of a few per lane — and one warp vote
+// skips the whole update; without it the compiler predicates the update, a dozen issue slots per row spent on nothing.
+// In table mode every lane feeds its own (route, route) entry and thr is simply its own best delta.
 template <int MODE>
 __device__ __forceinline__ void score_pair(const EvalArgs &a, int P, int p, const int4 &Hp, const int4 &p1, const int4 &p2,
                                            const ColQ &c, bool swap_tile, int2 c_up, int2 c_rt, int2 a_cur, int2 a_lf,
-                                           int2 a_dn, int &best_d, unsigned &best_i)
+                                           int2 a_dn, int &best_d, unsigned &best_i, int &thr)
 {
-    constexpr bool DUMP = MODE == kDump;
+    constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
     const int q = c.q;
     const bool other = (Hp.w & 0x7FFF) != c.q_route;
     // relocate(p -> between q and q+1): a -> u -> b replaces a -> b in route[q]
@@ -144,23 +150,19 @@ __device__ __forceinline__ void score_pair(const EvalArgs &a, int P, int p, cons
     const bool v_rel = c.rel_q && other;
     const bool ok_rel = v_rel && ((Hp.w >> 29) & 1) && p1.w <= c.capsl_q && ins <= c.distsl_q && tu <= p1.y &&
                         fadd(fadd(tu, p1.z), c_rt.y) <= c.zn_q;
+    bool hit_rel = ok_rel && d_rel <= thr, hit_swap = false;
+    int d_swap = 0;
     if (DUMP) {
         if (v_rel && a.dump_family == 1) {
             a.dump_delta[static_cast<size_t>(p) * P + q] = d_rel;
             a.dump_feas[static_cast<size_t>(p) * P + q] = ok_rel ? 1 : 0;
-        }
-    } else if (ok_rel && d_rel <= best_d) {  // rarely true: the update stays off the straight-line path
-        const unsigned idx = (1u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q);
-        if (d_rel < best_d || idx < best_i) {
-            best_d = d_rel;
-            best_i = idx;
         }
     }
     if (swap_tile) {
         // swap(p, q), p < q: pu -> v -> nu in route[p], pw -> u -> nw in route[q]
         const int d1 = fadd(fadd(c_up.x, a_dn.x), -Hp.y);
         const int d2 = fadd(fadd(a_lf.x, c_rt.x), -c.Hq.y);
-        const int d_swap = fadd(d1, d2);
+        d_swap = fadd(d1, d2);
         const int tv = max(c.qB.x, fadd(p2.y, c_up.y));
         const int tw = max(p1.x, fadd(c.depprev_q, a_lf.y));
         const int dd = fadd(c.qB.w, -p1.w);
@@ -168,18 +170,31 @@ __device__ __forceinline__ void score_pair(const EvalArgs &a, int P, int p, cons
         const bool ok_swap = v_swap && dd <= p2.z && -dd <= c.capsl_q && d1 <= p2.w && d2 <= c.distsl_q &&
                              tv <= c.qB.y && fadd(fadd(tv, c.qB.z), a_dn.y) <= p2.x && tw <= p1.y &&
                              fadd(fadd(tw, p1.z), c_rt.y) <= c.zn_q;
+        hit_swap = ok_swap && d_swap <= thr;
         if (DUMP) {
             if (v_swap && a.dump_family == 2) {
                 a.dump_delta[static_cast<size_t>(p) * P + q] = d_swap;
                 a.dump_feas[static_cast<size_t>(p) * P + q] = ok_swap ? 1 : 0;
             }
-        } else if (ok_swap && d_swap <= best_d) {
+        }
+    }
+    if (DUMP) return;
+    if (__any_sync(0xffffffffu, hit_rel || hit_swap)) {  // rare
+        if (hit_rel) {
+            const unsigned idx = (1u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q);
+            if (d_rel < best_d || (d_rel == best_d && idx < best_i)) {
+                best_d = d_rel;
+                best_i = idx;
+            }
+        }
+        if (hit_swap) {
             const unsigned idx = (2u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q);
-            if (d_swap < best_d || idx < best_i) {
+            if (d_swap < best_d || (d_swap == best_d && idx < best_i)) {
                 best_d = d_swap;
                 best_i = idx;
             }
         }
+        thr = TABLE ? best_d : __reduce_min_sync(0xffffffffu, best_d);
     }
 }
 
@@ -247,7 +262,7 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
     const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q};
     const bool swap_tile = (a.families & 4) && p0 < q0 + kInterThreads - 1;  // some pair of the tile has p < q
 
-    int best_d = INT_MAX;
+    int best_d = INT_MAX, thr = INT_MAX;
     unsigned best_i = 0xFFFFFFFFu;  // family << 30 | p << 15 | q
     int cur_ra = -1;                // table mode: the route the running best belongs to
     unsigned long long *trow = TABLE ? a.inter + static_cast<size_t>(b) * a.cr * a.cr + q_route : nullptr;
@@ -256,6 +271,7 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
             atomicMin(trow + static_cast<size_t>(cur_ra) * a.cr,
                       (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i);
         best_d = INT_MAX;
+        thr = INT_MAX;
         best_i = 0xFFFFFFFFu;
     };
     const int rows = min(kStripRows, p_hi - p0);
@@ -302,7 +318,7 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
                 flush();
                 cur_ra = Hp.w & 0x7FFF;
             }
-            score_pair<MODE>(a, P, p, Hp, p1, p2, col, swap_tile, c_up, c_rt, a_cur, a_lf, a_dn, best_d, best_i);
+            score_pair<MODE>(a, P, p, Hp, p1, p2, col, swap_tile, c_up, c_rt, a_cur, a_lf, a_dn, best_d, best_i, thr);
         }
         c_up = c_cur;
         c_lf = n_lf;
@@ -370,7 +386,9 @@ __device__ __forceinline__ double lds64(unsigned addr)
     return v;
 }
 
-template <int MODE>
+// FAST: the launcher has proved from the coordinates' bounding box that no pair of the batch can leave the
+// straight-line range of the cell function (any metro-sized instance), so the per-cell range test is compiled out.
+template <int MODE, bool FAST>
 __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(const EvalArgs a)
 {
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
@@ -432,7 +450,7 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
     const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q};
     const bool swap_tile = (a.families & 4) && p0 < q0 + kFusedCols - 1;  // some pair of the tile has p < q
 
-    int best_d = INT_MAX;
+    int best_d = INT_MAX, thr = INT_MAX;
     unsigned best_i = 0xFFFFFFFFu;
     int cur_ra = -1;
     unsigned long long *trow = TABLE ? a.inter + static_cast<size_t>(b) * a.cr * a.cr + q_route : nullptr;
@@ -441,6 +459,7 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
             atomicMin(trow + static_cast<size_t>(cur_ra) * a.cr,
                       (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i);
         best_d = INT_MAX;
+        thr = INT_MAX;
         best_i = 0xFFFFFFFFu;
     };
     // slot address in a per-thread register (the shift is zero for every thread of a 128-thread block; it only keeps
@@ -449,11 +468,16 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
     const float fd = a.fd, ft = a.ft;
     const int lim_hi = a.lim_hi;
     auto cell_slot = [&](unsigned addr) {  // cell(position of that slot, q)
-        return cell_from_vectors(lds64(addr + 48), lds64(addr + 56), lds64(addr + 64), bx, by, bz, fd, ft, lim_hi);
+        const double ax = lds64(addr + 48), ay = lds64(addr + 56), az = lds64(addr + 64);
+        if (FAST) {
+            const double dx = ax - bx, dy = ay - by, dz = az - bz;
+            return cell_i32_fast(fma(dx, dx, fma(dy, dy, dz * dz)), fd, ft);
+        }
+        return cell_from_vectors(ax, ay, az, bx, by, bz, fd, ft, lim_hi);
     };
     int2 c_up = cell_slot(sa), c_cur = cell_slot(sa + 80);
     const unsigned full = 0xffffffffu;
-#pragma unroll 2
+#pragma unroll 3
     for (int rr = 0; rr < rows; ++rr, sa += 80) {
         const int p = p0 + rr;
         const int2 c_dn = cell_slot(sa + 160);
@@ -466,7 +490,7 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
                 flush();
                 cur_ra = Hp.w & 0x7FFF;
             }
-            score_pair<MODE>(a, P, p, Hp, p1, p2, col, swap_tile, c_up, c_rt, c_cur, c_lf, c_dn, best_d, best_i);
+            score_pair<MODE>(a, P, p, Hp, p1, p2, col, swap_tile, c_up, c_rt, c_cur, c_lf, c_dn, best_d, best_i, thr);
         }
         c_up = c_cur;
         c_cur = c_dn;
@@ -970,6 +994,17 @@ int launch_intra(rt_problem *p, const EvalArgs &a, int shard_rows, int batch, cu
     return RT_OK;
 }
 
+// chord^2 <= angle^2 <= dlat^2 + dlon^2 over the bounding box of every coordinate of the batch (p->angle2_bound, kept
+// by the entry points that receive coordinates): below the fast path's limit, with a margin, no cell can need the
+// guarded form.
+bool all_pairs_in_fast_range(const rt_problem *p, const EvalArgs &a)
+{
+    long long bits = static_cast<long long>(a.lim_hi) << 32;  // the smallest double with that high word
+    double lim;
+    memcpy(&lim, &bits, sizeof(lim));
+    return p->angle2_bound >= 0.0 && p->angle2_bound * 1.001 < lim;
+}
+
 // The tile kernel of this launch: without a matrix where the cells are SPEC 2 of the problem's coordinates, on G
 // (and GT for a directional matrix) otherwise.
 template <int MODE>
@@ -979,7 +1014,8 @@ int launch_inter(rt_problem *p, EvalArgs &a, int pmax, int shard_rows, int batch
     const int cols = fused ? kFusedCols : kInterThreads;
     a.strip_rows = strip_rows > 0 ? strip_rows : pick_strip_rows(pmax, shard_rows, batch, !p->symmetric, cols);
     dim3 grid((pmax + cols - 1) / cols, (shard_rows + a.strip_rows - 1) / a.strip_rows, batch);
-    if (fused) eval_inter_fused_kernel<MODE><<<grid, kInterThreads, 0, st>>>(a);
+    if (fused && all_pairs_in_fast_range(p, a)) eval_inter_fused_kernel<MODE, true><<<grid, kInterThreads, 0, st>>>(a);
+    else if (fused) eval_inter_fused_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
     else if (p->symmetric) eval_inter_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
     else eval_inter_kernel<MODE, true><<<grid, kInterThreads, 0, st>>>(a);
     RT_CUDA(p->e, cudaGetLastError());

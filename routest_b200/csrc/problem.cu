@@ -72,6 +72,22 @@ __global__ void cells_to_planes_kernel(const int2 *__restrict__ cells, int n, in
 // Host side of rt_problem_plan: every id in [0, n) and exactly n-1 customers among the P positions.  On the call's
 // critical path (the GPU is only busy with the input copies meanwhile), hence four ids per step: the sign bit of
 // v | (n-1 - v) is set iff v is negative or above n-1.
+// dlat^2 + dlon^2 in radians over the bounding box of the coordinates: an upper bound of every pair's squared central
+// angle, hence of its chord^2 (the move kernels drop the cell function's range test when it is small enough).
+double angle2_bound_of(const double *lat, const double *lon, long long count)
+{
+    double la0 = lat[0], la1 = lat[0], lo0 = lon[0], lo1 = lon[0];
+    for (long long i = 1; i < count; ++i) {
+        la0 = lat[i] < la0 ? lat[i] : la0;
+        la1 = lat[i] > la1 ? lat[i] : la1;
+        lo0 = lon[i] < lo0 ? lon[i] : lo0;
+        lo1 = lon[i] > lo1 ? lon[i] : lo1;
+    }
+    const double DEG = 0.017453292519943295, dla = (la1 - la0) * DEG, dlo = (lo1 - lo0) * DEG;
+    const double b = dla * dla + dlo * dlo;
+    return b == b ? b : -1.0;  // a NaN coordinate: unknown (the pass is refused elsewhere)
+}
+
 bool positions_well_formed(const int32_t *nd, int P, int n)
 {
     const int32_t top = n - 1;
@@ -243,6 +259,7 @@ int rt_problem_set_coords(rt_problem *p, const double *lat, const double *lon)
     p->has_coords = true;
     p->has_matrix = false;
     p->cells_from_coords = false;
+    p->angle2_bound = angle2_bound_of(lat, lon, total);
     return RT_OK;
 }
 
@@ -632,6 +649,7 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
             return fail(e, RT_ERR_INVALID_ARG, "instance %zu: position array must hold node ids below %zu with %zu customers", b, N, N - 1);
         }
     }
+    p->angle2_bound = angle2_bound_of(lat, lon, static_cast<long long>(B * N));
     p->plan_t[2] = dbg ? now() : 0;
     // the matrix of this pass is built in route order by the refresh below (state.cu); the node-order copy that
     // rt_problem_build_matrix keeps for the greedy and for rt_problem_get_matrix is not needed here

@@ -57,6 +57,7 @@ struct rt_problem {
     unsigned long long *ext_best = nullptr;  // caller's key buffer of the plan call in progress: the refresh resets it too
     bool ext_best_clean = false;           //   ... and it holds "none" in signed-order form right now
     bool cells_from_coords = false;        // the matrix is SPEC §2 of this problem's coordinates
+    double angle2_bound = -1.0;            // dlat^2 + dlon^2 (radians) over the bounding box of all coordinates; < 0 = unknown
     int *Bv = nullptr, *Zv = nullptr, *route = nullptr, *rstart = nullptr;
     long long *rload = nullptr, *rdist = nullptr;
     long long *cost = nullptr;             // [batch]

@@ -148,7 +148,7 @@ class Engine:
 
     def pipe_peak(self, mode: int = 0, iters: int = 20000):
         """Measured instruction-rate peak in warp instructions per second (rt_selftest_pipe_peak): mode 0 = ALU pipe,
-        1 = FMA pipe, 2 = both interleaved (issue limit).  Returns (rate, elapsed_ms)."""
+        1 = FMA pipe (IMAD), 2 = ALU + IMAD interleaved, 3 = ALU + immediate-form FFMA interleaved (issue limit).  Returns (rate, elapsed_ms)."""
         rate, ms = C.c_double(0), C.c_double(0)
         self._check(self._lib.rt_selftest_pipe_peak(self._h, int(mode), int(iters), C.byref(rate), C.byref(ms)))
         return float(rate.value), float(ms.value)
