@@ -572,13 +572,13 @@ int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int
     RT_TRY(check_scales(e, dist_scale, time_scale));
     DeviceGuard dg(e->device);
     cudaStream_t st = pick_stream(e, stream);
-    RT_TRY(position_unit_vectors_launch(p, st));  // unit vectors, already in route order
+    p->ext_best = static_cast<unsigned long long *>(best_keys_d);  // reset by the refresh, reduced into directly
+    RT_TRY(position_unit_vectors_launch(p, st));  // unit vectors, already in route order (+ the route scan)
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     p->cells_from_coords = true;
     p->symmetric = true;  // whatever matrix was installed before, this pass runs on SPEC §2 cells
     p->supplied = 0;
-    p->ext_best = static_cast<unsigned long long *>(best_keys_d);  // reset by the refresh, reduced into directly
     int rc = state_refresh(p, st, nullptr, /*vectors_ready=*/true);
     // a replica of a multi-GPU search scores the shard set by rt_problem_set_shard (default: everything)
     if (rc == RT_OK)
@@ -639,11 +639,24 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
     // customer is not repeated is not checked here: a repeat gives a meaningless plan, not a fault.  Coordinates
     // are range-checked by that kernel (off the host's critical path); stop records are taken as they are
     // (rt_problem_set_stops is the validating entry point) — out-of-range values cannot fault a kernel.
+    // sizes first (they depend on npos[] only, checked above): the vector kernel carries the route scan of large instances
+    p->pmax = 0;
+    p->pmin = npos[0];
+    for (size_t b = 0; b < B; ++b) {
+        p->pmax = std::max(p->pmax, npos[b]);
+        p->pmin = std::min(p->pmin, npos[b]);
+    }
+    p->cells_from_coords = true;
+    p->symmetric = true;
+    RT_TRY(ensure_position_matrix(p));
     p->plan_flag_seq = ++p->plan_seq;  // the flag is written with this call's number: no reset launch needed
+    p->ext_best = keys_dev;  // (may be null) reset by the scan that rides along, reduced into directly by the evaluation
     RT_TRY(position_unit_vectors_launch(p, st, keys_dev ? nullptr : p->coord_flag, p->plan_flag_seq));
     for (size_t b = 0; b < B; ++b) {
         if (!positions_well_formed(node + b * PS, npos[b], static_cast<int>(N))) {
             p->has_routes = false;  // the copy above has already replaced the previous routes
+            p->ext_best = nullptr;
+            p->scan_done = false;
             cudaStreamSynchronize(st);  // the caller's buffers are still being read
             cudaStreamSynchronize(cs);
             return fail(e, RT_ERR_INVALID_ARG, "instance %zu: position array must hold node ids below %zu with %zu customers", b, N, N - 1);
@@ -658,16 +671,9 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
     p->cells_from_coords = true;
     p->symmetric = true;
     p->supplied = 0;
-    p->pmax = 0;
-    p->pmin = npos[0];
-    for (size_t b = 0; b < B; ++b) {
-        p->pmax = std::max(p->pmax, npos[b]);
-        p->pmin = std::min(p->pmin, npos[b]);
-    }
     p->dist_scale = dist_scale;
     p->time_scale = time_scale;
     RT_TRY(ensure_position_matrix(p));
-    p->ext_best = keys_dev;  // (may be null) reset by the refresh, reduced into directly by the evaluation
     int rc_refresh = state_refresh(p, st, keys_dev ? nullptr : p->ev_in[1], /*vectors_ready=*/true);
     // a replica of a multi-GPU search scores its own shard (rt_problem_set_shard); the default is everything
     if (keys_dev) {

@@ -56,6 +56,7 @@ struct rt_problem {
     bool best_clean = false;               // p->best holds "no move" for every instance (set by the state refresh)
     unsigned long long *ext_best = nullptr;  // caller's key buffer of the plan call in progress: the refresh resets it too
     bool ext_best_clean = false;           //   ... and it holds "none" in signed-order form right now
+    bool scan_done = false;                // the vector kernel just enqueued also scanned the routes (large instances)
     bool cells_from_coords = false;        // the matrix is SPEC §2 of this problem's coordinates
     double angle2_bound = -1.0;            // dlat^2 + dlon^2 (radians) over the bounding box of all coordinates; < 0 = unknown
     int *Bv = nullptr, *Zv = nullptr, *route = nullptr, *rstart = nullptr;

@@ -18,13 +18,102 @@ namespace rt {
 
 namespace {
 
+struct RoutesArgs {
+    const int *node, *npos;
+    int *nroutes;
+    int pstride, rstride;
+    int *route, *rstart;
+    long long *cost;
+    int *feasible;
+    unsigned long long *best;
+    unsigned long long *ext_best;  // optional: the caller's key buffer (signed-order form), reset alongside
+};
+
+
+// The same scan for a 256-thread block that is the extra last block of a vector kernel (large instances): the route
+// table then costs no launch of its own.  Warp w walks a contiguous slice of the positions 32 at a time (coalesced),
+// the separators of a chunk are one ballot; pass 1 counts, pass 2 — after the eight warp totals have been combined —
+// writes rstart[].  route[] is left to the per-route kernel.  Robust against a malformed node array (the plan entry
+// points launch this before the host has finished validating it): nothing is written beyond rstride + 1 entries.
+constexpr int kPrepThreads = 256;
+
+__device__ __forceinline__ void routes_scan_small_block(const RoutesArgs &a, int b)
+{
+    __shared__ int s_tot[kPrepThreads / 32];
+    __shared__ unsigned s_mask[kMaxPositions / 32];  // one ballot per 32 positions
+    const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
+    const int P = min(a.npos[b], a.pstride);
+    const int *node = a.node + static_cast<size_t>(b) * a.pstride;
+    int *rstart = a.rstart + static_cast<size_t>(b) * (a.rstride + 1);
+    const int chunks = (P + 31) / 32, per_warp = (chunks + kPrepThreads / 32 - 1) / (kPrepThreads / 32);
+    const int c0 = min(chunks, wrp * per_warp), c1 = min(chunks, c0 + per_warp);
+    // pass 1: eight independent loads in flight per lane (the ballots would otherwise serialise one memory round trip
+    // per chunk), masks kept in shared memory for pass 2
+    int cnt = 0;
+    for (int c = c0; c < c1; c += 8) {
+        int v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int p = (c + k) * 32 + lane;
+            v[k] = (c + k < c1 && p < P) ? node[p] : 1;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const unsigned m = __ballot_sync(0xffffffffu, v[k] == 0);
+            if (c + k < c1) {
+                if (lane == 0) s_mask[c + k] = m;
+                cnt += __popc(m);
+            }
+        }
+    }
+    if (lane == 0) s_tot[wrp] = cnt;
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int i = 0; i < kPrepThreads / 32; ++i) {
+        before += i < wrp ? s_tot[i] : 0;
+        total += s_tot[i];
+    }
+    // pass 2: lane l takes the chunks c0 + l, c0 + l + 32, ... of its warp; the rank of a chunk's first separator is a
+    // running sum over the warp's masks
+    int r = before;
+    for (int c = c0; c < c1; c += 32) {
+        const unsigned m = c + lane < c1 ? s_mask[c + lane] : 0u;
+        int pc = __popc(m), incl = pc;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += t;
+        }
+        int k = r + incl - pc;  // separators before this lane's chunk
+        unsigned mm = m;
+        while (mm) {
+            const int bit = __ffs(mm) - 1;
+            mm &= mm - 1;
+            if (k <= a.rstride) rstart[k] = (c + lane) * 32 + bit;
+            ++k;
+        }
+        r += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (tid == 0) {
+        a.nroutes[b] = total - 1;
+        a.cost[b] = 0;
+        a.feasible[b] = 1;
+        a.best[b] = kNoMove;
+        if (a.ext_best) a.ext_best[b] = kNoMove ^ 0x8000000000000000ull;
+    }
+}
+
 // PX[c][p] = xyz[c][node p]; positions beyond P repeat the depot so that G needs no bounds checks.
 __global__ void __launch_bounds__(256) position_vectors_kernel(const double *__restrict__ xyz,
                                                                const int *__restrict__ node,
                                                                const int *__restrict__ npos, int n, int pstride,
-                                                               double *__restrict__ PX)
+                                                               double *__restrict__ PX, const RoutesArgs ra, int with_scan)
 {
     const int b = blockIdx.y;
+    if (with_scan && blockIdx.x == gridDim.x - 1) {  // the extra block: route scan of this instance
+        routes_scan_small_block(ra, b);
+        return;
+    }
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= pstride) return;
     const int cur = p < npos[b] ? node[static_cast<size_t>(b) * pstride + p] : 0;
@@ -44,10 +133,15 @@ __global__ void __launch_bounds__(256) position_unit_vectors_kernel(const double
                                                                     const int *__restrict__ node,
                                                                     const int *__restrict__ npos, int n, int pstride,
                                                                     double *__restrict__ xyz, double *__restrict__ PX,
-                                                                    int *__restrict__ bad_flag, int bad_value)
+                                                                    int *__restrict__ bad_flag, int bad_value,
+                                                                    const RoutesArgs ra, int with_scan)
 {
     const double DEG = 0.017453292519943295;
     const int b = blockIdx.y;
+    if (with_scan && blockIdx.x == gridDim.x - 1) {  // the extra block: route scan of this instance
+        routes_scan_small_block(ra, b);
+        return;
+    }
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= pstride) return;
     int cur = p < npos[b] ? node[static_cast<size_t>(b) * pstride + p] : 0;
@@ -178,17 +272,6 @@ __device__ __forceinline__ void gather_position(const GatherArgs &a, int b, int 
 
 // K2a: one block per instance — route ids by a block scan over the separators; resets the per-instance results.
 constexpr int kScanThreads = 1024;
-
-struct RoutesArgs {
-    const int *node, *npos;
-    int *nroutes;
-    int pstride, rstride;
-    int *route, *rstart;
-    long long *cost;
-    int *feasible;
-    unsigned long long *best;
-    unsigned long long *ext_best;  // optional: the caller's key buffer (signed-order form), reset alongside
-};
 
 // all kScanThreads threads of the block
 __device__ __forceinline__ void routes_block(const RoutesArgs &a, int b)
@@ -476,48 +559,67 @@ __device__ __forceinline__ void route_tables_warp(const StateArgs &a, int b, int
     const int2 *E = w.E + po;
     int *Bv = w.Bv + po, *Zv = w.Zv + po;
     const int4 depot = w.stops[static_cast<size_t>(b) * w.n];
-    int Bcur = depot.x, svc_prev = depot.z;
+    // Forward: B[p] = max(ready[p], B[p-1] + service[p-1] + T[p-1][p]) is the composition of the maps
+    // t -> max(t + w, ready); two of them compose to (w1 + w2, max(r1 + w2, r2)), so the B of 32 consecutive positions
+    // is one warp scan (five shuffle steps) applied to the value carried in from the chunk below.  Z likewise,
+    // downwards, with t -> min(t - c, due).  Exact integer max-plus algebra: the same values as the step-by-step walk.
+    int Bcur = depot.x;
     long long load = 0, dist = 0;
     bool feas = true;
+    int svc_last = depot.z;  // service time of the position just below the chunk
     for (int base = s + 1; base < e; base += 32) {
         const int p = base + lane;
         const bool in = p < e;
-        const int4 rb = in ? RB[p] : make_int4(0, 0, 0, 0);
+        const int4 rb = in ? RB[p] : make_int4(INT_MIN / 2, INT_MAX, 0, 0);
         const int2 ed = in ? E[p - 1] : make_int2(0, 0);
-        const int cntc = min(32, e - base);
-        int myB = 0;
-        for (int k = 0; k < cntc; ++k) {
-            const int ready = __shfl_sync(full, rb.x, k), due = __shfl_sync(full, rb.y, k);
-            const int svc = __shfl_sync(full, rb.z, k), dem = __shfl_sync(full, rb.w, k);
-            const int ed_d = __shfl_sync(full, ed.x, k), ed_t = __shfl_sync(full, ed.y, k);
-            Bcur = max(ready, Bcur + svc_prev + ed_t);
-            feas = feas && Bcur <= due;
-            if (k == lane) myB = Bcur;
-            svc_prev = svc;
-            load += dem;
-            dist += ed_d;
+        int svc_prev = __shfl_up_sync(full, rb.z, 1);
+        if (lane == 0) svc_prev = svc_last;
+        int fa = in ? svc_prev + ed.y : 0, fb = in ? rb.x : INT_MIN / 2;   // identity map for lanes beyond the route
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int la = __shfl_up_sync(full, fa, off), lb = __shfl_up_sync(full, fb, off);
+            if (lane >= off) {
+                fb = max(lb + fa, fb);
+                fa = la + fa;
+            }
         }
+        const int myB = max(Bcur + fa, fb);
+        feas = feas && __all_sync(full, !in || myB <= rb.y);
         if (in) Bv[p] = myB;
+        long long ld = in ? rb.w : 0, dd = in ? ed.x : 0;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            ld += __shfl_xor_sync(full, ld, off);
+            dd += __shfl_xor_sync(full, dd, off);
+        }
+        load += ld;
+        dist += dd;
+        const int lastl = min(31, e - 1 - base);
+        Bcur = __shfl_sync(full, myB, lastl);
+        svc_last = __shfl_sync(full, rb.z, lastl);
     }
     const int2 lastE = E[e - 1];
-    feas = feas && (Bcur + svc_prev + lastE.y <= depot.y);
+    feas = feas && (Bcur + svc_last + lastE.y <= depot.y);
     dist += lastE.x;
     feas = feas && load <= w.cap[b] && dist <= w.maxd[b];
     int Zn = depot.y;
-    for (int top = e - 1; top > s; top -= 32) {
+    for (int top = e - 1; top > s; top -= 32) {  // chunk [top-31, top], lane l holds position top - l
         const int p = top - lane;
         const bool in = p > s;
-        const int4 rb = in ? RB[p] : make_int4(0, 0, 0, 0);
+        const int4 rb = in ? RB[p] : make_int4(0, INT_MAX, 0, 0);
         const int2 ed = in ? E[p] : make_int2(0, 0);
-        const int cntc = min(32, top - s);
-        int myZ = 0;
-        for (int k = 0; k < cntc; ++k) {
-            const int due = __shfl_sync(full, rb.y, k), svc = __shfl_sync(full, rb.z, k);
-            const int ed_t = __shfl_sync(full, ed.y, k);
-            Zn = min(due, Zn - ed_t - svc);
-            if (k == lane) myZ = Zn;
+        int gc = in ? ed.y + rb.z : 0, gd = rb.y;  // z -> min(z - gc, gd)
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int lc = __shfl_up_sync(full, gc, off), ldue = __shfl_up_sync(full, gd, off);
+            if (lane >= off) {
+                gd = min(ldue - gc, gd);
+                gc = lc + gc;
+            }
         }
+        const int myZ = min(Zn - gc, gd);
         if (in) Zv[p] = myZ;
+        Zn = __shfl_sync(full, myZ, min(31, top - s - 1));
     }
     if (lane == 0) {
         Bv[s] = depot.x;
@@ -624,6 +726,9 @@ __global__ void __launch_bounds__(256) apply_moves_kernel(const unsigned long lo
 
 }  // namespace
 
+constexpr int kFusedStatePositions = 4096;
+static void launch_position_vectors(rt_problem *p, cudaStream_t st);
+
 int ensure_position_matrix(rt_problem *p, bool need_buffer)
 {
     const int rows = p->pmax > 0 ? p->pmax : p->pstride;
@@ -658,8 +763,8 @@ int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready)
     }
     if (p->cells_from_coords) {
         if (!vectors_ready) {
-            dim3 g0((p->pstride + 255) / 256, p->batch);
-            position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
+            launch_position_vectors(p, st);
+            p->scan_done = false;  // the tables are not refreshed here: whoever does it next scans for itself
             RT_CUDA(e, cudaGetLastError());
         }
         RT_TRY(launch_matrix_cells_ld(e, p->PX, p->grows, p->pstride, p->batch, r0, r1, p->dist_scale, p->time_scale, G,
@@ -680,7 +785,24 @@ int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready)
 
 // E/SK/RB, B/Z/load/dist, the packed records; resets the best keys.  Up to kFusedStatePositions positions per instance
 // one block per instance does it all in a single launch.
-constexpr int kFusedStatePositions = 4096;
+
+static RoutesArgs routes_args(rt_problem *p)
+{
+    return RoutesArgs{p->node, p->npos, p->nroutes, p->pstride, p->rstride, p->route, p->rstart, p->cost, p->feasible, p->best,
+                      p->ext_best};
+}
+
+// large instances: the vector kernel that precedes the tables carries the route scan as an extra block
+static bool scan_rides_along(const rt_problem *p) { return p->grows > kFusedStatePositions; }
+
+static void launch_position_vectors(rt_problem *p, cudaStream_t st)
+{
+    const int ws = scan_rides_along(p) ? 1 : 0;
+    dim3 g0((p->pstride + 255) / 256 + ws, p->batch);
+    position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX, routes_args(p), ws);
+    p->scan_done = ws != 0;
+    p->best_clean = p->best_clean || ws != 0;
+}
 
 static StateArgs state_args(rt_problem *p, bool fused_vectors)
 {
@@ -688,8 +810,7 @@ static StateArgs state_args(rt_problem *p, bool fused_vectors)
     a.g = GatherArgs{p->cells_from_coords ? p->PX : nullptr, p->cells, p->stops, p->node, p->npos, p->n, p->pitch, p->pstride,
                      static_cast<float>(RT_EARTH_RADIUS_M * p->dist_scale), static_cast<float>(RT_EARTH_RADIUS_M * p->time_scale),
                      p->RB, p->E, p->SK, p->symmetric ? nullptr : p->ER, fused_vectors ? p->xyz : nullptr, p->PX};
-    a.r = RoutesArgs{p->node, p->npos, p->nroutes, p->pstride, p->rstride, p->route, p->rstart, p->cost, p->feasible, p->best,
-                     p->ext_best};
+    a.r = routes_args(p);
     a.w = WalkArgs{p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap, p->max_dist, p->RB, p->E, p->Bv, p->Zv, p->rstart,
                    p->rload, p->rdist, p->cost, p->feasible};
     a.c = RecordsArgs{p->node, p->npos, p->n, p->pstride, p->rstride, p->stops, p->cap, p->max_dist, p->RB, p->E, p->SK, p->Bv,
@@ -705,13 +826,17 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors)
     p->best_clean = true;  // the route scan resets the best keys
     p->ext_best_clean = p->ext_best != nullptr;
     if (p->grows <= kFusedStatePositions) {
+        p->scan_done = false;
         state_fused_kernel<<<p->batch, kScanThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
         return RT_OK;
     }
-    // route scan, then one warp per route: gather + walk + records of its own positions
-    state_routes_kernel<<<p->batch, kScanThreads, 0, st>>>(a.r);
-    RT_CUDA(e, cudaGetLastError());
+    // route scan (unless the vector kernel in front carried it), then one warp per route: gather + walk + records
+    if (!p->scan_done) {
+        state_routes_kernel<<<p->batch, kScanThreads, 0, st>>>(a.r);
+        RT_CUDA(e, cudaGetLastError());
+    }
+    p->scan_done = false;
     const int rmax = std::max(1, p->grows - p->n);  // most routes of any instance
     dim3 gw((rmax + kRouteWarps - 1) / kRouteWarps, p->batch);
     state_route_tables_kernel<<<gw, kRouteWarps * 32, 0, st>>>(a);
@@ -723,9 +848,11 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors)
 // latency-bound kernels run on a side stream underneath the matrix kernel and join before anything evaluates moves.
 int position_unit_vectors_launch(rt_problem *p, cudaStream_t st, int *bad_flag, int bad_value)
 {
-    dim3 g0((p->pstride + 255) / 256, p->batch);
+    const int ws = scan_rides_along(p) ? 1 : 0;
+    dim3 g0((p->pstride + 255) / 256 + ws, p->batch);
     position_unit_vectors_kernel<<<g0, 256, 0, st>>>(p->lat, p->lon, p->node, p->npos, p->n, p->pstride, p->xyz, p->PX,
-                                                     bad_flag, bad_value);
+                                                     bad_flag, bad_value, routes_args(p), ws);
+    p->scan_done = ws != 0;
     RT_CUDA(p->e, cudaGetLastError());
     return RT_OK;
 }
@@ -740,8 +867,7 @@ int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for, b
     }
     if (p->cells_from_coords && !vectors_ready) {
         // the position-ordered vectors feed both halves: produce them first, then fork
-        dim3 g0((p->pstride + 255) / 256, p->batch);
-        position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
+        launch_position_vectors(p, st);
         RT_CUDA(e, cudaGetLastError());
     }
     if (eval_without_matrix(p)) {
@@ -761,8 +887,8 @@ int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for, b
 
 int position_vectors_refresh(rt_problem *p, cudaStream_t st)
 {
-    dim3 g0((p->pstride + 255) / 256, p->batch);
-    position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX);
+    launch_position_vectors(p, st);
+    p->scan_done = false;
     RT_CUDA(p->e, cudaGetLastError());
     return RT_OK;
 }
