@@ -35,7 +35,7 @@ struct RoutesArgs {
 // the separators of a chunk are one ballot; pass 1 counts, pass 2 — after the eight warp totals have been combined —
 // writes rstart[].  route[] is left to the per-route kernel.  Robust against a malformed node array (the plan entry
 // points launch this before the host has finished validating it): nothing is written beyond rstride + 1 entries.
-constexpr int kPrepThreads = 256;
+constexpr int kPrepThreads = 1024;  // the vector kernels are launched with this many threads when the scan rides along
 
 __device__ __forceinline__ void routes_scan_small_block(const RoutesArgs &a, int b)
 {
@@ -104,7 +104,7 @@ __device__ __forceinline__ void routes_scan_small_block(const RoutesArgs &a, int
 }
 
 // PX[c][p] = xyz[c][node p]; positions beyond P repeat the depot so that G needs no bounds checks.
-__global__ void __launch_bounds__(256) position_vectors_kernel(const double *__restrict__ xyz,
+__global__ void __launch_bounds__(kPrepThreads) position_vectors_kernel(const double *__restrict__ xyz,
                                                                const int *__restrict__ node,
                                                                const int *__restrict__ npos, int n, int pstride,
                                                                double *__restrict__ PX, const RoutesArgs ra, int with_scan)
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(256) position_vectors_kernel(const double *__r
 // node occupies at least one position, the node-order array xyz on the side.  One launch instead of two on the plan
 // path.  A node id outside [0, n) reads the depot instead (the host rejects such input, but only after this launch);
 // a coordinate out of range is neutralised and reported through bad_flag = bad_value.
-__global__ void __launch_bounds__(256) position_unit_vectors_kernel(const double *__restrict__ lat,
+__global__ void __launch_bounds__(kPrepThreads) position_unit_vectors_kernel(const double *__restrict__ lat,
                                                                     const double *__restrict__ lon,
                                                                     const int *__restrict__ node,
                                                                     const int *__restrict__ npos, int n, int pstride,
@@ -797,9 +797,9 @@ static bool scan_rides_along(const rt_problem *p) { return p->grows > kFusedStat
 
 static void launch_position_vectors(rt_problem *p, cudaStream_t st)
 {
-    const int ws = scan_rides_along(p) ? 1 : 0;
-    dim3 g0((p->pstride + 255) / 256 + ws, p->batch);
-    position_vectors_kernel<<<g0, 256, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX, routes_args(p), ws);
+    const int ws = scan_rides_along(p) ? 1 : 0, th = ws ? kPrepThreads : 256;
+    dim3 g0((p->pstride + th - 1) / th + ws, p->batch);
+    position_vectors_kernel<<<g0, th, 0, st>>>(p->xyz, p->node, p->npos, p->n, p->pstride, p->PX, routes_args(p), ws);
     p->scan_done = ws != 0;
     p->best_clean = p->best_clean || ws != 0;
 }
@@ -848,9 +848,9 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors)
 // latency-bound kernels run on a side stream underneath the matrix kernel and join before anything evaluates moves.
 int position_unit_vectors_launch(rt_problem *p, cudaStream_t st, int *bad_flag, int bad_value)
 {
-    const int ws = scan_rides_along(p) ? 1 : 0;
-    dim3 g0((p->pstride + 255) / 256 + ws, p->batch);
-    position_unit_vectors_kernel<<<g0, 256, 0, st>>>(p->lat, p->lon, p->node, p->npos, p->n, p->pstride, p->xyz, p->PX,
+    const int ws = scan_rides_along(p) ? 1 : 0, th = ws ? kPrepThreads : 256;
+    dim3 g0((p->pstride + th - 1) / th + ws, p->batch);
+    position_unit_vectors_kernel<<<g0, th, 0, st>>>(p->lat, p->lon, p->node, p->npos, p->n, p->pstride, p->xyz, p->PX,
                                                      bad_flag, bad_value, routes_args(p), ws);
     p->scan_done = ws != 0;
     RT_CUDA(p->e, cudaGetLastError());
