@@ -224,9 +224,12 @@ __global__ void __launch_bounds__(kSelectThreads) batch_apply_kernel(const Batch
 
 // Up to kFusedRoutes routes per instance the whole selection is small enough for one block: the three rounds and the
 // apply step run in ONE kernel (row minima by a warp per route, m[] / claims / the batch in shared memory) instead of
-// eight dependent launches.  Same selection, same order.  Beyond that one block is slower than the launches
-// (measured at 262 routes: 0.32 s instead of 0.28 s for the 10,000-stop solve).
-constexpr int kFusedRoutes = 128;
+// eight dependent launches.  The R x R table is copied into (dynamic) shared memory once and the three rounds read it
+// from there (row minima by a warp per row, column minima by a warp per column, no atomics): 8 R^2 bytes next to the ~30 KB of the selection and apply arrays caps R at 152 (a 5,000-stop / 50-vehicle
+// instance has 140 routes).  Same selection, same order.  Beyond that the separate launches are used (one block reading
+// a 262 x 262 table three times from global memory was slower than them: 0.32 s instead of 0.28 s for the 10,000-stop
+// solve).
+constexpr int kFusedRoutes = 152;
 
 __global__ void __launch_bounds__(kSelectThreads) batch_fused_kernel(const BatchArgs a)
 {
@@ -239,19 +242,23 @@ __global__ void __launch_bounds__(kSelectThreads) batch_fused_kernel(const Batch
     const int *route = a.route + static_cast<size_t>(b) * a.pstride;
     if (tid < kFusedRoutes) s_taken[tid] = 0;
     if (tid == 0) s_count = 0;
+    // the table, once, into shared memory: [R][RS] packed keys (unsigned form), odd row stride so that a column walk
+    // touches different banks
+    extern __shared__ unsigned long long s_tab[];
+    const int RS = R | 1;
+    for (int ra = w; ra < R; ra += kSelectThreads / 32)
+        for (int rb = lane; rb < R; rb += 32) s_tab[ra * RS + rb] = a.inter[(ro + ra) * a.cr + rb] ^ a.xmask;
+    __syncthreads();
     for (int round = 0; round < kRounds; ++round) {
-        if (tid < kFusedRoutes) s_m[tid] = kNoMove;
-        __syncthreads();
+        // m[r] = minimum over the entries that touch r with both routes unclaimed = min(row r, column r, intra[r]):
+        // one warp per row, then one warp per column — no atomics (64-bit minima on shared memory are CAS loops)
         for (int ra = w; ra < R; ra += kSelectThreads / 32) {
             unsigned long long best = kNoMove;
             if (!s_taken[ra]) {
-                const unsigned long long *row = a.inter + (ro + ra) * a.cr;
+                const unsigned long long *row = s_tab + ra * RS;
                 for (int rb = lane; rb < R; rb += 32) {
-                    if (s_taken[rb]) continue;
-                    const unsigned long long k = row[rb] ^ a.xmask;
-                    if (k == kNoMove) continue;
+                    const unsigned long long k = s_taken[rb] ? kNoMove : row[rb];
                     best = k < best ? k : best;
-                    if (k < s_m[rb]) atomicMin(&s_m[rb], k);  // s_m[] only decreases: a stale read costs one redundant atomic
                 }
                 if (lane == 0) {
                     const unsigned long long k = a.intra[ro + ra] ^ a.xmask;
@@ -262,10 +269,26 @@ __global__ void __launch_bounds__(kSelectThreads) batch_fused_kernel(const Batch
                     const unsigned long long o = __shfl_xor_sync(0xffffffffu, best, off);
                     best = o < best ? o : best;
                 }
-                if (lane == 0 && best != kNoMove) atomicMin(&s_m[ra], best);
             }
             if (lane == 0) s_rowbest[ra] = best;
         }
+        for (int rb = w; rb < R; rb += kSelectThreads / 32) {
+            unsigned long long best = kNoMove;
+            if (!s_taken[rb]) {
+                for (int ra = lane; ra < R; ra += 32) {
+                    const unsigned long long k = s_taken[ra] ? kNoMove : s_tab[ra * RS + rb];
+                    best = k < best ? k : best;
+                }
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) {
+                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, best, off);
+                    best = o < best ? o : best;
+                }
+            }
+            if (lane == 0) s_m[rb] = best;   // column part; the row part joins below
+        }
+        __syncthreads();
+        if (tid < R) s_m[tid] = s_rowbest[tid] < s_m[tid] ? s_rowbest[tid] : s_m[tid];
         __syncthreads();
         unsigned long long K = kNoMove;
         int rb = 0;
@@ -281,7 +304,7 @@ __global__ void __launch_bounds__(kSelectThreads) batch_fused_kernel(const Batch
         if (lane == 0) s_warp[w] = __popc(ball);
         __syncthreads();
         int before = 0, total = 0;
-        for (int i = 0; i < kFusedRoutes / 32; ++i) {  // routes live in the first kFusedRoutes threads
+        for (int i = 0; i < (kFusedRoutes + 31) / 32; ++i) {  // routes live in the first kFusedRoutes threads
             const int c = s_warp[i];
             before += i < w ? c : 0;
             total += c;
@@ -362,7 +385,14 @@ int batch_select_apply(rt_problem *p, const unsigned long long *table, bool sign
     rt_engine *e = p->e;
     const BatchArgs a = batch_args(p, table, signed_keys);
     if (p->cache_r <= kFusedRoutes) {
-        batch_fused_kernel<<<p->batch, kSelectThreads, 0, st>>>(a);
+        const size_t tab_bytes = static_cast<size_t>(p->cache_r) * (p->cache_r | 1) * 8;
+        static bool attr_set = false;  // once per process: the kernel may use up to 8 * kFusedRoutes^2 bytes on top of its statics
+        if (!attr_set) {
+            RT_CUDA(e, cudaFuncSetAttribute(batch_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            kFusedRoutes * (kFusedRoutes | 1) * 8));
+            attr_set = true;
+        }
+        batch_fused_kernel<<<p->batch, kSelectThreads, tab_bytes, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
         return state_refresh(p, st);
     }

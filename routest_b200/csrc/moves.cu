@@ -82,6 +82,13 @@ __device__ __forceinline__ void block_min_to_global(unsigned long long best, uns
     }
 }
 
+// minimum into a table entry that holds either packed keys or their signed-order form (see block_min_to_global)
+__device__ __forceinline__ void table_min(unsigned long long *dst, unsigned long long key, int signed_dst)
+{
+    if (signed_dst) atomicMin(reinterpret_cast<long long *>(dst), static_cast<long long>(key ^ 0x8000000000000000ull));
+    else atomicMin(dst, key);
+}
+
 struct EvalArgs {
     const int2 *G;         // [batch][grows][gpitch] route-order matrix, G[p][q] = M[node p][node q]
     const int2 *GT;        // its transpose GT[p][q] = M[node q][node p] (asymmetric matrices only)
@@ -268,8 +275,8 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
     unsigned long long *trow = TABLE ? a.inter + static_cast<size_t>(b) * a.cr * a.cr + q_route : nullptr;
     auto flush = [&]() {
         if (best_i != 0xFFFFFFFFu)
-            atomicMin(trow + static_cast<size_t>(cur_ra) * a.cr,
-                      (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i);
+            table_min(trow + static_cast<size_t>(cur_ra) * a.cr,
+                      (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i, a.signed_dst);
         best_d = INT_MAX;
         thr = INT_MAX;
         best_i = 0xFFFFFFFFu;
@@ -481,8 +488,9 @@ __global__ void __launch_bounds__(kInterThreads, COLS == 1 ? 8 : 5) eval_inter_f
 #pragma unroll
         for (int c = 0; c < COLS; ++c) {
             if (best_i[c] != 0xFFFFFFFFu)
-                atomicMin(a.inter + (static_cast<size_t>(b) * a.cr + cur_ra) * a.cr + col[c].q_route,
-                          (static_cast<unsigned long long>(static_cast<unsigned>(best_d[c]) + 0x80000000u) << 32) | best_i[c]);
+                table_min(a.inter + (static_cast<size_t>(b) * a.cr + cur_ra) * a.cr + col[c].q_route,
+                          (static_cast<unsigned long long>(static_cast<unsigned>(best_d[c]) + 0x80000000u) << 32) | best_i[c],
+                          a.signed_dst);
             best_d[c] = thr[c] = INT_MAX;
             best_i[c] = 0xFFFFFFFFu;
         }
@@ -764,7 +772,7 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
         }
     }
     if (TABLE) {
-        if (best != kNoMove) atomicMin(a.intra + static_cast<size_t>(b) * a.cr + t_route, best);
+        if (best != kNoMove) table_min(a.intra + static_cast<size_t>(b) * a.cr + t_route, best, a.signed_dst);
     } else if (!DUMP) {
         block_min_to_global<kIntraThreads>(best, a.best + b, a.signed_dst != 0);
     }
@@ -985,7 +993,7 @@ __global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const
     }
     if (TABLE) {
         best = warp_min_u64(best);
-        if (lane == 0 && best != kNoMove) atomicMin(a.intra + static_cast<size_t>(b) * a.cr + t_route, best);
+        if (lane == 0 && best != kNoMove) table_min(a.intra + static_cast<size_t>(b) * a.cr + t_route, best, a.signed_dst);
     } else if (!DUMP) {
         block_min_to_global<kIntraWarps * 32>(best, a.best + b, a.signed_dst != 0);
     }
@@ -1119,10 +1127,10 @@ __global__ void fill_keys_kernel(unsigned long long *dst, int batch)
     if (i < batch) dst[i] = kNoMove;
 }
 
-__global__ void flip_keys_kernel(unsigned long long *keys, size_t count)
+__global__ void fill_signed_none_kernel(unsigned long long *keys, size_t count)
 {
     const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i < count) keys[i] ^= 0x8000000000000000ull;
+    if (i < count) keys[i] = 0x7FFFFFFFFFFFFFFFull;
 }
 
 }  // namespace
@@ -1181,7 +1189,14 @@ int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_co
     a.inter = table_d;
     a.intra = table_d + B * cr * cr;
     a.cr = p->cache_r;
-    RT_CUDA(e, cudaMemsetAsync(table_d, 0xFF, B * (cr * cr + cr) * 8, st));
+    const size_t count = B * (cr * cr + cr);
+    if (signed_keys) {  // "none" in signed-order form is INT64_MAX: the kernels reduce with the signed atomic, no conversion pass
+        fill_signed_none_kernel<<<static_cast<unsigned>((count + 255) / 256), 256, 0, st>>>(table_d, count);
+        RT_CUDA(e, cudaGetLastError());
+        a.signed_dst = 1;
+    } else {
+        RT_CUDA(e, cudaMemsetAsync(table_d, 0xFF, count * 8, st));
+    }
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
     const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
     const bool overlap = (families & 6) && p->side_stream;
@@ -1197,11 +1212,6 @@ int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_co
     if (overlap) {
         RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
         RT_CUDA(e, cudaStreamWaitEvent(st, p->ev_join, 0));
-    }
-    if (signed_keys) {
-        const size_t count = B * (cr * cr + cr);
-        flip_keys_kernel<<<static_cast<unsigned>((count + 255) / 256), 256, 0, st>>>(table_d, count);
-        RT_CUDA(e, cudaGetLastError());
     }
     return RT_OK;
 }
