@@ -727,12 +727,15 @@ def block_solve(cx):
     """C5: 5,000 stops / 50 vehicles, greedy start -> local optimum with batched iterations (SPEC.md §8.1) over the
     replicas: shard tables, ONE int64 MIN all-reduce per iteration, the same batch applied everywhere."""
     torch, eng, rank, world = cx.torch, cx.eng, cx.rank, cx.world
-    from routest_b200.dist import DistributedSearch
+    from routest_b200.dist import DistributedSearch, PeerExchangeUnavailable
     t0 = time.perf_counter()
     pr, w = build_problem(eng, SEED_5K, 5000, 50)
     t_build = time.perf_counter() - t0
     cost0 = int(pr.get_state(0)["cost"])
-    search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True)
+    try:     # the table travels through peer memory where CUDA IPC works on every rank, through NCCL otherwise
+        search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True, exchange="peer")
+    except PeerExchangeUnavailable:
+        search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True, exchange="nccl")
     cx.barrier()
     t0 = time.perf_counter()
     moves, cost = search.run()
@@ -751,7 +754,11 @@ def block_solve(cx):
     res = {"local_search_ms": dt * 1e3, "moves": int(moves[0]), "routes": len(routes), "cost_greedy": cost0,
            "cost_local_optimum": int(cost[0]), "n_gpus": world, "ranks_agree": agree, "routes_crc32": sig,
            "graph_replayed": search._graph is not None, "setup_incl_greedy_ms": t_build * 1e3,
-           "driver": "DistributedSearch(batched=True): eval_table_dev -> NCCL MIN all_reduce of R^2+R keys -> apply_batch_dev"}
+           "exchange": search.exchange,
+           "driver": "DistributedSearch(batched=True): every rank scores its shard into the table of best keys per route pair "
+                     "(R^2 + R int64), the tables are MIN-combined (peer: all-gather into the replicas' memory over NVLink + "
+                     "local minimum; nccl: one all_reduce), every rank selects and applies the same batch; iterations "
+                     "replayed from a CUDA graph"}
     if rank == 0:   # the single-GPU driver on the same instance: same moves, cost and routes
         pr1, _ = build_problem(eng, SEED_5K, 5000, 50)
         t0 = time.perf_counter()

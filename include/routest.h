@@ -287,6 +287,19 @@ int rt_problem_apply_moves_xchg_dev(rt_problem *p, int improving_only, void *str
 /* The wait alone: the reduced keys (packed, unsigned form) land in keys_d [batch] and nothing is applied. */
 int rt_problem_collect_keys_xchg_dev(rt_problem *p, void *keys_d, void *stream);
 
+/* The same for the batched iterations' table: the replicas all-gather their shard tables into each other's memory
+ * (plain coalesced stores over NVLink, one copy per rank and slot) and every replica takes the minimum locally, so the
+ * batched search needs no collective call in its loop either.  Order of calls: rt_problem_table_exchange_export(world)
+ * on every rank (after the routes are installed: it sizes the buffer for the table) -> all-gather the handles ->
+ * rt_problem_table_exchange_connect -> per iteration rt_problem_eval_table_xchg_dev (scores this replica's shard into
+ * table_d and publishes it), rt_problem_apply_batch_xchg_dev (waits, reduces into table_d, selects and applies the
+ * batch, refreshes the state).  table_d: device int64 [rt_problem_table_entries + 1] owned by the caller.  Same bounded
+ * wait and collective abort as above.  No reference counterpart. */
+int rt_problem_table_exchange_export(rt_problem *p, int world, void *handle_out);
+int rt_problem_table_exchange_connect(rt_problem *p, const void *handles, int rank, int world);
+int rt_problem_eval_table_xchg_dev(rt_problem *p, int families, void *table_d, void *stream);
+int rt_problem_apply_batch_xchg_dev(rt_problem *p, void *table_d, void *stream);
+
 /* Synchronises the device and reads the search bookkeeping: done [batch], moves [batch], cost [batch]. */
 int rt_problem_search_status(rt_problem *p, int32_t *done_out, int32_t *moves_out, int64_t *cost_out);
 

@@ -89,6 +89,10 @@ SIGNATURES = {
     "rt_problem_eval_moves_xchg_dev": (C.c_int, [c_problem_p, C.c_int, C.c_void_p]),
     "rt_problem_apply_moves_xchg_dev": (C.c_int, [c_problem_p, C.c_int, C.c_void_p]),
     "rt_problem_collect_keys_xchg_dev": (C.c_int, [c_problem_p, C.c_void_p, C.c_void_p]),
+    "rt_problem_table_exchange_export": (C.c_int, [c_problem_p, C.c_int, C.c_void_p]),
+    "rt_problem_table_exchange_connect": (C.c_int, [c_problem_p, C.c_void_p, C.c_int, C.c_int]),
+    "rt_problem_eval_table_xchg_dev": (C.c_int, [c_problem_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "rt_problem_apply_batch_xchg_dev": (C.c_int, [c_problem_p, C.c_void_p, C.c_void_p]),
     "rt_problem_search_status": (C.c_int, [c_problem_p, c_i32_p, c_i32_p, c_i64_p]),
     "rt_eta_load_model": (C.c_int, [c_engine_p, C.c_void_p, C.c_size_t]),
     "rt_eta_model_info": (C.c_int, [c_engine_p, c_i32_p, c_i32_p]),

@@ -236,6 +236,9 @@ void rt_problem_destroy(rt_problem *p)
     for (int i = 0; i < p->n_xpeer_mapped; ++i) cudaIpcCloseMemHandle(p->xpeer_mapped[i]);
     if (p->xpeers) cudaFree(p->xpeers);
     if (p->xbuf) cudaFree(p->xbuf);
+    for (int i = 0; i < p->n_xtab_mapped; ++i) cudaIpcCloseMemHandle(p->xtab_mapped[i]);
+    if (p->xtab_peers) cudaFree(p->xtab_peers);
+    if (p->xtab) cudaFree(p->xtab);
     for (rt::DevBuf *bf : {&p->cache_inter, &p->cache_intra, &p->cache_tiles, &p->cache_misc, &p->batch_buf})
         if (bf->p) cudaFree(bf->p);
     if (p->Gbuf.p) cudaFree(p->Gbuf.p);

@@ -93,6 +93,12 @@ struct rt_problem {
     unsigned long long **xpeers = nullptr;     // device table of every replica's slot buffer
     void *xpeer_mapped[64] = {nullptr};
     int n_xpeer_mapped = 0, xrank = 0, xworld = 0, xiter = 0;
+    // peer exchange of the batched search's table (exchange.cu)
+    unsigned long long *xtab = nullptr;        // this replica's buffer: control words + [2][world][entries] keys
+    size_t xtab_words = 0;
+    unsigned long long **xtab_peers = nullptr; // device table of every replica's buffer (+ a block counter behind it)
+    void *xtab_mapped[64] = {nullptr};
+    int n_xtab_mapped = 0, xtab_rank = 0, xtab_world = 0, xtab_iter = 0;
     void *all_allocs[64] = {nullptr};
     int n_allocs = 0;
 };

@@ -9,7 +9,8 @@ Where the path shards:
     so `ReduceOp.MIN` on int64 picks the lowest (delta, family, p, q) and INT64_MAX means "no move".
     With `batched=True` an iteration applies a whole set of independent moves (SPEC.md §8.1): every rank scores
     its shard into a table of best keys per ordered route pair, the ranks MIN-reduce that table (R^2 + R int64 per
-    instance) in one all-reduce, and every rank selects and applies the same batch.
+    instance) — one all-reduce, or an all-gather into peer memory plus a local minimum — and every rank selects and
+    applies the same batch.
   * greedy construction                               -> replicas only (sequential chain).
 The reduce is 8 bytes per instance and latency bound.  The host does not pace the kernels one by one: everything
 between two all-reduces (apply the winner, rebuild this rank's matrix rows and the route state, score the shard) is
@@ -21,7 +22,10 @@ Two transports for that reduce:
   exchange="peer"  no collective call in the loop: the replicas export a slot buffer through CUDA IPC once, and the
                    evaluation step MIN-reduces its keys straight into every peer's buffer with system-scope atomics
                    over NVLink (routest_b200/csrc/exchange.cu); torch.distributed only carries the handles at set-up.
-                   Two iterations (the two slots) form one graph.
+                   The batched table travels the same way (every rank stores its shard table into every replica's
+                   buffer, each replica takes the minimum locally).  Two iterations (the two slots) form one graph.
+                   An NCCL all-reduce costs 18 us on two B200s and 29-40 us on eight whatever its size up to 0.5 MB;
+                   the peer exchange about a third of that.
 """
 from __future__ import annotations
 
@@ -30,6 +34,11 @@ import torch.distributed as dist
 
 INT64_NONE = 2 ** 63 - 1
 DONE_ABORTED = 3  # rt_problem_search_status: a replica gave up waiting for a peer (exchange.cu)
+
+
+class PeerExchangeUnavailable(RuntimeError):
+    """CUDA IPC export or mapping failed on some rank.  Raised on EVERY rank of the group together (the ranks agree on
+    it through the handles they gather and one flag all-reduce), so callers can fall back to exchange="nccl" in step."""
 
 
 class ReplicaAborted(RuntimeError):
@@ -66,32 +75,50 @@ class DistributedSearch:
             problem.set_shard(self.rank, self.world)
         if exchange not in ("nccl", "peer"):
             raise ValueError("exchange must be 'nccl' or 'peer'")
-        if batched and exchange != "nccl":
-            raise ValueError("batched iterations exchange their table through the collective (exchange='nccl')")
         self.exchange = exchange
         self.batched = batched
-        self.table = (torch.empty(problem.table_entries(), dtype=torch.int64, device=device) if batched else None)
+        # one spare entry: the peer exchange moves the table in 16-byte pairs
+        self.table = (torch.full((problem.table_entries() + 1,), INT64_NONE, dtype=torch.int64, device=device)
+                      if batched else None)
         self.use_graph = bool(graph) and self.keys.is_cuda
         self._graph = None       # everything between two all-reduces (nccl) / two whole iterations (peer)
         self._primed = False     # nccl: the first evaluation has been enqueued
         self._capture_refused = False
         if exchange == "peer":
-            handle = problem.exchange_export()
+            try:
+                handle = problem.table_exchange_export(self.world) if batched else problem.exchange_export()
+            except Exception:
+                handle = None
             handles = [None] * self.world
             if self.world > 1:
                 dist.all_gather_object(handles, handle, group=group)
             else:
                 handles[0] = handle
-            problem.exchange_connect(handles, self.rank, self.world)
-            if self.world > 1:
-                dist.barrier(group=group)  # nobody publishes into a buffer that is not mapped yet
+            if any(h is None for h in handles):
+                raise PeerExchangeUnavailable("CUDA IPC export failed on a rank")
+            ok = True
+            try:
+                if batched:
+                    problem.table_exchange_connect(handles, self.rank, self.world)
+                else:
+                    problem.exchange_connect(handles, self.rank, self.world)
+            except Exception:
+                ok = False
+            if self.world > 1:   # also the barrier: nobody publishes into a buffer that is not mapped yet
+                flag = torch.tensor([1 if ok else 0], device=self.keys.device)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+                ok = bool(flag.item())
+            if not ok:
+                raise PeerExchangeUnavailable("mapping a peer's exchange buffer failed on a rank")
 
     def _stream(self) -> int:
         return torch.cuda.current_stream().cuda_stream if self.keys.is_cuda else 0
 
     # -- the pieces of an iteration, stream-ordered ---------------------------------------------------------------
     def _evaluate(self, s):
-        if self.batched:
+        if self.batched and self.exchange == "peer":
+            self.problem.eval_table_xchg_dev(self.table.data_ptr(), self.families, s)
+        elif self.batched:
             self.problem.eval_table_dev(self.table.data_ptr(), self.families, (self.rank, self.world), s)
         elif self.exchange == "peer":
             self.problem.eval_moves_xchg_dev(self.families, s)
@@ -103,7 +130,9 @@ class DistributedSearch:
             allreduce_min_keys(self.table if self.batched else self.keys, self.group)
 
     def _apply(self, s):
-        if self.batched:
+        if self.batched and self.exchange == "peer":
+            self.problem.apply_batch_xchg_dev(self.table.data_ptr(), s)
+        elif self.batched:
             self.problem.apply_batch_dev(self.table.data_ptr(), s)
         elif self.exchange == "peer":
             self.problem.apply_moves_xchg_dev(True, s)

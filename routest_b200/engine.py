@@ -6,7 +6,9 @@ handle and never synchronise — torch supplies device memory, streams and NCCL,
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
+import threading
 import weakref
 
 import numpy as np
@@ -72,10 +74,13 @@ class Engine:
             raise EngineError(rc, (msg or b"rt_create failed").decode())
         self.device = int(device)
         self._problems = weakref.WeakSet()   # closed before the engine: a problem's handle points into it
+        self._pool, self._pool_lock = {}, threading.Lock()   # idle single-instance problems by node count (lease_problem)
 
     # -- lifetime -----------------------------------------------------------------------------------------------
     def close(self):
         if getattr(self, "_h", None):
+            with self._pool_lock:
+                self._pool.clear()
             for pr in list(getattr(self, "_problems", ())):
                 pr.close()
             self._lib.rt_destroy(self._h)
@@ -244,6 +249,40 @@ class Engine:
 
     def problem(self, n: int, batch: int = 1) -> "Problem":
         return Problem(self, n, batch)
+
+    POOL_MAX_NODES = 2048      # larger problems are created and destroyed per use (their matrix alone is > 32 MB)
+    POOL_MAX_IDLE_PER_SIZE = 4
+
+    @contextlib.contextmanager
+    def lease_problem(self, n: int):
+        """A single-instance problem of n nodes for the duration of one request.  rt_problem_create / _destroy are some
+        forty cudaMalloc / cudaFree calls — 0.3-0.4 ms, most of a small request — so idle problems are kept per node
+        count and handed out again (the reference's handlers run on arbitrary Flask worker threads, app.py:8: concurrent
+        requests each get their own problem; a size seen for the first time is created on the spot).  The caller
+        re-installs coordinates / matrix / stops / routes as it goes; nothing of the previous request is read."""
+        pr = None
+        if n <= self.POOL_MAX_NODES:
+            with self._pool_lock:
+                idle = self._pool.get(n)
+                if idle:
+                    pr = idle.pop()
+        if pr is None:
+            pr = Problem(self, n, 1)
+        try:
+            yield pr
+        except BaseException:
+            pr.close()   # whatever went wrong, do not hand this one out again
+            raise
+        else:
+            keep = False
+            if n <= self.POOL_MAX_NODES and getattr(pr, "_p", None):
+                with self._pool_lock:
+                    idle = self._pool.setdefault(n, [])
+                    if len(idle) < self.POOL_MAX_IDLE_PER_SIZE:
+                        idle.append(pr)
+                        keep = True
+            if not keep:
+                pr.close()
 
 
 NO_MOVE = 0xFFFFFFFFFFFFFFFF
@@ -584,6 +623,22 @@ class Problem:
 
     def collect_keys_xchg_dev(self, keys_ptr: int, stream: int = 0):
         self._check(self._lib.rt_problem_collect_keys_xchg_dev(self._p, keys_ptr, stream or None))
+
+    def table_exchange_export(self, world: int) -> bytes:
+        buf = C.create_string_buffer(int(self._lib.rt_problem_exchange_handle_bytes()))
+        self._check(self._lib.rt_problem_table_exchange_export(self._p, int(world), C.cast(buf, C.c_void_p)))
+        return buf.raw
+
+    def table_exchange_connect(self, handles, rank: int, world: int):
+        blob = b"".join(handles)
+        buf = C.create_string_buffer(blob, len(blob))
+        self._check(self._lib.rt_problem_table_exchange_connect(self._p, C.cast(buf, C.c_void_p), int(rank), int(world)))
+
+    def eval_table_xchg_dev(self, table_ptr: int, families: int = ALL_FAMILIES, stream: int = 0):
+        self._check(self._lib.rt_problem_eval_table_xchg_dev(self._p, int(families), table_ptr, stream or None))
+
+    def apply_batch_xchg_dev(self, table_ptr: int, stream: int = 0):
+        self._check(self._lib.rt_problem_apply_batch_xchg_dev(self._p, table_ptr, stream or None))
 
     def search_status(self):
         done = np.zeros(self.batch, np.int32)

@@ -220,8 +220,7 @@ def _solve_on_device(eng, all_points, profile_type, demand, cap, max_dist, desti
     lon = np.array([float(p["lon"]) for p in all_points])
     ds, ts = DEFAULT_DIST_SCALE, time_scale_for_profile(profile_type)
     extended = _wants_extension(destinations, driver_details)
-    pr = eng.problem(n, 1)
-    try:
+    with eng.lease_problem(n) as pr:   # kept per size on the engine: no forty cudaMalloc / cudaFree per request
         pr.set_coords(lat, lon)
         pr.build_matrix(ds, ts)
         md_units = min(max_dist * ds, 9e18)
@@ -237,8 +236,6 @@ def _solve_on_device(eng, all_points, profile_type, demand, cap, max_dist, desti
         if extended and driver_details.get("improve"):
             trips = _improve(pr, trips, driver_details)
         D, T = pr.get_matrix(0) if n <= 2048 else (None, None)
-    finally:
-        pr.close()
     return {"trips": trips, "offline": _OfflineDirections(eng, profile_type, lat=lat, lon=lon, D=D, T=T, ds=ds)}
 
 

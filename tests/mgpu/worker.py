@@ -128,9 +128,11 @@ def main():
     ok = True
     ok &= pass_case(eng, rank, world)
     for exchange, batched, graph in (("nccl", False, True), ("nccl", False, False), ("peer", False, True),
-                                     ("peer", False, False), ("nccl", True, True)):
+                                     ("peer", False, False), ("nccl", True, True), ("peer", True, True),
+                                     ("peer", True, False)):
         ok &= search_case(eng, rank, world, 600, 8, exchange, batched, 24 if not batched else 6, graph)
-    ok &= search_case(eng, rank, world, 5000, 50, "nccl", True, 4, True)    # multi-launch state tables, 50 routes
+    ok &= search_case(eng, rank, world, 5000, 50, "nccl", True, 4, True)    # multi-launch state tables, 140 routes
+    ok &= search_case(eng, rank, world, 5000, 50, "peer", True, 4, True)
     ok &= eta_case(eng, rank, world)
     all_ok = agree([1 if ok else 0]) and ok
     eng.close()

@@ -507,6 +507,22 @@ def test_peer_exchange_entry_points_single_replica(engine):
         assert np.array_equal(pr.get_state(0)["node"], final)
 
 
+def test_table_exchange_entry_points_single_replica(engine):
+    """The batched search's table through the peer exchange (all-gather into the replicas' buffers + local minimum),
+    here with one replica and many iterations through both slots: the oracle's batches, key for key."""
+    import torch
+    from routest_b200.dist import DistributedSearch
+    inst, node, raw = synth_vrptw(16, 180, 7)
+    final, okeys, sizes, ocost = O.local_search_batched(inst, node, threads=O.num_threads())
+    for graph in (False, True):
+        with _load(engine, [(inst, node, raw)]) as pr:
+            search = DistributedSearch(pr, 1, device="cuda", check_every=3, exchange="peer", batched=True, graph=graph)
+            moves, cost = search.run()
+            assert moves[0] == okeys.size and cost[0] == ocost
+            assert np.array_equal(pr.get_state(0)["node"], final)
+            assert (search._graph is not None) == graph
+
+
 def test_plan_upload_dev_scores_the_replica_shard(engine):
     """rt_problem_plan_upload_dev: host inputs in, the keys of THIS replica's shard left on the device in signed-order
     form; the minimum over the shards (what the NCCL MIN computes across ranks) is the oracle's best move."""

@@ -25,5 +25,5 @@ def test_two_ranks_real_nccl_and_ipc_match_the_oracle():
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=850)
     lines = [json.loads(ln) for ln in res.stdout.splitlines() if ln.startswith("{")]
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
-    assert len(lines) == 8 and all(ln["ok"] for ln in lines), lines
+    assert len(lines) == 11 and all(ln["ok"] for ln in lines), lines
     assert any(ln.get("graph") for ln in lines if ln["case"] == "search"), "no search ran from a CUDA graph"

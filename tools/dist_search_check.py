@@ -55,7 +55,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = Engine(local)
     pr, trips = build(eng, 5678, a.stops, a.vehicles)
-    search = DistributedSearch(pr, 1, device="cuda", check_every=4 if a.batched else 32, exchange=a.exchange,
+    search = DistributedSearch(pr, 1, device="cuda", check_every=8 if a.batched else 32, exchange=a.exchange,
                                batched=a.batched)
     torch.cuda.synchronize()
     if world > 1:
