@@ -733,7 +733,8 @@ def block_solve(cx):
     t_build = time.perf_counter() - t0
     cost0 = int(pr.get_state(0)["cost"])
     try:     # the table travels through peer memory where CUDA IPC works on every rank, through NCCL otherwise
-        search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True, exchange="peer")
+        search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True,
+                                   exchange="peer" if world > 1 else "nccl")   # one rank: nothing to exchange
     except PeerExchangeUnavailable:
         search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True, exchange="nccl")
     cx.barrier()

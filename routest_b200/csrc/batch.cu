@@ -152,7 +152,8 @@ __device__ __forceinline__ void apply_batch(const BatchArgs &a, int b, const uns
     const size_t po = static_cast<size_t>(b) * a.pstride;
     const int *rstart = a.rstart + static_cast<size_t>(b) * (a.rstride + 1);
     const int *route = a.route + po;
-    int *node = a.node + po, *tmp = a.tmp + po;
+    int *__restrict__ node = a.node + po;
+    int *__restrict__ tmp = a.tmp + po;   // distinct arrays: lets the copy loops below keep several loads in flight
     s_type[tid] = kKeep;
     s_len[tid] = tid < R ? rstart[tid + 1] - rstart[tid] : 0;
     __syncthreads();
@@ -193,6 +194,7 @@ __device__ __forceinline__ void apply_batch(const BatchArgs &a, int b, const uns
     for (int r = tid >> 5; r < R; r += kSelectThreads / 32) {
         const int os = rstart[r], ns = s_scan[r] - s_len[r], L = s_len[r];
         const int type = s_type[r], x = s_x[r], y = s_y[r], src = s_src[r];
+#pragma unroll 4
         for (int j = lane; j < L; j += 32) {
             int from = os + j;
             switch (type) {
@@ -212,6 +214,7 @@ __device__ __forceinline__ void apply_batch(const BatchArgs &a, int b, const uns
     }
     if (tid == 0) tmp[P - 1] = 0;
     __syncthreads();
+#pragma unroll 8
     for (int i = tid; i < P; i += kSelectThreads) node[i] = tmp[i];
 }
 
@@ -246,8 +249,18 @@ __global__ void __launch_bounds__(kSelectThreads) batch_fused_kernel(const Batch
     // touches different banks
     extern __shared__ unsigned long long s_tab[];
     const int RS = R | 1;
-    for (int ra = w; ra < R; ra += kSelectThreads / 32)
-        for (int rb = lane; rb < R; rb += 32) s_tab[ra * RS + rb] = a.inter[(ro + ra) * a.cr + rb] ^ a.xmask;
+    __shared__ unsigned long long s_intra[kFusedRoutes];
+    constexpr int kColChunks = (kFusedRoutes + 31) / 32;
+    for (int ra = w; ra < R; ra += kSelectThreads / 32) {  // a warp per row, the row's loads all in flight at once
+        const unsigned long long *row = a.inter + (ro + ra) * a.cr;
+        unsigned long long v[kColChunks];
+#pragma unroll
+        for (int k = 0; k < kColChunks; ++k) v[k] = lane + 32 * k < R ? row[lane + 32 * k] : 0ull;
+#pragma unroll
+        for (int k = 0; k < kColChunks; ++k)
+            if (lane + 32 * k < R) s_tab[ra * RS + lane + 32 * k] = v[k] ^ a.xmask;
+    }
+    if (tid < R) s_intra[tid] = a.intra[ro + tid] ^ a.xmask;
     __syncthreads();
     for (int round = 0; round < kRounds; ++round) {
         // m[r] = minimum over the entries that touch r with both routes unclaimed = min(row r, column r, intra[r]):
@@ -260,10 +273,7 @@ __global__ void __launch_bounds__(kSelectThreads) batch_fused_kernel(const Batch
                     const unsigned long long k = s_taken[rb] ? kNoMove : row[rb];
                     best = k < best ? k : best;
                 }
-                if (lane == 0) {
-                    const unsigned long long k = a.intra[ro + ra] ^ a.xmask;
-                    best = k < best ? k : best;
-                }
+                if (lane == 0) best = s_intra[ra] < best ? s_intra[ra] : best;
 #pragma unroll
                 for (int off = 16; off > 0; off >>= 1) {
                     const unsigned long long o = __shfl_xor_sync(0xffffffffu, best, off);
