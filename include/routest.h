@@ -338,8 +338,7 @@ int rt_selftest_pipe_peak(rt_engine *e, int mode, int iters, double *warp_inst_p
 /* Test and measurement knobs (process-wide, not for production use): "strip_rows" = rows per block of the tile kernel
  * (0 = let the launcher pick, 8..64), "intra_kernel" = which same-route kernel runs (0 = pick, 1 = one thread per
  * anchor, 2 = one warp per anchor), "fused_eval" = 1 (default): move kernels rebuild matrix cells from unit vectors
- * where the matrix is SPEC.md §2 of the problem's coordinates, 0: always write the route-order matrix and read it back;
- * "fused_cols" = columns per thread of that kernel (1 by default, 2).
+ * where the matrix is SPEC.md §2 of the problem's coordinates, 0: always write the route-order matrix and read it back.
  * Every choice gives the same keys; the tests run them against each other and the oracle.  No reference counterpart. */
 int rt_debug_set(const char *name, int value);
 

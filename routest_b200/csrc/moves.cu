@@ -359,6 +359,10 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
 // memory (broadcast LDS); per row it computes ONE new cell, (p+1, q), rotates (p, q) and (p-1, q) down its register
 // window, and gets (p, q-1) and (p, q+1) from its lane neighbours with four shuffles.  Lanes 0 and 31 of a warp only
 // feed their neighbours (a warp scores 30 columns).  No G write, no G read: a pass touches O(n) bytes of HBM.
+// (Two adjacent columns per thread — shared-memory loads and loop overhead paid once for two pairs, 2 of 64 columns halo
+// instead of 2 of 32 — was built and measured: 94 registers instead of 56, 314 vs 313 us on one GPU, 64 vs 61 us on a
+// 1/8 shard.  Not kept.)
+constexpr int kFusedCols = 120;  // columns scored per block: 4 warps x 30
 
 __device__ __forceinline__ int2 cell_from_vectors(double ax, double ay, double az, double bx, double by, double bz, float fd,
                                                   float ft, int lim_hi)
@@ -394,23 +398,10 @@ __device__ __forceinline__ double lds64(unsigned addr)
 
 // FAST: the launcher has proved from the coordinates' bounding box that no pair of the batch can leave the
 // straight-line range of the cell function (any metro-sized instance), so the per-cell range test is compiled out.
-// COLS: columns per thread.  With two, a lane owns the adjacent columns (2l-1, 2l) of its warp's 64: the row's shared
-// memory loads, its flag decoding and the loop overhead are paid once for two pairs, the inner neighbours are the
-// thread's own registers (two shuffles per pair instead of four), and only 2 of 64 columns are halo instead of 2 of 32
-// — at 94 registers instead of 56, i.e. 20 resident warps instead of 32.  Measured on the 10,000-stop pass: no
-// gain on one GPU (314 vs 313 us) and a loss on a 1/8 shard (64 vs 61 us); one column is the default, two stay
-// selectable (rt_debug_set "fused_cols") and tested.
-template <int COLS>
-struct FusedGeom {
-    static constexpr int kWarpCols = 32 * COLS - 2;              // columns a warp scores
-    static constexpr int kBlockCols = (kInterThreads / 32) * kWarpCols;
-};
-
-template <int MODE, bool FAST, int COLS>
-__global__ void __launch_bounds__(kInterThreads, COLS == 1 ? 8 : 5) eval_inter_fused_kernel(const EvalArgs a)
+template <int MODE, bool FAST>
+__global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(const EvalArgs a)
 {
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
-    constexpr int kBlockCols = FusedGeom<COLS>::kBlockCols, kWarpCols = FusedGeom<COLS>::kWarpCols;
     __shared__ RowSlot slots[kMaxStripRows + 2];
     const int kStripRows = a.strip_rows;
 
@@ -418,12 +409,15 @@ __global__ void __launch_bounds__(kInterThreads, COLS == 1 ? 8 : 5) eval_inter_f
     const int P = a.npos[b];
     int p_lo, p_hi;
     shard_range(P, a.shard_index, a.shard_count, p_lo, p_hi);
-    const int p0 = p_lo + blockIdx.y * kStripRows, q0 = blockIdx.x * kBlockCols;
+    const int p0 = p_lo + blockIdx.y * kStripRows, q0 = blockIdx.x * kFusedCols;
     if (p0 >= p_hi || q0 >= P) return;
 
     const size_t po = static_cast<size_t>(b) * a.pstride;
     const double *__restrict__ PX = a.PX + static_cast<size_t>(b) * 3 * a.pstride;
     const int tid = threadIdx.x, lane = tid & 31;
+    const int q = q0 + (tid >> 5) * 30 + lane - 1;            // lanes 0 and 31 are the warp's halo columns
+    const bool owner = lane >= 1 && lane <= 30;
+    const bool q_in = owner && q < P;
     const int rows = min(kStripRows, p_hi - p0);
     if (tid < rows + 2) {
         RowSlot sl;
@@ -443,116 +437,81 @@ __global__ void __launch_bounds__(kInterThreads, COLS == 1 ? 8 : 5) eval_inter_f
         sl.pad = 0.0;
         slots[tid] = sl;
     }
-    // this thread's columns: the first and the last column of a warp are halo (they only feed their neighbours)
-    ColQ col[COLS];
-    double bx[COLS], by[COLS], bz[COLS];
-    const int qw = q0 + (tid >> 5) * kWarpCols - 1 + lane * COLS;
-#pragma unroll
-    for (int c = 0; c < COLS; ++c) {
-        const int q = qw + c;
-        const bool halo = (lane == 0 && c == 0) || (lane == 31 && c == COLS - 1);
-        const bool q_in = !halo && q < P;
-        int4 Hq = make_int4(0, 0, 0, -1), qB = make_int4(0, 0, 0, 0);
-        int dep_q = 0, zn_q = 0, depprev_q = 0, capsl_q = 0, distsl_q = 0;
-        if (q_in) {
-            const int4 rA = a.RA[po + q], rC = a.RC[po + q], rD = a.RD[po + q];
-            Hq = a.H[po + q];
-            qB = a.RB[po + q];
-            dep_q = rA.x;
-            zn_q = rA.y;
-            depprev_q = rC.x;
-            capsl_q = rD.x;
-            distsl_q = rD.y;
-        }
-        const int qv = min(max(q, 0), a.pstride - 1);   // positions beyond P repeat the depot's vector
-        bx[c] = PX[qv];
-        by[c] = PX[a.pstride + qv];
-        bz[c] = PX[2 * static_cast<size_t>(a.pstride) + qv];
-        const int q_route = Hq.w & 0x7FFF;
-        const bool q_cust = q_in && ((Hq.w >> 30) & 1);
-        const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
-        const bool swap_q = q_cust && (a.families & 4);
-        col[c] = ColQ{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q};
+    int4 Hq = make_int4(0, 0, 0, -1), qB = make_int4(0, 0, 0, 0);
+    int dep_q = 0, zn_q = 0, depprev_q = 0, capsl_q = 0, distsl_q = 0;
+    if (q_in) {
+        const int4 rA = a.RA[po + q], rC = a.RC[po + q], rD = a.RD[po + q];
+        Hq = a.H[po + q];
+        qB = a.RB[po + q];
+        dep_q = rA.x;
+        zn_q = rA.y;
+        depprev_q = rC.x;
+        capsl_q = rD.x;
+        distsl_q = rD.y;
     }
+    const int qv = min(max(q, 0), a.pstride - 1);   // positions beyond P repeat the depot's vector
+    const double bx = PX[qv], by = PX[a.pstride + qv], bz = PX[2 * static_cast<size_t>(a.pstride) + qv];
     __syncthreads();
-    const bool swap_tile = (a.families & 4) && p0 < q0 + kBlockCols - 1;  // some pair of the tile has p < q
 
-    int best_d[COLS], thr[COLS], cur_ra = -1;
-    unsigned best_i[COLS];
-#pragma unroll
-    for (int c = 0; c < COLS; ++c) {
-        best_d[c] = thr[c] = INT_MAX;
-        best_i[c] = 0xFFFFFFFFu;
-    }
+    const int q_route = Hq.w & 0x7FFF;
+    const bool q_cust = q_in && ((Hq.w >> 30) & 1);
+    const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
+    const bool swap_q = q_cust && (a.families & 4);
+    const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q};
+    const bool swap_tile = (a.families & 4) && p0 < q0 + kFusedCols - 1;  // some pair of the tile has p < q
+
+    int best_d = INT_MAX, thr = INT_MAX;
+    unsigned best_i = 0xFFFFFFFFu;
+    int cur_ra = -1;
+    unsigned long long *trow = TABLE ? a.inter + static_cast<size_t>(b) * a.cr * a.cr + q_route : nullptr;
     auto flush = [&]() {
-#pragma unroll
-        for (int c = 0; c < COLS; ++c) {
-            if (best_i[c] != 0xFFFFFFFFu)
-                table_min(a.inter + (static_cast<size_t>(b) * a.cr + cur_ra) * a.cr + col[c].q_route,
-                          (static_cast<unsigned long long>(static_cast<unsigned>(best_d[c]) + 0x80000000u) << 32) | best_i[c],
-                          a.signed_dst);
-            best_d[c] = thr[c] = INT_MAX;
-            best_i[c] = 0xFFFFFFFFu;
-        }
+        if (best_i != 0xFFFFFFFFu)
+            table_min(trow + static_cast<size_t>(cur_ra) * a.cr,
+                      (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i, a.signed_dst);
+        best_d = INT_MAX;
+        thr = INT_MAX;
+        best_i = 0xFFFFFFFFu;
     };
-    unsigned sa = static_cast<unsigned>(__cvta_generic_to_shared(slots));
+    // slot address in a per-thread register (the shift is zero for every thread of a 128-thread block; it only keeps
+    // the compiler from proving the address uniform and moving it back into the uniform datapath)
+    unsigned sa = static_cast<unsigned>(__cvta_generic_to_shared(slots)) + (threadIdx.x >> 10);
     const float fd = a.fd, ft = a.ft;
     const int lim_hi = a.lim_hi;
-    auto cells_of_slot = [&](unsigned addr, int2 (&out)[COLS]) {  // cell(position of that slot, each of my columns)
+    auto cell_slot = [&](unsigned addr) {  // cell(position of that slot, q)
         const double ax = lds64(addr + 48), ay = lds64(addr + 56), az = lds64(addr + 64);
-#pragma unroll
-        for (int c = 0; c < COLS; ++c) {
-            if (FAST) {
-                const double dx = ax - bx[c], dy = ay - by[c], dz = az - bz[c];
-                out[c] = cell_i32_fast(fma(dx, dx, fma(dy, dy, dz * dz)), fd, ft);
-            } else {
-                out[c] = cell_from_vectors(ax, ay, az, bx[c], by[c], bz[c], fd, ft, lim_hi);
-            }
+        if (FAST) {
+            const double dx = ax - bx, dy = ay - by, dz = az - bz;
+            return cell_i32_fast(fma(dx, dx, fma(dy, dy, dz * dz)), fd, ft);
         }
+        return cell_from_vectors(ax, ay, az, bx, by, bz, fd, ft, lim_hi);
     };
-    int2 c_up[COLS], c_cur[COLS], c_dn[COLS];
-    cells_of_slot(sa, c_up);
-    cells_of_slot(sa + 80, c_cur);
+    int2 c_up = cell_slot(sa), c_cur = cell_slot(sa + 80);
     const unsigned full = 0xffffffffu;
 #pragma unroll 3
     for (int rr = 0; rr < rows; ++rr, sa += 80) {
         const int p = p0 + rr;
-        cells_of_slot(sa + 160, c_dn);
+        const int2 c_dn = cell_slot(sa + 160);
         const int4 Hp = lds128(sa);
         if ((Hp.w >> 30) & 1) {  // p is a customer (block-uniform)
-            // outer neighbours from the adjacent lanes, inner ones (COLS == 2) are this thread's own cells
-            const int2 from_left = make_int2(__shfl_up_sync(full, c_cur[COLS - 1].x, 1), __shfl_up_sync(full, c_cur[COLS - 1].y, 1));
-            const int2 from_right = make_int2(__shfl_down_sync(full, c_cur[0].x, 1), __shfl_down_sync(full, c_cur[0].y, 1));
+            const int2 c_lf = make_int2(__shfl_up_sync(full, c_cur.x, 1), __shfl_up_sync(full, c_cur.y, 1));
+            const int2 c_rt = make_int2(__shfl_down_sync(full, c_cur.x, 1), __shfl_down_sync(full, c_cur.y, 1));
             const int4 p1 = lds128(sa + 16), p2 = lds128(sa + 32);
             if (TABLE && (Hp.w & 0x7FFF) != cur_ra) {
                 flush();
                 cur_ra = Hp.w & 0x7FFF;
             }
-#pragma unroll
-            for (int c = 0; c < COLS; ++c) {
-                const int2 c_lf = c == 0 ? from_left : c_cur[c - 1];
-                const int2 c_rt = c == COLS - 1 ? from_right : c_cur[c + 1];
-                score_pair<MODE>(a, P, p, Hp, p1, p2, col[c], swap_tile, c_up[c], c_rt, c_cur[c], c_lf, c_dn[c], best_d[c],
-                                 best_i[c], thr[c]);
-            }
+            score_pair<MODE>(a, P, p, Hp, p1, p2, col, swap_tile, c_up, c_rt, c_cur, c_lf, c_dn, best_d, best_i, thr);
         }
-#pragma unroll
-        for (int c = 0; c < COLS; ++c) {
-            c_up[c] = c_cur[c];
-            c_cur[c] = c_dn[c];
-        }
+        c_up = c_cur;
+        c_cur = c_dn;
     }
     if (TABLE) {
         flush();
     } else if (!DUMP) {
-        unsigned long long best = kNoMove;
-#pragma unroll
-        for (int c = 0; c < COLS; ++c) {
-            if (best_i[c] == 0xFFFFFFFFu) continue;
-            const unsigned long long k =
-                (static_cast<unsigned long long>(static_cast<unsigned>(best_d[c]) + 0x80000000u) << 32) | best_i[c];
-            best = k < best ? k : best;
-        }
+        const unsigned long long best =
+            best_i == 0xFFFFFFFFu
+                ? kNoMove
+                : (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i;
         block_min_to_global<kInterThreads>(best, a.best + b, a.signed_dst != 0);
     }
 }
@@ -1007,7 +966,6 @@ __global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const
 // and a half-empty last wave simply runs faster.)  ROUTEST_STRIP_ROWS overrides, for experiments.
 int g_strip_rows = 0;    // rt_debug_set("strip_rows", h): 0 = pick, else the height to use
 int g_intra_kernel = 0;  // rt_debug_set("intra_kernel", k): 0 = pick, 1 = one thread per anchor, 2 = one warp per anchor
-int g_fused_cols = 1;    // rt_debug_set("fused_cols", c): columns per thread of the no-matrix tile kernel (1 or 2)
 
 int pick_strip_rows(int pmax, int rows, int batch, bool asym, int cols_per_block)
 {
@@ -1063,17 +1021,11 @@ template <int MODE>
 int launch_inter(rt_problem *p, EvalArgs &a, int pmax, int shard_rows, int batch, int strip_rows, cudaStream_t st)
 {
     const bool fused = eval_without_matrix(p);
-    const int fcols = g_fused_cols == 2 ? 2 : 1;
-    const int cols = !fused ? kInterThreads : fcols == 1 ? FusedGeom<1>::kBlockCols : FusedGeom<2>::kBlockCols;
+    const int cols = fused ? kFusedCols : kInterThreads;
     a.strip_rows = strip_rows > 0 ? strip_rows : pick_strip_rows(pmax, shard_rows, batch, !p->symmetric, cols);
     dim3 grid((pmax + cols - 1) / cols, (shard_rows + a.strip_rows - 1) / a.strip_rows, batch);
-    if (fused) {
-        const bool fast = all_pairs_in_fast_range(p, a);
-        if (fcols == 1 && fast) eval_inter_fused_kernel<MODE, true, 1><<<grid, kInterThreads, 0, st>>>(a);
-        else if (fcols == 1) eval_inter_fused_kernel<MODE, false, 1><<<grid, kInterThreads, 0, st>>>(a);
-        else if (fast) eval_inter_fused_kernel<MODE, true, 2><<<grid, kInterThreads, 0, st>>>(a);
-        else eval_inter_fused_kernel<MODE, false, 2><<<grid, kInterThreads, 0, st>>>(a);
-    }
+    if (fused && all_pairs_in_fast_range(p, a)) eval_inter_fused_kernel<MODE, true><<<grid, kInterThreads, 0, st>>>(a);
+    else if (fused) eval_inter_fused_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
     else if (p->symmetric) eval_inter_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
     else eval_inter_kernel<MODE, true><<<grid, kInterThreads, 0, st>>>(a);
     RT_CUDA(p->e, cudaGetLastError());
@@ -1236,7 +1188,6 @@ extern "C" int rt_debug_set(const char *name, int value)
     if (!strcmp(name, "strip_rows")) rt::g_strip_rows = value;
     else if (!strcmp(name, "intra_kernel")) rt::g_intra_kernel = value;
     else if (!strcmp(name, "fused_eval")) rt::g_fused_eval = value;
-    else if (!strcmp(name, "fused_cols")) rt::g_fused_cols = value;
     else return RT_ERR_INVALID_ARG;
     return RT_OK;
 }

@@ -593,8 +593,7 @@ def test_measured_pipe_peaks_are_plausible(engine):
     assert 1.6 < both / alu < 2.1
 
 
-@pytest.mark.parametrize("fused", [2, 1, 0], ids=["cells-from-vectors-2-columns", "cells-from-vectors-1-column",
-                                              "route-order-matrix"])
+@pytest.mark.parametrize("fused", [1, 0], ids=["cells-from-vectors", "route-order-matrix"])
 @pytest.mark.parametrize("kernel", [1, 2], ids=["thread-per-anchor", "warp-per-anchor"])
 @pytest.mark.parametrize("seed,stops,veh,kw", [(11, 40, 6, {}), (12, 150, 4, dict(half_lo=7200, half_hi=20000)),
                                                 (13, 260, 3, dict(half_lo=20000, half_hi=43200))])
@@ -606,8 +605,7 @@ def test_kernel_variants_agree_with_the_oracle(engine, fused, kernel, seed, stop
     searches too."""
     inst, node0, raw = synth_vrptw(seed, stops, veh, **kw)
     engine.debug_set("intra_kernel", kernel)
-    engine.debug_set("fused_eval", 1 if fused else 0)
-    engine.debug_set("fused_cols", fused if fused else 1)
+    engine.debug_set("fused_eval", fused)
     try:
         for node in (node0, _walk(inst, node0, seed, 10)):
             with _load(engine, [(inst, node0, raw)], [node]) as pr:
@@ -634,4 +632,3 @@ def test_kernel_variants_agree_with_the_oracle(engine, fused, kernel, seed, stop
     finally:
         engine.debug_set("intra_kernel", 0)
         engine.debug_set("fused_eval", 1)
-        engine.debug_set("fused_cols", 1)

@@ -25,12 +25,10 @@ def main():
     ap.add_argument("--once", action="store_true")
     ap.add_argument("--fused", type=int, default=1, help="0: write the route-order matrix and read it back")
     ap.add_argument("--strip", type=int, default=0)
-    ap.add_argument("--cols", type=int, default=1, help="columns per thread of the no-matrix tile kernel")
     a = ap.parse_args()
     eng = Engine(0)
     eng.debug_set("fused_eval", a.fused)
     eng.debug_set("strip_rows", a.strip)
-    eng.debug_set("fused_cols", a.cols)
     pr, w = bench.build_problem(eng, bench.SEED_10K, a.stops, a.vehicles)
     pr.set_shard(a.rank, a.world)
     keys = torch.zeros(1, dtype=torch.int64, device="cuda")
@@ -57,7 +55,7 @@ def main():
         return e0.elapsed_time(e1) / reps * 1e3
 
     replay, graphed = bench.capture(torch, one)
-    out = {"stops": a.stops, "shard": [a.rank, a.world], "fused": a.fused, "strip": a.strip, "cols": a.cols, "graphed": graphed,
+    out = {"stops": a.stops, "shard": [a.rank, a.world], "fused": a.fused, "strip": a.strip, "graphed": graphed,
            "us_matrix": timed(lambda: pr.refresh_dev(4, s)), "us_state": timed(lambda: pr.refresh_dev(2, s)),
            "us_refresh": timed(lambda: pr.refresh_dev(3, s)),
            "us_eval": timed(lambda: pr.eval_moves_dev(keys.data_ptr(), ALL_FAMILIES, (a.rank, a.world), s)),
