@@ -1,25 +1,26 @@
 // moves.cu — cost delta + capacity/distance/time-window feasibility of local-search moves and the best-move
 // argmin (SPEC.md §7).  No reference counterpart (the reference has no improvement phase, utils.py:111-139).
 //
-// Both kernels read the stop matrix in ROUTE ORDER, G[p][q] = M[node p][node q] (state.cu), so a thread that owns
-// insertion point / partner q and walks down the moved positions p touches G[p-1..p+1][q-1..q+1]: each warp-wide
-// load is one contiguous 256-byte run of a row, every cell comes from DRAM/L2 once per strip and its four
-// re-uses (left/right/up/down neighbours) are L1 hits or register rotations.
-//   * eval_inter_kernel — candidates between two different routes (relocate, swap): O(1) each from the 16-byte
-//     "hot" record of p and of q (removal delta, old-edge sum, edge after, route id) plus five cells.  Only the
-//     minimum key matters, so the full feasibility test (capacity, distance limit, time windows; cold records)
-//     runs only for candidates whose delta can still beat the best feasible key seen so far.
-//   * eval_intra_kernel — candidates inside one route (2-opt, relocate, swap): one thread per anchor position
-//     sweeps its route keeping two segment summaries (a, b, L) — forward and reversed — so every candidate is
-//     again O(1) and exact for time windows.
+// Where the matrix is SPEC.md §2 of the problem's own coordinates (the engine's normal case) NO matrix is read: every
+// kernel rebuilds the cells it needs from the position-ordered unit vectors with the device functions the matrix
+// kernel itself uses (geometry.cuh), so a pass moves O(n) bytes.  A caller-supplied matrix (road distances, possibly
+// directional) is read in ROUTE ORDER instead, G[p][q] = M[node p][node q] (state.cu): a thread that owns column q
+// and walks down the rows p touches G[p-1..p+1][q-1..q+1], each warp-wide load one contiguous 256-byte run.
+//   * eval_inter_fused_kernel / eval_inter_kernel — candidates between two different routes (relocate, swap): delta
+//     AND the full feasibility test (capacity, distance limit, time windows) for every pair, straight line — in a
+//     realistic state a large share of the candidates beats the best feasible delta while being infeasible, so pruning
+//     on the delta leaves almost every warp with some lane in the slow path.  What IS skipped is the best-key update:
+//     one warp vote against the smallest best delta of the warp.
+//   * eval_intra_kernel — candidates inside one route (2-opt, relocate, swap): one thread per anchor position sweeps
+//     its route keeping two segment summaries (a, b, L) — forward and reversed — so every candidate is O(1) and exact
+//     for time windows.  eval_intra_warp_kernel: the same summaries as two warp scans, one warp per anchor.
 // Each thread keeps the minimum packed key of its feasible candidates; warp shuffles and one shared-memory step
 // reduce it to one 64-bit atomicMin per block.  The minimum of packed keys is order independent, so the chosen
 // move does not depend on the thread, block or GPU partition.
 //
 // ASYM: a caller-supplied matrix may be directional (road networks are).  The kernels then read a second array,
 // GT[p][q] = M[node q][node p], wherever a cell is needed in the "towards p" orientation, so every access stays
-// row-contiguous; for a symmetric matrix (SPEC.md §2 always is) GT is G and the extra loads disappear at compile
-// time.
+// row-contiguous; for a symmetric matrix GT is G and the extra loads disappear at compile time.
 #include <climits>
 #include <cstdlib>
 #include <cstring>
