@@ -244,9 +244,10 @@ int rt_problem_plan_dev(rt_problem *p, double dist_scale, double time_scale, int
 int rt_problem_build_matrix_dev(rt_problem *p, double dist_scale, double time_scale, void *stream);
 int rt_problem_refresh_dev(rt_problem *p, int what, void *stream);
 
-/* Declares which part of the candidate space this replica evaluates (multi-GPU search: rank i of c).  From then
- * on every refresh rebuilds only the rows of the route-order matrix that shard needs, and rt_problem_eval_moves[_dev]
- * accepts only that shard.  Default 0 of 1 = everything. */
+/* Declares which part of the candidate space this replica evaluates (multi-GPU search: rank i of c): a contiguous range
+ * of rows p of the (p, q) plane, cut so that the c parts cost the same (early rows also score swaps against every later
+ * column, so they are about 1.4x as expensive as late ones and get fewer rows).  From then on every refresh rebuilds
+ * only what that shard needs, and rt_problem_eval_moves[_dev] accepts only that shard.  Default 0 of 1 = everything. */
 int rt_problem_set_shard(rt_problem *p, int shard_index, int shard_count);
 
 /* The same two steps on a caller's stream, for a multi-GPU search: every rank holds a replica of the problem,

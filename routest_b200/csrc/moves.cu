@@ -119,11 +119,7 @@ struct EvalArgs {
     unsigned char *dump_feas;
 };
 
-__device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, int &hi)
-{
-    lo = static_cast<int>(static_cast<long long>(P) * idx / cnt);
-    hi = static_cast<int>(static_cast<long long>(P) * (idx + 1) / cnt);
-}
+__device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, int &hi) { shard_bounds(P, idx, cnt, lo, hi); }
 
 enum { kBest = 0, kDump = 1, kTable = 2 };
 
@@ -1033,6 +1029,15 @@ int launch_inter(rt_problem *p, EvalArgs &a, int pmax, int shard_rows, int batch
     return RT_OK;
 }
 
+// Rows the grids must cover for shard idx of cnt: instances of a batch differ in P (pmin..pmax), and so do their
+// boundaries; the widest shard of the largest instance plus one row of slack bounds them all.
+int max_shard_rows(int pmax, int idx, int cnt)
+{
+    int lo, hi;
+    shard_bounds(pmax, idx, cnt, lo, hi);
+    return hi - lo + 2;
+}
+
 EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d)
 {
     EvalArgs a{};
@@ -1107,7 +1112,7 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     EvalArgs a = make_args(p, families, shard_index, shard_count, direct ? best_d : p->best);
     a.signed_dst = direct ? 1 : 0;
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;  // largest P of the batch
-    const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
+    const int shard_rows = max_shard_rows(pmax, shard_index, shard_count);
     // The sweep kernel is latency bound (a sequential walk per anchor, a few warps per SM) and the tile kernel is ALU
     // bound: they only share the best[] atomics, so the sweep runs on the side stream underneath the tile kernel.
     const bool overlap = (families & 6) && p->side_stream;
@@ -1151,7 +1156,7 @@ int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaMemsetAsync(table_d, 0xFF, count * 8, st));
     }
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
-    const int shard_rows = (pmax + shard_count - 1) / shard_count + 1;
+    const int shard_rows = max_shard_rows(pmax, shard_index, shard_count);
     const bool overlap = (families & 6) && p->side_stream;
     cudaStream_t st_intra = st;
     if (overlap) {

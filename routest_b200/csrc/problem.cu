@@ -697,13 +697,22 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
 }
 
 // Waits for the pass enqueued last and hands its keys out.
-static int plan_collect(rt_problem *p, uint64_t *best_keys_out, const char *who)
+// have_lock: the caller holds the engine's lock (rt_problem_plan).  rt_problem_plan_end does not — its wait must not
+// keep other threads from enqueueing — so a failure takes the lock just for the moment it writes the engine's error
+// text; the pass's own bookkeeping (plan_pending, the staging buffer) belongs to this problem alone, one pass per
+// problem being in flight by contract.
+static int plan_collect(rt_problem *p, uint64_t *best_keys_out, const char *who, bool have_lock)
 {
     rt_engine *e = p->e;
-    if (!best_keys_out) return fail(e, RT_ERR_INVALID_ARG, "%s: NULL argument", who);
-    if (!p->plan_pending) return fail(e, RT_ERR_STATE, "%s: no pass has been begun on this problem", who);
+    auto failed = [&](int code, const char *msg) {
+        if (have_lock) return fail(e, code, "%s: %s", who, msg);
+        std::lock_guard<std::mutex> lk(e->mu);
+        return fail(e, code, "%s: %s", who, msg);
+    };
+    if (!best_keys_out) return failed(RT_ERR_INVALID_ARG, "NULL argument");
+    if (!p->plan_pending) return failed(RT_ERR_STATE, "no pass has been begun on this problem");
     p->plan_pending = false;
-    RT_CUDA(e, cudaEventSynchronize(p->ev_done));
+    if (cudaEventSynchronize(p->ev_done) != cudaSuccess) return failed(RT_ERR_CUDA, "waiting for the pass failed");
     if (p->plan_t[0] != 0) {
         static double acc[4];
         static int calls;
@@ -723,7 +732,7 @@ static int plan_collect(rt_problem *p, uint64_t *best_keys_out, const char *who)
     memcpy(best_keys_out, res_h, B * 8);
     if (*reinterpret_cast<const int *>(res_h + B) == p->plan_flag_seq) {
         p->has_coords = p->has_routes = false;
-        return fail(e, RT_ERR_INVALID_ARG, "a coordinate is out of range or not finite");
+        return failed(RT_ERR_INVALID_ARG, "a coordinate is out of range or not finite");
     }
     return RT_OK;
 }
@@ -736,7 +745,7 @@ int rt_problem_plan(rt_problem *p, const double *lat, const double *lon, const i
     if (!best_keys_out) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_plan: bad argument");
     RT_TRY(plan_enqueue(p, lat, lon, stops, cap, max_dist, node, npos, dist_scale, time_scale, families, false,
                         "rt_problem_plan"));
-    return plan_collect(p, best_keys_out, "rt_problem_plan");
+    return plan_collect(p, best_keys_out, "rt_problem_plan", /*have_lock=*/true);
 }
 
 int rt_problem_plan_begin(rt_problem *p, const double *lat, const double *lon, const int32_t *stops, const int32_t *cap,
@@ -752,7 +761,7 @@ int rt_problem_plan_end(rt_problem *p, uint64_t *best_keys_out)
 {
     if (!p) return RT_ERR_INVALID_ARG;
     DeviceGuard dg(p->e->device);  // no engine lock: the wait must not keep other requests from being enqueued
-    return plan_collect(p, best_keys_out, "rt_problem_plan_end");
+    return plan_collect(p, best_keys_out, "rt_problem_plan_end", /*have_lock=*/false);
 }
 
 int rt_problem_plan_upload_dev(rt_problem *p, const double *lat, const double *lon, const int32_t *stops,
