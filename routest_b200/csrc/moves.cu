@@ -21,6 +21,7 @@
 // ASYM: a caller-supplied matrix may be directional (road networks are).  The kernels then read a second array,
 // GT[p][q] = M[node q][node p], wherever a cell is needed in the "towards p" orientation, so every access stays
 // row-contiguous; for a symmetric matrix GT is G and the extra loads disappear at compile time.
+#include <algorithm>
 #include <climits>
 #include <cstdlib>
 #include <cstring>
@@ -107,6 +108,7 @@ struct EvalArgs {
     int n, pitch, pstride;
     int families;            // bit 0 = 2-opt, 1 = relocate, 2 = swap
     int shard_index, shard_count;
+    double beta_inter, beta_intra;  // work model of the shard boundaries (problem.cuh: shard_boundary)
     unsigned long long *best;  // [batch]
     int signed_dst;            // best[] is in signed-order form (see block_min_to_global)
     int strip_rows;            // rows per block of the tile kernel (<= its ROWS template bound)
@@ -119,7 +121,10 @@ struct EvalArgs {
     unsigned char *dump_feas;
 };
 
-__device__ __forceinline__ void shard_range(int P, int idx, int cnt, int &lo, int &hi) { shard_bounds(P, idx, cnt, lo, hi); }
+__device__ __forceinline__ void shard_range(int P, int idx, int cnt, double beta, int &lo, int &hi)
+{
+    shard_bounds(P, idx, cnt, beta, lo, hi);
+}
 
 enum { kBest = 0, kDump = 1, kTable = 2 };
 
@@ -221,7 +226,7 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
     const int b = DUMP ? a.dump_instance : blockIdx.z;
     const int P = a.npos[b];
     int p_lo, p_hi;
-    shard_range(P, a.shard_index, a.shard_count, p_lo, p_hi);
+    shard_range(P, a.shard_index, a.shard_count, a.beta_inter, p_lo, p_hi);
     const int p0 = p_lo + blockIdx.y * kStripRows, q0 = blockIdx.x * kInterThreads;
     if (p0 >= p_hi || q0 >= P) return;
 
@@ -369,13 +374,91 @@ __device__ __forceinline__ int2 cell_from_vectors(double ax, double ay, double a
     return __double2hiint(s2) < lim_hi ? cell_i32_fast(s2, fd, ft) : cell_i32(ax, ay, az, bx, by, bz, fd, ft);
 }
 
+// The pair (p, q), p < q, of two different routes, scored for everything it can mean: relocate(p -> after q),
+// relocate(q -> after p) and swap(p, q).  The SPEC 2 matrix is symmetric, so the cells of the mirrored relocate are the
+// ones already in the window — (p, q) and (p+1, q) — and the tiles below the diagonal never run: every cell is rebuilt
+// once per unordered pair instead of twice.  best / thr: the direct candidates; mbest / mthr: in table mode the
+// mirrored relocate belongs to the entry (route q, route p) and keeps its own running best (otherwise they alias the
+// same variables).
+template <int MODE>
+__device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, const int4 &Hp, const int4 &p1, const int4 &p2,
+                                               int dep_p, const ColQ &c, bool q_rem_ok, bool q_cust, int2 c_up, int2 c_rt,
+                                               int2 c_cur, int2 c_lf, int2 c_dn, int &best_d, unsigned &best_i, int &thr,
+                                               int &mbest_d, unsigned &mbest_i, int &mthr)
+{
+    constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
+    const int q = c.q;
+    const bool p_cust = (Hp.w >> 30) & 1;
+    const bool pair = (Hp.w & 0x7FFF) != c.q_route && p < q;
+    // relocate(p -> between q and q+1)
+    const int ins = fadd(fadd(c_cur.x, c_rt.x), -c.Hq.z);
+    const int d_rel = fadd(Hp.x, ins);
+    const int tu = max(p1.x, fadd(c.dep_q, c_cur.y));
+    const bool v_rel = c.rel_q && pair && p_cust;
+    const bool ok_rel = v_rel && ((Hp.w >> 29) & 1) && p1.w <= c.capsl_q && ins <= c.distsl_q && tu <= p1.y &&
+                        fadd(fadd(tu, p1.z), c_rt.y) <= c.zn_q;
+    // relocate(q -> between p and p+1): the same with the roles exchanged, cells (p, q) and (p+1, q)
+    const int mins = fadd(fadd(c_cur.x, c_dn.x), -Hp.z);
+    const int d_mir = fadd(c.Hq.x, mins);
+    const int mtu = max(c.qB.x, fadd(dep_p, c_cur.y));
+    const bool v_mir = q_cust && (a.families & 2) && pair && p <= P - 2;
+    const bool ok_mir = v_mir && q_rem_ok && c.qB.w <= p2.z && mins <= p2.w && mtu <= c.qB.y &&
+                        fadd(fadd(mtu, c.qB.z), c_dn.y) <= p2.x;
+    // swap(p, q): pu -> v -> nu in route[p], pw -> u -> nw in route[q]
+    const int d1 = fadd(fadd(c_up.x, c_dn.x), -Hp.y);
+    const int d2 = fadd(fadd(c_lf.x, c_rt.x), -c.Hq.y);
+    const int d_swap = fadd(d1, d2);
+    const int tv = max(c.qB.x, fadd(p2.y, c_up.y));
+    const int tw = max(p1.x, fadd(c.depprev_q, c_lf.y));
+    const int dd = fadd(c.qB.w, -p1.w);
+    const bool v_swap = c.swap_q && pair && p_cust;
+    const bool ok_swap = v_swap && dd <= p2.z && -dd <= c.capsl_q && d1 <= p2.w && d2 <= c.distsl_q && tv <= c.qB.y &&
+                         fadd(fadd(tv, c.qB.z), c_dn.y) <= p2.x && tw <= p1.y && fadd(fadd(tw, p1.z), c_rt.y) <= c.zn_q;
+    if (DUMP) {
+        if (a.dump_family == 1) {
+            if (v_rel) {
+                a.dump_delta[static_cast<size_t>(p) * P + q] = d_rel;
+                a.dump_feas[static_cast<size_t>(p) * P + q] = ok_rel ? 1 : 0;
+            }
+            if (v_mir) {
+                a.dump_delta[static_cast<size_t>(q) * P + p] = d_mir;
+                a.dump_feas[static_cast<size_t>(q) * P + p] = ok_mir ? 1 : 0;
+            }
+        } else if (a.dump_family == 2 && v_swap) {
+            a.dump_delta[static_cast<size_t>(p) * P + q] = d_swap;
+            a.dump_feas[static_cast<size_t>(p) * P + q] = ok_swap ? 1 : 0;
+        }
+        return;
+    }
+    const bool hit_rel = ok_rel && d_rel <= thr, hit_swap = ok_swap && d_swap <= thr, hit_mir = ok_mir && d_mir <= mthr;
+    if (__any_sync(0xffffffffu, hit_rel || hit_swap || hit_mir)) {  // rare
+        auto take = [](int d, unsigned idx, int &bd, unsigned &bi) {
+            if (d < bd || (d == bd && idx < bi)) {
+                bd = d;
+                bi = idx;
+            }
+        };
+        if (hit_rel) take(d_rel, (1u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q), best_d, best_i);
+        if (hit_swap) take(d_swap, (2u << 30) | (static_cast<unsigned>(p) << 15) | static_cast<unsigned>(q), best_d, best_i);
+        if (hit_mir) take(d_mir, (1u << 30) | (static_cast<unsigned>(q) << 15) | static_cast<unsigned>(p), mbest_d, mbest_i);
+        if (TABLE) {
+            thr = best_d;
+            mthr = mbest_d;
+        } else {
+            thr = __reduce_min_sync(0xffffffffu, best_d);   // best / mbest are the same variables here, and so are thr / mthr
+            mthr = thr;
+        }
+    }
+}
+
 // One shared-memory slot per row of the strip (+2): slot i holds the unit vector of position p0 - 1 + i and, for
 // i < rows, the three records of strip row i.  One array and explicit 32-bit shared addresses: with three separate
 // arrays indexed by the (uniform) loop counter the compiler rebuilt every array's shared-window address in the uniform
 // datapath on every iteration — a quarter of the loop's instructions.
 struct __align__(16) RowSlot {
     int4 H, P1, P2;
-    double vx, vy, vz, pad;
+    double vx, vy, vz;
+    int dep, pad;   // B[p] + service[p]: what an insertion after p starts from
 };
 static_assert(sizeof(RowSlot) == 80, "row slot layout");
 
@@ -405,8 +488,24 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
     const int b = DUMP ? a.dump_instance : blockIdx.z;
     const int P = a.npos[b];
     int p_lo, p_hi;
-    shard_range(P, a.shard_index, a.shard_count, p_lo, p_hi);
-    const int p0 = p_lo + blockIdx.y * kStripRows, q0 = blockIdx.x * kFusedCols;
+    shard_range(P, a.shard_index, a.shard_count, a.beta_inter, p_lo, p_hi);
+    // Only pairs p < q are scored (score_pair_tri), so a strip's tiles start at the diagonal: strip y has
+    // n(y) = nxb - (p0(y) + 1) / C of them, fewer and fewer towards the bottom.  A rectangular grid over that triangle
+    // would be half empty blocks (each still costs a launch slot and a load of npos: 6 us on the last rank of eight),
+    // so strip y shares its grid row with strip S-1-y: n(y) + n(S-1-y) is nearly constant.
+    const int S = (p_hi - p_lo + kStripRows - 1) / kStripRows, nxb = (P + kFusedCols - 1) / kFusedCols;
+    int y = blockIdx.y, tile = blockIdx.x;
+    if (2 * y >= S) return;
+    {
+        const int n1 = max(0, nxb - (p_lo + y * kStripRows + 1) / kFusedCols);
+        if (tile >= n1) {
+            tile -= n1;
+            if (S - 1 - y == y) return;
+            y = S - 1 - y;
+        }
+    }
+    const int p0 = p_lo + y * kStripRows;
+    const int q0 = ((p0 + 1) / kFusedCols + tile) * kFusedCols;
     if (p0 >= p_hi || q0 >= P) return;
 
     const size_t po = static_cast<size_t>(b) * a.pstride;
@@ -419,6 +518,7 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
     if (tid < rows + 2) {
         RowSlot sl;
         sl.H = sl.P1 = sl.P2 = make_int4(0, 0, 0, 0);
+        sl.dep = sl.pad = 0;
         if (tid < rows && p0 + tid < P) {
             const size_t o = po + p0 + tid;
             const int4 rA = a.RA[o], rC = a.RC[o], rD = a.RD[o];
@@ -426,16 +526,17 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
             sl.H.w |= (rC.w & 2) << 28;  // rem_ok -> bit 29
             sl.P1 = a.RB[o];
             sl.P2 = make_int4(rA.y, rC.x, rD.x, rD.y);
+            sl.dep = rA.x;
         }
         const int pv = min(max(p0 - 1 + tid, 0), a.pstride - 1);
         sl.vx = PX[pv];
         sl.vy = PX[a.pstride + pv];
         sl.vz = PX[2 * static_cast<size_t>(a.pstride) + pv];
-        sl.pad = 0.0;
         slots[tid] = sl;
     }
     int4 Hq = make_int4(0, 0, 0, -1), qB = make_int4(0, 0, 0, 0);
     int dep_q = 0, zn_q = 0, depprev_q = 0, capsl_q = 0, distsl_q = 0;
+    bool q_rem_ok = false;
     if (q_in) {
         const int4 rA = a.RA[po + q], rC = a.RC[po + q], rD = a.RD[po + q];
         Hq = a.H[po + q];
@@ -445,6 +546,7 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
         depprev_q = rC.x;
         capsl_q = rD.x;
         distsl_q = rD.y;
+        q_rem_ok = rC.w & 2;
     }
     const int qv = min(max(q, 0), a.pstride - 1);   // positions beyond P repeat the depot's vector
     const double bx = PX[qv], by = PX[a.pstride + qv], bz = PX[2 * static_cast<size_t>(a.pstride) + qv];
@@ -455,19 +557,20 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
     const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
     const bool swap_q = q_cust && (a.families & 4);
     const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q};
-    const bool swap_tile = (a.families & 4) && p0 < q0 + kFusedCols - 1;  // some pair of the tile has p < q
 
-    int best_d = INT_MAX, thr = INT_MAX;
-    unsigned best_i = 0xFFFFFFFFu;
+    int best_d = INT_MAX, thr = INT_MAX, tb_d = INT_MAX, tb_thr = INT_MAX;   // tb_*: table mode's mirrored-relocate entry
+    unsigned best_i = 0xFFFFFFFFu, tb_i = 0xFFFFFFFFu;
     int cur_ra = -1;
-    unsigned long long *trow = TABLE ? a.inter + static_cast<size_t>(b) * a.cr * a.cr + q_route : nullptr;
     auto flush = [&]() {
+        unsigned long long *tab = a.inter + static_cast<size_t>(b) * a.cr * a.cr;
         if (best_i != 0xFFFFFFFFu)
-            table_min(trow + static_cast<size_t>(cur_ra) * a.cr,
+            table_min(tab + static_cast<size_t>(cur_ra) * a.cr + q_route,
                       (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i, a.signed_dst);
-        best_d = INT_MAX;
-        thr = INT_MAX;
-        best_i = 0xFFFFFFFFu;
+        if (tb_i != 0xFFFFFFFFu)
+            table_min(tab + static_cast<size_t>(q_route) * a.cr + cur_ra,
+                      (static_cast<unsigned long long>(static_cast<unsigned>(tb_d) + 0x80000000u) << 32) | tb_i, a.signed_dst);
+        best_d = thr = tb_d = tb_thr = INT_MAX;
+        best_i = tb_i = 0xFFFFFFFFu;
     };
     // slot address in a per-thread register (the shift is zero for every thread of a 128-thread block; it only keeps
     // the compiler from proving the address uniform and moving it back into the uniform datapath)
@@ -489,15 +592,22 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
         const int p = p0 + rr;
         const int2 c_dn = cell_slot(sa + 160);
         const int4 Hp = lds128(sa);
-        if ((Hp.w >> 30) & 1) {  // p is a customer (block-uniform)
+        {   // every row: a separator is never moved but is an insertion point of the mirrored relocate
             const int2 c_lf = make_int2(__shfl_up_sync(full, c_cur.x, 1), __shfl_up_sync(full, c_cur.y, 1));
             const int2 c_rt = make_int2(__shfl_down_sync(full, c_cur.x, 1), __shfl_down_sync(full, c_cur.y, 1));
             const int4 p1 = lds128(sa + 16), p2 = lds128(sa + 32);
+            int dep_p;
+            asm volatile("ld.shared.s32 %0, [%1];" : "=r"(dep_p) : "r"(sa + 72));
             if (TABLE && (Hp.w & 0x7FFF) != cur_ra) {
                 flush();
                 cur_ra = Hp.w & 0x7FFF;
             }
-            score_pair<MODE>(a, P, p, Hp, p1, p2, col, swap_tile, c_up, c_rt, c_cur, c_lf, c_dn, best_d, best_i, thr);
+            if (TABLE)
+                score_pair_tri<MODE>(a, P, p, Hp, p1, p2, dep_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf, c_dn, best_d,
+                                     best_i, thr, tb_d, tb_i, tb_thr);
+            else
+                score_pair_tri<MODE>(a, P, p, Hp, p1, p2, dep_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf, c_dn, best_d,
+                                     best_i, thr, best_d, best_i, thr);
         }
         c_up = c_cur;
         c_cur = c_dn;
@@ -549,7 +659,7 @@ __global__ void __launch_bounds__(kIntraThreads) eval_intra_kernel(const EvalArg
     const int b = DUMP ? a.dump_instance : blockIdx.y;
     const int P = a.npos[b];
     int t_lo, t_hi;
-    shard_range(P, a.shard_index, a.shard_count, t_lo, t_hi);  // same-route work is sharded by anchor
+    shard_range(P, a.shard_index, a.shard_count, a.beta_intra, t_lo, t_hi);  // same-route work is sharded by anchor
     const int t = t_lo + blockIdx.x * kIntraThreads + threadIdx.x;
     unsigned long long best = kNoMove;
     int t_route = 0;
@@ -771,7 +881,7 @@ __global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const
     const int b = DUMP ? a.dump_instance : blockIdx.y;
     const int P = a.npos[b];
     int t_lo, t_hi;
-    shard_range(P, a.shard_index, a.shard_count, t_lo, t_hi);  // same-route work is sharded by anchor
+    shard_range(P, a.shard_index, a.shard_count, a.beta_intra, t_lo, t_hi);  // same-route work is sharded by anchor
     const int lane = threadIdx.x & 31;
     const int t = t_lo + blockIdx.x * kIntraWarps + (threadIdx.x >> 5);
     unsigned long long best = kNoMove;
@@ -970,7 +1080,8 @@ int pick_strip_rows(int pmax, int rows, int batch, bool asym, int cols_per_block
     const int forced = g_strip_rows ? g_strip_rows : env;
     if (forced >= 8 && forced <= kMaxStripRows) return forced;
     const long long col_blocks = (pmax + cols_per_block - 1) / cols_per_block;
-    const long long blocks64 = col_blocks * ((rows + 63) / 64) * batch;
+    // (the kernel without a matrix runs only the tiles above the diagonal: about half of the grid)
+    const long long blocks64 = col_blocks * ((rows + 63) / 64) * batch / (cols_per_block == kFusedCols ? 2 : 1);
     return (!asym && blocks64 >= 4LL * kNumSMs * 9) ? 64 : kStripRows;
 }
 
@@ -1021,6 +1132,17 @@ int launch_inter(rt_problem *p, EvalArgs &a, int pmax, int shard_rows, int batch
     const int cols = fused ? kFusedCols : kInterThreads;
     a.strip_rows = strip_rows > 0 ? strip_rows : pick_strip_rows(pmax, shard_rows, batch, !p->symmetric, cols);
     dim3 grid((pmax + cols - 1) / cols, (shard_rows + a.strip_rows - 1) / a.strip_rows, batch);
+    if (fused) {
+        // the triangle above the diagonal, two strips per grid row (see the kernel); sized for the largest instance of
+        // the batch from this shard's first row on, with slack for instances whose boundaries differ by a row or two
+        int lo, hi;
+        shard_bounds(pmax, a.shard_index, a.shard_count, a.beta_inter, lo, hi);
+        const int h = a.strip_rows, S = (hi - lo + 2 + h - 1) / h, nxb = (pmax + cols - 1) / cols;
+        auto n_of = [&](int yy) { return std::max(0, nxb - (std::max(lo - 2, 0) + yy * h + 1) / cols); };
+        int width = 1;
+        for (int yy = 0; 2 * yy < S; ++yy) width = std::max(width, n_of(yy) + (S - 1 - yy != yy ? n_of(S - 1 - yy) : 0));
+        grid = dim3(width + 2, (S + 1) / 2 + 1, batch);
+    }
     if (fused && all_pairs_in_fast_range(p, a)) eval_inter_fused_kernel<MODE, true><<<grid, kInterThreads, 0, st>>>(a);
     else if (fused) eval_inter_fused_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
     else if (p->symmetric) eval_inter_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
@@ -1031,10 +1153,10 @@ int launch_inter(rt_problem *p, EvalArgs &a, int pmax, int shard_rows, int batch
 
 // Rows the grids must cover for shard idx of cnt: instances of a batch differ in P (pmin..pmax), and so do their
 // boundaries; the widest shard of the largest instance plus one row of slack bounds them all.
-int max_shard_rows(int pmax, int idx, int cnt)
+int max_shard_rows(int pmax, int idx, int cnt, double beta)
 {
     int lo, hi;
-    shard_bounds(pmax, idx, cnt, lo, hi);
+    shard_bounds(pmax, idx, cnt, beta, lo, hi);
     return hi - lo + 2;
 }
 
@@ -1067,6 +1189,10 @@ EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count
     a.families = families;
     a.shard_index = shard_index;
     a.shard_count = shard_count;
+    // without a matrix the tile kernel scores the triangle p < q and nothing ties the same-route anchors to its rows;
+    // on a stored matrix both kernels read the rows of G this replica keeps fresh, so they share one range
+    a.beta_inter = eval_without_matrix(p) ? kBetaTriangle : kBetaStoredMatrix;
+    a.beta_intra = eval_without_matrix(p) ? kBetaUniform : kBetaStoredMatrix;
     a.best = best_d;
     a.strip_rows = kStripRows;
     return a;
@@ -1112,7 +1238,8 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     EvalArgs a = make_args(p, families, shard_index, shard_count, direct ? best_d : p->best);
     a.signed_dst = direct ? 1 : 0;
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;  // largest P of the batch
-    const int shard_rows = max_shard_rows(pmax, shard_index, shard_count);
+    const int shard_rows = max_shard_rows(pmax, shard_index, shard_count, a.beta_inter);
+    const int anchor_rows = max_shard_rows(pmax, shard_index, shard_count, a.beta_intra);
     // The sweep kernel is latency bound (a sequential walk per anchor, a few warps per SM) and the tile kernel is ALU
     // bound: they only share the best[] atomics, so the sweep runs on the side stream underneath the tile kernel.
     const bool overlap = (families & 6) && p->side_stream;
@@ -1122,7 +1249,7 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, p->ev_fork, 0));
         st_intra = p->side_stream;
     }
-    RT_TRY(launch_intra<kBest>(p, a, shard_rows, p->batch, st_intra));
+    RT_TRY(launch_intra<kBest>(p, a, anchor_rows, p->batch, st_intra));
     if (families & 6) RT_TRY(launch_inter<kBest>(p, a, pmax, shard_rows, p->batch, 0, st));
     if (overlap) {
         RT_CUDA(e, cudaEventRecord(p->ev_join, p->side_stream));
@@ -1156,7 +1283,8 @@ int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaMemsetAsync(table_d, 0xFF, count * 8, st));
     }
     const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
-    const int shard_rows = max_shard_rows(pmax, shard_index, shard_count);
+    const int shard_rows = max_shard_rows(pmax, shard_index, shard_count, a.beta_inter);
+    const int anchor_rows = max_shard_rows(pmax, shard_index, shard_count, a.beta_intra);
     const bool overlap = (families & 6) && p->side_stream;
     cudaStream_t st_intra = st;
     if (overlap) {
@@ -1164,7 +1292,7 @@ int eval_table_launch(rt_problem *p, int families, int shard_index, int shard_co
         RT_CUDA(e, cudaStreamWaitEvent(p->side_stream, p->ev_fork, 0));
         st_intra = p->side_stream;
     }
-    RT_TRY(launch_intra<kTable>(p, a, shard_rows, p->batch, st_intra));
+    RT_TRY(launch_intra<kTable>(p, a, anchor_rows, p->batch, st_intra));
     // table mode flushes per route change: short strips keep the flush count low
     if (families & 6) RT_TRY(launch_inter<kTable>(p, a, pmax, shard_rows, p->batch, kStripRows, st));
     if (overlap) {

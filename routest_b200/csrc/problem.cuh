@@ -105,26 +105,31 @@ struct rt_problem {
 
 namespace rt {
 
-// Row range [lo, hi) of shard idx of cnt over P positions.  Rows are not equally expensive: every row scores a
-// relocate against all P columns but a swap only against the columns to its right (p < q), so the first rows of an
-// instance cost about 1.4x the last ones (82 against 58 instructions per pair).  With equal row counts rank 0 of eight
-// took 68 us where rank 4 took 61 — and a pass is as slow as its slowest rank.  The boundaries therefore split the
-// cumulative work x - 0.15 x^2 (x = p / P; cost per row 1 - 0.3 x) evenly.  Plain IEEE double arithmetic with the
-// correctly rounded sqrt, one expression on host and device: every rank computes the same boundaries.
-__host__ __device__ inline int shard_boundary(int P, int k, int cnt)
+// Row range [lo, hi) of shard idx of cnt over P positions.  Rows are not equally expensive, and a pass is as slow as
+// its slowest rank, so the boundaries split the cumulative WORK evenly, not the rows.  With cost per row 1 - beta x
+// (x = p / P) the cumulative work is x - (beta / 2) x^2:
+//   beta = 1    the tile kernel without a matrix scores only pairs p < q: row p costs P - p columns (a triangle);
+//   beta = 0.3  the tile kernel on a stored matrix scores a relocate against all P columns and a swap against the
+//               columns to the right of p: 82 against 58 instructions per pair (rank 0 of eight took 68 us where rank 4
+//               took 61 with equal row counts);
+//   beta = 0    equal row counts (same-route candidates: sharded by anchor).
+// Plain IEEE double arithmetic with the correctly rounded sqrt, one expression on host and device: every rank computes
+// the same boundaries.
+__host__ __device__ inline int shard_boundary(int P, int k, int cnt, double beta)
 {
     if (k <= 0) return 0;
     if (k >= cnt) return P;
     const double t = static_cast<double>(k) / static_cast<double>(cnt);
-    const double x = (1.0 - sqrt(1.0 - 0.51 * t)) / 0.3;
+    const double x = beta > 0.0 ? (1.0 - sqrt(1.0 - 2.0 * beta * t * (1.0 - 0.5 * beta))) / beta : t;
     int b = static_cast<int>(x * static_cast<double>(P));
     return b < 0 ? 0 : (b > P ? P : b);
 }
-__host__ __device__ inline void shard_bounds(int P, int idx, int cnt, int &lo, int &hi)
+__host__ __device__ inline void shard_bounds(int P, int idx, int cnt, double beta, int &lo, int &hi)
 {
-    lo = shard_boundary(P, idx, cnt);
-    hi = shard_boundary(P, idx + 1, cnt);
+    lo = shard_boundary(P, idx, cnt, beta);
+    hi = shard_boundary(P, idx + 1, cnt, beta);
 }
+constexpr double kBetaTriangle = 1.0, kBetaStoredMatrix = 0.3, kBetaUniform = 0.0;
 
 // rt_debug_set("fused_eval", v): 1 (default) = the move kernels rebuild matrix cells from the position-ordered unit
 // vectors wherever the matrix is SPEC 2 of the problem's own coordinates, so no route-order matrix is written or read;

@@ -756,8 +756,8 @@ int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready)
     // rows any instance of the batch can need: shard [P*i/c, P*(i+1)/c) over P in [pmin, pmax], one halo row each side
     int r0 = 0, r1 = p->grows;
     if (p->shard_count > 1) {
-        const long long lo = static_cast<long long>(shard_boundary(p->pmin, p->shard_index, p->shard_count)) - 1;
-        const long long hi = static_cast<long long>(shard_boundary(p->pmax, p->shard_index + 1, p->shard_count)) + 2;
+        const long long lo = static_cast<long long>(shard_boundary(p->pmin, p->shard_index, p->shard_count, kBetaStoredMatrix)) - 1;
+        const long long hi = static_cast<long long>(shard_boundary(p->pmax, p->shard_index + 1, p->shard_count, kBetaStoredMatrix)) + 2;
         r0 = static_cast<int>(std::max<long long>(lo, 0));
         r1 = static_cast<int>(std::min<long long>(hi, p->grows));
     }
