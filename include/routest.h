@@ -222,7 +222,8 @@ int rt_problem_plan_end(rt_problem *p, uint64_t *best_keys_out);
  * the keys stay on the device — best_keys_d is device int64[batch] in signed-order form, ready for the MIN
  * all-reduce that combines the shards (NCCL through torch.distributed, or the peer exchange below).  Nothing is
  * synchronised: the host buffers must stay unchanged until the stream has passed the copies (pinned memory makes them
- * asynchronous).  Coordinates and the position arrays are validated on the host before anything is enqueued.
+ * asynchronous).  Coordinates and the position arrays are validated on the host while the copies are in flight; a
+ * refused call waits for them before it returns.
  * No reference counterpart (the reference handles one request on one thread: routes.py:89-127). */
 int rt_problem_plan_upload_dev(rt_problem *p, const double *lat, const double *lon, const int32_t *stops,
                                const int32_t *cap, const int64_t *max_dist, const int32_t *node, const int32_t *npos,

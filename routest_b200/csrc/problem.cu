@@ -73,19 +73,50 @@ __global__ void cells_to_planes_kernel(const int2 *__restrict__ cells, int n, in
 // critical path (the GPU is only busy with the input copies meanwhile), hence four ids per step: the sign bit of
 // v | (n-1 - v) is set iff v is negative or above n-1.
 // dlat^2 + dlon^2 in radians over the bounding box of the coordinates: an upper bound of every pair's squared central
-// angle, hence of its chord^2 (the move kernels drop the cell function's range test when it is small enough).
-double angle2_bound_of(const double *lat, const double *lon, long long count)
+// angle, hence of its chord^2 (the move kernels drop the cell function's range test when it is small enough).  The same
+// pass says whether every coordinate is finite and in range (a NaN fails every comparison, so it can neither move the
+// box nor pass the range test): *valid.  On a request's critical path, hence two values per step.
+double angle2_bound_of(const double *lat, const double *lon, long long count, bool *valid = nullptr)
 {
     double la0 = lat[0], la1 = lat[0], lo0 = lon[0], lo1 = lon[0];
-    for (long long i = 1; i < count; ++i) {
+    long long i = 0;
+    bool ok = true;
+#if defined(__SSE2__)
+    __m128d vla0 = _mm_set1_pd(la0), vla1 = vla0, vlo0 = _mm_set1_pd(lo0), vlo1 = vlo0;
+    __m128d vok = _mm_castsi128_pd(_mm_set1_epi32(-1));
+    const __m128d la_lo = _mm_set1_pd(-90.0), la_hi = _mm_set1_pd(90.0), lo_lo = _mm_set1_pd(-180.0), lo_hi = _mm_set1_pd(180.0);
+    for (; i + 2 <= count; i += 2) {
+        const __m128d a = _mm_loadu_pd(lat + i), o = _mm_loadu_pd(lon + i);
+        vla0 = _mm_min_pd(vla0, a);
+        vla1 = _mm_max_pd(vla1, a);
+        vlo0 = _mm_min_pd(vlo0, o);
+        vlo1 = _mm_max_pd(vlo1, o);
+        vok = _mm_and_pd(vok, _mm_and_pd(_mm_and_pd(_mm_cmpge_pd(a, la_lo), _mm_cmple_pd(a, la_hi)),
+                                         _mm_and_pd(_mm_cmpge_pd(o, lo_lo), _mm_cmple_pd(o, lo_hi))));
+    }
+    alignas(16) double t[2];
+    _mm_store_pd(t, vla0);
+    la0 = t[0] < t[1] ? t[0] : t[1];
+    _mm_store_pd(t, vla1);
+    la1 = t[0] > t[1] ? t[0] : t[1];
+    _mm_store_pd(t, vlo0);
+    lo0 = t[0] < t[1] ? t[0] : t[1];
+    _mm_store_pd(t, vlo1);
+    lo1 = t[0] > t[1] ? t[0] : t[1];
+    ok = _mm_movemask_pd(vok) == 3;
+#endif
+    for (; i < count; ++i) {
         la0 = lat[i] < la0 ? lat[i] : la0;
         la1 = lat[i] > la1 ? lat[i] : la1;
         lo0 = lon[i] < lo0 ? lon[i] : lo0;
         lo1 = lon[i] > lo1 ? lon[i] : lo1;
+        ok = ok && lat[i] >= -90.0 && lat[i] <= 90.0 && lon[i] >= -180.0 && lon[i] <= 180.0;
     }
+    ok = ok && lat[0] >= -90.0 && lat[0] <= 90.0 && lon[0] >= -180.0 && lon[0] <= 180.0;
+    if (valid) *valid = ok;
     const double DEG = 0.017453292519943295, dla = (la1 - la0) * DEG, dlo = (lo1 - lo0) * DEG;
     const double b = dla * dla + dlo * dlo;
-    return b == b ? b : -1.0;  // a NaN coordinate: unknown (the pass is refused elsewhere)
+    return (ok && b == b) ? b : -1.0;  // unknown when a coordinate is unusable (the pass is refused elsewhere)
 }
 
 bool positions_well_formed(const int32_t *nd, int P, int n)
@@ -665,7 +696,17 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
             return fail(e, RT_ERR_INVALID_ARG, "instance %zu: position array must hold node ids below %zu with %zu customers", b, N, N - 1);
         }
     }
-    p->angle2_bound = angle2_bound_of(lat, lon, static_cast<long long>(B * N));
+    // the box of the coordinates, and — for the caller's-stream form, which has no later host step that could report the
+    // device-side flag — their validity, while the GPU is busy with the copies and the vector kernel
+    bool coords_ok = true;
+    p->angle2_bound = angle2_bound_of(lat, lon, static_cast<long long>(B * N), &coords_ok);
+    if (keys_dev && !coords_ok) {
+        p->has_coords = p->has_routes = false;
+        p->ext_best = nullptr;
+        p->scan_done = false;
+        cudaStreamSynchronize(st);  // the caller's buffers are still being read
+        return fail(e, RT_ERR_INVALID_ARG, "%s: a coordinate is out of range or not finite", who);
+    }
     p->plan_t[2] = dbg ? now() : 0;
     // the matrix of this pass is built in route order by the refresh below (state.cu); the node-order copy that
     // rt_problem_build_matrix keeps for the greedy and for rt_problem_get_matrix is not needed here
@@ -771,12 +812,6 @@ int rt_problem_plan_upload_dev(rt_problem *p, const double *lat, const double *l
     if (!p) return RT_ERR_INVALID_ARG;
     rt_engine *e = p->e;
     if (!best_keys_d) return fail(e, RT_ERR_INVALID_ARG, "rt_problem_plan_upload_dev: bad argument");
-    if (lat && lon) {  // checked on the host here: there is no later host step that could report a device-side flag
-        const long long total = static_cast<long long>(p->n) * p->batch;
-        for (long long i = 0; i < total; ++i)
-            if (!(lat[i] >= -90.0 && lat[i] <= 90.0) || !(lon[i] >= -180.0 && lon[i] <= 180.0))
-                return fail(e, RT_ERR_INVALID_ARG, "coordinate %lld out of range or not finite", i);
-    }
     DeviceGuard dg(e->device);
     return plan_enqueue(p, lat, lon, stops, cap, max_dist, node, npos, dist_scale, time_scale, families, false,
                         "rt_problem_plan_upload_dev", static_cast<unsigned long long *>(best_keys_d),
