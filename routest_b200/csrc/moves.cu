@@ -25,6 +25,7 @@
 #include <climits>
 #include <cstdlib>
 #include <cstring>
+#include <type_traits>
 
 #include "geometry.cuh"
 #include "problem.cuh"
@@ -41,10 +42,13 @@ constexpr int kMaxStripRows = 64;  // the launcher picks the height per launch (
 
 // a + b on the FMA pipe (IMAD with multiplier 1): the move kernels are bound by the ALU pipe (compares, min/max,
 // selects, three-input adds), while the FMA pipe idles — plain sums go there.
+__constant__ int kOne = 1;  // a multiplier the assembler cannot see through: with a literal 1 it folds pairs of these
+                            // sums back into three-input IADD3s on the ALU pipe
+
 __device__ __forceinline__ int fadd(int a, int b)
 {
     int r;
-    asm("mad.lo.s32 %0, %1, 1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(kOne), "r"(b));
     return r;
 }
 
@@ -134,6 +138,11 @@ struct ColQ {
     int dep_q, zn_q, depprev_q, capsl_q, distsl_q;
     int q, q_route;
     bool rel_q, swap_q;
+    // validity folded into data (score_pair_tri, non-dump modes): a candidate that is not one fails a comparison it
+    // makes anyway instead of costing flag tests and predicate logic on the ALU pipe
+    int capsl_rel;   // capacity slack of q's route for relocate(p -> q); below any demand where q takes no insertion
+    int qdem_mir;    // demand of q for relocate(q -> p); above any slack where q cannot be moved
+    int qdue_swap;   // due time of q for swap; -1 where q cannot be swapped
 };
 
 // relocate(p -> between q and q+1) and swap(p, q) for one customer row p against column q: delta AND feasibility,
@@ -268,7 +277,7 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
     const bool q_cust = q_in && ((Hq.w >> 30) & 1);
     const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
     const bool swap_q = q_cust && (a.families & 4);
-    const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q};
+    const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q, 0, 0, 0};
     const bool swap_tile = (a.families & 4) && p0 < q0 + kInterThreads - 1;  // some pair of the tile has p < q
 
     int best_d = INT_MAX, thr = INT_MAX;
@@ -380,30 +389,26 @@ __device__ __forceinline__ int2 cell_from_vectors(double ax, double ay, double a
 // once per unordered pair instead of twice.  best / thr: the direct candidates; mbest / mthr: in table mode the
 // mirrored relocate belongs to the entry (route q, route p) and keeps its own running best (otherwise they alias the
 // same variables).
-template <int MODE>
+constexpr int kNever = 1 << 30;  // a demand no capacity slack reaches (slacks are clamped to 2^30, demands to 2^28)
+
+template <int MODE, bool DIAG>
 __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, const int4 &Hp, const int4 &p1, const int4 &p2,
-                                               int dep_p, const ColQ &c, bool q_rem_ok, bool q_cust, int2 c_up, int2 c_rt,
-                                               int2 c_cur, int2 c_lf, int2 c_dn, int &best_d, unsigned &best_i, int &thr,
-                                               int &mbest_d, unsigned &mbest_i, int &mthr)
+                                               int dep_p, int reldem_p, const ColQ &c, bool q_rem_ok, bool q_cust, int2 c_up,
+                                               int2 c_rt, int2 c_cur, int2 c_lf, int2 c_dn, int &best_d, unsigned &best_i,
+                                               int &thr, int &mbest_d, unsigned &mbest_i, int &mthr)
 {
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
     const int q = c.q;
-    const bool p_cust = (Hp.w >> 30) & 1;
-    const bool pair = (Hp.w & 0x7FFF) != c.q_route && p < q;
+    // DIAG: the tile touches the diagonal, so p < q has to be tested per pair; everywhere else it holds for the tile
+    const bool pair = (Hp.w & 0x7FFF) != c.q_route && (!DIAG || p < q);
     // relocate(p -> between q and q+1)
     const int ins = fadd(fadd(c_cur.x, c_rt.x), -c.Hq.z);
     const int d_rel = fadd(Hp.x, ins);
     const int tu = max(p1.x, fadd(c.dep_q, c_cur.y));
-    const bool v_rel = c.rel_q && pair && p_cust;
-    const bool ok_rel = v_rel && ((Hp.w >> 29) & 1) && p1.w <= c.capsl_q && ins <= c.distsl_q && tu <= p1.y &&
-                        fadd(fadd(tu, p1.z), c_rt.y) <= c.zn_q;
     // relocate(q -> between p and p+1): the same with the roles exchanged, cells (p, q) and (p+1, q)
     const int mins = fadd(fadd(c_cur.x, c_dn.x), -Hp.z);
     const int d_mir = fadd(c.Hq.x, mins);
     const int mtu = max(c.qB.x, fadd(dep_p, c_cur.y));
-    const bool v_mir = q_cust && (a.families & 2) && pair && p <= P - 2;
-    const bool ok_mir = v_mir && q_rem_ok && c.qB.w <= p2.z && mins <= p2.w && mtu <= c.qB.y &&
-                        fadd(fadd(mtu, c.qB.z), c_dn.y) <= p2.x;
     // swap(p, q): pu -> v -> nu in route[p], pw -> u -> nw in route[q]
     const int d1 = fadd(fadd(c_up.x, c_dn.x), -Hp.y);
     const int d2 = fadd(fadd(c_lf.x, c_rt.x), -c.Hq.y);
@@ -411,10 +416,17 @@ __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, 
     const int tv = max(c.qB.x, fadd(p2.y, c_up.y));
     const int tw = max(p1.x, fadd(c.depprev_q, c_lf.y));
     const int dd = fadd(c.qB.w, -p1.w);
-    const bool v_swap = c.swap_q && pair && p_cust;
-    const bool ok_swap = v_swap && dd <= p2.z && -dd <= c.capsl_q && d1 <= p2.w && d2 <= c.distsl_q && tv <= c.qB.y &&
-                         fadd(fadd(tv, c.qB.z), c_dn.y) <= p2.x && tw <= p1.y && fadd(fadd(tw, p1.z), c_rt.y) <= c.zn_q;
-    if (DUMP) {
+    bool ok_rel, ok_mir, ok_swap;
+    if (DUMP) {   // explicit validity: the dump reports which pairs are candidates at all (the slots hold plain data)
+        const bool p_cust = (Hp.w >> 30) & 1;
+        const bool v_rel = c.rel_q && pair && p_cust;
+        const bool v_mir = q_cust && (a.families & 2) && pair && p <= P - 2;
+        const bool v_swap = c.swap_q && pair && p_cust;
+        ok_rel = v_rel && ((Hp.w >> 29) & 1) && p1.w <= c.capsl_q && ins <= c.distsl_q && tu <= p1.y &&
+                 fadd(fadd(tu, p1.z), c_rt.y) <= c.zn_q;
+        ok_mir = v_mir && q_rem_ok && c.qB.w <= p2.z && mins <= p2.w && mtu <= c.qB.y && fadd(fadd(mtu, c.qB.z), c_dn.y) <= p2.x;
+        ok_swap = v_swap && dd <= p2.z && -dd <= c.capsl_q && d1 <= p2.w && d2 <= c.distsl_q && tv <= c.qB.y &&
+                  fadd(fadd(tv, c.qB.z), c_dn.y) <= p2.x && tw <= p1.y && fadd(fadd(tw, p1.z), c_rt.y) <= c.zn_q;
         if (a.dump_family == 1) {
             if (v_rel) {
                 a.dump_delta[static_cast<size_t>(p) * P + q] = d_rel;
@@ -430,6 +442,14 @@ __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, 
         }
         return;
     }
+    // validity rides on the data: a row that is no customer carries due = -1 (no arrival is that early) and, like a stop
+    // that cannot be removed, the demand kNever for relocate; a column that takes no insertion / cannot be moved /
+    // cannot be swapped carries capsl_rel / qdem_mir / qdue_swap to the same effect; the closing depot's row has
+    // capacity slack -1.  So every test below is one the candidate needs anyway.
+    ok_rel = pair && reldem_p <= c.capsl_rel && ins <= c.distsl_q && tu <= p1.y && fadd(fadd(tu, p1.z), c_rt.y) <= c.zn_q;
+    ok_mir = pair && c.qdem_mir <= p2.z && mins <= p2.w && mtu <= c.qB.y && fadd(fadd(mtu, c.qB.z), c_dn.y) <= p2.x;
+    ok_swap = pair && dd <= p2.z && -dd <= c.capsl_q && d1 <= p2.w && d2 <= c.distsl_q && tv <= c.qdue_swap &&
+              fadd(fadd(tv, c.qB.z), c_dn.y) <= p2.x && tw <= p1.y && fadd(fadd(tw, p1.z), c_rt.y) <= c.zn_q;
     const bool hit_rel = ok_rel && d_rel <= thr, hit_swap = ok_swap && d_swap <= thr, hit_mir = ok_mir && d_mir <= mthr;
     if (__any_sync(0xffffffffu, hit_rel || hit_swap || hit_mir)) {  // rare
         auto take = [](int d, unsigned idx, int &bd, unsigned &bi) {
@@ -458,7 +478,8 @@ __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, 
 struct __align__(16) RowSlot {
     int4 H, P1, P2;
     double vx, vy, vz;
-    int dep, pad;   // B[p] + service[p]: what an insertion after p starts from
+    int dep;        // B[p] + service[p]: what an insertion after p starts from
+    int reldem;     // demand of p for relocate(p -> q), kNever where p cannot be moved (see score_pair_tri)
 };
 static_assert(sizeof(RowSlot) == 80, "row slot layout");
 
@@ -518,7 +539,10 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
     if (tid < rows + 2) {
         RowSlot sl;
         sl.H = sl.P1 = sl.P2 = make_int4(0, 0, 0, 0);
-        sl.dep = sl.pad = 0;
+        sl.dep = 0;
+        sl.reldem = kNever;
+        sl.P1.y = -1;   // beyond the instance: no customer
+        sl.P2.z = -1;   //   ... and no room for an insertion
         if (tid < rows && p0 + tid < P) {
             const size_t o = po + p0 + tid;
             const int4 rA = a.RA[o], rC = a.RC[o], rD = a.RD[o];
@@ -527,6 +551,11 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
             sl.P1 = a.RB[o];
             sl.P2 = make_int4(rA.y, rC.x, rD.x, rD.y);
             sl.dep = rA.x;
+            if (!DUMP) {  // validity folded into the data (score_pair_tri)
+                const bool cust = rC.w & 1;
+                sl.reldem = (cust && (rC.w & 2) && (a.families & 2)) ? sl.P1.w : kNever;
+                if (!cust) sl.P1.y = -1;
+            }
         }
         const int pv = min(max(p0 - 1 + tid, 0), a.pstride - 1);
         sl.vx = PX[pv];
@@ -556,7 +585,8 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
     const bool q_cust = q_in && ((Hq.w >> 30) & 1);
     const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
     const bool swap_q = q_cust && (a.families & 4);
-    const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q};
+    const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q,
+                   rel_q ? capsl_q : -1, (q_cust && q_rem_ok && (a.families & 2)) ? qB.w : kNever, swap_q ? qB.y : -1};
 
     int best_d = INT_MAX, thr = INT_MAX, tb_d = INT_MAX, tb_thr = INT_MAX;   // tb_*: table mode's mirrored-relocate entry
     unsigned best_i = 0xFFFFFFFFu, tb_i = 0xFFFFFFFFu;
@@ -587,31 +617,36 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
     };
     int2 c_up = cell_slot(sa), c_cur = cell_slot(sa + 80);
     const unsigned full = 0xffffffffu;
+    auto run_rows = [&](auto diag_tag) {
+        constexpr bool DIAG = decltype(diag_tag)::value;
 #pragma unroll 3
-    for (int rr = 0; rr < rows; ++rr, sa += 80) {
-        const int p = p0 + rr;
-        const int2 c_dn = cell_slot(sa + 160);
-        const int4 Hp = lds128(sa);
-        {   // every row: a separator is never moved but is an insertion point of the mirrored relocate
+        for (int rr = 0; rr < rows; ++rr, sa += 80) {
+            const int p = p0 + rr;
+            const int2 c_dn = cell_slot(sa + 160);
+            const int4 Hp = lds128(sa);
+            // every row: a separator is never moved but is an insertion point of the mirrored relocate
             const int2 c_lf = make_int2(__shfl_up_sync(full, c_cur.x, 1), __shfl_up_sync(full, c_cur.y, 1));
             const int2 c_rt = make_int2(__shfl_down_sync(full, c_cur.x, 1), __shfl_down_sync(full, c_cur.y, 1));
             const int4 p1 = lds128(sa + 16), p2 = lds128(sa + 32);
-            int dep_p;
-            asm volatile("ld.shared.s32 %0, [%1];" : "=r"(dep_p) : "r"(sa + 72));
+            int dep_p, reldem_p;
+            asm volatile("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(dep_p), "=r"(reldem_p) : "r"(sa + 72));
             if (TABLE && (Hp.w & 0x7FFF) != cur_ra) {
                 flush();
                 cur_ra = Hp.w & 0x7FFF;
             }
             if (TABLE)
-                score_pair_tri<MODE>(a, P, p, Hp, p1, p2, dep_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf, c_dn, best_d,
-                                     best_i, thr, tb_d, tb_i, tb_thr);
+                score_pair_tri<MODE, DIAG>(a, P, p, Hp, p1, p2, dep_p, reldem_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf,
+                                           c_dn, best_d, best_i, thr, tb_d, tb_i, tb_thr);
             else
-                score_pair_tri<MODE>(a, P, p, Hp, p1, p2, dep_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf, c_dn, best_d,
-                                     best_i, thr, best_d, best_i, thr);
+                score_pair_tri<MODE, DIAG>(a, P, p, Hp, p1, p2, dep_p, reldem_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf,
+                                           c_dn, best_d, best_i, thr, best_d, best_i, thr);
+            c_up = c_cur;
+            c_cur = c_dn;
         }
-        c_up = c_cur;
-        c_cur = c_dn;
-    }
+    };
+    // p < q holds for every pair of a tile whose first column lies beyond the strip's last row
+    if (q0 > p0 + rows - 1) run_rows(std::false_type{});
+    else run_rows(std::true_type{});
     if (TABLE) {
         flush();
     } else if (!DUMP) {
