@@ -400,7 +400,8 @@ __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, 
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
     const int q = c.q;
     // DIAG: the tile touches the diagonal, so p < q has to be tested per pair; everywhere else it holds for the tile
-    const bool pair = (Hp.w & 0x7FFF) != c.q_route && (!DIAG || p < q);
+    // (outside the dump the slot's H.w is the bare route id: the flags beside it moved into the data, see below)
+    const bool pair = (DUMP ? (Hp.w & 0x7FFF) : Hp.w) != c.q_route && (!DIAG || p < q);
     // relocate(p -> between q and q+1)
     const int ins = fadd(fadd(c_cur.x, c_rt.x), -c.Hq.z);
     const int d_rel = fadd(Hp.x, ins);
@@ -555,6 +556,7 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
                 const bool cust = rC.w & 1;
                 sl.reldem = (cust && (rC.w & 2) && (a.families & 2)) ? sl.P1.w : kNever;
                 if (!cust) sl.P1.y = -1;
+                sl.H.w &= 0x7FFF;
             }
         }
         const int pv = min(max(p0 - 1 + tid, 0), a.pstride - 1);
@@ -1107,6 +1109,7 @@ __global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const
 // 32 rows, 47 us at 41 rows = exactly two full waves — filling whole waves does not pay, the dispatcher back-fills
 // and a half-empty last wave simply runs faster.)  ROUTEST_STRIP_ROWS overrides, for experiments.
 int g_strip_rows = 0;    // rt_debug_set("strip_rows", h): 0 = pick, else the height to use
+int g_small_strips = 1;  // rt_debug_set("small_strips", 0/1): short strips where the whole grid fits one wave
 int g_intra_kernel = 0;  // rt_debug_set("intra_kernel", k): 0 = pick, 1 = one thread per anchor, 2 = one warp per anchor
 
 int pick_strip_rows(int pmax, int rows, int batch, bool asym, int cols_per_block)
@@ -1116,8 +1119,16 @@ int pick_strip_rows(int pmax, int rows, int batch, bool asym, int cols_per_block
     if (forced >= 8 && forced <= kMaxStripRows) return forced;
     const long long col_blocks = (pmax + cols_per_block - 1) / cols_per_block;
     // (the kernel without a matrix runs only the tiles above the diagonal: about half of the grid)
-    const long long blocks64 = col_blocks * ((rows + 63) / 64) * batch / (cols_per_block == kFusedCols ? 2 : 1);
-    return (!asym && blocks64 >= 4LL * kNumSMs * 9) ? 64 : kStripRows;
+    const int tri = cols_per_block == kFusedCols ? 2 : 1;
+    const long long blocks64 = col_blocks * ((rows + 63) / 64) * batch / tri;
+    if (!asym && blocks64 >= 4LL * kNumSMs * 9) return 64;
+    // A small grid is bound by the latency of one block (a dependent chain of ~0.15 us per row behind a ~3 us
+    // prologue), not by throughput: while every block is resident at once, shorter strips mean a shorter kernel
+    // (1,010 positions: 11.3 us at 32 rows, 144 blocks).
+    if (g_small_strips && tri == 2)
+        for (int h = 8; h < kStripRows; h *= 2)
+            if (col_blocks * ((rows + h - 1) / h) * batch / tri <= 8LL * kNumSMs) return h;
+    return kStripRows;
 }
 
 // One warp per anchor while the launch has too few anchors to hide the sweep's latency behind other work (a single
@@ -1355,6 +1366,9 @@ extern "C" int rt_debug_set(const char *name, int value)
 {
     if (!name) return RT_ERR_INVALID_ARG;
     if (!strcmp(name, "strip_rows")) rt::g_strip_rows = value;
+    else if (!strcmp(name, "state_fused_max")) rt::g_state_fused_max = value;
+    else if (!strcmp(name, "apply_prep")) rt::g_apply_prep = value;
+    else if (!strcmp(name, "small_strips")) rt::g_small_strips = value;
     else if (!strcmp(name, "intra_kernel")) rt::g_intra_kernel = value;
     else if (!strcmp(name, "fused_eval")) rt::g_fused_eval = value;
     else return RT_ERR_INVALID_ARG;

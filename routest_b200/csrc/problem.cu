@@ -1035,9 +1035,10 @@ static int local_search_impl(rt_problem *p, int families, int max_moves, int mod
     const bool batched = mode & 2;  // SPEC.md §8.1: max_moves counts iterations, each applies a batch of moves
     if (batched && !batch_usable(p))
         return fail(e, RT_ERR_INVALID_ARG, "rt_problem_local_search_batched handles at most 1024 routes per instance");
-    // (below ~1,500 positions re-scoring everything on G is the faster of the two: 47 vs 61 µs per move at 100 stops,
-    // 44 vs 49 at 400, equal at 1,000, 81 vs 77 at 2,000 — the table's bookkeeping kernels cost more than they save)
-    int cache_from = 1536;  // positions; ROUTEST_LS_INCREMENTAL_FROM overrides (the tests force either driver at any size)
+    // (up to ~5,000 positions re-scoring everything is the faster of the two — us per move, full vs table: 33 vs 55 at
+    // 1,500 stops, 36 vs 59 at 2,000, 47 vs 66 at 3,000, 78 vs 79 at 5,000, 124 vs 89 at 7,000: an iteration of the
+    // full search is two or three dependent launches, the table's bookkeeping is a longer chain of small ones)
+    int cache_from = 4608;  // positions; ROUTEST_LS_INCREMENTAL_FROM overrides (the tests force either driver at any size)
     if (const char *ev = getenv("ROUTEST_LS_INCREMENTAL_FROM")) cache_from = atoi(ev);
     const bool cached = !batched && !(mode & 1) && cache_usable(p) && p->pmax > cache_from;
     if (batched) RT_TRY(batch_begin(p, e->stream));

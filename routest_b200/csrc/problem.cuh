@@ -134,7 +134,7 @@ constexpr double kBetaTriangle = 1.0, kBetaStoredMatrix = 0.3, kBetaUniform = 0.
 // rt_debug_set("fused_eval", v): 1 (default) = the move kernels rebuild matrix cells from the position-ordered unit
 // vectors wherever the matrix is SPEC 2 of the problem's own coordinates, so no route-order matrix is written or read;
 // 0 = always materialise G and read it (the write-then-read form, kept for measurement and for supplied matrices).
-extern int g_fused_eval;
+extern int g_fused_eval, g_state_fused_max, g_apply_prep;
 inline bool eval_without_matrix(const rt_problem *p) { return g_fused_eval != 0 && p->cells_from_coords && p->symmetric; }
 
 // first cell of G (the buffer starts with 16 pad cells)

@@ -649,14 +649,29 @@ __global__ void __launch_bounds__(kRouteWarps * 32) state_route_tables_kernel(co
 
 // Applies one move per instance (SPEC.md §8).  keys are the packed keys of SPEC.md §7, optionally in the
 // order-preserving signed form (key ^ 2^63) that the _dev entry points exchange with NCCL.
-__global__ void __launch_bounds__(256) apply_moves_kernel(const unsigned long long *__restrict__ keys, int signed_keys,
-                                                          int improving_only, int *__restrict__ node_all,
-                                                          int *__restrict__ tmp_all, const int *__restrict__ npos,
-                                                          int pstride, int *__restrict__ done, int *__restrict__ moves,
-                                                          unsigned long long *__restrict__ hist, int hist_cap,
-                                                          const int *__restrict__ route_all, int *__restrict__ dirty)
+struct ApplyArgs {
+    const unsigned long long *keys;
+    int signed_keys, improving_only;
+    int *node_all, *tmp_all;
+    const int *npos;
+    int pstride;
+    int *done, *moves;
+    unsigned long long *hist;
+    int hist_cap;
+    const int *route_all;
+    int *dirty;
+};
+
+// Every branch that leaves early is uniform over the block and comes before the one barrier.
+__device__ __forceinline__ void apply_move_block(const ApplyArgs &ap, int b)
 {
-    const int b = blockIdx.x, tid = threadIdx.x;
+    const unsigned long long *__restrict__ keys = ap.keys;
+    const int signed_keys = ap.signed_keys, improving_only = ap.improving_only, pstride = ap.pstride, hist_cap = ap.hist_cap;
+    int *__restrict__ node_all = ap.node_all, *__restrict__ tmp_all = ap.tmp_all;
+    const int *__restrict__ npos = ap.npos, *__restrict__ route_all = ap.route_all;
+    int *__restrict__ done = ap.done, *__restrict__ moves = ap.moves, *__restrict__ dirty = ap.dirty;
+    unsigned long long *__restrict__ hist = ap.hist;
+    const int tid = threadIdx.x;
     unsigned long long key = keys[b];
     if (signed_keys) key ^= 0x8000000000000000ull;
     if (dirty && tid == 0) {  // incremental search: which routes this move touches (none if nothing is applied)
@@ -724,9 +739,30 @@ __global__ void __launch_bounds__(256) apply_moves_kernel(const unsigned long lo
     }
 }
 
+__global__ void __launch_bounds__(256) apply_moves_kernel(const ApplyArgs ap) { apply_move_block(ap, blockIdx.x); }
+
+// The one-move search on small and medium instances is a chain of short launches, each waiting for the one before
+// (about 3 us per link in a replayed graph, beside 4-5 us of dependent loads inside each).  This kernel is up to four
+// links in one, one block per instance: the move, the route scan of the new order and — where every route gets a warp
+// of its own (with_tables) — the per-route tables, whose gather also writes the position-ordered vectors.  The key
+// is read before the first barrier, the scan's reset of best[] comes after it.
+__global__ void __launch_bounds__(kPrepThreads) apply_state_kernel(const ApplyArgs ap, const StateArgs a, int with_tables)
+{
+    const int b = blockIdx.x;
+    apply_move_block(ap, b);
+    __syncthreads();
+    routes_scan_small_block(a.r, b);
+    if (!with_tables) return;
+    __syncthreads();
+    const int R = a.w.npos[b] - a.w.n;
+    for (int rr = threadIdx.x >> 5; rr < R; rr += kPrepThreads / 32) route_tables_warp(a, b, rr);
+}
+
 }  // namespace
 
-constexpr int kFusedStatePositions = 4096;
+constexpr int kFusedStatePositions = 0;  // (the one-block state kernel: measured slower than scan + per-route warps from 400 stops up, equal below)
+int g_state_fused_max = -1;  // rt_debug_set("state_fused_max", positions): -1 = the default below
+int g_apply_prep = 1;        // rt_debug_set("apply_prep", 0/1): the merged apply + vectors + scan launch
 static void launch_position_vectors(rt_problem *p, cudaStream_t st);
 
 int ensure_position_matrix(rt_problem *p, bool need_buffer)
@@ -793,7 +829,8 @@ static RoutesArgs routes_args(rt_problem *p)
 }
 
 // large instances: the vector kernel that precedes the tables carries the route scan as an extra block
-static bool scan_rides_along(const rt_problem *p) { return p->grows > kFusedStatePositions; }
+static int state_fused_max() { return g_state_fused_max >= 0 ? g_state_fused_max : kFusedStatePositions; }
+static bool scan_rides_along(const rt_problem *p) { return p->grows > state_fused_max(); }
 
 static void launch_position_vectors(rt_problem *p, cudaStream_t st)
 {
@@ -825,8 +862,7 @@ int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors)
     const StateArgs a = state_args(p, fused);
     p->best_clean = true;  // the route scan resets the best keys
     p->ext_best_clean = p->ext_best != nullptr;
-    if (p->grows <= kFusedStatePositions) {
-        p->scan_done = false;
+    if (!p->scan_done && p->grows <= state_fused_max()) {
         state_fused_kernel<<<p->batch, kScanThreads, 0, st>>>(a);
         RT_CUDA(e, cudaGetLastError());
         return RT_OK;
@@ -893,19 +929,39 @@ int position_vectors_refresh(rt_problem *p, cudaStream_t st)
     return RT_OK;
 }
 
+static ApplyArgs apply_args(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
+                            int *dirty_d)
+{
+    return ApplyArgs{keys_d, signed_keys ? 1 : 0, improving_only ? 1 : 0, p->node, p->node_tmp, p->npos, p->pstride,
+                     p->done,  p->moves, p->hist, p->hist_cap, p->route, dirty_d};
+}
+
 int apply_only_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
                       cudaStream_t st, int *dirty_d)
 {
-    apply_moves_kernel<<<p->batch, 256, 0, st>>>(keys_d, signed_keys ? 1 : 0, improving_only ? 1 : 0, p->node,
-                                                 p->node_tmp, p->npos, p->pstride, p->done, p->moves, p->hist,
-                                                 p->hist_cap, p->route, dirty_d);
+    apply_moves_kernel<<<p->batch, 256, 0, st>>>(apply_args(p, keys_d, signed_keys, improving_only, dirty_d));
     RT_CUDA(p->e, cudaGetLastError());
     return RT_OK;
 }
 
+// Up to this many positions one block per instance applies the move and scans the routes (apply_state_kernel); with
+// at most one route per warp of that block it fills the tables too, otherwise the per-route kernel follows.
+constexpr int kApplyStatePositions = 4096;
+
 int apply_moves_launch(rt_problem *p, const unsigned long long *keys_d, bool signed_keys, bool improving_only,
                        cudaStream_t st)
 {
+    if (g_apply_prep && p->cells_from_coords && eval_without_matrix(p) && p->xyz && p->grows <= kApplyStatePositions) {
+        const int rmax = std::max(1, (p->pmax > 0 ? p->pmax : p->grows) - p->n);  // most routes of any instance
+        const bool with_tables = rmax <= kPrepThreads / 32;
+        apply_state_kernel<<<p->batch, kPrepThreads, 0, st>>>(apply_args(p, keys_d, signed_keys, improving_only, nullptr),
+                                                              state_args(p, /*fused_vectors=*/true), with_tables ? 1 : 0);
+        RT_CUDA(p->e, cudaGetLastError());
+        p->best_clean = true;  // the route scan resets the best keys
+        p->ext_best_clean = p->ext_best != nullptr;
+        p->scan_done = !with_tables;
+        return with_tables ? RT_OK : state_tables_refresh(p, st, /*with_vectors=*/true);
+    }
     RT_TRY(apply_only_launch(p, keys_d, signed_keys, improving_only, st));
     return state_refresh(p, st);
 }

@@ -632,3 +632,32 @@ def test_kernel_variants_agree_with_the_oracle(engine, fused, kernel, seed, stop
     finally:
         engine.debug_set("intra_kernel", 0)
         engine.debug_set("fused_eval", 1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("state_fused_max,apply_prep,small_strips", [(-1, 1, 1), (-1, 0, 1), (4096, 1, 0), (4096, 0, 0)],
+                         ids=["default", "separate-apply", "one-block-state", "round-1-chain"])
+@pytest.mark.parametrize("seed,stops,veh,kw", [(21, 12, 1, {}), (22, 150, 4, dict(half_lo=7200, half_hi=20000)),
+                                                (23, 420, 40, {})])
+def test_search_launch_variants_agree_with_the_oracle(engine, state_fused_max, apply_prep, small_strips, seed, stops, veh,
+                                                      kw):
+    """The one-move search reaches the oracle's keys, cost and routes whichever way an iteration is cut into launches:
+    the move + route scan + per-route tables in one launch (rt_debug_set "apply_prep"; more than 32 routes leave the
+    tables to their own kernel: the 40-vehicle case), the one-block state kernel or one warp per route
+    ("state_fused_max"), short strips for small grids ("small_strips").  SPEC.md §8; no reference counterpart."""
+    inst, node0, raw = synth_vrptw(seed, stops, veh, **kw)
+    engine.debug_set("state_fused_max", state_fused_max)
+    engine.debug_set("apply_prep", apply_prep)
+    engine.debug_set("small_strips", small_strips)
+    try:
+        with _load(engine, [(inst, node0, raw)]) as pr:
+            assert int(pr.eval_moves()[0]) == O.best_move(inst, node0)
+            moves, cost, keys = pr.local_search(max_moves=40, keys_capacity=64, full=True)
+            final, okeys, ocost = O.local_search(inst, node0, max_moves=40)
+            assert np.array_equal(keys[0], okeys) and cost[0] == ocost
+            assert np.array_equal(pr.get_state(0)["node"], final)
+            assert int(pr.eval_moves()[0]) == O.best_move(inst, final)
+    finally:
+        engine.debug_set("state_fused_max", -1)
+        engine.debug_set("apply_prep", 1)
+        engine.debug_set("small_strips", 1)

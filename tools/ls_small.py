@@ -1,19 +1,32 @@
-"""Sequential local search on small instances: incremental vs full re-scoring driver (development aid)."""
-import json, os, sys, time
+"""One-move local search on a small instance: time per applied move (development aid; --moves bounds the run so a
+launch list of it stays short)."""
+import argparse, json, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from routest_b200 import Engine
 from tools.dist_search_check import build
 
+ap = argparse.ArgumentParser()
+ap.add_argument("--stops", type=int, default=1000)
+ap.add_argument("--vehicles", type=int, default=10)
+ap.add_argument("--moves", type=int, default=1 << 30)
+ap.add_argument("--full", type=int, default=0)
+ap.add_argument("--repeat", type=int, default=3)
+ap.add_argument("--state-fused-max", type=int, default=-1)
+ap.add_argument("--apply-prep", type=int, default=1)
+ap.add_argument("--small-strips", type=int, default=1)
+a = ap.parse_args()
 eng = Engine(0)
-for stops, veh in ((100, 10), (200, 10), (400, 10), (1000, 10), (2000, 20)):
-    out = {"stops": stops}
-    for name, kw in (("incremental", {}), ("full", {"full": True}), ("batched", {"batched": True})):
-        best = 1e9
-        for rep in range(3):
-            pr, trips = build(eng, 5678, stops, veh)
-            t0 = time.perf_counter()
-            moves, cost, _ = pr.local_search(**kw)
-            best = min(best, time.perf_counter() - t0)
-            pr.close()
-        out[name] = {"moves": int(moves[0]), "ms": round(best * 1e3, 2), "us_per_move": round(1e6 * best / max(1, int(moves[0])), 1)}
-    print(json.dumps(out))
+eng.debug_set("state_fused_max", a.state_fused_max)
+eng.debug_set("apply_prep", a.apply_prep)
+eng.debug_set("small_strips", a.small_strips)
+best = None
+for _ in range(a.repeat):
+    pr, trips = build(eng, 5678, a.stops, a.vehicles)
+    t0 = time.perf_counter()
+    moves, cost, _ = pr.local_search(max_moves=a.moves, full=bool(a.full))
+    dt = time.perf_counter() - t0
+    pr.close()
+    if best is None or dt < best[0]:
+        best = (dt, int(moves[0]), int(cost[0]))
+print(json.dumps({"knobs": [a.state_fused_max, a.apply_prep, a.small_strips], "stops": a.stops, "vehicles": a.vehicles, "full": a.full, "moves": best[1], "cost": best[2],
+                  "s": round(best[0], 5), "us_per_move": round(1e6 * best[0] / max(1, best[1]), 2)}))
