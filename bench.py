@@ -578,10 +578,10 @@ def kernel_block(ms_matrix, ms_state, ms_eval, ms_own, ms_wtr, P, n, world, cand
 
 def roofline_block(ms_matrix, ms_eval, P, n, world, cand, clocks, peaks):
     """Dominant kernel = move evaluation (tile kernel that rebuilds its cells from unit vectors).  It touches O(n) bytes
-    of HBM, so its roofline is an instruction rate, and the unit that binds is the ALU pipe: achieved = ALU-pipe warp
-    instructions per launch (ncu counter of the same workload, profiles/r2_counters.json; a shard executes 1/N of them)
-    / live duration, against the ALU peak measured in this run (rt_selftest_pipe_peak); all instructions against the
-    issue limit are given beside it.  The matrix kernel, which the pass no longer needs, keeps its HBM form (measured
+    of HBM, so its roofline is an instruction rate: achieved = warp instructions per launch (ncu counter of the same
+    workload, profiles/r2_counters.json; a shard executes 1/N of them) / live duration against the issue limit, and
+    the ALU-pipe share of them against the ALU peak measured in this run (rt_selftest_pipe_peak); `bound` is the one
+    closer to its peak.  The matrix kernel, which the pass no longer needs, keeps its HBM form (measured
     on this rank's rows)."""
     hbm = hbm_peak()
     hbm_src = ("measured (MEASURED_PEAKS.json hbm_gbs)" if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json"))
@@ -601,28 +601,38 @@ def roofline_block(ms_matrix, ms_eval, P, n, world, cand, clocks, peaks):
     ev = counters.get("eval_moves") or {}
     alu_inst, all_inst = ev.get("alu_warp_inst"), ev.get("warp_inst")
     roof = {"kernel": "eval_inter_fused_kernel + same-route kernel (move evaluation, cells rebuilt from unit vectors)",
-            "bound": "alu", "unit": "G warp-instructions/s on the ALU pipe", "achieved": None, "peak": None, "frac": None,
+            "bound": "issue", "unit": "G warp-instructions/s", "achieved": None, "peak": None, "frac": None,
             "traffic": ev.get("dram_bytes"),
-            "note": "no matrix is written or read: HBM traffic is O(n) per pass, so the bound is an instruction rate. ncu: "
-                    "ALU pipe 76 % busy (compares, min/max, three-input adds, logic) with math-pipe throttle the first "
-                    "stall reason, issue slots 74 %; SURVEY.md §8(d) already rules HBM out for this kernel",
+            "note": "no matrix is written or read: HBM traffic is O(n) per pass, so the bound is an instruction rate "
+                    "(SURVEY.md §8(d) already rules HBM out for this kernel). ncu of the tile kernel "
+                    "(profiles/r2_pass10k_kernels_ncu.txt): issue slots 87 % busy, ALU pipe 59 %, FMA-heavy pipe 56 % "
+                    "(the sums run there as IMAD), LSU 37 %, XU 15 %, FP64 11 %; `bound` names whichever of the issue "
+                    "limit and the ALU pipe is closer to its peak in this run, the other is given beside it",
             "matrix_kernel": mat}
-    if alu_inst and peaks:      # the binding unit: the ALU pipe, against the ALU peak measured in this run
-        ach = alu_inst / world / (ms_eval / 1e3)
-        roof.update(achieved=ach / 1e9, peak=peaks["alu"] / 1e9, frac=ach / peaks["alu"],
-                    alu_warp_inst_per_launch=alu_inst / world,
-                    peak_source="measured in this run: rt_selftest_pipe_peak mode 0 (independent LOP3/IMNMX chains, CUDA "
-                                f"events, SM clock {clocks.get('sm_mhz') if clocks else None} MHz) = one ALU-pipe warp "
-                                "instruction per two clocks per scheduler",
-                    counter_source="profiles/r2_counters.json (ncu smsp__inst_executed_pipe_alu.sum / smsp__inst_executed"
-                                   ".sum of one pass, tile + same-route kernel, N = 1; a shard executes 1/N of them)")
-    if all_inst and peaks:      # beside it: all instructions against the issue limit
+    forms = {}
+    if all_inst and peaks:      # all instructions against the issue limit
         ach = all_inst / world / (ms_eval / 1e3)
-        roof["issue"] = {"achieved": ach / 1e9, "peak": peaks["issue_limit"] / 1e9, "frac": ach / peaks["issue_limit"],
-                         "unit": "G warp-instructions/s", "warp_inst_per_launch": all_inst / world,
-                         "peak_source": "148 SMs x 4 schedulers x 1 warp instruction per clock at the SM clock sampled in "
-                                        "this run (what ncu's issue-active is a percentage of)",
-                         "measured_mixes_Ginst_s": {k: v / 1e9 for k, v in peaks["issue_measured_mixes"].items()}}
+        forms["issue"] = {"achieved": ach / 1e9, "peak": peaks["issue_limit"] / 1e9, "frac": ach / peaks["issue_limit"],
+                          "unit": "G warp-instructions/s", "warp_inst_per_launch": all_inst / world,
+                          "peak_source": "148 SMs x 4 schedulers x 1 warp instruction per clock at the SM clock sampled in "
+                                         f"this run ({clocks.get('sm_mhz') if clocks else None} MHz): what ncu's "
+                                         "issue-active is a percentage of; instruction mixes measured in this run "
+                                         "(rt_selftest_pipe_peak) beside it",
+                          "measured_mixes_Ginst_s": {k: v / 1e9 for k, v in peaks["issue_measured_mixes"].items()}}
+    if alu_inst and peaks:      # ALU-pipe instructions against the ALU peak measured in this run
+        ach = alu_inst / world / (ms_eval / 1e3)
+        forms["alu"] = {"achieved": ach / 1e9, "peak": peaks["alu"] / 1e9, "frac": ach / peaks["alu"],
+                        "unit": "G warp-instructions/s on the ALU pipe", "alu_warp_inst_per_launch": alu_inst / world,
+                        "peak_source": "measured in this run: rt_selftest_pipe_peak mode 0 (independent LOP3/IMNMX chains, "
+                                       "CUDA events) = one ALU-pipe warp instruction per two clocks per scheduler"}
+    if forms:
+        bound = max(forms, key=lambda k: forms[k]["frac"])
+        roof.update(bound=bound, **forms[bound])
+        for k in forms:
+            if k != bound:
+                roof[k] = forms[k]
+        roof["counter_source"] = ("profiles/r2_counters.json (ncu smsp__inst_executed.sum / smsp__inst_executed_pipe_alu.sum "
+                                  "of one pass, tile + same-route kernel, N = 1; a shard executes 1/N of them)")
     roof["algorithmic_matrix_reads"] = {
         "bytes": sum(cand[f] * BYTES_PER_EVAL[f] for f in cand) // world,
         "GBs": sum(cand[f] * BYTES_PER_EVAL[f] for f in cand) / world / ms_eval / 1e6,

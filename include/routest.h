@@ -340,7 +340,13 @@ int rt_selftest_pipe_peak(rt_engine *e, int mode, int iters, double *warp_inst_p
 /* Test and measurement knobs (process-wide, not for production use): "strip_rows" = rows per block of the tile kernel
  * (0 = let the launcher pick, 8..64), "intra_kernel" = which same-route kernel runs (0 = pick, 1 = one thread per
  * anchor, 2 = one warp per anchor), "fused_eval" = 1 (default): move kernels rebuild matrix cells from unit vectors
- * where the matrix is SPEC.md §2 of the problem's coordinates, 0: always write the route-order matrix and read it back.
+ * where the matrix is SPEC.md §2 of the problem's coordinates, 0: always write the route-order matrix and read it back;
+ * "small_strips" = 1 (default): strips of 8 or 16 rows where the whole tile grid is resident at once; how the one-move
+ * search cuts an iteration into launches: "persistent_search" = 0 never / 1 (default) the whole search as one
+ * cooperative launch where that is the faster form (small instances) / 2 wherever it can run, "persist_blocks" = most
+ * blocks per SM of that launch (0 = all that fit), "apply_prep" = 1 (default): move + route scan (+ per-route tables up
+ * to 32 routes) in one launch, "state_fused_max" = positions up to which one block per instance builds the whole route
+ * state (-1 = default: never, one warp per route instead).
  * Every choice gives the same keys; the tests run them against each other and the oracle.  No reference counterpart. */
 int rt_debug_set(const char *name, int value);
 

@@ -27,18 +27,26 @@
 #include <cstring>
 #include <type_traits>
 
+#include <cooperative_groups.h>
+
 #include "geometry.cuh"
 #include "problem.cuh"
+#include "state_device.cuh"
 
 namespace rt {
 
 int g_fused_eval = 1;  // see problem.cuh
+int g_persistent_search = 1;  // rt_debug_set("persistent_search", v): 0 = never, 1 = where it is the faster form,
+                              // 2 = wherever it can run (see search_persistent_launch)
+int g_persist_blocks = 0;     // rt_debug_set("persist_blocks", k): at most k blocks per SM in that kernel (0 = all that fit)
 
 namespace {
 
 constexpr int kInterThreads = 128;  // one column q per thread
 constexpr int kStripRows = 32;     // default rows p per block
 constexpr int kMaxStripRows = 64;  // the launcher picks the height per launch (pick_strip_rows)
+constexpr int kPersistMaxPositions = 4608;  // the one-launch search (search_persistent_kernel) can run up to here ...
+constexpr int kPersistPositions = 256;      // ... and is the faster form up to here (see search_persistent_launch)
 
 // a + b on the FMA pipe (IMAD with multiplier 1): the move kernels are bound by the ALU pipe (compares, min/max,
 // selects, three-input adds), while the FMA pipe idles — plain sums go there.
@@ -500,14 +508,16 @@ __device__ __forceinline__ double lds64(unsigned addr)
 
 // FAST: the launcher has proved from the coordinates' bounding box that no pair of the batch can leave the
 // straight-line range of the cell function (any metro-sized instance), so the per-cell range test is compiled out.
+// (The body is a device function of the block's place in the grid: the persistent search kernel runs the same tiles
+// from a loop.)
 template <int MODE, bool FAST>
-__global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(const EvalArgs a)
+__device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int grid_x, int grid_y, int grid_z)
 {
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
     __shared__ RowSlot slots[kMaxStripRows + 2];
     const int kStripRows = a.strip_rows;
 
-    const int b = DUMP ? a.dump_instance : blockIdx.z;
+    const int b = DUMP ? a.dump_instance : grid_z;
     const int P = a.npos[b];
     int p_lo, p_hi;
     shard_range(P, a.shard_index, a.shard_count, a.beta_inter, p_lo, p_hi);
@@ -516,7 +526,7 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
     // would be half empty blocks (each still costs a launch slot and a load of npos: 6 us on the last rank of eight),
     // so strip y shares its grid row with strip S-1-y: n(y) + n(S-1-y) is nearly constant.
     const int S = (p_hi - p_lo + kStripRows - 1) / kStripRows, nxb = (P + kFusedCols - 1) / kFusedCols;
-    int y = blockIdx.y, tile = blockIdx.x;
+    int y = grid_y, tile = grid_x;
     if (2 * y >= S) return;
     {
         const int n1 = max(0, nxb - (p_lo + y * kStripRows + 1) / kFusedCols);
@@ -658,6 +668,12 @@ __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(cons
                 : (static_cast<unsigned long long>(static_cast<unsigned>(best_d) + 0x80000000u) << 32) | best_i;
         block_min_to_global<kInterThreads>(best, a.best + b, a.signed_dst != 0);
     }
+}
+
+template <int MODE, bool FAST>
+__global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(const EvalArgs a)
+{
+    eval_inter_fused_tile<MODE, FAST>(a, blockIdx.x, blockIdx.y, blockIdx.z);
 }
 
 // ---- same-route candidates ------------------------------------------------------------------------------------
@@ -911,16 +927,16 @@ __device__ __forceinline__ Seg seg_of(const SegW &s) { return Seg{s.a, s.b, s.L,
 
 constexpr int kIntraWarps = 4;
 
-template <int MODE, bool FUSED = false>
-__global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const EvalArgs a)
+template <int MODE, bool FUSED>
+__device__ __forceinline__ void eval_intra_warp_block(const EvalArgs &a, int grid_x, int grid_y)
 {
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
-    const int b = DUMP ? a.dump_instance : blockIdx.y;
+    const int b = DUMP ? a.dump_instance : grid_y;
     const int P = a.npos[b];
     int t_lo, t_hi;
     shard_range(P, a.shard_index, a.shard_count, a.beta_intra, t_lo, t_hi);  // same-route work is sharded by anchor
     const int lane = threadIdx.x & 31;
-    const int t = t_lo + blockIdx.x * kIntraWarps + (threadIdx.x >> 5);
+    const int t = t_lo + grid_x * kIntraWarps + (threadIdx.x >> 5);
     unsigned long long best = kNoMove;
     int t_route = 0;
 
@@ -1102,6 +1118,12 @@ __global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const
     }
 }
 
+template <int MODE, bool FUSED = false>
+__global__ void __launch_bounds__(kIntraWarps * 32) eval_intra_warp_kernel(const EvalArgs a)
+{
+    eval_intra_warp_block<MODE, FUSED>(a, blockIdx.x, blockIdx.y);
+}
+
 // Strip height of the tile kernel.  Taller strips amortise the per-block prologue (the column's records, the window's
 // first rows, the block reduction: worth about four rows — 0.249 -> 0.236 ms on the 64 x 1,000 batch going from 32 to
 // 64), shorter ones shorten the tail in which the last blocks leave SMs idle.  64 rows where at least four waves of
@@ -1169,6 +1191,21 @@ bool all_pairs_in_fast_range(const rt_problem *p, const EvalArgs &a)
     return p->angle2_bound >= 0.0 && p->angle2_bound * 1.001 < lim;
 }
 
+// Grid of the tile kernel without a matrix: the triangle above the diagonal, two strips per grid row (see the kernel);
+// sized for the largest instance of the batch from this shard's first row on, with slack for instances whose
+// boundaries differ by a row or two.  a.strip_rows must be set.
+dim3 fused_tile_grid(const EvalArgs &a, int pmax, int batch)
+{
+    const int cols = kFusedCols;
+    int lo, hi;
+    shard_bounds(pmax, a.shard_index, a.shard_count, a.beta_inter, lo, hi);
+    const int h = a.strip_rows, S = (hi - lo + 2 + h - 1) / h, nxb = (pmax + cols - 1) / cols;
+    auto n_of = [&](int yy) { return std::max(0, nxb - (std::max(lo - 2, 0) + yy * h + 1) / cols); };
+    int width = 1;
+    for (int yy = 0; 2 * yy < S; ++yy) width = std::max(width, n_of(yy) + (S - 1 - yy != yy ? n_of(S - 1 - yy) : 0));
+    return dim3(width + 2, (S + 1) / 2 + 1, batch);
+}
+
 // The tile kernel of this launch: without a matrix where the cells are SPEC 2 of the problem's coordinates, on G
 // (and GT for a directional matrix) otherwise.
 template <int MODE>
@@ -1178,17 +1215,7 @@ int launch_inter(rt_problem *p, EvalArgs &a, int pmax, int shard_rows, int batch
     const int cols = fused ? kFusedCols : kInterThreads;
     a.strip_rows = strip_rows > 0 ? strip_rows : pick_strip_rows(pmax, shard_rows, batch, !p->symmetric, cols);
     dim3 grid((pmax + cols - 1) / cols, (shard_rows + a.strip_rows - 1) / a.strip_rows, batch);
-    if (fused) {
-        // the triangle above the diagonal, two strips per grid row (see the kernel); sized for the largest instance of
-        // the batch from this shard's first row on, with slack for instances whose boundaries differ by a row or two
-        int lo, hi;
-        shard_bounds(pmax, a.shard_index, a.shard_count, a.beta_inter, lo, hi);
-        const int h = a.strip_rows, S = (hi - lo + 2 + h - 1) / h, nxb = (pmax + cols - 1) / cols;
-        auto n_of = [&](int yy) { return std::max(0, nxb - (std::max(lo - 2, 0) + yy * h + 1) / cols); };
-        int width = 1;
-        for (int yy = 0; 2 * yy < S; ++yy) width = std::max(width, n_of(yy) + (S - 1 - yy != yy ? n_of(S - 1 - yy) : 0));
-        grid = dim3(width + 2, (S + 1) / 2 + 1, batch);
-    }
+    if (fused) grid = fused_tile_grid(a, pmax, batch);
     if (fused && all_pairs_in_fast_range(p, a)) eval_inter_fused_kernel<MODE, true><<<grid, kInterThreads, 0, st>>>(a);
     else if (fused) eval_inter_fused_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
     else if (p->symmetric) eval_inter_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
@@ -1242,6 +1269,90 @@ EvalArgs make_args(rt_problem *p, int families, int shard_index, int shard_count
     a.best = best_d;
     a.strip_rows = kStripRows;
     return a;
+}
+
+// ---- one-move search as ONE launch (SPEC.md §8) ----
+// Up to a few thousand positions an iteration of the best-improvement search is three short phases — score every
+// candidate, apply the best one and rescan the routes, rebuild the per-route tables — each a chain of dependent loads
+// a few microseconds long.  As separate launches (even replayed from a graph) every phase also pays ~3 us of launch
+// dependency; here the phases are loops over the same device functions inside one cooperative kernel, separated by
+// grid-wide barriers, and the host is out of the loop until the search is over (or pa.iters have run).  Used for
+// small instances, where it is the faster form (kPersistPositions; the measurements are in search_persistent_launch).
+//   E  every block takes tiles of the triangle and same-route anchors (eval_inter_fused_tile, eval_intra_warp_block)
+//      of every instance that is not done; minima go to best[] by atomicMin as in the separate kernels
+//   A  the block that leaves E last applies best[b] to node[] (apply_move_block: sets done[b] where nothing
+//      improves) and, if a move was applied, rescans the routes (resets best[b], cost[b]); with at most four routes
+//      it rebuilds the tables as well and the iteration has a single barrier
+//   T  otherwise one warp per route, over the whole grid, rebuilds vectors, tables and records of the instances
+//      still live (route_tables_warp)
+// done[] only changes in A, so after the barrier behind it every block takes the same decision to leave.  None of the
+// loads below may use the read-only path: what E reads is what T of the same launch wrote (no __restrict__ on them).
+struct PersistArgs {
+    int iters;               // iterations this launch may run
+    int batch;
+    int inter_gx, inter_gy;  // the tile kernel's grid per instance
+    int intra_gx;            // the same-route kernel's blocks per instance
+    int rmax;                // most routes of any instance
+    int tables_in_block;     // rmax <= warps of a block: the block that applies the move rebuilds the tables too
+    unsigned *ticket;        // arrival counter, zero at launch
+};
+
+constexpr int kPersistThreads = 128;
+static_assert(kPersistThreads == kInterThreads && kPersistThreads == kIntraWarps * 32, "the phases share one block shape");
+
+template <bool FAST>
+__global__ void __launch_bounds__(kPersistThreads, 4) search_persistent_kernel(const EvalArgs ea, const StateArgs sa,
+                                                                               const ApplyArgs ap, const PersistArgs pa)
+{
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    __shared__ int s_last;
+    const int n_inter = pa.inter_gx * pa.inter_gy, per_instance = pa.intra_gx + n_inter;
+    const int warps = gridDim.x * (kPersistThreads / 32);
+    for (int it = 0; it < pa.iters; ++it) {
+        // E (the same-route anchors first: theirs is the longer chain)
+        for (int v = blockIdx.x; v < per_instance * pa.batch; v += gridDim.x) {
+            const int b = v / per_instance, w = v - b * per_instance;
+            if (!ap.done[b]) {  // uniform over the block
+                if (w < pa.intra_gx) eval_intra_warp_block<kBest, true>(ea, w, b);
+                else eval_inter_fused_tile<kBest, FAST>(ea, (w - pa.intra_gx) % pa.inter_gx, (w - pa.intra_gx) / pa.inter_gx, b);
+            }
+            __syncthreads();  // the shared memory of a tile is reused by the next
+        }
+        // A: whichever block finishes E last goes straight on (its atomicMins are ordered before its ticket by the
+        // fence, everybody else's before theirs): one grid-wide barrier less per iteration
+        if (threadIdx.x == 0) {
+            __threadfence();
+            s_last = atomicAdd(pa.ticket, 1u) == static_cast<unsigned>(gridDim.x) * (it + 1) - 1u;
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            for (int b = 0; b < pa.batch; ++b) {
+                apply_move_block(ap, b);
+                __syncthreads();
+                if (!ap.done[b]) {
+                    routes_scan_small_block<kPersistThreads>(sa.r, b);
+                    if (pa.tables_in_block) {
+                        __syncthreads();
+                        route_tables_warp(sa, b, threadIdx.x >> 5);  // returns at once beyond the instance's routes
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        grid.sync();
+        // done[] only changed in A: every block sees the same values here
+        int live = 0;
+        for (int b = threadIdx.x; b < pa.batch; b += kPersistThreads) live |= ap.done[b] == 0;
+        if (!__syncthreads_or(live)) break;
+        if (pa.tables_in_block) continue;
+        // T
+        for (int v = blockIdx.x * (kPersistThreads / 32) + (threadIdx.x >> 5); v < pa.rmax * pa.batch; v += warps) {
+            const int b = v / pa.rmax;
+            if (!ap.done[b]) route_tables_warp(sa, b, v - b * pa.rmax);  // returns at once beyond the instance's routes
+        }
+        grid.sync();
+    }
 }
 
 __global__ void finish_keys_kernel(const unsigned long long *__restrict__ src, unsigned long long *__restrict__ dst,
@@ -1304,6 +1415,71 @@ int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_co
     if (!direct && (best_d != p->best || signed_keys))
         finish_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, best_d, p->batch, signed_keys ? 1 : 0);
     RT_CUDA(e, cudaGetLastError());
+    return RT_OK;
+}
+
+// Runs up to `iters` iterations of the one-move search in one cooperative launch (search_persistent_kernel); the state
+// must be fresh.  Returns RT_OK after enqueueing, -1 where this form does not apply (the caller then launches the
+// iterations kernel by kernel): a stored matrix, a sharded replica, an instance too large for one block to rescan,
+// a device without cooperative launch.
+int search_persistent_launch(rt_problem *p, int families, int iters, bool improving_only, cudaStream_t st)
+{
+    rt_engine *e = p->e;
+    const int pmax = p->pmax > 0 ? p->pmax : p->pstride;
+    // Measured per applied move, one launch vs the graph-replayed chain of three (B200, us): 13.9 vs 16.1 at 100 stops,
+    // 20.1 vs 19.2 at 400, 27.9 vs 23.7 at 1,000, 43.1 vs 31.9 at 2,000.  The barriers cost less than the launch
+    // dependencies they replace, but this kernel carries the registers of all three phases (121: four blocks per SM)
+    // and runs the two evaluation kernels one after the other inside a block instead of side by side — a price that
+    // grows with the instance.  So: the one launch for small instances, the chain above.
+    const int limit = g_persistent_search >= 2 ? kPersistMaxPositions : kPersistPositions;
+    if (!g_persistent_search || !eval_without_matrix(p) || !p->xyz || p->shard_count != 1 || pmax > limit ||
+        !intra_by_warp(p, pmax))
+        return -1;
+    static int coop = -1, blocks_per_sm[2] = {0, 0};
+    if (coop < 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) != cudaSuccess) coop = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm[0], search_persistent_kernel<false>,
+                                                          kPersistThreads, 0) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm[1], search_persistent_kernel<true>,
+                                                          kPersistThreads, 0) != cudaSuccess)
+            coop = 0;
+        (void)cudaGetLastError();
+    }
+    if (!coop) return -1;
+    if (!p->best_clean) {
+        fill_keys_kernel<<<(p->batch + 255) / 256, 256, 0, st>>>(p->best, p->batch);
+        RT_CUDA(e, cudaGetLastError());
+    }
+    EvalArgs ea = make_args(p, families, 0, 1, p->best);
+    ea.strip_rows = pick_strip_rows(pmax, pmax, p->batch, false, kFusedCols);
+    const dim3 tg = fused_tile_grid(ea, pmax, p->batch);
+    const bool fast = all_pairs_in_fast_range(p, ea);
+    PersistArgs pa{};
+    pa.iters = iters;
+    pa.batch = p->batch;
+    pa.inter_gx = (families & 6) ? static_cast<int>(tg.x) : 0;
+    pa.inter_gy = (families & 6) ? static_cast<int>(tg.y) : 0;
+    pa.intra_gx = (pmax + 2 + kIntraWarps - 1) / kIntraWarps;
+    pa.rmax = std::max(1, pmax - p->n);
+    pa.tables_in_block = pa.rmax <= kPersistThreads / 32 ? 1 : 0;
+    pa.ticket = p->ticket;
+    RT_CUDA(e, cudaMemsetAsync(p->ticket, 0, sizeof(unsigned), st));
+    StateArgs sa = state_args(p, /*fused_vectors=*/true);
+    ApplyArgs ap = apply_args(p, p->best, false, improving_only, nullptr);
+    const long long want = std::max<long long>({static_cast<long long>(pa.inter_gx * pa.inter_gy + pa.intra_gx) * p->batch,
+                                                 p->batch, (static_cast<long long>(pa.rmax) * p->batch + 3) / 4});
+    const int per_sm = g_persist_blocks > 0 ? std::min(g_persist_blocks, blocks_per_sm[fast ? 1 : 0]) : blocks_per_sm[fast ? 1 : 0];
+    const int grid = static_cast<int>(std::min<long long>(want, static_cast<long long>(per_sm) * kNumSMs));
+    if (grid < 1) return -1;
+    void *args[] = {&ea, &sa, &ap, &pa};
+    const void *fn = fast ? reinterpret_cast<const void *>(search_persistent_kernel<true>)
+                          : reinterpret_cast<const void *>(search_persistent_kernel<false>);
+    RT_CUDA(e, cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kPersistThreads), args, 0, st));
+    p->best_clean = false;  // a search that ended at its optimum leaves the last (non-improving) keys behind
+    p->ext_best_clean = false;
+    p->scan_done = false;
     return RT_OK;
 }
 
@@ -1371,6 +1547,8 @@ extern "C" int rt_debug_set(const char *name, int value)
     else if (!strcmp(name, "small_strips")) rt::g_small_strips = value;
     else if (!strcmp(name, "intra_kernel")) rt::g_intra_kernel = value;
     else if (!strcmp(name, "fused_eval")) rt::g_fused_eval = value;
+    else if (!strcmp(name, "persistent_search")) rt::g_persistent_search = value;
+    else if (!strcmp(name, "persist_blocks")) rt::g_persist_blocks = value;
     else return RT_ERR_INVALID_ARG;
     return RT_OK;
 }

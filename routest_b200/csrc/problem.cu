@@ -224,6 +224,7 @@ int rt_problem_create(rt_engine *e, int n, int batch, rt_problem **out)
     A(dev_alloc(p, p->best, B + 1));  // + the coordinate flag of rt_problem_plan: keys and flag leave in one copy
     A(dev_alloc(p, p->done, B));
     A(dev_alloc(p, p->moves, B));
+    A(dev_alloc(p, p->ticket, 1));
     A(dev_alloc(p, p->hist, B * p->hist_cap));
     A(dev_alloc(p, p->gkeys, B * n2));
     A(dev_alloc(p, p->gorder, B * n2));
@@ -1056,6 +1057,26 @@ static int local_search_impl(rt_problem *p, int families, int max_moves, int mod
         RT_TRY(eval_moves_launch(p, families, 0, 1, p->best, false, e->stream));
         return apply_moves_launch(p, p->best, false, true, e->stream);
     };
+    // One cooperative launch runs the whole search where that form applies (search_persistent_kernel: a fused-cell
+    // problem up to ~4,600 positions); the host only looks at done[] between launches of kPersistChunk iterations.
+    if (!batched && !cached && max_moves > 0) {
+        const int kPersistChunk = 4096;
+        int issued = 0, rc = RT_OK;
+        bool all_done = false;
+        while (!all_done && issued < max_moves) {
+            const int todo = std::min(kPersistChunk, max_moves - issued);
+            rc = search_persistent_launch(p, families, todo, true, e->stream);
+            if (rc != RT_OK) break;
+            issued += todo;
+            RT_CUDA(e, cudaMemcpyAsync(done_h, p->done, p->batch * 4, cudaMemcpyDeviceToHost, e->stream));
+            RT_CUDA(e, cudaStreamSynchronize(e->stream));
+            all_done = true;
+            for (int b = 0; b < p->batch; ++b) all_done = all_done && done_h[b] != 0;
+        }
+        if (rc > 0) return rc;
+        if (rc == RT_OK) max_moves = 0;  // done: fall through to the read-back below
+        if (getenv("ROUTEST_DEBUG") && rc == RT_OK) fprintf(stderr, "[routest] local search (full): one cooperative launch\n");
+    }
     // An iteration is a fixed sequence of a dozen small launches with constant arguments: it is captured once into a
     // CUDA graph and replayed (the loop is launch-bound at small and medium sizes).  If capture is refused for any
     // reason the iterations are launched one kernel at a time instead.

@@ -65,6 +65,7 @@ struct rt_problem {
     int *feasible = nullptr;               // [batch]
     unsigned long long *best = nullptr;    // [batch] packed keys (SPEC §7)
     int *done = nullptr, *moves = nullptr; // [batch] local-search bookkeeping
+    unsigned *ticket = nullptr;            // arrival counter of the one-launch search (search_persistent_kernel)
     int *coord_flag = nullptr;             // [1] set to plan_seq by the vector kernel on a bad coordinate (rt_problem_plan)
     int plan_seq = 0;                      // rt_problem_plan calls so far: the flag needs no reset between calls
     int plan_flag_seq = 0;                 // the number the pass in flight writes into the flag
@@ -147,6 +148,8 @@ int state_refresh(rt_problem *p, cudaStream_t st, cudaEvent_t tables_wait_for = 
 int position_unit_vectors_launch(rt_problem *p, cudaStream_t st, int *bad_flag = nullptr, int bad_value = 1);
 int position_matrix_refresh(rt_problem *p, cudaStream_t st, bool vectors_ready = false);
 int state_tables_refresh(rt_problem *p, cudaStream_t st, bool with_vectors = false);
+// up to `iters` iterations of the one-move search in one cooperative launch; -1 = not applicable here (moves.cu)
+int search_persistent_launch(rt_problem *p, int families, int iters, bool improving_only, cudaStream_t st);
 int eval_moves_launch(rt_problem *p, int families, int shard_index, int shard_count, unsigned long long *best_d,
                       bool signed_keys, cudaStream_t st);
 int eval_dump_launch(rt_problem *p, int instance, int family, int *delta_d, unsigned char *feas_d, cudaStream_t st);

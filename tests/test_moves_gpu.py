@@ -634,18 +634,23 @@ def test_kernel_variants_agree_with_the_oracle(engine, fused, kernel, seed, stop
         engine.debug_set("fused_eval", 1)
 
 
-@pytest.mark.gpu
-@pytest.mark.parametrize("state_fused_max,apply_prep,small_strips", [(-1, 1, 1), (-1, 0, 1), (4096, 1, 0), (4096, 0, 0)],
-                         ids=["default", "separate-apply", "one-block-state", "round-1-chain"])
+@pytest.mark.parametrize("persistent,state_fused_max,apply_prep,small_strips",
+                         [(2, -1, 1, 1), (2, -1, 1, 0), (0, -1, 1, 1), (0, -1, 0, 1), (0, 4096, 1, 0), (0, 4096, 0, 0)],
+                         ids=["one-launch", "one-launch-32-rows", "merged-apply", "separate-apply", "one-block-state",
+                              "round-1-chain"])
 @pytest.mark.parametrize("seed,stops,veh,kw", [(21, 12, 1, {}), (22, 150, 4, dict(half_lo=7200, half_hi=20000)),
                                                 (23, 420, 40, {})])
-def test_search_launch_variants_agree_with_the_oracle(engine, state_fused_max, apply_prep, small_strips, seed, stops, veh,
-                                                      kw):
+def test_search_launch_variants_agree_with_the_oracle(engine, persistent, state_fused_max, apply_prep, small_strips, seed,
+                                                      stops, veh, kw):
     """The one-move search reaches the oracle's keys, cost and routes whichever way an iteration is cut into launches:
-    the move + route scan + per-route tables in one launch (rt_debug_set "apply_prep"; more than 32 routes leave the
-    tables to their own kernel: the 40-vehicle case), the one-block state kernel or one warp per route
-    ("state_fused_max"), short strips for small grids ("small_strips").  SPEC.md §8; no reference counterpart."""
+    the whole search as one cooperative launch (rt_debug_set "persistent_search" = 2: wherever it can run, not only
+    at the small sizes where it is the default); the move + route scan + per-route
+    tables in one launch ("apply_prep"; more than 32 routes leave the tables to their own kernel: the 40-vehicle
+    case); the one-block state kernel or one warp per route ("state_fused_max"); short strips for small grids
+    ("small_strips").  A search cut short by max_moves and then resumed ends where the uninterrupted one does.
+    SPEC.md §8; no reference counterpart."""
     inst, node0, raw = synth_vrptw(seed, stops, veh, **kw)
+    engine.debug_set("persistent_search", persistent)
     engine.debug_set("state_fused_max", state_fused_max)
     engine.debug_set("apply_prep", apply_prep)
     engine.debug_set("small_strips", small_strips)
@@ -657,7 +662,33 @@ def test_search_launch_variants_agree_with_the_oracle(engine, state_fused_max, a
             assert np.array_equal(keys[0], okeys) and cost[0] == ocost
             assert np.array_equal(pr.get_state(0)["node"], final)
             assert int(pr.eval_moves()[0]) == O.best_move(inst, final)
+            st = pr.get_state(0)
+            ref = O.route_state(inst, final)
+            for k in ("route", "B", "Z", "rload", "rdist"):
+                assert np.array_equal(st[k], ref[k]), k
+            moves2, cost2, _ = pr.local_search(full=True)                      # on to the local optimum
+            final2, okeys2, ocost2 = O.local_search(inst, final)
+            assert moves2[0] == len(okeys2) and cost2[0] == ocost2
+            assert np.array_equal(pr.get_state(0)["node"], final2)
     finally:
+        engine.debug_set("persistent_search", 1)
         engine.debug_set("state_fused_max", -1)
         engine.debug_set("apply_prep", 1)
         engine.debug_set("small_strips", 1)
+
+
+def test_one_launch_search_on_a_batch(engine):
+    """The cooperative search kernel with several instances of different route counts in one problem: each stops at
+    its own local optimum (done[] per instance), the others go on."""
+    insts = [synth_vrptw(300 + b, 100, 3 + b) for b in range(5)]
+    n = insts[0][0].n
+    engine.debug_set("persistent_search", 2)
+    try:
+        with _load(engine, insts) as pr:
+            moves, cost, keys = pr.local_search(keys_capacity=4 * n, full=True)
+            for b, (inst, node, _) in enumerate(insts):
+                final, okeys, ocost = O.local_search(inst, node, threads=O.num_threads())
+                assert moves[b] == len(okeys) and np.array_equal(keys[b], okeys) and cost[b] == ocost
+                assert np.array_equal(pr.get_state(b)["node"], final)
+    finally:
+        engine.debug_set("persistent_search", 1)
