@@ -281,6 +281,8 @@ class Ctx:
         self.local = int(os.environ.get("LOCAL_RANK", "0"))
         torch.cuda.set_device(self.local)
         if world > 1:
+            if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+                os.environ["NCCL_DEBUG"] = "WARN"   # its banner goes to stdout, in front of the one JSON line
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local),
                                     timeout=datetime.timedelta(seconds=300))
         from routest_b200 import Engine
@@ -447,7 +449,12 @@ def run_engine(args, rank, world):
     eng.debug_set("fused_eval", 1)
     replay()
     torch.cuda.synchronize()
-    assert int(keys.item()) == key_wtr, "the two forms of the pass disagree"
+    # (the two forms cut the shards differently — the triangle p < q against rows of the stored matrix — so on N > 1
+    # ranks it is the minimum over the ranks that must agree, not each rank's own key)
+    both = torch.tensor([int(keys.item()), key_wtr], dtype=torch.int64, device="cuda")
+    if world > 1:
+        cx.dist.all_reduce(both, op=cx.dist.ReduceOp.MIN)
+    assert int(both[0].item()) == int(both[1].item()) == key_device, "the two forms of the pass disagree"
     # a longer loop of the same pass so that the clock sampler sees the GPU under this very load
     t_load = time.perf_counter()
     while time.perf_counter() - t_load < 0.6:
