@@ -6,7 +6,9 @@
 // kernel itself uses (geometry.cuh), so a pass moves O(n) bytes.  A caller-supplied matrix (road distances, possibly
 // directional) is read in ROUTE ORDER instead, G[p][q] = M[node p][node q] (state.cu): a thread that owns column q
 // and walks down the rows p touches G[p-1..p+1][q-1..q+1], each warp-wide load one contiguous 256-byte run.
-//   * eval_inter_fused_kernel / eval_inter_kernel — candidates between two different routes (relocate, swap): delta
+//   * eval_inter_fused_kernel / eval_inter_kernel — candidates between two different routes (relocate, swap).  The
+//     fused form scores the triangle p < q only: relocate(p -> q), relocate(q -> p) and swap(p, q) come from one
+//     window of cells, so each cell is rebuilt once per unordered pair.  Delta
 //     AND the full feasibility test (capacity, distance limit, time windows) for every pair, straight line — in a
 //     realistic state a large share of the candidates beats the best feasible delta while being infeasible, so pruning
 //     on the delta leaves almost every warp with some lane in the slow path.  What IS skipped is the best-key update:
@@ -14,6 +16,8 @@
 //   * eval_intra_kernel — candidates inside one route (2-opt, relocate, swap): one thread per anchor position sweeps
 //     its route keeping two segment summaries (a, b, L) — forward and reversed — so every candidate is O(1) and exact
 //     for time windows.  eval_intra_warp_kernel: the same summaries as two warp scans, one warp per anchor.
+//   * search_persistent_kernel — the whole one-move search (SPEC.md §8) of small instances as ONE cooperative launch:
+//     the device functions above and those of state_device.cuh in a loop, grid-wide barriers between the phases.
 // Each thread keeps the minimum packed key of its feasible candidates; warp shuffles and one shared-memory step
 // reduce it to one 64-bit atomicMin per block.  The minimum of packed keys is order independent, so the chosen
 // move does not depend on the thread, block or GPU partition.

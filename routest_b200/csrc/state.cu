@@ -7,7 +7,11 @@
 // the current solution.  When the matrix is the great-circle matrix of the problem's coordinates, G is produced by
 // the matrix kernel itself running on the position-ordered unit vectors (same cell function, so the same bits, at
 // the HBM write roofline); a caller-supplied matrix is permuted instead.  Every later access of the move kernels
-// — a row of G per moved stop, consecutive columns per insertion point — is then contiguous.
+// — a row of G per moved stop, consecutive columns per insertion point — is then contiguous.  (Where the move kernels
+// rebuild their cells from the unit vectors — eval_without_matrix — no G is written at all.)
+//
+// The device code lives in state_device.cuh (shared with the one-launch search of moves.cu); this file holds the
+// launches: state_refresh / state_tables_refresh, apply_moves_launch.
 #define RT_STATE_KERNELS
 #include "state_device.cuh"
 
