@@ -178,7 +178,9 @@ int rt_problem_apply_moves(rt_problem *p, const uint64_t *keys);
 /* Best-improvement local search to a local optimum or max_moves applied moves per instance (SPEC.md §8).
  * moves_out [batch], cost_out [batch]; keys_out [batch][keys_capacity] receives the applied keys (may be NULL).
  * Above ~4,600 positions per instance the search keeps a per-route-pair table and re-scores only what a move touched;
- * below that it re-scores everything each iteration, which is faster there.  Same keys, same routes either way. */
+ * below that it re-scores everything each iteration, which is faster there (an iteration is then two dependent
+ * launches replayed from a CUDA graph; up to 256 positions the whole search is ONE cooperative launch with grid-wide
+ * barriers between its phases).  Same keys, same routes either way. */
 int rt_problem_local_search(rt_problem *p, int families, int max_moves, int32_t *moves_out, int64_t *cost_out,
                             uint64_t *keys_out, int keys_capacity);
 /* The same search with every iteration re-scoring the whole neighbourhood on the route-order matrix, i.e. without
