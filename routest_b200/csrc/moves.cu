@@ -417,17 +417,17 @@ __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, 
     // relocate(p -> between q and q+1)
     const int ins = fadd(fadd(c_cur.x, c_rt.x), -c.Hq.z);
     const int d_rel = fadd(Hp.x, ins);
-    const int tu = max(p1.x, fadd(c.dep_q, c_cur.y));
+    const int tu = __viaddmax_s32(c.dep_q, c_cur.y, p1.x);       // max(dep_q + t, ready_p): one VIADDMNMX
     // relocate(q -> between p and p+1): the same with the roles exchanged, cells (p, q) and (p+1, q)
     const int mins = fadd(fadd(c_cur.x, c_dn.x), -Hp.z);
     const int d_mir = fadd(c.Hq.x, mins);
-    const int mtu = max(c.qB.x, fadd(dep_p, c_cur.y));
+    const int mtu = __viaddmax_s32(dep_p, c_cur.y, c.qB.x);
     // swap(p, q): pu -> v -> nu in route[p], pw -> u -> nw in route[q]
     const int d1 = fadd(fadd(c_up.x, c_dn.x), -Hp.y);
     const int d2 = fadd(fadd(c_lf.x, c_rt.x), -c.Hq.y);
     const int d_swap = fadd(d1, d2);
-    const int tv = max(c.qB.x, fadd(p2.y, c_up.y));
-    const int tw = max(p1.x, fadd(c.depprev_q, c_lf.y));
+    const int tv = __viaddmax_s32(p2.y, c_up.y, c.qB.x);
+    const int tw = __viaddmax_s32(c.depprev_q, c_lf.y, p1.x);
     const int dd = fadd(c.qB.w, -p1.w);
     bool ok_rel, ok_mir, ok_swap;
     if (DUMP) {   // explicit validity: the dump reports which pairs are candidates at all (the slots hold plain data)
@@ -484,6 +484,8 @@ __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, 
     }
 }
 
+__device__ __forceinline__ int wrap_add(int a, unsigned b) { return static_cast<int>(static_cast<unsigned>(a) + b); }
+
 // One shared-memory slot per row of the strip (+2): slot i holds the unit vector of position p0 - 1 + i and, for
 // i < rows, the three records of strip row i.  One array and explicit 32-bit shared addresses: with three separate
 // arrays indexed by the (uniform) loop counter the compiler rebuilt every array's shared-window address in the uniform
@@ -491,6 +493,8 @@ __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, 
 struct __align__(16) RowSlot {
     int4 H, P1, P2;
     double vx, vy, vz;
+    // the last 16 bytes of slot i: vz of its vector, and dep / reldem of the row TWO slots back — the row loop reads the
+    // vector two slots ahead of the records, so one LDS.128 fetches both
     int dep;        // B[p] + service[p]: what an insertion after p starts from
     int reldem;     // demand of p for relocate(p -> q), kNever where p cannot be moved (see score_pair_tri)
 };
@@ -571,13 +575,29 @@ __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int gri
                 sl.reldem = (cust && (rC.w & 2) && (a.families & 2)) ? sl.P1.w : kNever;
                 if (!cust) sl.P1.y = -1;
                 sl.H.w &= 0x7FFF;
+                // the cells of the row loop carry kCellBias (cell_i32_fast_biased): every sum they enter has a constant
+                // of the row or of the column in it, which takes the bias out again (wrap-around arithmetic, exact)
+                sl.H.y = wrap_add(sl.H.y, 2u * kCellBias);    // d1   = c_up.x + c_dn.x - H.y
+                sl.H.z = wrap_add(sl.H.z, 2u * kCellBias);    // mins = c_cur.x + c_dn.x - H.z
+                sl.P1.z = wrap_add(sl.P1.z, 0u - kCellBias);  // arrival = t + service + c_rt.y
+                sl.P2.y = wrap_add(sl.P2.y, 0u - kCellBias);  // tv   = max(P2.y + c_up.y, ready)
+                sl.dep = wrap_add(sl.dep, 0u - kCellBias);    // mtu  = max(dep + c_cur.y, ready)
             }
         }
         const int pv = min(max(p0 - 1 + tid, 0), a.pstride - 1);
         sl.vx = PX[pv];
         sl.vy = PX[a.pstride + pv];
         sl.vz = PX[2 * static_cast<size_t>(a.pstride) + pv];
-        slots[tid] = sl;
+        slots[tid].H = sl.H;
+        slots[tid].P1 = sl.P1;
+        slots[tid].P2 = sl.P2;
+        slots[tid].vx = sl.vx;
+        slots[tid].vy = sl.vy;
+        slots[tid].vz = sl.vz;
+        if (tid < rows) {   // (slots 0 and 1 keep no row's dep / reldem: nothing reads them)
+            slots[tid + 2].dep = sl.dep;
+            slots[tid + 2].reldem = sl.reldem;
+        }
     }
     int4 Hq = make_int4(0, 0, 0, -1), qB = make_int4(0, 0, 0, 0);
     int dep_q = 0, zn_q = 0, depprev_q = 0, capsl_q = 0, distsl_q = 0;
@@ -599,6 +619,13 @@ __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int gri
 
     const int q_route = Hq.w & 0x7FFF;
     const bool q_cust = q_in && ((Hq.w >> 30) & 1);
+    if (!DUMP) {  // the column's share of taking kCellBias out of the sums (see the slots)
+        Hq.y = wrap_add(Hq.y, 2u * kCellBias);        // d2  = c_lf.x + c_rt.x - Hq.y
+        Hq.z = wrap_add(Hq.z, 2u * kCellBias);        // ins = c_cur.x + c_rt.x - Hq.z
+        dep_q = wrap_add(dep_q, 0u - kCellBias);      // tu  = max(dep_q + c_cur.y, ready)
+        depprev_q = wrap_add(depprev_q, 0u - kCellBias);
+        qB.z = wrap_add(qB.z, 0u - kCellBias);        // arrival = t + service + c_dn.y
+    }
     const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
     const bool swap_q = q_cust && (a.families & 4);
     const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q,
@@ -623,29 +650,35 @@ __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int gri
     unsigned sa = static_cast<unsigned>(__cvta_generic_to_shared(slots)) + (threadIdx.x >> 10);
     const float fd = a.fd, ft = a.ft;
     const int lim_hi = a.lim_hi;
-    auto cell_slot = [&](unsigned addr) {  // cell(position of that slot, q)
-        const double ax = lds64(addr + 48), ay = lds64(addr + 56), az = lds64(addr + 64);
+    auto cell_slot = [&](unsigned addr, int &dep_back2, int &reldem_back2) {  // cell(position of that slot, q)
+        double ax, ay, az;
+        asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(ax), "=d"(ay) : "r"(addr + 48));
+        asm volatile("{ .reg .b64 t; ld.shared.v2.b64 {%0, t}, [%3]; mov.b64 {%1, %2}, t; }"
+                     : "=d"(az), "=r"(dep_back2), "=r"(reldem_back2)
+                     : "r"(addr + 64));
         if (FAST) {
             const double dx = ax - bx, dy = ay - by, dz = az - bz;
-            return cell_i32_fast(fma(dx, dx, fma(dy, dy, dz * dz)), fd, ft);
+            const double s2 = fma(dx, dx, fma(dy, dy, dz * dz));
+            return DUMP ? cell_i32_fast(s2, fd, ft) : cell_i32_fast_biased(s2, fd, ft);
         }
-        return cell_from_vectors(ax, ay, az, bx, by, bz, fd, ft, lim_hi);
+        const int2 c = cell_from_vectors(ax, ay, az, bx, by, bz, fd, ft, lim_hi);
+        return DUMP ? c : make_int2(wrap_add(c.x, kCellBias), wrap_add(c.y, kCellBias));
     };
-    int2 c_up = cell_slot(sa), c_cur = cell_slot(sa + 80);
+    int unused0, unused1;
+    int2 c_up = cell_slot(sa, unused0, unused1), c_cur = cell_slot(sa + 80, unused0, unused1);
     const unsigned full = 0xffffffffu;
     auto run_rows = [&](auto diag_tag) {
         constexpr bool DIAG = decltype(diag_tag)::value;
 #pragma unroll 3
         for (int rr = 0; rr < rows; ++rr, sa += 80) {
             const int p = p0 + rr;
-            const int2 c_dn = cell_slot(sa + 160);
+            int dep_p, reldem_p;
+            const int2 c_dn = cell_slot(sa + 160, dep_p, reldem_p);
             const int4 Hp = lds128(sa);
             // every row: a separator is never moved but is an insertion point of the mirrored relocate
             const int2 c_lf = make_int2(__shfl_up_sync(full, c_cur.x, 1), __shfl_up_sync(full, c_cur.y, 1));
             const int2 c_rt = make_int2(__shfl_down_sync(full, c_cur.x, 1), __shfl_down_sync(full, c_cur.y, 1));
             const int4 p1 = lds128(sa + 16), p2 = lds128(sa + 32);
-            int dep_p, reldem_p;
-            asm volatile("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(dep_p), "=r"(reldem_p) : "r"(sa + 72));
             if (TABLE && (Hp.w & 0x7FFF) != cur_ra) {
                 flush();
                 cur_ra = Hp.w & 0x7FFF;
