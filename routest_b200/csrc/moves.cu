@@ -155,6 +155,7 @@ struct ColQ {
     int capsl_rel;   // capacity slack of q's route for relocate(p -> q); below any demand where q takes no insertion
     int qdem_mir;    // demand of q for relocate(q -> p); above any slack where q cannot be moved
     int qdue_swap;   // due time of q for swap; -1 where q cannot be swapped
+    int ncapsl_q;    // -capsl_q: swap's second capacity test as dd >= -capsl_q, no negation per pair
 };
 
 // relocate(p -> between q and q+1) and swap(p, q) for one customer row p against column q: delta AND feasibility,
@@ -289,7 +290,7 @@ __global__ void __launch_bounds__(kInterThreads, ASYM ? 6 : 9) eval_inter_kernel
     const bool q_cust = q_in && ((Hq.w >> 30) & 1);
     const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
     const bool swap_q = q_cust && (a.families & 4);
-    const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q, 0, 0, 0};
+    const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q, 0, 0, 0, 0};
     const bool swap_tile = (a.families & 4) && p0 < q0 + kInterThreads - 1;  // some pair of the tile has p < q
 
     int best_d = INT_MAX, thr = INT_MAX;
@@ -403,7 +404,9 @@ __device__ __forceinline__ int2 cell_from_vectors(double ax, double ay, double a
 // same variables).
 constexpr int kNever = 1 << 30;  // a demand no capacity slack reaches (slacks are clamped to 2^30, demands to 2^28)
 
-template <int MODE, bool DIAG>
+// NOLIM: no instance of the launch has a distance limit (every distance slack sits at its clamp 2^30, above any sum
+// of three cells), so the four tests against the slacks are compiled out.
+template <int MODE, bool DIAG, bool NOLIM>
 __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, const int4 &Hp, const int4 &p1, const int4 &p2,
                                                int dep_p, int reldem_p, const ColQ &c, bool q_rem_ok, bool q_cust, int2 c_up,
                                                int2 c_rt, int2 c_cur, int2 c_lf, int2 c_dn, int &best_d, unsigned &best_i,
@@ -459,10 +462,15 @@ __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, 
     // that cannot be removed, the demand kNever for relocate; a column that takes no insertion / cannot be moved /
     // cannot be swapped carries capsl_rel / qdem_mir / qdue_swap to the same effect; the closing depot's row has
     // capacity slack -1.  So every test below is one the candidate needs anyway.
-    ok_rel = pair && reldem_p <= c.capsl_rel && ins <= c.distsl_q && tu <= p1.y && fadd(fadd(tu, p1.z), c_rt.y) <= c.zn_q;
-    ok_mir = pair && c.qdem_mir <= p2.z && mins <= p2.w && mtu <= c.qB.y && fadd(fadd(mtu, c.qB.z), c_dn.y) <= p2.x;
-    ok_swap = pair && dd <= p2.z && -dd <= c.capsl_q && d1 <= p2.w && d2 <= c.distsl_q && tv <= c.qdue_swap &&
-              fadd(fadd(tv, c.qB.z), c_dn.y) <= p2.x && tw <= p1.y && fadd(fadd(tw, p1.z), c_rt.y) <= c.zn_q;
+    ok_rel = pair && reldem_p <= c.capsl_rel && (NOLIM || ins <= c.distsl_q) && tu <= p1.y &&
+             fadd(fadd(tu, p1.z), c_rt.y) <= c.zn_q;
+    ok_mir = pair && c.qdem_mir <= p2.z && (NOLIM || mins <= p2.w) && mtu <= c.qB.y &&
+             fadd(fadd(mtu, c.qB.z), c_dn.y) <= p2.x;
+    // (bitwise ands: with && the compiler turns the second half of this chain into a divergent branch, which a warp
+    // almost never takes as a whole)
+    ok_swap = pair & (dd <= p2.z) & (dd >= c.ncapsl_q) & (NOLIM || ((d1 <= p2.w) & (d2 <= c.distsl_q))) &
+              (tv <= c.qdue_swap) & (fadd(fadd(tv, c.qB.z), c_dn.y) <= p2.x) & (tw <= p1.y) &
+              (fadd(fadd(tw, p1.z), c_rt.y) <= c.zn_q);
     const bool hit_rel = ok_rel && d_rel <= thr, hit_swap = ok_swap && d_swap <= thr, hit_mir = ok_mir && d_mir <= mthr;
     if (__any_sync(0xffffffffu, hit_rel || hit_swap || hit_mir)) {  // rare
         auto take = [](int d, unsigned idx, int &bd, unsigned &bi) {
@@ -518,10 +526,11 @@ __device__ __forceinline__ double lds64(unsigned addr)
 // straight-line range of the cell function (any metro-sized instance), so the per-cell range test is compiled out.
 // (The body is a device function of the block's place in the grid: the persistent search kernel runs the same tiles
 // from a loop.)
-template <int MODE, bool FAST>
+// FORM: 0 = any coordinates, 1 = FAST, 2 = FAST and no instance has a distance limit (score_pair_tri's NOLIM).
+template <int MODE, int FORM>
 __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int grid_x, int grid_y, int grid_z)
 {
-    constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
+    constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable, FAST = FORM >= 1, NOLIM = FORM == 2 && !DUMP;
     __shared__ RowSlot slots[kMaxStripRows + 2];
     const int kStripRows = a.strip_rows;
 
@@ -629,7 +638,8 @@ __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int gri
     const bool rel_q = q_in && (a.families & 2) && q <= P - 2;
     const bool swap_q = q_cust && (a.families & 4);
     const ColQ col{Hq, qB, dep_q, zn_q, depprev_q, capsl_q, distsl_q, q, q_route, rel_q, swap_q,
-                   rel_q ? capsl_q : -1, (q_cust && q_rem_ok && (a.families & 2)) ? qB.w : kNever, swap_q ? qB.y : -1};
+                   rel_q ? capsl_q : -1, (q_cust && q_rem_ok && (a.families & 2)) ? qB.w : kNever, swap_q ? qB.y : -1,
+                   -capsl_q};
 
     int best_d = INT_MAX, thr = INT_MAX, tb_d = INT_MAX, tb_thr = INT_MAX;   // tb_*: table mode's mirrored-relocate entry
     unsigned best_i = 0xFFFFFFFFu, tb_i = 0xFFFFFFFFu;
@@ -684,10 +694,10 @@ __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int gri
                 cur_ra = Hp.w & 0x7FFF;
             }
             if (TABLE)
-                score_pair_tri<MODE, DIAG>(a, P, p, Hp, p1, p2, dep_p, reldem_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf,
+                score_pair_tri<MODE, DIAG, NOLIM>(a, P, p, Hp, p1, p2, dep_p, reldem_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf,
                                            c_dn, best_d, best_i, thr, tb_d, tb_i, tb_thr);
             else
-                score_pair_tri<MODE, DIAG>(a, P, p, Hp, p1, p2, dep_p, reldem_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf,
+                score_pair_tri<MODE, DIAG, NOLIM>(a, P, p, Hp, p1, p2, dep_p, reldem_p, col, q_rem_ok, q_cust, c_up, c_rt, c_cur, c_lf,
                                            c_dn, best_d, best_i, thr, best_d, best_i, thr);
             c_up = c_cur;
             c_cur = c_dn;
@@ -707,10 +717,10 @@ __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int gri
     }
 }
 
-template <int MODE, bool FAST>
+template <int MODE, int FORM>
 __global__ void __launch_bounds__(kInterThreads, 8) eval_inter_fused_kernel(const EvalArgs a)
 {
-    eval_inter_fused_tile<MODE, FAST>(a, blockIdx.x, blockIdx.y, blockIdx.z);
+    eval_inter_fused_tile<MODE, FORM>(a, blockIdx.x, blockIdx.y, blockIdx.z);
 }
 
 // ---- same-route candidates ------------------------------------------------------------------------------------
@@ -1253,8 +1263,10 @@ int launch_inter(rt_problem *p, EvalArgs &a, int pmax, int shard_rows, int batch
     a.strip_rows = strip_rows > 0 ? strip_rows : pick_strip_rows(pmax, shard_rows, batch, !p->symmetric, cols);
     dim3 grid((pmax + cols - 1) / cols, (shard_rows + a.strip_rows - 1) / a.strip_rows, batch);
     if (fused) grid = fused_tile_grid(a, pmax, batch);
-    if (fused && all_pairs_in_fast_range(p, a)) eval_inter_fused_kernel<MODE, true><<<grid, kInterThreads, 0, st>>>(a);
-    else if (fused) eval_inter_fused_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
+    const bool fast = fused && all_pairs_in_fast_range(p, a);
+    if (fast && p->dist_unlimited && MODE != kDump) eval_inter_fused_kernel<MODE, 2><<<grid, kInterThreads, 0, st>>>(a);
+    else if (fast) eval_inter_fused_kernel<MODE, 1><<<grid, kInterThreads, 0, st>>>(a);
+    else if (fused) eval_inter_fused_kernel<MODE, 0><<<grid, kInterThreads, 0, st>>>(a);
     else if (p->symmetric) eval_inter_kernel<MODE, false><<<grid, kInterThreads, 0, st>>>(a);
     else eval_inter_kernel<MODE, true><<<grid, kInterThreads, 0, st>>>(a);
     RT_CUDA(p->e, cudaGetLastError());
@@ -1351,7 +1363,7 @@ __global__ void __launch_bounds__(kPersistThreads, 4) search_persistent_kernel(c
             const int b = v / per_instance, w = v - b * per_instance;
             if (!ap.done[b]) {  // uniform over the block
                 if (w < pa.intra_gx) eval_intra_warp_block<kBest, true>(ea, w, b);
-                else eval_inter_fused_tile<kBest, FAST>(ea, (w - pa.intra_gx) % pa.inter_gx, (w - pa.intra_gx) / pa.inter_gx, b);
+                else eval_inter_fused_tile<kBest, FAST ? 1 : 0>(ea, (w - pa.intra_gx) % pa.inter_gx, (w - pa.intra_gx) / pa.inter_gx, b);
             }
             __syncthreads();  // the shared memory of a tile is reused by the next
         }

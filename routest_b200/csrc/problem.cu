@@ -315,6 +315,7 @@ int rt_problem_set_stops(rt_problem *p, const int32_t *stops, const int32_t *cap
     RT_CUDA(e, cudaMemcpyAsync(p->stops, stops, total * sizeof(int4), cudaMemcpyHostToDevice, e->stream));
     RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, p->batch * sizeof(int), cudaMemcpyHostToDevice, e->stream));
     RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, p->batch * sizeof(long long), cudaMemcpyHostToDevice, e->stream));
+    p->dist_unlimited = std::all_of(max_dist, max_dist + p->batch, [](int64_t v) { return v >= (1LL << 61); });
     RT_CUDA(e, cudaStreamSynchronize(e->stream));
     p->has_stops = true;
     return RT_OK;
@@ -666,6 +667,7 @@ static int plan_enqueue(rt_problem *p, const double *lat, const double *lon, con
     RT_CUDA(e, cudaMemcpyAsync(p->stops, stops, B * N * 16, cudaMemcpyHostToDevice, cs));
     RT_CUDA(e, cudaMemcpyAsync(p->cap, cap, B * 4, cudaMemcpyHostToDevice, cs));
     RT_CUDA(e, cudaMemcpyAsync(p->max_dist, max_dist, B * 8, cudaMemcpyHostToDevice, cs));
+    p->dist_unlimited = std::all_of(max_dist, max_dist + B, [](int64_t v) { return v >= (1LL << 61); });
     RT_CUDA(e, cudaEventRecord(p->ev_in[1], cs));
     p->plan_t[1] = dbg ? now() : 0;
     // The unit vectors go out first (the kernel itself falls back to the depot for a node id it cannot index), so the

@@ -65,6 +65,7 @@ struct rt_problem {
     int *feasible = nullptr;               // [batch]
     unsigned long long *best = nullptr;    // [batch] packed keys (SPEC §7)
     int *done = nullptr, *moves = nullptr; // [batch] local-search bookkeeping
+    bool dist_unlimited = false;           // every instance's max_dist as last uploaded from the host is >= 2^61
     unsigned *ticket = nullptr;            // arrival counter of the one-launch search (search_persistent_kernel)
     int *coord_flag = nullptr;             // [1] set to plan_seq by the vector kernel on a bad coordinate (rt_problem_plan)
     int plan_seq = 0;                      // rt_problem_plan calls so far: the flag needs no reset between calls

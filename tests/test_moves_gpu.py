@@ -692,3 +692,28 @@ def test_one_launch_search_on_a_batch(engine):
                 assert np.array_equal(pr.get_state(b)["node"], final)
     finally:
         engine.debug_set("persistent_search", 1)
+
+
+@pytest.mark.parametrize("seed,stops,veh", [(31, 80, 6), (32, 300, 12)])
+def test_binding_distance_limit_through_search(engine, seed, stops, veh):
+    """A distance limit that binds (the median route length: half of the routes are already over it and accept
+    nothing, the others have little room): best move, one-move search and batched
+    iterations against the oracle.  Without a limit the tile kernel runs a form with the slack tests compiled out
+    (every other test of this file); here they decide which candidates are feasible."""
+    inst, node, raw = synth_vrptw(seed, stops, veh)
+    rdist = O.route_state(inst, node)["rdist"]
+    lim = O.Instance(inst.D, inst.T, inst.stops, inst.cap, max_dist=int(np.median(rdist)) + 200)
+    lim_key = O.best_move(lim, node)
+    assert lim_key != O.best_move(inst, node)   # the limit decides the very first move, or this test tests nothing
+    with _load(engine, [(lim, node, raw)]) as pr:
+        assert int(pr.eval_moves()[0]) == lim_key
+        parts = [int(pr.eval_moves(shard=(i, 3))[0]) for i in range(3)]
+        assert min(parts) == lim_key
+        moves, cost, keys = pr.local_search(max_moves=30, keys_capacity=64, full=True)
+        final, okeys, ocost = O.local_search(lim, node, max_moves=30)
+        assert np.array_equal(keys[0], okeys) and cost[0] == ocost
+        assert np.array_equal(pr.get_state(0)["node"], final)
+    with _load(engine, [(lim, node, raw)]) as pr:
+        bmoves, bcost, bkeys = pr.local_search(max_moves=4, keys_capacity=1024, batched=True)
+        bfinal, obkeys, _, obcost = O.local_search_batched(lim, node, max_iters=4)
+        assert np.array_equal(bkeys[0], obkeys) and bcost[0] == obcost
