@@ -414,9 +414,11 @@ __device__ __forceinline__ void score_pair_tri(const EvalArgs &a, int P, int p, 
 {
     constexpr bool DUMP = MODE == kDump, TABLE = MODE == kTable;
     const int q = c.q;
-    // DIAG: the tile touches the diagonal, so p < q has to be tested per pair; everywhere else it holds for the tile
+    // DIAG: the tile lies near the diagonal — some of its columns may belong to the route of one of its rows, or not
+    // lie to the right of them — so "another route" and p < q are tested per pair; everywhere else both hold for the
+    // whole tile (routes are runs of consecutive positions).
     // (outside the dump the slot's H.w is the bare route id: the flags beside it moved into the data, see below)
-    const bool pair = (DUMP ? (Hp.w & 0x7FFF) : Hp.w) != c.q_route && (!DIAG || p < q);
+    const bool pair = !DIAG || ((DUMP ? (Hp.w & 0x7FFF) : Hp.w) != c.q_route && p < q);
     // relocate(p -> between q and q+1)
     const int ins = fadd(fadd(c_cur.x, c_rt.x), -c.Hq.z);
     const int d_rel = fadd(Hp.x, ins);
@@ -564,6 +566,15 @@ __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int gri
     const bool owner = lane >= 1 && lane <= 30;
     const bool q_in = owner && q < P;
     const int rows = min(kStripRows, p_hi - p0);
+    // first position after the route of the strip's last row (what decides the form of the row loop at the bottom;
+    // two dependent loads, issued here so that they are back by then)
+    int route_end;
+    {
+        const int p_last = min(p0 + rows, P) - 1;
+        const int r_last = a.H[po + p_last].w & 0x7FFF;
+        route_end = r_last < P - a.n ? a.rstart[static_cast<size_t>(b) * (a.rstride + 1) + r_last + 1] : P;
+        route_end = max(route_end, p0 + rows);   // (never below the strip itself, whatever the arrays hold)
+    }
     if (tid < rows + 2) {
         RowSlot sl;
         sl.H = sl.P1 = sl.P2 = make_int4(0, 0, 0, 0);
@@ -679,7 +690,7 @@ __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int gri
     const unsigned full = 0xffffffffu;
     auto run_rows = [&](auto diag_tag) {
         constexpr bool DIAG = decltype(diag_tag)::value;
-#pragma unroll 3
+#pragma unroll(TABLE ? 3 : 6)  // the register window rotates with period 3; the table form is out of registers at 6
         for (int rr = 0; rr < rows; ++rr, sa += 80) {
             const int p = p0 + rr;
             int dep_p, reldem_p;
@@ -703,8 +714,9 @@ __device__ __forceinline__ void eval_inter_fused_tile(const EvalArgs &a, int gri
             c_cur = c_dn;
         }
     };
-    // p < q holds for every pair of a tile whose first column lies beyond the strip's last row
-    if (q0 > p0 + rows - 1) run_rows(std::false_type{});
+    // Every pair of a tile whose first column lies beyond the ROUTE of the strip's last row has p < q and two different
+    // routes: route_end is the first position after that route (loaded at the top of the kernel)
+    if (q0 >= route_end) run_rows(std::false_type{});
     else run_rows(std::true_type{});
     if (TABLE) {
         flush();
