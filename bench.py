@@ -746,20 +746,29 @@ def block_solve(cx):
     replicas: shard tables, ONE int64 MIN all-reduce per iteration, the same batch applied everywhere."""
     torch, eng, rank, world = cx.torch, cx.eng, cx.rank, cx.world
     from routest_b200.dist import DistributedSearch, PeerExchangeUnavailable
-    t0 = time.perf_counter()
-    pr, w = build_problem(eng, SEED_5K, 5000, 50)
-    t_build = time.perf_counter() - t0
-    cost0 = int(pr.get_state(0)["cost"])
-    try:     # the table travels through peer memory where CUDA IPC works on every rank, through NCCL otherwise
-        search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True,
-                                   exchange="peer" if world > 1 else "nccl")   # one rank: nothing to exchange
-    except PeerExchangeUnavailable:
-        search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True, exchange="nccl")
-    cx.barrier()
-    t0 = time.perf_counter()
-    moves, cost = search.run()
-    torch.cuda.synchronize()
-    dt = cx.max_over_ranks(time.perf_counter() - t0)
+    # Two whole solves (each on a freshly built problem, each with its own graph capture inside the timed region): one
+    # solve is a long row of host-paced chunks on N processes, and a single late rank shows up in full; the faster of the two is
+    # reported, both are kept beside it.
+    runs = []
+    pr = None
+    for _ in range(2):
+        if pr is not None:
+            pr.close()
+        t0 = time.perf_counter()
+        pr, w = build_problem(eng, SEED_5K, 5000, 50)
+        t_build = time.perf_counter() - t0
+        cost0 = int(pr.get_state(0)["cost"])
+        try:     # the table travels through peer memory where CUDA IPC works on every rank, through NCCL otherwise
+            search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True,
+                                       exchange="peer" if world > 1 else "nccl")   # one rank: nothing to exchange
+        except PeerExchangeUnavailable:
+            search = DistributedSearch(pr, 1, device="cuda", check_every=8, batched=True, exchange="nccl")
+        cx.barrier()
+        t0 = time.perf_counter()
+        moves, cost = search.run()
+        torch.cuda.synchronize()
+        runs.append(cx.max_over_ranks(time.perf_counter() - t0))
+    dt = min(runs)
     routes = pr.get_routes()[0]
     sig = zlib.crc32(json.dumps(routes).encode())
     agree = True
@@ -770,7 +779,7 @@ def block_solve(cx):
         cx.dist.all_reduce(hi, op=cx.dist.ReduceOp.MAX)
         agree = bool((lo == hi).all().item())
     pr.close()
-    res = {"local_search_ms": dt * 1e3, "moves": int(moves[0]), "routes": len(routes), "cost_greedy": cost0,
+    res = {"local_search_ms": dt * 1e3, "local_search_ms_runs": [r * 1e3 for r in runs], "moves": int(moves[0]), "routes": len(routes), "cost_greedy": cost0,
            "cost_local_optimum": int(cost[0]), "n_gpus": world, "ranks_agree": agree, "routes_crc32": sig,
            "graph_replayed": search._graph is not None, "setup_incl_greedy_ms": t_build * 1e3,
            "exchange": search.exchange,
