@@ -41,3 +41,18 @@ def test_create_fails_loudly_without_a_gpu():
     with pytest.raises(EngineError) as ei:
         Engine(0)
     assert ei.value.code == N.RT_ERR_NO_DEVICE and "no CPU fallback" in str(ei.value)
+
+
+def test_every_debug_knob_is_documented_in_the_header():
+    """rt_debug_set takes its knobs by name; every name the library accepts (csrc/moves.cu) is described in the
+    comment above its declaration in include/routest.h, and the header describes none that does not exist."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = open(os.path.join(root, "routest_b200", "csrc", "moves.cu")).read()
+    body = src[src.index('extern "C" int rt_debug_set'):]
+    accepted = set(re.findall(r'strcmp\(name, "([a-z_]+)"\)', body))
+    assert {"strip_rows", "fused_eval", "persistent_search", "apply_prep"} <= accepted
+    hdr = open(os.path.join(root, "include", "routest.h")).read()
+    doc = hdr[hdr.index("/* Test and measurement knobs"):hdr.index("int rt_debug_set")]
+    documented = set(re.findall(r'"([a-z_]+)"', doc))
+    assert accepted == documented, (sorted(accepted - documented), sorted(documented - accepted))
