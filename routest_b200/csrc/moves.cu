@@ -402,7 +402,7 @@ __device__ __forceinline__ int2 cell_from_vectors(double ax, double ay, double a
 // once per unordered pair instead of twice.  best / thr: the direct candidates; mbest / mthr: in table mode the
 // mirrored relocate belongs to the entry (route q, route p) and keeps its own running best (otherwise they alias the
 // same variables).
-constexpr int kNever = 1 << 30;  // a demand no capacity slack reaches (slacks are clamped to 2^30, demands to 2^28)
+constexpr int kNever = INT_MAX;  // a demand no capacity slack reaches (slacks are clamped to 2^30; only ever compared)
 
 // NOLIM: no instance of the launch has a distance limit (every distance slack sits at its clamp 2^30, above any sum
 // of three cells), so the four tests against the slacks are compiled out.

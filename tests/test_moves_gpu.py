@@ -717,3 +717,22 @@ def test_binding_distance_limit_through_search(engine, seed, stops, veh):
         bmoves, bcost, bkeys = pr.local_search(max_moves=4, keys_capacity=1024, batched=True)
         bfinal, obkeys, _, obcost = O.local_search_batched(lim, node, max_iters=4)
         assert np.array_equal(bkeys[0], obkeys) and bcost[0] == obcost
+
+
+@pytest.mark.parametrize("seed,stops,veh,kw", [(41, 60, 5, dict(half_lo=300, half_hi=900)), (42, 150, 4, {})])
+def test_unlimited_capacity_meets_the_validity_sentinels(engine, seed, stops, veh, kw):
+    """Capacity 2^31 - 1: every capacity slack sits at its clamp (2^30), the largest value the tile kernel ever
+    compares a demand with — the stand-in demand of a stop that may not be moved has to stay above it.  Tight windows
+    make many stops immovable (removing them would break their route's schedule)."""
+    inst, node, raw = synth_vrptw(seed, stops, veh, **kw)
+    big = O.Instance(inst.D, inst.T, inst.stops, 2 ** 31 - 1, inst.max_dist)
+    with _load(engine, [(big, node, raw)]) as pr:
+        assert int(pr.eval_moves()[0]) == O.best_move(big, node)
+        moves, cost, keys = pr.local_search(max_moves=60, keys_capacity=64, full=True)
+        final, okeys, ocost = O.local_search(big, node, max_moves=60)
+        assert np.array_equal(keys[0], okeys) and cost[0] == ocost
+        assert np.array_equal(pr.get_state(0)["node"], final)
+    with _load(engine, [(big, node, raw)]) as pr:
+        bmoves, bcost, bkeys = pr.local_search(max_moves=4, keys_capacity=1024, batched=True)
+        _, obkeys, _, obcost = O.local_search_batched(big, node, max_iters=4)
+        assert np.array_equal(bkeys[0], obkeys) and bcost[0] == obcost
