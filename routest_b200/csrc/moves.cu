@@ -1537,7 +1537,14 @@ int search_persistent_launch(rt_problem *p, int families, int iters, bool improv
     void *args[] = {&ea, &sa, &ap, &pa};
     const void *fn = fast ? reinterpret_cast<const void *>(search_persistent_kernel<true>)
                           : reinterpret_cast<const void *>(search_persistent_kernel<false>);
-    RT_CUDA(e, cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kPersistThreads), args, 0, st));
+    const cudaError_t ce = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kPersistThreads), args, 0, st);
+    if (ce == cudaErrorCooperativeLaunchTooLarge || ce == cudaErrorNotSupported) {
+        // fewer SMs than the occupancy query promised (a partitioned GPU): the chain of launches serves from now on
+        (void)cudaGetLastError();
+        coop = 0;
+        return -1;
+    }
+    RT_CUDA(e, ce);
     p->best_clean = false;  // a search that ended at its optimum leaves the last (non-improving) keys behind
     p->ext_best_clean = false;
     p->scan_done = false;
