@@ -517,13 +517,6 @@ __device__ __forceinline__ int4 lds128(unsigned addr)
     return v;
 }
 
-__device__ __forceinline__ double lds64(unsigned addr)
-{
-    double v;
-    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
-    return v;
-}
-
 // FAST: the launcher has proved from the coordinates' bounding box that no pair of the batch can leave the
 // straight-line range of the cell function (any metro-sized instance), so the per-cell range test is compiled out.
 // (The body is a device function of the block's place in the grid: the persistent search kernel runs the same tiles
